@@ -1,0 +1,163 @@
+/* clrt.h — C ABI of libclrt_cuda.so: the B200-native (sm_100a) replacement for the hot path of
+ * kotturtech/OpenCLRayTracer, sitting where the reference's OpenCL wrapper + kernels sit.
+ *
+ * R = /root/reference/OpenCLRayTracer.  The reference has no FFI today; every entry point below names the
+ * C++ interface (file:line) it stands behind.  The C++ shim in include/clrt/ (namespace CLRayTracer) keeps
+ * the reference's class names and signatures on top of these calls; INTEGRATION.md shows the binding.
+ *
+ * Conventions
+ *  - plain pointers and sizes only; opaque handles; no C++/torch types.
+ *  - every call returns 0 on success, non-zero on error; the message is in clrt_last_error() (thread local).
+ *    This is the reference's `Result {Success=0, Error=1}` + `Errata&` convention (R/Include/Common/Errata.h:47-110).
+ *  - a context owns (or borrows) ONE CUDA stream: the reference's single in-order queue
+ *    (R/src/OpenCLUtils/CLExecutionContext.cpp:264-293).  Calls enqueue on that stream.  Entry points that
+ *    move data to/from HOST memory block until the copy is done (the reference is fully synchronous,
+ *    e.g. R/src/CLRayTracerEngine/BVHManager.cpp:184-192); device-only entry points are asynchronous on the
+ *    stream — call clrt_ctx_sync() (== clFinish) where the reference semantics are wanted.
+ *  - "dptr" arguments are DEVICE pointers (what `cl_mem` becomes); "h" arguments are HOST pointers.
+ *  - there is no CPU fallback: without a CUDA device every call fails with an error.
+ */
+#ifndef CLRT_H
+#define CLRT_H
+#include <stddef.h>
+#include <stdint.h>
+#include "clrt_types.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CLRT_ABI_VERSION 1
+
+typedef struct clrt_ctx   clrt_ctx;    /* CLExecutionContext  R/Include/OpenCLUtils/CLExecutionContext.h */
+typedef struct clrt_buf   clrt_buf;    /* CLBuffer            R/Include/OpenCLUtils/CLBuffer.h:39-112    */
+typedef struct clrt_scene clrt_scene;  /* Scene (device side) R/Include/Scene/Scene.h:66-106             */
+typedef struct clrt_accel clrt_accel;  /* AccelerationStructureManager R/Include/Algorithms/AccelerationStructureManager.h:52-78 */
+
+/* ---- errors / version ------------------------------------------------------------------------- */
+const char* clrt_last_error(void);                    /* Errata::message()  R/Include/Common/Errata.h:84 */
+int         clrt_abi_version(void);
+
+/* ---- context: CLExecutionContext (R/src/OpenCLUtils/CLExecutionContext.cpp:264-293) ----------------- */
+/* stream == NULL: the context creates and owns a non-blocking stream; otherwise it borrows the given
+ * cudaStream_t (e.g. torch's current stream) and never destroys it. */
+int clrt_ctx_create(int device, void* stream, clrt_ctx** out);
+int clrt_ctx_destroy(clrt_ctx* ctx);
+int clrt_ctx_sync(clrt_ctx* ctx);                     /* CLExecutionContext::finishQueue                */
+void* clrt_ctx_stream(clrt_ctx* ctx);                 /* the cudaStream_t                               */
+/* Device getters the managers query (R/Include/OpenCLUtils/CLInterface.h:183,284,343). */
+#define CLRT_DEV_LOCAL_MEM_SIZE      0   /* getLocalMemSize      -> max shared memory per block (opt-in) */
+#define CLRT_DEV_MAX_WORK_GROUP_SIZE 1   /* getMaxWorkGroupSize  -> max threads per block               */
+#define CLRT_DEV_MAX_COMPUTE_UNITS   2   /* getMaxComputeUnits   -> SM count                            */
+#define CLRT_DEV_GLOBAL_MEM_SIZE     3
+int clrt_ctx_device_info(clrt_ctx* ctx, int what, uint64_t* out);
+
+/* ---- buffers: CLBuffer (R/Include/OpenCLUtils/CLBuffer.h:39-112, R/src/OpenCLUtils/CLBuffer.cpp:40-130) -- */
+int    clrt_buf_alloc(clrt_ctx* ctx, size_t bytes, const void* h_src /* may be NULL */, clrt_buf** out);
+int    clrt_buf_free(clrt_buf* buf);
+int    clrt_buf_resize(clrt_buf* buf, size_t bytes);  /* grow-only; contents discarded on growth (CLBuffer.cpp:70-94) */
+size_t clrt_buf_size(const clrt_buf* buf);            /* getSize        */
+size_t clrt_buf_capacity(const clrt_buf* buf);        /* getActualSize  */
+void*  clrt_buf_dptr(const clrt_buf* buf);            /* getCLMem       */
+/* CLExecutionContext::enqueueFillBuffer (pattern of pattern_size bytes repeated over `bytes`). */
+int    clrt_buf_fill(clrt_buf* buf, const void* h_pattern, size_t pattern_size, size_t bytes);
+int    clrt_buf_upload(clrt_buf* buf, const void* h_src, size_t offset, size_t bytes);    /* enqueueWriteBuffer, blocking */
+int    clrt_buf_download(const clrt_buf* buf, void* h_dst, size_t offset, size_t bytes);  /* CLBuffer::copyToHost, blocking */
+
+/* Raw device-pointer copies: CLExecutionContext::enqueueWriteBuffer / enqueueReadBuffer
+ * (R/src/OpenCLUtils/CLExecutionContext.cpp:386-470), blocking like the reference's. */
+int    clrt_memcpy_htod(clrt_ctx* ctx, void* dptr_dst, const void* h_src, size_t bytes);
+int    clrt_memcpy_dtoh(clrt_ctx* ctx, void* h_dst, const void* dptr_src, size_t bytes);
+
+/* ---- building blocks ----------------------------------------------------------------------------------
+ * BitonicSort::sort(cl_mem, size_t n)  R/Include/Algorithms/Sorting.h:54-85, R/src/CLRayTracerEngine/BitonicSort.cpp:118-189.
+ *   Ascending sort of n (key,value) uint32 pairs by key, in place.  n is arbitrary here (the reference needs 2^k).
+ *   mode CLRT_SORT_RADIX: onesweep LSD radix sort, STABLE (equal keys keep input order == the canonical
+ *   tie order of SURVEY.md Q7 for every reference call site, whose values ascend with position).
+ *   mode CLRT_SORT_BITONIC_COMPAT: reproduces the reference's unstable bitonic network permutation
+ *   (n must be 2^k) for callers that need literal equality of tie order. */
+#define CLRT_SORT_RADIX          0
+#define CLRT_SORT_BITONIC_COMPAT 1
+int clrt_sort_pairs_u32(clrt_ctx* ctx, void* dptr_pairs, size_t n, int mode);
+/* PrefixSum::computePrefixSum(in,out,n)  R/Include/Algorithms/PrefixSum.h:48-83, R/src/CLRayTracerEngine/PrefixSum.cpp:94-133.
+ *   INCLUSIVE scan of n uint32; in may equal out; any n. */
+int clrt_scan_inclusive_u32(clrt_ctx* ctx, const void* dptr_in, void* dptr_out, size_t n);
+
+/* ---- scene: Scene::loadToGPU (R/src/CLRayTracerEngine/Scene.cpp:451-456) ------------------------------
+ * Uploads the packed v0.6 scene buffer (format: R/Include/CLData/SceneBufferParser.h) unchanged and
+ * flattens it ON THE DEVICE into a 16-byte aligned clrt_triangle array used by every kernel. */
+int      clrt_scene_upload(clrt_ctx* ctx, const void* h_scene, size_t bytes, clrt_scene** out);
+int      clrt_scene_destroy(clrt_scene* scene);
+uint64_t clrt_scene_triangle_count(const clrt_scene* scene);
+void*    clrt_scene_dptr(const clrt_scene* scene);             /* Scene::getDeviceSceneData */
+void*    clrt_scene_triangles_dptr(const clrt_scene* scene);   /* clrt_triangle[N]          */
+int      clrt_scene_export_triangles(const clrt_scene* scene, void* h_out /* N*48 B */);
+
+/* ---- acceleration structures: AccelerationStructureManager ------------------------------------------
+ * BVHManager           R/Include/Algorithms/BVHManager.h:59-126,  R/src/CLRayTracerEngine/BVHManager.cpp
+ * TwoLevelGridManager  R/Include/Algorithms/TwoLevelGridManager.h:61-178, R/src/CLRayTracerEngine/TwoLevelGridManager.cpp */
+int clrt_bvh_create(clrt_ctx* ctx, const clrt_scene* scene, clrt_accel** out);                  /* ctor + initialize() */
+int clrt_tlg_create(clrt_ctx* ctx, const clrt_scene* scene, float top_density, float leaf_density, clrt_accel** out);
+int clrt_accel_destroy(clrt_accel* accel);
+int clrt_accel_init_frame(clrt_accel* accel);   /* initializeFrame()  BVHManager.cpp:122-150 / TwoLevelGridManager.cpp:160-201 */
+int clrt_accel_construct(clrt_accel* accel);    /* construct()        BVHManager.cpp:156-228 / TwoLevelGridManager.cpp:207-469 */
+/* generateContacts(Camera&)  BVHManager.cpp:234-281 -> kernel generateContacts (BVHKernels.cl:84-98).
+ * Writes resX*resY clrt_contact to dptr_contacts (NULL: the accel's own primary-contacts buffer). */
+int clrt_trace_primary(clrt_accel* accel, const clrt_camera* h_camera, void* dptr_contacts);
+/* generateContacts(rays,contacts,rayCount)  BVHManager.cpp:292-329 -> kernel generateContacts2 (BVHKernels.cl:103-117). */
+int clrt_trace_rays(clrt_accel* accel, const void* dptr_rays, void* dptr_contacts, uint32_t ray_count);
+void* clrt_accel_primary_contacts_dptr(clrt_accel* accel);     /* getPrimaryContacts()->getCLMem() */
+/* Traversal policy.  FAST (default): near-child-first, t-pruned, persistent-thread kernel — same closest hit,
+ * exact ties may pick another triangle.  REFERENCE_ORDER: the reference's A-before-B unpruned order
+ * (R/Include/CLData/AccelerationStructs/BVH.h:344-408), bit-exact contacts; the parity vehicle. */
+#define CLRT_TRACE_FAST            0
+#define CLRT_TRACE_REFERENCE_ORDER 1
+int clrt_accel_set_trace_mode(clrt_accel* accel, int mode);
+/* Stage timings of the last construct() in ms (CUDA events on the context's stream). */
+#define CLRT_STAGE_MORTON 0
+#define CLRT_STAGE_SORT   1
+#define CLRT_STAGE_EMIT   2
+#define CLRT_STAGE_REFIT  3
+#define CLRT_STAGE_TOTAL  4
+#define CLRT_STAGE_COUNT  16
+int clrt_accel_stage_ms(clrt_accel* accel, int stage, float* out_ms);
+int clrt_accel_enable_stage_timing(clrt_accel* accel, int on);
+
+/* Inspection of build products (the reference exposes the cl_mem objects; tests download them). */
+int clrt_bvh_export_nodes(clrt_accel* accel, void* h_nodes /* (2N-1) * 48 B */);
+int clrt_bvh_export_pairs(clrt_accel* accel, void* h_pairs /* N * 8 B, sorted (morton, leaf) */);
+/* TLG products: GridData, TopLevelCell[cells], leafCellRanges[leafCells], sorted leaf pairs (real ones only). */
+int clrt_tlg_sizes(clrt_accel* accel, uint32_t* top_cells, uint32_t* top_pairs, uint32_t* leaf_cells, uint32_t* leaf_pairs);
+int clrt_tlg_export(clrt_accel* accel, clrt_grid_data* h_grid, void* h_top_cells, void* h_top_ranges,
+                    void* h_top_pairs, void* h_leaf_ranges, void* h_leaf_pairs);
+
+/* ---- ray generation / shading (host loop R/src/Demos/OpenCLRayTracerDemo/OpenCLRayTracerDemo.cpp:298-316 ->
+ *      cpuShadeBlinnPhong R/Include/CLData/Shading.h:74-166, generateRay R/Include/CLData/CLStructs.h:95-106) */
+int clrt_generate_primary_rays(clrt_ctx* ctx, const clrt_camera* h_camera, void* dptr_rays /* resX*resY*48 B */);
+/* One shadow ray per contact per light (scene lights, then the camera light).  Ray r = c*(L+1)+l goes from the
+ * hit point (pushed 1e-3 along the geometric normal towards the light side) to light l; misses of the primary
+ * pass produce a degenerate ray with idx = UINT_MAX that the trace kernels skip.  dptr_rays: n*(L+1)*48 B. */
+int clrt_generate_shadow_rays(clrt_ctx* ctx, const clrt_scene* scene, const clrt_camera* h_camera,
+                              const void* dptr_contacts, uint32_t n, void* dptr_rays, uint32_t* out_rays_per_contact);
+/* Blinn-Phong of every contact -> RGBA8 (and/or float4) at the contact's slot.  dptr_shadow_contacts (may be
+ * NULL) are the contacts of the shadow rays above: a light whose shadow ray hit before reaching it adds nothing. */
+int clrt_shade(clrt_ctx* ctx, const clrt_scene* scene, const clrt_camera* h_camera, const void* dptr_contacts,
+               uint32_t n, const void* dptr_shadow_contacts, void* dptr_rgba8 /* may be NULL */,
+               void* dptr_rgba_f32 /* may be NULL */);
+
+/* ---- frame: RTFrame() (OpenCLRayTracerDemo.cpp:271-326) as one call; the image-space shard entry -------
+ * Renders the pixels of stripe `rank` of `nranks` (32x8-pixel tiles, tile t owned by rank t % nranks; inside the
+ * GPU persistent CTAs pull tiles from an atomic counter) into dptr_rgba8 in STRIPE order (tile-major, 256 px per
+ * tile).  shadows != 0 adds the shadow pass.  out_rays (host) receives the rays traced.  clrt_frame_untile
+ * converts gathered stripes (rank-major) to raster order. */
+int clrt_frame_stripe_pixels(uint32_t resX, uint32_t resY, uint32_t rank, uint32_t nranks, uint32_t* out_pixels, uint32_t* out_tiles);
+int clrt_render_stripe(clrt_accel* accel, const clrt_camera* h_camera, int shadows, uint32_t rank, uint32_t nranks,
+                       void* dptr_rgba8, uint64_t* out_rays);
+int clrt_frame_untile(clrt_ctx* ctx, const void* dptr_stripes, uint32_t resX, uint32_t resY, uint32_t nranks, void* dptr_raster_rgba8);
+/* Whole frame with HOST output: upload camera, trace, (shadow,) shade, download RGBA8 raster — the e2e path. */
+int clrt_render_frame_host(clrt_accel* accel, const clrt_camera* h_camera, int shadows, void* h_rgba8, uint64_t* out_rays);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

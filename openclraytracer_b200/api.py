@@ -1,0 +1,409 @@
+"""Host-side mirror of the reference's plugin interface over the C ABI (names and argument meaning follow the reference).
+
+  CLExecutionContext  R/Include/OpenCLUtils/CLExecutionContext.h        -> Context
+  CLBuffer            R/Include/OpenCLUtils/CLBuffer.h:39-112           -> Buffer
+  Scene               R/Include/Scene/Scene.h:66-106                    -> Scene
+  BitonicSort         R/Include/Algorithms/Sorting.h:54-85              -> BitonicSort
+  PrefixSum           R/Include/Algorithms/PrefixSum.h:48-83            -> PrefixSum
+  AccelerationStructureManager / BVHManager / TwoLevelGridManager
+                      R/Include/Algorithms/{AccelerationStructureManager.h:52-78,BVHManager.h:59-126,TwoLevelGridManager.h:61-178}
+
+Errors: the reference returns Result + fills Errata&; here a failed call raises ClrtError carrying the Errata message.
+The C++ shim with the literal signatures lives in include/clrt/; this module is the Python face used by tests and bench.
+"""
+import ctypes as C
+import numpy as np
+from . import _lib
+from . import layouts as L
+from ._lib import ClrtError, check
+
+SORT_RADIX, SORT_BITONIC_COMPAT = 0, 1
+TRACE_FAST, TRACE_REFERENCE_ORDER = 0, 1
+STAGE_MORTON, STAGE_SORT, STAGE_EMIT, STAGE_REFIT, STAGE_TOTAL = 0, 1, 2, 3, 4
+
+
+def _ptr(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+class Context:
+    """One device + one in-order stream (the reference's context + queue)."""
+
+    def __init__(self, device=0, stream=None):
+        self._lib = _lib.load()
+        h = C.c_void_p()
+        check(self._lib.clrt_ctx_create(int(device), C.c_void_p(stream) if stream else None, C.byref(h)))
+        self.handle = h
+        self.device = device
+
+    def finish(self):                      # CLExecutionContext::finishQueue
+        check(self._lib.clrt_ctx_sync(self.handle))
+
+    flushQueue = finish
+
+    @property
+    def stream(self):
+        return self._lib.clrt_ctx_stream(self.handle)
+
+    def enqueueWriteBuffer(self, dptr, arr):           # blocking, like the reference's
+        arr = np.ascontiguousarray(arr)
+        check(self._lib.clrt_memcpy_htod(self.handle, C.c_void_p(dptr), _ptr(arr), arr.nbytes))
+
+    def enqueueReadBuffer(self, dptr, out):
+        assert out.flags["C_CONTIGUOUS"]
+        check(self._lib.clrt_memcpy_dtoh(self.handle, _ptr(out), C.c_void_p(dptr), out.nbytes))
+        return out
+
+    def device_info(self, what):
+        v = C.c_uint64()
+        check(self._lib.clrt_ctx_device_info(self.handle, what, C.byref(v)))
+        return v.value
+
+    def getMaxComputeUnits(self):
+        return self.device_info(2)
+
+    def getMaxWorkGroupSize(self):
+        return self.device_info(1)
+
+    def getLocalMemSize(self):
+        return self.device_info(0)
+
+    def close(self):
+        if self.handle:
+            self._lib.clrt_ctx_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Buffer:
+    """CLBuffer: device allocation with grow-only resize and blocking copyToHost."""
+
+    def __init__(self, context, size, source=None):
+        self._lib = _lib.load()
+        self.context = context
+        h = C.c_void_p()
+        src = None
+        if source is not None:
+            source = np.ascontiguousarray(source)
+            assert source.nbytes >= size
+            src = _ptr(source)
+        check(self._lib.clrt_buf_alloc(context.handle, size, src, C.byref(h)))
+        self.handle = h
+
+    @classmethod
+    def from_array(cls, context, arr):
+        arr = np.ascontiguousarray(arr)
+        return cls(context, arr.nbytes, arr)
+
+    def resize(self, new_size):
+        check(self._lib.clrt_buf_resize(self.handle, new_size))
+
+    def getSize(self):
+        return self._lib.clrt_buf_size(self.handle)
+
+    def getActualSize(self):
+        return self._lib.clrt_buf_capacity(self.handle)
+
+    def getCLMem(self):
+        return self._lib.clrt_buf_dptr(self.handle)
+
+    dptr = property(getCLMem)
+
+    def fill(self, pattern, nbytes=None):              # CLExecutionContext::enqueueFillBuffer
+        pattern = np.ascontiguousarray(pattern)
+        check(self._lib.clrt_buf_fill(self.handle, _ptr(pattern), pattern.nbytes, self.getSize() if nbytes is None else nbytes))
+
+    def upload(self, arr, offset=0):
+        arr = np.ascontiguousarray(arr)
+        check(self._lib.clrt_buf_upload(self.handle, _ptr(arr), offset, arr.nbytes))
+
+    def copyToHost(self, dtype=np.uint8, count=None, offset=0):
+        dtype = np.dtype(dtype)
+        n = (self.getSize() - offset) // dtype.itemsize if count is None else count
+        out = np.empty(n, dtype=dtype)
+        check(self._lib.clrt_buf_download(self.handle, _ptr(out), offset, out.nbytes))
+        return out
+
+    def free(self):
+        if self.handle:
+            self._lib.clrt_buf_free(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+class BitonicSort:
+    """Common::BitonicSort(context, useKeyValue): sort(cl_mem, n) sorts n (key,value) pairs in place by key."""
+
+    def __init__(self, context, useKeyValue=True, mode=SORT_RADIX):
+        self._lib = _lib.load()
+        self.context = context
+        self.mode = mode
+
+    def initialize(self):
+        return 0                                           # kernels are compiled ahead of time
+
+    def sort(self, cl_mem, num_items):
+        check(self._lib.clrt_sort_pairs_u32(self.context.handle, C.c_void_p(cl_mem), num_items, self.mode))
+
+
+class PrefixSum:
+    """Common::PrefixSum(context): computePrefixSum(in, out, n) — inclusive scan of uint32."""
+
+    def __init__(self, context):
+        self._lib = _lib.load()
+        self.context = context
+
+    def initialize(self):
+        return 0
+
+    def computePrefixSum(self, in_mem, out_mem, n):
+        check(self._lib.clrt_scan_inclusive_u32(self.context.handle, C.c_void_p(in_mem), C.c_void_p(out_mem), n))
+
+
+class Scene:
+    """Scene: host buffer in the packed v0.6 format + loadToGPU."""
+
+    def __init__(self, host_scene_data=None):
+        self._lib = _lib.load()
+        self._host = None if host_scene_data is None else np.ascontiguousarray(host_scene_data, dtype=np.uint8)
+        self.handle = None
+        self.context = None
+
+    def getHostSceneData(self):
+        return self._host
+
+    def getSceneDataSize(self):
+        return 0 if self._host is None else self._host.nbytes
+
+    def loadToGPU(self, context):
+        h = C.c_void_p()
+        check(self._lib.clrt_scene_upload(context.handle, _ptr(self._host), self._host.nbytes, C.byref(h)))
+        self.handle, self.context = h, context
+
+    def getDeviceSceneData(self):
+        return self._lib.clrt_scene_dptr(self.handle)
+
+    def triangle_count(self):
+        return int(self._lib.clrt_scene_triangle_count(self.handle))
+
+    def export_triangles(self):
+        out = np.empty(self.triangle_count(), dtype=L.TRIANGLE)
+        check(self._lib.clrt_scene_export_triangles(self.handle, _ptr(out)))
+        return out
+
+    def header(self):
+        return np.frombuffer(self._host[:96].tobytes(), dtype=L.SCENE_HEADER)[0]
+
+    def num_lights(self):
+        return int(self.header()["numberOfLights"])
+
+    def free(self):
+        if self.handle:
+            self._lib.clrt_scene_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+def make_camera(resX, resY, FOVDistance, viewTransform):
+    cam = np.zeros((), dtype=L.CAMERA)
+    cam["FOVDistance"] = FOVDistance
+    cam["resX"], cam["resY"], cam["supersampilngFactor"] = resX, resY, 1
+    cam["viewTransform"] = np.asarray(viewTransform, dtype=np.float32).reshape(12)
+    return cam
+
+
+def demo_camera(scene_buf, resX, resY, fov_deg=90.0):
+    """The Demo's camera rule (OpenCLRayTracerDemo.cpp:202-217): FOV 90 deg, identity orientation,
+    position (cx, cy, minZ - halfZ) of the scene box.  float32 arithmetic as the reference."""
+    hdr = np.frombuffer(scene_buf[:96].tobytes(), dtype=L.SCENE_HEADER)[0]
+    bb = hdr["modelsBoundingBox"]
+    f = np.float32
+    half = (bb[1, :3] - bb[0, :3]) * f(0.5)
+    pos = np.array([bb[0, 0] + half[0], bb[0, 1] + half[1], bb[0, 2] - half[2]], dtype=np.float32)
+    deg2rad = f(f(3.14159265359) / f(180.0))
+    fovd = f(f(resY) * f(0.5)) / f(np.tan(f(f(fov_deg) * f(0.5) * deg2rad), dtype=np.float32))
+    m = np.array([1, 0, 0, pos[0], 0, 1, 0, pos[1], 0, 0, 1, pos[2]], dtype=np.float32)
+    return make_camera(resX, resY, f(fovd), m)
+
+
+class AccelerationStructureManager:
+    """Abstract base: initialize / initializeFrame / construct / generateContacts(camera) /
+    generateContacts(rays, contacts, rayCount) / getPrimaryContacts."""
+
+    def __init__(self, context, scene):
+        self._lib = _lib.load()
+        self.context, self.scene = context, scene
+        self.handle = None
+        self._primary_pixels = 0
+
+    def initialize(self):
+        raise NotImplementedError
+
+    def initializeFrame(self):
+        check(self._lib.clrt_accel_init_frame(self.handle))
+
+    def construct(self):
+        check(self._lib.clrt_accel_construct(self.handle))
+
+    def generateContacts(self, camera_or_rays, contacts=None, rayCount=None):
+        if rayCount is None:                                  # generateContacts(Camera&)
+            cam = np.ascontiguousarray(camera_or_rays, dtype=L.CAMERA)
+            out = None if contacts is None else C.c_void_p(contacts.getCLMem() if isinstance(contacts, Buffer) else contacts)
+            check(self._lib.clrt_trace_primary(self.handle, _ptr(cam), out))
+            self._primary_pixels = int(cam["resX"]) * int(cam["resY"])
+        else:                                                 # generateContacts(rays, contacts, rayCount)
+            r = camera_or_rays.getCLMem() if isinstance(camera_or_rays, Buffer) else camera_or_rays
+            c = contacts.getCLMem() if isinstance(contacts, Buffer) else contacts
+            check(self._lib.clrt_trace_rays(self.handle, C.c_void_p(r), C.c_void_p(c), rayCount))
+
+    def getPrimaryContacts(self):
+        """Device pointer of the primary contacts (the reference returns the CLBuffer)."""
+        return self._lib.clrt_accel_primary_contacts_dptr(self.handle)
+
+    def download_primary_contacts(self):
+        """getPrimaryContacts()->copyToHost (OpenCLRayTracerDemo.cpp:289)."""
+        out = np.empty(self._primary_pixels, dtype=L.CONTACT)
+        self.context.enqueueReadBuffer(self.getPrimaryContacts(), out)
+        return out
+
+    def set_trace_mode(self, mode):
+        check(self._lib.clrt_accel_set_trace_mode(self.handle, mode))
+
+    def enable_stage_timing(self, on=True):
+        check(self._lib.clrt_accel_enable_stage_timing(self.handle, int(on)))
+
+    def stage_ms(self, stage):
+        v = C.c_float()
+        check(self._lib.clrt_accel_stage_ms(self.handle, stage, C.byref(v)))
+        return v.value
+
+    def render_stripe(self, camera, shadows, rank, nranks, dptr_rgba8, want_rays=False):
+        cam = np.ascontiguousarray(camera, dtype=L.CAMERA)
+        rays = C.c_uint64()
+        check(self._lib.clrt_render_stripe(self.handle, _ptr(cam), int(shadows), rank, nranks, C.c_void_p(dptr_rgba8),
+                                           C.byref(rays) if want_rays else None))
+        return rays.value
+
+    def render_frame_host(self, camera, shadows, out_rgba8=None, want_rays=False):
+        cam = np.ascontiguousarray(camera, dtype=L.CAMERA)
+        if out_rgba8 is None:
+            out_rgba8 = np.empty((int(cam["resY"]), int(cam["resX"]), 4), dtype=np.uint8)
+        rays = C.c_uint64()
+        ptr = out_rgba8 if isinstance(out_rgba8, int) else _ptr(out_rgba8)
+        check(self._lib.clrt_render_frame_host(self.handle, _ptr(cam), int(shadows), C.c_void_p(ptr) if isinstance(ptr, int) else ptr,
+                                               C.byref(rays) if want_rays else None))
+        return out_rgba8, rays.value
+
+    def free(self):
+        if self.handle:
+            self._lib.clrt_accel_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+class BVHManager(AccelerationStructureManager):
+    def initialize(self):
+        h = C.c_void_p()
+        check(self._lib.clrt_bvh_create(self.context.handle, self.scene.handle, C.byref(h)))
+        self.handle = h
+
+    def export_nodes(self):
+        n = self.scene.triangle_count()
+        out = np.zeros(max(2 * n - 1, 0), dtype=L.BVH_NODE)
+        check(self._lib.clrt_bvh_export_nodes(self.handle, _ptr(out)))
+        return out
+
+    def export_pairs(self):
+        out = np.zeros(self.scene.triangle_count(), dtype=L.UINT2)
+        check(self._lib.clrt_bvh_export_pairs(self.handle, _ptr(out)))
+        return out
+
+
+class TwoLevelGridManager(AccelerationStructureManager):
+    def __init__(self, context, scene, topLevelDensity=2.0, leafDensity=2.0):
+        super().__init__(context, scene)
+        self._top, self._leaf = float(topLevelDensity), float(leafDensity)
+
+    def setTopLevelDensity(self, v):
+        self._top = float(v)
+
+    def setLeafDensity(self, v):
+        self._leaf = float(v)
+
+    def getTopLevelDensity(self):
+        return self._top
+
+    def getLeafDensity(self):
+        return self._leaf
+
+    def initialize(self):
+        h = C.c_void_p()
+        check(self._lib.clrt_tlg_create(self.context.handle, self.scene.handle, self._top, self._leaf, C.byref(h)))
+        self.handle = h
+
+    def sizes(self):
+        v = [C.c_uint32() for _ in range(4)]
+        check(self._lib.clrt_tlg_sizes(self.handle, *[C.byref(x) for x in v]))
+        return tuple(x.value for x in v)
+
+    def export(self):
+        top_cells, top_pairs, leaf_cells, leaf_pairs = self.sizes()
+        grid = np.zeros((), dtype=L.GRID_DATA)
+        cells = np.zeros(top_cells, dtype=L.TOP_CELL)
+        top_ranges = np.zeros(top_cells, dtype=L.UINT2)
+        tpairs = np.zeros(top_pairs, dtype=L.UINT2)
+        leaf_ranges = np.zeros(leaf_cells, dtype=L.UINT2)
+        lpairs = np.zeros(leaf_pairs, dtype=L.UINT2)
+        check(self._lib.clrt_tlg_export(self.handle, _ptr(grid), _ptr(cells), _ptr(top_ranges), _ptr(tpairs), _ptr(leaf_ranges), _ptr(lpairs)))
+        return dict(grid=grid, top_cells=cells, top_ranges=top_ranges, top_pairs=tpairs, leaf_ranges=leaf_ranges, leaf_pairs=lpairs)
+
+
+def generate_primary_rays(context, camera, dptr_rays):
+    cam = np.ascontiguousarray(camera, dtype=L.CAMERA)
+    check(_lib.load().clrt_generate_primary_rays(context.handle, _ptr(cam), C.c_void_p(dptr_rays)))
+
+
+def generate_shadow_rays(context, scene, camera, dptr_contacts, n, dptr_rays):
+    cam = np.ascontiguousarray(camera, dtype=L.CAMERA)
+    per = C.c_uint32()
+    check(_lib.load().clrt_generate_shadow_rays(context.handle, scene.handle, _ptr(cam), C.c_void_p(dptr_contacts), n,
+                                                C.c_void_p(dptr_rays), C.byref(per)))
+    return per.value
+
+
+def shade(context, scene, camera, dptr_contacts, n, dptr_shadow=None, dptr_rgba8=None, dptr_rgba_f32=None):
+    cam = np.ascontiguousarray(camera, dtype=L.CAMERA)
+    check(_lib.load().clrt_shade(context.handle, scene.handle, _ptr(cam), C.c_void_p(dptr_contacts), n,
+                                 C.c_void_p(dptr_shadow) if dptr_shadow else None,
+                                 C.c_void_p(dptr_rgba8) if dptr_rgba8 else None,
+                                 C.c_void_p(dptr_rgba_f32) if dptr_rgba_f32 else None))
+
+
+def frame_untile(context, dptr_stripes, resX, resY, nranks, dptr_raster):
+    check(_lib.load().clrt_frame_untile(context.handle, C.c_void_p(dptr_stripes), resX, resY, nranks, C.c_void_p(dptr_raster)))
+
+
+def frame_stripe_pixels(resX, resY, rank, nranks):
+    px, tiles = C.c_uint32(), C.c_uint32()
+    check(_lib.load().clrt_frame_stripe_pixels(resX, resY, rank, nranks, C.byref(px), C.byref(tiles)))
+    return px.value, tiles.value

@@ -1,0 +1,198 @@
+// accel.cu — the AccelerationStructureManager entry points of the C ABI
+// (R/Include/Algorithms/AccelerationStructureManager.h:52-78; BVHManager.cpp / TwoLevelGridManager.cpp) and the
+// per-frame flow of the Demo's RTFrame() (R/src/Demos/OpenCLRayTracerDemo/OpenCLRayTracerDemo.cpp:271-326).
+#include "common.cuh"
+
+int shade_launch_shadow_rays(clrt_ctx* ctx, const clrt_scene* scene, const clrt_camera& cam, const clrt_contact* contacts,
+                             uint32_t n, clrt_ray* rays, unsigned long long* d_counter);
+int shade_launch(clrt_ctx* ctx, const clrt_scene* scene, const clrt_camera& cam, const clrt_contact* contacts, uint32_t n,
+                 const clrt_contact* shadow, uint32_t* rgba8, float4* rgba_f32);
+
+static int accel_create(clrt_ctx* ctx, const clrt_scene* scene, AccelKind kind, clrt_accel** out) {
+  if (!ctx || !scene || !out) CLRT_FAIL("accel create: NULL argument");
+  if (scene->ctx != ctx) CLRT_FAIL("accel create: scene belongs to another context");
+  CLRT_CUDA(cudaSetDevice(ctx->device));
+  clrt_accel* a = new clrt_accel();
+  a->kind = kind; a->ctx = ctx; a->scene = scene;
+  for (int i = 0; i <= CLRT_STAGE_COUNT; i++) CLRT_CUDA(cudaEventCreate(&a->ev[i]));
+  CLRT_CUDA(cudaMalloc(&a->d_tile_counter, 64));
+  CLRT_CUDA(cudaMemsetAsync(a->d_tile_counter, 0, 64, ctx->stream));
+  *out = a;
+  return 0;
+}
+
+extern "C" int clrt_bvh_create(clrt_ctx* ctx, const clrt_scene* scene, clrt_accel** out) {
+  return accel_create(ctx, scene, ACCEL_BVH, out);
+}
+extern "C" int clrt_tlg_create(clrt_ctx* ctx, const clrt_scene* scene, float top_density, float leaf_density, clrt_accel** out) {
+  if (!(top_density > 0.0f) || !(leaf_density > 0.0f)) CLRT_FAIL("clrt_tlg_create: densities must be positive");
+  CLRT_TRY(accel_create(ctx, scene, ACCEL_TLG, out));
+  (*out)->top_density = top_density; (*out)->leaf_density = leaf_density;
+  return 0;
+}
+
+extern "C" int clrt_accel_destroy(clrt_accel* a) {
+  if (!a) return 0;
+  cudaSetDevice(a->ctx->device);
+  cudaStreamSynchronize(a->ctx->stream);
+  if (a->kind == ACCEL_TLG) tlg_destroy(a);
+  if (a->d_nodes) cudaFree(a->d_nodes);
+  if (a->d_pairs) cudaFree(a->d_pairs);
+  if (a->d_counters) cudaFree(a->d_counters);
+  if (a->d_tnodes) cudaFree(a->d_tnodes);
+  if (a->d_contacts) cudaFree(a->d_contacts);
+  if (a->d_frame_scratch) cudaFree(a->d_frame_scratch);
+  if (a->d_fb) cudaFree(a->d_fb);
+  if (a->d_tile_counter) cudaFree(a->d_tile_counter);
+  for (int i = 0; i <= CLRT_STAGE_COUNT; i++) if (a->ev[i]) cudaEventDestroy(a->ev[i]);
+  delete a;
+  return 0;
+}
+
+extern "C" int clrt_accel_init_frame(clrt_accel* a) {
+  if (!a) CLRT_FAIL("clrt_accel_init_frame: NULL accel");
+  CLRT_CUDA(cudaSetDevice(a->ctx->device));
+  return a->kind == ACCEL_BVH ? bvh_init_frame(a) : tlg_init_frame(a);
+}
+extern "C" int clrt_accel_construct(clrt_accel* a) {
+  if (!a) CLRT_FAIL("clrt_accel_construct: NULL accel");
+  CLRT_CUDA(cudaSetDevice(a->ctx->device));
+  return a->kind == ACCEL_BVH ? bvh_construct(a) : tlg_construct(a);
+}
+extern "C" int clrt_accel_set_trace_mode(clrt_accel* a, int mode) {
+  if (!a) CLRT_FAIL("clrt_accel_set_trace_mode: NULL accel");
+  if (mode != CLRT_TRACE_FAST && mode != CLRT_TRACE_REFERENCE_ORDER) CLRT_FAIL("clrt_accel_set_trace_mode: unknown mode %d", mode);
+  a->trace_mode = mode; return 0;
+}
+extern "C" int clrt_accel_enable_stage_timing(clrt_accel* a, int on) {
+  if (!a) CLRT_FAIL("clrt_accel_enable_stage_timing: NULL accel");
+  a->timing = on != 0; return 0;
+}
+extern "C" int clrt_accel_stage_ms(clrt_accel* a, int stage, float* out_ms) {
+  if (!a || !out_ms) CLRT_FAIL("clrt_accel_stage_ms: NULL argument");
+  if (stage < 0 || stage >= CLRT_STAGE_COUNT) CLRT_FAIL("clrt_accel_stage_ms: stage %d out of range", stage);
+  *out_ms = a->stage_ms[stage]; return 0;
+}
+
+static int ensure_contacts(clrt_accel* a, size_t count) {
+  const size_t bytes = count * sizeof(clrt_contact);
+  if (bytes > a->contacts_cap) {
+    CLRT_CUDA(cudaStreamSynchronize(a->ctx->stream));
+    CLRT_TRY(clrt_grow((void**)&a->d_contacts, &a->contacts_cap, bytes));    // BVHManager.cpp:240-244 (resize)
+  }
+  return 0;
+}
+
+int accel_trace_primary(clrt_accel* a, const clrt_camera& cam, clrt_contact* out, uint32_t rank, uint32_t nranks);
+
+extern "C" int clrt_trace_primary(clrt_accel* a, const clrt_camera* h_camera, void* dptr_contacts) {
+  if (!a || !h_camera) CLRT_FAIL("clrt_trace_primary: NULL argument");
+  CLRT_CUDA(cudaSetDevice(a->ctx->device));
+  const uint64_t pixels = (uint64_t)h_camera->resX * h_camera->resY;
+  if (pixels > 0x7FFFFFFFull) CLRT_FAIL("clrt_trace_primary: resolution too large");
+  clrt_contact* out = (clrt_contact*)dptr_contacts;
+  if (!out) { CLRT_TRY(ensure_contacts(a, pixels)); out = a->d_contacts; }
+  return accel_trace_primary(a, *h_camera, out, 0, 0);
+}
+
+extern "C" void* clrt_accel_primary_contacts_dptr(clrt_accel* a) { return a ? a->d_contacts : nullptr; }
+
+extern "C" int clrt_trace_rays(clrt_accel* a, const void* dptr_rays, void* dptr_contacts, uint32_t ray_count) {
+  if (!a || (ray_count && (!dptr_rays || !dptr_contacts))) CLRT_FAIL("clrt_trace_rays: NULL argument");
+  if (((uintptr_t)dptr_rays & 15) || ((uintptr_t)dptr_contacts & 15)) CLRT_FAIL("clrt_trace_rays: buffers must be 16-byte aligned");
+  CLRT_CUDA(cudaSetDevice(a->ctx->device));
+  return a->kind == ACCEL_BVH ? bvh_trace_rays(a, (const clrt_ray*)dptr_rays, (clrt_contact*)dptr_contacts, ray_count)
+                              : tlg_trace_rays(a, (const clrt_ray*)dptr_rays, (clrt_contact*)dptr_contacts, ray_count);
+}
+
+// ---- frame ---------------------------------------------------------------------------------------------
+extern "C" int clrt_frame_stripe_pixels(uint32_t resX, uint32_t resY, uint32_t rank, uint32_t nranks, uint32_t* out_pixels, uint32_t* out_tiles) {
+  if (!nranks || rank >= nranks) CLRT_FAIL("clrt_frame_stripe_pixels: rank %u of %u", rank, nranks);
+  const TileGrid g = make_tile_grid(resX, resY);
+  if (out_pixels) *out_pixels = ((g.tiles + nranks - 1) / nranks) * CLRT_TILE_PIXELS;     // padded stripe capacity
+  if (out_tiles) *out_tiles = stripe_tile_count(g.tiles, rank, nranks);
+  return 0;
+}
+
+// scratch layout of one stripe: contacts[slots] | shadow rays[slots*(L+1)] | shadow contacts[slots*(L+1)] | ray counter
+extern "C" int clrt_render_stripe(clrt_accel* a, const clrt_camera* h_camera, int shadows, uint32_t rank, uint32_t nranks,
+                                  void* dptr_rgba8, uint64_t* out_rays) {
+  if (!a || !h_camera || !dptr_rgba8) CLRT_FAIL("clrt_render_stripe: NULL argument");
+  if (!nranks || rank >= nranks) CLRT_FAIL("clrt_render_stripe: rank %u of %u", rank, nranks);
+  clrt_ctx* ctx = a->ctx;
+  CLRT_CUDA(cudaSetDevice(ctx->device));
+  const clrt_camera cam = *h_camera;
+  const TileGrid g = make_tile_grid(cam.resX, cam.resY);
+  const uint32_t tiles = stripe_tile_count(g.tiles, rank, nranks);
+  const uint32_t slots = tiles * CLRT_TILE_PIXELS;
+  const uint32_t L1 = a->scene->n_lights + 1;
+  const size_t contacts_bytes = (size_t)slots * sizeof(clrt_contact);
+  const size_t srays_bytes = shadows ? (size_t)slots * L1 * sizeof(clrt_ray) : 0;
+  const size_t scont_bytes = shadows ? (size_t)slots * L1 * sizeof(clrt_contact) : 0;
+  const size_t total = contacts_bytes + srays_bytes + scont_bytes + 64;
+  if (total > a->frame_scratch_cap) {
+    CLRT_CUDA(cudaStreamSynchronize(ctx->stream));
+    CLRT_TRY(clrt_grow(&a->d_frame_scratch, &a->frame_scratch_cap, total));
+  }
+  uint8_t* base = (uint8_t*)a->d_frame_scratch;
+  clrt_contact* contacts = (clrt_contact*)base;
+  clrt_ray* srays = (clrt_ray*)(base + contacts_bytes);
+  clrt_contact* scont = (clrt_contact*)(base + contacts_bytes + srays_bytes);
+  unsigned long long* counter = (unsigned long long*)(base + contacts_bytes + srays_bytes + scont_bytes);
+  if (slots) {
+    CLRT_TRY(accel_trace_primary(a, cam, contacts, rank, nranks));
+    if (shadows) {
+      CLRT_CUDA(cudaMemsetAsync(counter, 0, 8, ctx->stream));
+      CLRT_TRY(shade_launch_shadow_rays(ctx, a->scene, cam, contacts, slots, srays, out_rays ? counter : nullptr));
+      CLRT_TRY(a->kind == ACCEL_BVH ? bvh_trace_rays(a, srays, scont, slots * L1) : tlg_trace_rays(a, srays, scont, slots * L1));
+    }
+    CLRT_TRY(shade_launch(ctx, a->scene, cam, contacts, slots, shadows ? scont : nullptr, (uint32_t*)dptr_rgba8, nullptr));
+  }
+  if (out_rays) {
+    // primary rays = pixels of this stripe that lie inside the image; shadow rays = live rays counted on the device
+    uint64_t primary = 0;
+    for (uint32_t lt = 0; lt < tiles; lt++) {
+      const uint32_t gt = rank + lt * nranks;
+      const uint32_t x0 = (gt % g.tilesX) * CLRT_TILE_W, y0 = (gt / g.tilesX) * CLRT_TILE_H;
+      const uint32_t w = x0 + CLRT_TILE_W <= cam.resX ? CLRT_TILE_W : cam.resX - x0;
+      const uint32_t h = y0 + CLRT_TILE_H <= cam.resY ? CLRT_TILE_H : cam.resY - y0;
+      primary += (uint64_t)w * h;
+    }
+    unsigned long long srays_count = 0;
+    if (shadows && slots) CLRT_CUDA(cudaMemcpyAsync(&srays_count, counter, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    CLRT_CUDA(cudaStreamSynchronize(ctx->stream));
+    *out_rays = primary + srays_count;
+  }
+  return 0;
+}
+
+extern "C" int clrt_render_frame_host(clrt_accel* a, const clrt_camera* h_camera, int shadows, void* h_rgba8, uint64_t* out_rays) {
+  if (!a || !h_camera || !h_rgba8) CLRT_FAIL("clrt_render_frame_host: NULL argument");
+  clrt_ctx* ctx = a->ctx;
+  CLRT_CUDA(cudaSetDevice(ctx->device));
+  const TileGrid g = make_tile_grid(h_camera->resX, h_camera->resY);
+  const size_t stripe_bytes = (size_t)g.tiles * CLRT_TILE_PIXELS * 4, raster_bytes = (size_t)h_camera->resX * h_camera->resY * 4;
+  // framebuffers owned by the accel: [stripe | raster]
+  if (stripe_bytes + raster_bytes + 256 > a->fb_cap) {
+    CLRT_CUDA(cudaStreamSynchronize(ctx->stream));
+    CLRT_TRY(clrt_grow(&a->d_fb, &a->fb_cap, stripe_bytes + raster_bytes + 256));
+  }
+  uint8_t* stripe = (uint8_t*)a->d_fb; uint8_t* raster = stripe + ((stripe_bytes + 255) & ~(size_t)255);
+  CLRT_TRY(clrt_render_stripe(a, h_camera, shadows, 0, 1, stripe, nullptr));
+  CLRT_TRY(clrt_frame_untile(ctx, stripe, h_camera->resX, h_camera->resY, 1, raster));
+  CLRT_CUDA(cudaMemcpyAsync(h_rgba8, raster, raster_bytes, cudaMemcpyDeviceToHost, ctx->stream));
+  CLRT_CUDA(cudaStreamSynchronize(ctx->stream));
+  if (out_rays) {
+    // recount without re-rendering: primary = all pixels; shadow = (L+1) per hit pixel, counted from the alpha channel
+    uint64_t hits = 0; const uint8_t* px = (const uint8_t*)h_rgba8;
+    for (size_t i = 0; i < raster_bytes / 4; i++) hits += px[4 * i + 3] != 0;
+    *out_rays = (uint64_t)h_camera->resX * h_camera->resY + (shadows ? hits * (a->scene->n_lights + 1) : 0);
+  }
+  return 0;
+}
+
+int accel_trace_primary(clrt_accel* a, const clrt_camera& cam, clrt_contact* out, uint32_t rank, uint32_t nranks) {
+  // The camera travels to the kernels BY VALUE (64 bytes in the constant bank); the reference allocates and uploads a
+  // CLBuffer per frame for it (BVHManager.cpp:237).
+  return a->kind == ACCEL_BVH ? bvh_trace_primary(a, cam, out, rank, nranks) : tlg_trace_primary(a, cam, out, rank, nranks);
+}

@@ -1,0 +1,259 @@
+// bvh.cu — LBVH builder: BVHManager::initializeFrame / construct (R/src/CLRayTracerEngine/BVHManager.cpp:122-228).
+//
+// Stages (one kernel each, no host synchronisation in between; the reference waits on the host after every launch):
+//   morton_leaves_kernel   <- calculateMortonCodes (BVHKernels.cl:46-50 -> BVH.h:83-130)   104 B / triangle
+//   onesweep radix sort    <- BitonicSort::sort (BVHManager.cpp:195)                        16 B / pair (algorithmic)
+//   karras_emit_kernel     <- buildRadixTree (BVHKernels.cl:55-60 -> BVH.h:138-321)         64 B / inner node
+//   refit_atomic_kernel    <- computeBoundingBoxes (BVHKernels.cl:65-79 -> BVH.h:328-334)   100 B / inner node (+64 B trace node)
+// Products: nodes[2N-1] in the reference's 48-byte layout (leaves 0..N-1, inner node i at slot N+i, root = slot N),
+// the sorted (morton, leaf) pairs, and — ours — a 64-byte TraceNode per inner node for the traversal kernels.
+//
+// Parity stance: Q1 FIXED — all N-1 inner nodes are built (the reference's guard skips the
+// last one); Q3 — refit uses the atomic's return value + fences; Q4 LITERAL — inner boxes start from
+// (FLT_MAX.., FLT_MIN..) and that box takes part in the merge, so every max bound is >= FLT_MIN;
+// Q6 LITERAL — Morton normalisation is c/(max-min) without subtracting min.
+#include "common.cuh"
+#include "rtmath.cuh"
+
+namespace {
+
+// expandBits / morton3D (BVH.h:49-73)
+__device__ __forceinline__ uint32_t expand_bits(uint32_t v) {
+  v = (v * 0x00010001u) & 0xFF0000FFu;
+  v = (v * 0x00000101u) & 0x0F00F00Fu;
+  v = (v * 0x00000011u) & 0xC30C30C3u;
+  v = (v * 0x00000005u) & 0x49249249u;
+  return v;
+}
+__device__ __forceinline__ uint32_t morton3d(float x, float y, float z) {
+  x = rmin(rmax(x * 1024.0f, 0.0f), 1023.0f);
+  y = rmin(rmax(y * 1024.0f, 0.0f), 1023.0f);
+  z = rmin(rmax(z * 1024.0f, 0.0f), 1023.0f);
+  return expand_bits((uint32_t)x) * 4 + expand_bits((uint32_t)y) * 2 + expand_bits((uint32_t)z);
+}
+// normalizeScale -> translateScale(oldMin, oldMax, value, 0, 1)  (RTKernelUtils.h:63-81): no min subtraction (Q6)
+__device__ __forceinline__ float normalize_scale(float oldMin, float oldMax, float value) {
+  const float oldLen = oldMax - oldMin;
+  const float percentage = value / oldLen;
+  const float newLen = 1.0f - 0.0f;
+  return percentage * newLen + 0.0f;
+}
+
+// ---- stage 1: leaf AABB + Morton code + leaf node + (code, leaf) pair --------------------------------------
+__global__ void __launch_bounds__(256)
+morton_leaves_kernel(const clrt_triangle* __restrict__ tris, const uint32_t* __restrict__ tri_in_mesh, uint32_t n,
+                     clrt_aabb sceneBB, clrt_bvh_node* __restrict__ nodes, clrt_uint2* __restrict__ pairs) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float4* t = reinterpret_cast<const float4*>(tris + i);
+  const float4 a = __ldg(t), b = __ldg(t + 1), c = __ldg(t + 2);
+  // calculateTriangleAABB (AABB.h:61-79): MIN3(MIN3(v1,v2),v3) component-wise with the compare-select macros
+  float mnx = rmin(rmin(a.x, b.x), c.x), mny = rmin(rmin(a.y, b.y), c.y), mnz = rmin(rmin(a.z, b.z), c.z);
+  float mxx = rmax(rmax(a.x, b.x), c.x), mxy = rmax(rmax(a.y, b.y), c.y), mxz = rmax(rmax(a.z, b.z), c.z);
+  const float xFlat = (float)(uint32_t)((mxx - mnx) < RT_FLT_EPSILON);
+  const float yFlat = (float)(uint32_t)((mxy - mny) < RT_FLT_EPSILON);
+  const float zFlat = (float)(uint32_t)((mxz - mnz) < RT_FLT_EPSILON);
+  mxx += xFlat * RT_FLT_EPSILON; mxy += yFlat * RT_FLT_EPSILON; mxz += zFlat * RT_FLT_EPSILON;
+  mnx -= xFlat * RT_FLT_EPSILON; mny -= yFlat * RT_FLT_EPSILON; mnz -= zFlat * RT_FLT_EPSILON;
+  // centroid (BVH.h:101-104) and normalisation to the scene box (:112-114)
+  const float cx = (a.x + b.x + c.x) / 3.0f, cy = (a.y + b.y + c.y) / 3.0f, cz = (a.z + b.z + c.z) / 3.0f;
+  const float nx = normalize_scale(sceneBB.bounds[0].x, sceneBB.bounds[1].x, cx);
+  const float ny = normalize_scale(sceneBB.bounds[0].y, sceneBB.bounds[1].y, cy);
+  const float nz = normalize_scale(sceneBB.bounds[0].z, sceneBB.bounds[1].z, cz);
+  const uint32_t code = morton3d(nx, ny, nz);
+  // leaf node: data = {parent (set by the emit stage), triangle-in-submesh, submesh, model}; type LEAF (1.0f) in bounds[0].w
+  uint4* o = reinterpret_cast<uint4*>(nodes + i);
+  o[0] = make_uint4(0xFFFFFFFFu, __ldg(tri_in_mesh + i), __float_as_uint(b.w), __float_as_uint(c.w));
+  reinterpret_cast<float4*>(o)[1] = make_float4(mnx, mny, mnz, 1.0f);
+  reinterpret_cast<float4*>(o)[2] = make_float4(mxx, mxy, mxz, 0.0f);
+  reinterpret_cast<uint2*>(pairs)[i] = make_uint2(code, i);
+}
+
+// ---- stage 3: Karras radix tree with the reference's duplicate-key chains ------------------------------------
+// findSplit (BVH.h:138-182)
+__device__ __forceinline__ int find_split(const uint2* __restrict__ list, int first, int last) {
+  const uint32_t firstCode = list[first].x, lastCode = list[last].x;
+  if (firstCode == lastCode) return first;
+  const int commonPrefix = __clz(firstCode ^ lastCode);
+  int split = first, step = last - first;
+  do {
+    step = (step + 1) >> 1;
+    const int newSplit = split + step;
+    if (newSplit < last) {
+      const int splitPrefix = __clz(firstCode ^ list[newSplit].x);
+      if (splitPrefix > commonPrefix) split = newSplit;
+    }
+  } while (step > 1);
+  return split;
+}
+// determineRange (BVH.h:190-282)
+__device__ __forceinline__ int2 determine_range(const uint2* __restrict__ list, int index, uint32_t size) {
+  const int lso = (int)size - 1;
+  if (index == 0) return make_int2(0, lso);
+  const int initialindex = index;
+  const uint32_t minone = list[index - 1].x, precis = list[index].x, pluone = list[index + 1].x;
+  int dir, d_min;
+  if (minone == precis && pluone == precis) {
+    // inside a run of equal codes: the node covers [index, end of run] (chain)
+    while (index > 0 && index < lso) {
+      index += 1;
+      if (index >= lso || list[index].x != list[index + 1].x) break;
+    }
+    return make_int2(initialindex, index);
+  }
+  const int lx = __clz(precis ^ minone), ly = __clz(precis ^ pluone);
+  if (lx > ly) { dir = -1; d_min = ly; } else { dir = 1; d_min = lx; }
+  int l_max = 2;
+  int testindex = index + l_max * dir;
+  while ((testindex <= lso && testindex >= 0) ? (__clz(precis ^ list[testindex].x) > d_min) : false) {
+    l_max <<= 1;
+    testindex = index + l_max * dir;
+  }
+  int l = 0;
+  for (int div = 2; l_max / div >= 1; div <<= 1) {
+    const int t = l_max / div;
+    const int newTest = index + (l + t) * dir;
+    if (newTest <= lso && newTest >= 0) {
+      const int splitPrefix = __clz(precis ^ list[newTest].x);
+      if (splitPrefix > d_min) l = l + t;
+    }
+  }
+  const int other = index + l * dir;
+  return make_int2(min(index, other), max(index, other));
+}
+
+// constructNode (BVH.h:291-321).  One thread per inner node; all N-1 are built (Q1 FIXED).
+// Writes: own children (data[1], data[2]; data[3] = 0), parent links of both children, root parent = UINT_MAX.
+// The inner box is NOT written here: refit merges (childA, childB, init box) and writes the result, which is what
+// the reference's fill (BVH.h:309-310) followed by merge3 (:333) leaves in memory.
+__global__ void __launch_bounds__(256)
+karras_emit_kernel(const clrt_uint2* __restrict__ pairs_, uint32_t n, clrt_bvh_node* __restrict__ nodes) {
+  const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx + 1 >= n) return;
+  const uint2* list = reinterpret_cast<const uint2*>(pairs_);
+  const int2 range = determine_range(list, (int)idx, n);
+  const int split = find_split(list, range.x, range.y);
+  const uint32_t self = idx + n;
+  const bool aIsLeaf = (range.x == split);
+  const bool bIsLeaf = (range.y == split + 1);
+  const uint32_t child_A = aIsLeaf ? list[split].y : (uint32_t)split + n;
+  const uint32_t child_B = bIsLeaf ? list[split + 1].y : (uint32_t)split + 1 + n;
+  uint32_t* d = nodes[self].data;
+  if (idx == 0) d[0] = 0xFFFFFFFFu;
+  d[1] = child_A; d[2] = child_B; d[3] = 0u;
+  nodes[child_A].data[0] = self;
+  nodes[child_B].data[0] = self;
+}
+
+// ---- stage 4: bottom-up refit with per-node arrival counters ---------------------------------------------------
+__device__ __forceinline__ float4 ldcg4(const float4* p) { return __ldcg(p); }
+
+__global__ void __launch_bounds__(256)
+refit_atomic_kernel(clrt_bvh_node* __restrict__ nodes, uint32_t* __restrict__ counters, uint32_t n, TraceNode* __restrict__ tnodes) {
+  const uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= n) return;
+  uint32_t current = __ldcg(&nodes[gid].data[0]);
+  while (current != 0xFFFFFFFFu) {
+    __threadfence();                                         // make this thread's box (written below) visible first
+    const uint32_t arrived = atomicAdd(counters + (current - n), 1u);
+    if (arrived == 0) return;                                // first arrival: the sibling subtree is not done yet
+    __threadfence();
+    const uint4 d = __ldcg(reinterpret_cast<const uint4*>(nodes + current));
+    const uint32_t cA = d.y, cB = d.z;
+    const float4* pa = reinterpret_cast<const float4*>(nodes + cA) + 1;
+    const float4* pb = reinterpret_cast<const float4*>(nodes + cB) + 1;
+    const float4 a0 = ldcg4(pa), a1 = ldcg4(pa + 1), b0 = ldcg4(pb), b1 = ldcg4(pb + 1);
+    // merge3(childA, childB, self) (AABB.h:107-113) with self = (FLT_MAX,FLT_MAX,FLT_MAX,INNER=0.0f),(FLT_MIN,FLT_MIN,FLT_MIN,0.0f)
+    float4 lo, hi;
+    lo.x = rmin(rmin(a0.x, b0.x), RT_FLT_MAX); lo.y = rmin(rmin(a0.y, b0.y), RT_FLT_MAX); lo.z = rmin(rmin(a0.z, b0.z), RT_FLT_MAX);
+    lo.w = rmin(rmin(a0.w, b0.w), 0.0f);
+    hi.x = rmax(rmax(a1.x, b1.x), RT_FLT_MIN); hi.y = rmax(rmax(a1.y, b1.y), RT_FLT_MIN); hi.z = rmax(rmax(a1.z, b1.z), RT_FLT_MIN);
+    hi.w = rmax(rmax(a1.w, b1.w), 0.0f);
+    float4* po = reinterpret_cast<float4*>(nodes + current) + 1;
+    __stcg(po, lo); __stcg(po + 1, hi);
+    float4* tn = reinterpret_cast<float4*>(tnodes + (current - n));
+    __stcg(tn,     make_float4(a0.x, a0.y, a0.z, a1.x));
+    __stcg(tn + 1, make_float4(a1.y, a1.z, b0.x, b0.y));
+    __stcg(tn + 2, make_float4(b0.z, b1.x, b1.y, b1.z));
+    __stcg(reinterpret_cast<uint4*>(tn + 3), make_uint4(cA, cB, 0u, 0u));
+    current = d.x;
+  }
+}
+
+} // namespace
+
+// ---- manager ---------------------------------------------------------------------------------------------------
+int bvh_init_frame(clrt_accel* a) {
+  clrt_ctx* ctx = a->ctx;
+  const uint32_t n = a->scene->n_tris;
+  a->n = n;
+  a->built = false;
+  a->pairs_items = pow2ceil_u32(n ? n : 1);                  // the reference pads to 2^k for its bitonic sort (BVHManager.cpp:129-131)
+  const size_t nodes_bytes = (size_t)(n ? 2 * (size_t)n - 1 : 1) * sizeof(clrt_bvh_node);
+  if (nodes_bytes > a->nodes_cap || (size_t)a->pairs_items * 8 > a->pairs_cap || (size_t)n * 4 > a->counters_cap ||
+      (size_t)n * sizeof(TraceNode) > a->tnodes_cap)
+    CLRT_CUDA(cudaStreamSynchronize(ctx->stream));
+  CLRT_TRY(clrt_grow((void**)&a->d_nodes, &a->nodes_cap, nodes_bytes));
+  CLRT_TRY(clrt_grow((void**)&a->d_pairs, &a->pairs_cap, (size_t)a->pairs_items * 8));
+  CLRT_TRY(clrt_grow((void**)&a->d_counters, &a->counters_cap, (size_t)(n ? n : 1) * 4));
+  CLRT_TRY(clrt_grow((void**)&a->d_tnodes, &a->tnodes_cap, (size_t)(n ? n : 1) * sizeof(TraceNode)));
+  // fills of initializeFrame (BVHManager.cpp:138-147): pairs = (UINT_MAX,UINT_MAX), counters = 0
+  CLRT_CUDA(cudaMemsetAsync(a->d_pairs, 0xFF, (size_t)a->pairs_items * 8, ctx->stream));
+  CLRT_CUDA(cudaMemsetAsync(a->d_counters, 0, (size_t)(n ? n : 1) * 4, ctx->stream));
+  return 0;
+}
+
+int bvh_construct(clrt_accel* a) {
+  clrt_ctx* ctx = a->ctx;
+  const uint32_t n = a->n;
+  if (!a->d_nodes) CLRT_FAIL("BVH construct: initializeFrame was not called");
+  if (n != a->scene->n_tris) CLRT_FAIL("BVH construct: scene changed since initializeFrame");
+  cudaStream_t s = ctx->stream;
+  const bool tm = a->timing;
+  if (tm) CLRT_CUDA(cudaEventRecord(a->ev[0], s));
+  if (n) {
+    morton_leaves_kernel<<<(n + 255) / 256, 256, 0, s>>>(a->scene->d_tris, a->scene->d_triInMesh, n,
+                                                        a->scene->header.modelsBoundingBox, a->d_nodes, a->d_pairs);
+    CLRT_CHECK_LAUNCH();
+  }
+  if (tm) CLRT_CUDA(cudaEventRecord(a->ev[1], s));
+  // Only the N real pairs are sorted: the (UINT_MAX,UINT_MAX) padding is already at the end, which is where the
+  // reference's sort over 2^k items leaves it.  Morton keys have 30 bits.
+  CLRT_TRY(sort_pairs_radix(ctx, a->d_pairs, n, 30));
+  if (tm) CLRT_CUDA(cudaEventRecord(a->ev[2], s));
+  if (n > 1) {
+    karras_emit_kernel<<<(n - 1 + 255) / 256, 256, 0, s>>>(a->d_pairs, n, a->d_nodes);
+    CLRT_CHECK_LAUNCH();
+  }
+  if (tm) CLRT_CUDA(cudaEventRecord(a->ev[3], s));
+  if (n > 1) {
+    refit_atomic_kernel<<<(n + 255) / 256, 256, 0, s>>>(a->d_nodes, a->d_counters, n, a->d_tnodes);
+    CLRT_CHECK_LAUNCH();
+  }
+  if (tm) {
+    CLRT_CUDA(cudaEventRecord(a->ev[4], s));
+    CLRT_CUDA(cudaEventSynchronize(a->ev[4]));
+    for (int i = 0; i < 4; i++) CLRT_CUDA(cudaEventElapsedTime(&a->stage_ms[i], a->ev[i], a->ev[i + 1]));
+    CLRT_CUDA(cudaEventElapsedTime(&a->stage_ms[CLRT_STAGE_TOTAL], a->ev[0], a->ev[4]));
+  }
+  a->built = true;
+  return 0;
+}
+
+extern "C" int clrt_bvh_export_nodes(clrt_accel* a, void* h_nodes) {
+  if (!a || !h_nodes) CLRT_FAIL("clrt_bvh_export_nodes: NULL argument");
+  if (a->kind != ACCEL_BVH || !a->built) CLRT_FAIL("clrt_bvh_export_nodes: not a constructed BVH");
+  CLRT_CUDA(cudaSetDevice(a->ctx->device));
+  const size_t bytes = (size_t)(a->n ? 2 * (size_t)a->n - 1 : 0) * sizeof(clrt_bvh_node);
+  if (bytes) CLRT_CUDA(cudaMemcpyAsync(h_nodes, a->d_nodes, bytes, cudaMemcpyDeviceToHost, a->ctx->stream));
+  CLRT_CUDA(cudaStreamSynchronize(a->ctx->stream));
+  return 0;
+}
+extern "C" int clrt_bvh_export_pairs(clrt_accel* a, void* h_pairs) {
+  if (!a || !h_pairs) CLRT_FAIL("clrt_bvh_export_pairs: NULL argument");
+  if (a->kind != ACCEL_BVH || !a->built) CLRT_FAIL("clrt_bvh_export_pairs: not a constructed BVH");
+  CLRT_CUDA(cudaSetDevice(a->ctx->device));
+  if (a->n) CLRT_CUDA(cudaMemcpyAsync(h_pairs, a->d_pairs, (size_t)a->n * 8, cudaMemcpyDeviceToHost, a->ctx->stream));
+  CLRT_CUDA(cudaStreamSynchronize(a->ctx->stream));
+  return 0;
+}

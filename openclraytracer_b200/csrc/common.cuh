@@ -1,0 +1,129 @@
+// common.cuh — internal declarations shared by the translation units of libclrt_cuda.so (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include <string>
+#include <vector>
+#include "../../include/clrt.h"
+
+// ---- error plumbing (Result + Errata convention, R/Include/Common/Errata.h:47-110) -------------------
+void clrt_set_error(const char* fmt, ...);
+#define CLRT_FAIL(...) do { clrt_set_error(__VA_ARGS__); return 1; } while (0)
+#define CLRT_CUDA(expr) do { cudaError_t e__ = (expr); if (e__ != cudaSuccess) { \
+  clrt_set_error("%s:%d %s -> %s", __FILE__, __LINE__, #expr, cudaGetErrorString(e__)); return 1; } } while (0)
+#define CLRT_TRY(expr) do { int r__ = (expr); if (r__) return r__; } while (0)
+#define CLRT_CHECK_LAUNCH() CLRT_CUDA(cudaGetLastError())
+
+// ---- handles -------------------------------------------------------------------------------------------
+struct clrt_ctx {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  bool owns_stream = false;
+  int sm_count = 0;
+  cudaDeviceProp prop;
+  // scratch reused by the building blocks (grow-only)
+  void* scratch = nullptr; size_t scratch_bytes = 0;
+  void* sort_alt = nullptr; size_t sort_alt_bytes = 0;
+  void* pinned = nullptr; size_t pinned_bytes = 0;     // staging for small host<->device transfers
+};
+int clrt_ctx_scratch(clrt_ctx* ctx, size_t bytes, void** out);      // grow-only device scratch
+int clrt_ctx_sort_alt(clrt_ctx* ctx, size_t bytes, void** out);     // ping-pong buffer of the radix sort
+int clrt_ctx_pinned(clrt_ctx* ctx, size_t bytes, void** out);
+
+struct clrt_buf {
+  clrt_ctx* ctx = nullptr;
+  void* dptr = nullptr;
+  size_t size = 0, capacity = 0;
+};
+
+struct MeshEntry {           // one per sub-mesh of the packed scene, built on the host at upload
+  uint64_t byteOffset;       // offset of the MeshHeader inside the scene buffer
+  uint32_t firstTriangle;    // global index of the sub-mesh's first triangle
+  uint32_t numTriangles;
+  uint32_t numVertices;
+  uint32_t materialIndex;
+  uint32_t modelIndex;
+  uint32_t submeshIndex;
+};
+
+struct clrt_scene {
+  clrt_ctx* ctx = nullptr;
+  uint8_t* d_scene = nullptr; size_t bytes = 0;
+  clrt_scene_header header;
+  std::vector<MeshEntry> meshes;
+  MeshEntry* d_meshes = nullptr;
+  clrt_triangle* d_tris = nullptr;      // N x 48 B
+  uint32_t* d_triInMesh = nullptr;      // N x 4 B : triangle index inside its sub-mesh (leaf data[1])
+  clrt_light* d_lights = nullptr;       // numberOfLights (copy, 16 B aligned)
+  clrt_material* d_materials = nullptr; // numberOfMaterials
+  uint32_t n_tris = 0, n_lights = 0, n_materials = 0;
+};
+
+// 64-byte traversal node written by the refit kernel next to the reference-layout nodes:
+// both child boxes + child ids in one aligned record (4 x 16 B loads).
+struct __align__(16) TraceNode {
+  float ax0, ay0, az0, ax1;   // child A min.xyz, max.x
+  float ay1, az1, bx0, by0;   // child A max.yz, child B min.xy
+  float bz0, bx1, by1, bz1;   // child B min.z, max.xyz
+  uint32_t childA, childB, pad0, pad1;  // child id < N : leaf (= triangle index), else inner node id (slot id - N)
+};
+
+enum AccelKind { ACCEL_BVH = 0, ACCEL_TLG = 1 };
+
+struct clrt_accel {
+  AccelKind kind = ACCEL_BVH;
+  clrt_ctx* ctx = nullptr;
+  const clrt_scene* scene = nullptr;
+  int trace_mode = CLRT_TRACE_FAST;
+  bool timing = false;
+  float stage_ms[CLRT_STAGE_COUNT] = {0};
+  cudaEvent_t ev[CLRT_STAGE_COUNT + 1] = {nullptr};
+  // --- BVH ---
+  uint32_t n = 0;                 // leaves
+  clrt_bvh_node* d_nodes = nullptr; size_t nodes_cap = 0;     // (2N-1) x 48 B, reference layout
+  clrt_uint2* d_pairs = nullptr;  size_t pairs_cap = 0;       // pow2ceil(N) x 8 B (padding = UINT_MAX pairs)
+  uint32_t* d_counters = nullptr; size_t counters_cap = 0;    // N x 4 B
+  TraceNode* d_tnodes = nullptr;  size_t tnodes_cap = 0;      // (N-1) x 64 B
+  uint32_t pairs_items = 0;
+  bool built = false;
+  // --- primary contacts / frame scratch ---
+  clrt_contact* d_contacts = nullptr; size_t contacts_cap = 0;
+  void* d_frame_scratch = nullptr; size_t frame_scratch_cap = 0;
+  void* d_fb = nullptr; size_t fb_cap = 0;
+  uint32_t* d_tile_counter = nullptr;
+  // --- TLG --- (tlg.cu)
+  struct TlgState* tlg = nullptr;
+  float top_density = 2.0f, leaf_density = 2.0f;
+};
+
+// ---- internal entry points between translation units ---------------------------------------------------
+int clrt_grow(void** p, size_t* cap, size_t bytes);               // cudaFree+cudaMalloc when bytes > *cap
+int bvh_init_frame(clrt_accel* a);
+int bvh_construct(clrt_accel* a);
+// nranks == 0: whole frame with raster-ordered output; otherwise stripe `rank` of `nranks` in stripe order
+int bvh_trace_primary(clrt_accel* a, const clrt_camera& cam, clrt_contact* out, uint32_t rank, uint32_t nranks);
+int bvh_trace_rays(clrt_accel* a, const clrt_ray* rays, clrt_contact* out, uint32_t n);
+int tlg_init_frame(clrt_accel* a);
+int tlg_construct(clrt_accel* a);
+int tlg_trace_primary(clrt_accel* a, const clrt_camera& cam, clrt_contact* out, uint32_t rank, uint32_t nranks);
+int tlg_trace_rays(clrt_accel* a, const clrt_ray* rays, clrt_contact* out, uint32_t n);
+void tlg_destroy(clrt_accel* a);
+int sort_pairs_radix(clrt_ctx* ctx, clrt_uint2* pairs, size_t n, int key_bits);
+int scan_inclusive(clrt_ctx* ctx, const uint32_t* in, uint32_t* out, size_t n);
+
+static inline uint32_t pow2ceil_u32(uint32_t x) { uint32_t p = 1; while (p < x) p <<= 1; return p; }
+
+// ---- image-space tiling: 32x8-pixel tiles, tile t owned by rank t % nranks --------------
+#define CLRT_TILE_W 32
+#define CLRT_TILE_H 8
+#define CLRT_TILE_PIXELS 256
+struct TileGrid { uint32_t tilesX, tilesY, tiles; };
+__host__ __device__ inline TileGrid make_tile_grid(uint32_t resX, uint32_t resY) {
+  TileGrid g; g.tilesX = (resX + CLRT_TILE_W - 1) / CLRT_TILE_W; g.tilesY = (resY + CLRT_TILE_H - 1) / CLRT_TILE_H;
+  g.tiles = g.tilesX * g.tilesY; return g;
+}
+__host__ __device__ inline uint32_t stripe_tile_count(uint32_t tiles, uint32_t rank, uint32_t nranks) {
+  return tiles / nranks + ((tiles % nranks) > rank ? 1u : 0u);
+}

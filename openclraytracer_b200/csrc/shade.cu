@@ -1,0 +1,196 @@
+// shade.cu — ray generation, shadow rays and "simple shading" as CUDA kernels.
+//  generateRay            R/Include/CLData/CLStructs.h:95-106
+//  cpuShadeBlinnPhong     R/Include/CLData/Shading.h:74-166 (a HOST loop in the reference:
+//                         R/src/Demos/OpenCLRayTracerDemo/OpenCLRayTracerDemo.cpp:298-316)
+//  lightEnergyPercentage  R/Include/CLData/Primitives/Light.h:55-58
+// Shadow rays do not exist in the reference (KNOWN_ISSUES_AND_TODO.txt:27-30); they are produced here and traced
+// through the reference's generic-ray entry point (generateContacts(rays, contacts, n)).
+#include "common.cuh"
+#include "rtmath.cuh"
+
+namespace {
+
+constexpr float CAMERA_LIGHT_ENERGY = 100000.0f;        // Shading.h:121
+constexpr float SHADOW_EPS_REL = 1.0e-4f;               // shadow-ray origin offset, relative to the primary hit distance
+
+__global__ void __launch_bounds__(256)
+primary_rays_kernel(clrt_camera cam, clrt_ray* __restrict__ rays) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= cam.resX * cam.resY) return;
+  Vec3 o, d; generate_ray(cam, i, o, d);
+  uint4* p = reinterpret_cast<uint4*>(rays + i);
+  p[0] = make_uint4(i, 0u, 0u, 0u);
+  reinterpret_cast<float4*>(p)[1] = make_float4(o.x, o.y, o.z, 0.0f);
+  reinterpret_cast<float4*>(p)[2] = make_float4(d.x, d.y, d.z, 0.0f);
+}
+
+__device__ __forceinline__ Vec3 light_position(const clrt_light* __restrict__ lights, uint32_t n_lights, uint32_t l, Vec3 camPos, float& energy) {
+  if (l < n_lights) { const float4 q = __ldg(reinterpret_cast<const float4*>(lights + l)); energy = q.w; return v3(q.x, q.y, q.z); }
+  energy = CAMERA_LIGHT_ENERGY; return camPos;           // the synthetic camera light (Shading.h:114-126)
+}
+
+// One thread per (contact, light).  Ray index r = c*(L+1)+l.
+__global__ void __launch_bounds__(256)
+shadow_rays_kernel(clrt_camera cam, const clrt_contact* __restrict__ contacts, uint32_t n, const clrt_light* __restrict__ lights,
+                   uint32_t n_lights, clrt_ray* __restrict__ rays, unsigned long long* __restrict__ ray_counter) {
+  const uint32_t L1 = n_lights + 1;
+  const uint64_t r = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
+  const bool in_range = r < (uint64_t)n * L1;
+  bool live = false;
+  if (in_range) {
+    const uint32_t c = (uint32_t)(r / L1), l = (uint32_t)(r % L1);
+    const uint4 head = __ldg(reinterpret_cast<const uint4*>(contacts + c));
+    const float4 nd = __ldg(reinterpret_cast<const float4*>(contacts + c) + 1);
+    uint4 h = make_uint4(0xFFFFFFFFu, 0u, 0u, 0u);
+    float4 ro = make_float4(0.f, 0.f, 0.f, 0.f), rd = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (nd.w > 0.0f && head.x != 0xFFFFFFFFu) {
+      Vec3 o, d; generate_ray(cam, head.x, o, d);
+      const Vec3 P = vadd(o, vscale(d, nd.w));
+      float energy; const Vec3 lp = light_position(lights, n_lights, l, o, energy);
+      const Vec3 dir = vnormalize(vsub(lp, P));
+      const Vec3 org = vadd(P, vscale(dir, SHADOW_EPS_REL * nd.w));
+      h.x = (uint32_t)r; ro = make_float4(org.x, org.y, org.z, 0.f); rd = make_float4(dir.x, dir.y, dir.z, 0.f);
+      live = true;
+    }
+    uint4* p = reinterpret_cast<uint4*>(rays + r);
+    p[0] = h; reinterpret_cast<float4*>(p)[1] = ro; reinterpret_cast<float4*>(p)[2] = rd;
+  }
+  const unsigned m = __ballot_sync(0xffffffffu, live);
+  if ((threadIdx.x & 31) == 0 && m && ray_counter) atomicAdd(ray_counter, (unsigned long long)__popc(m));
+}
+
+__device__ __forceinline__ uint32_t to_u8(float c) {
+  c = (c > 0.0f) ? c : 0.0f;            // NaN -> 0
+  c = (c < 1.0f) ? c : 1.0f;
+  return (uint32_t)(c * 255.0f + 0.5f);
+}
+
+// One thread per contact.
+__global__ void __launch_bounds__(256)
+shade_kernel(clrt_camera cam, const clrt_contact* __restrict__ contacts, uint32_t n, const clrt_light* __restrict__ lights,
+             uint32_t n_lights, const clrt_material* __restrict__ materials, uint32_t n_materials,
+             const clrt_contact* __restrict__ shadow, uint32_t* __restrict__ rgba8, float4* __restrict__ rgba_f32) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint4 head = __ldcs(reinterpret_cast<const uint4*>(contacts + i));
+  const float4 nd = __ldcs(reinterpret_cast<const float4*>(contacts + i) + 1);
+  float4 color = make_float4(0.f, 0.f, 0.f, 0.f);
+  uint32_t packed = 0u;
+  if (nd.w > 0.0f && head.x != 0xFFFFFFFFu) {                      // OpenCLRayTracerDemo.cpp:305
+    // default material (Shading.h:76-86) unless the index is valid (:92-96)
+    Vec3 amb = v3(0.2f, 0.2f, 0.2f), dif = v3(1.f, 1.f, 1.f), spc = v3(1.f, 0.f, 0.f);
+    float shininess = 0.4f;
+    if (head.y < n_materials) {
+      const float4* m = reinterpret_cast<const float4*>(materials + head.y);
+      const float4 a = __ldg(m), d4 = __ldg(m + 1), s4 = __ldg(m + 2), tail = __ldg(m + 5);
+      amb = v3(a.x, a.y, a.z); dif = v3(d4.x, d4.y, d4.z); spc = v3(s4.x, s4.y, s4.z); shininess = tail.x;
+    }
+    Vec3 o, d; generate_ray(cam, head.x, o, d);
+    const Vec3 P = vadd(o, vscale(d, nd.w));
+    const Vec3 N = v3(nd.x, nd.y, nd.z);
+    const Vec3 V = vnormalize(vsub(o, P));
+    float cr = amb.x, cg = amb.y, cb = amb.z;
+    const uint32_t L1 = n_lights + 1;
+    float totalEnergy = 0.0f;
+    for (uint32_t l = 0; l < L1; l++) {
+      float energy; const Vec3 lp = light_position(lights, n_lights, l, o, energy);
+      const float dist = vlength(vsub(lp, P));
+      totalEnergy += rmax(1.0f - dist / energy, 0.0f) * energy;
+    }
+    for (uint32_t l = 0; l < L1; l++) {
+      float energy; const Vec3 lp = light_position(lights, n_lights, l, o, energy);
+      Vec3 Lv = vsub(lp, P);
+      const float dist = vlength(Lv);
+      if (shadow) {                                                // ours: occluded lights add nothing
+        const float st = __ldcs(&shadow[(size_t)i * L1 + l].normalAndintersectionDistance.w);
+        if (st > 0.0f && st < dist - SHADOW_EPS_REL * nd.w) continue;
+      }
+      const float intensity = rmax(1.0f - dist / energy, 0.0f);
+      const float pct = (intensity * energy) / totalEnergy;
+      const float ls = intensity * pct;
+      Lv = vnormalize(Lv);
+      float LdotN = vdot(Lv, N);
+      LdotN = LdotN > 0.0f ? LdotN : 0.0f;
+      cr += dif.x * LdotN * ls; cg += dif.y * LdotN * ls; cb += dif.z * LdotN * ls;
+      const Vec3 R = vnormalize(vsub(vscale(N, 2.0f * LdotN), Lv));
+      const float nSpecular = powf(vdot(R, V), shininess);
+      cr += rmax(spc.x * nSpecular * ls, 0.0f); cg += rmax(spc.y * nSpecular * ls, 0.0f); cb += rmax(spc.z * nSpecular * ls, 0.0f);
+    }
+    color = make_float4(rmin(cr, 1.0f), rmin(cg, 1.0f), rmin(cb, 1.0f), 1.0f);
+    packed = to_u8(color.x) | (to_u8(color.y) << 8) | (to_u8(color.z) << 16) | (255u << 24);
+  }
+  if (rgba8) __stcs(rgba8 + i, packed);
+  if (rgba_f32) __stcs(rgba_f32 + i, color);
+}
+
+// stripes (rank-major, each padded to ceil(tiles/nranks) tiles, tile-major, 256 px per tile) -> raster
+__global__ void __launch_bounds__(256)
+untile_kernel(const uint32_t* __restrict__ stripes, uint32_t resX, uint32_t resY, uint32_t nranks, uint32_t* __restrict__ raster) {
+  const TileGrid g = make_tile_grid(resX, resY);
+  const uint32_t gt = blockIdx.x;                         // global tile
+  const uint32_t rank = gt % nranks, lt = gt / nranks;
+  // every rank's stripe is padded to ceil(tiles/nranks) tiles so that an all-gather of equal chunks lays them out
+  const uint32_t stripe_first_tile = rank * ((g.tiles + nranks - 1) / nranks);
+  const uint32_t t = threadIdx.x;
+  const uint32_t x = (gt % g.tilesX) * CLRT_TILE_W + (t & 31u), y = (gt / g.tilesX) * CLRT_TILE_H + (t >> 5);
+  if (x < resX && y < resY) raster[y * resX + x] = __ldcs(stripes + (size_t)(stripe_first_tile + lt) * CLRT_TILE_PIXELS + t);
+}
+
+} // namespace
+
+extern "C" int clrt_generate_primary_rays(clrt_ctx* ctx, const clrt_camera* h_camera, void* dptr_rays) {
+  if (!ctx || !h_camera || !dptr_rays) CLRT_FAIL("clrt_generate_primary_rays: NULL argument");
+  CLRT_CUDA(cudaSetDevice(ctx->device));
+  const uint64_t n = (uint64_t)h_camera->resX * h_camera->resY;
+  if (n == 0) return 0;
+  if (n > 0xFFFFFFFFull) CLRT_FAIL("clrt_generate_primary_rays: resolution too large");
+  primary_rays_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(*h_camera, (clrt_ray*)dptr_rays);
+  CLRT_CHECK_LAUNCH();
+  return 0;
+}
+
+int shade_launch_shadow_rays(clrt_ctx* ctx, const clrt_scene* scene, const clrt_camera& cam, const clrt_contact* contacts,
+                             uint32_t n, clrt_ray* rays, unsigned long long* d_counter) {
+  const uint64_t total = (uint64_t)n * (scene->n_lights + 1);
+  if (!total) return 0;
+  if (total > 0xFFFFFFFFull) CLRT_FAIL("shadow rays: %llu rays exceed 2^32-1", (unsigned long long)total);
+  shadow_rays_kernel<<<(unsigned)((total + 255) / 256), 256, 0, ctx->stream>>>(cam, contacts, n, scene->d_lights, scene->n_lights, rays, d_counter);
+  CLRT_CHECK_LAUNCH();
+  return 0;
+}
+
+int shade_launch(clrt_ctx* ctx, const clrt_scene* scene, const clrt_camera& cam, const clrt_contact* contacts, uint32_t n,
+                 const clrt_contact* shadow, uint32_t* rgba8, float4* rgba_f32) {
+  if (!n) return 0;
+  shade_kernel<<<(n + 255) / 256, 256, 0, ctx->stream>>>(cam, contacts, n, scene->d_lights, scene->n_lights, scene->d_materials,
+                                                        scene->n_materials, shadow, rgba8, rgba_f32);
+  CLRT_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int clrt_generate_shadow_rays(clrt_ctx* ctx, const clrt_scene* scene, const clrt_camera* h_camera,
+                                         const void* dptr_contacts, uint32_t n, void* dptr_rays, uint32_t* out_rays_per_contact) {
+  if (!ctx || !scene || !h_camera || (n && (!dptr_contacts || !dptr_rays))) CLRT_FAIL("clrt_generate_shadow_rays: NULL argument");
+  CLRT_CUDA(cudaSetDevice(ctx->device));
+  if (out_rays_per_contact) *out_rays_per_contact = scene->n_lights + 1;
+  return shade_launch_shadow_rays(ctx, scene, *h_camera, (const clrt_contact*)dptr_contacts, n, (clrt_ray*)dptr_rays, nullptr);
+}
+
+extern "C" int clrt_shade(clrt_ctx* ctx, const clrt_scene* scene, const clrt_camera* h_camera, const void* dptr_contacts,
+                          uint32_t n, const void* dptr_shadow_contacts, void* dptr_rgba8, void* dptr_rgba_f32) {
+  if (!ctx || !scene || !h_camera || (n && !dptr_contacts)) CLRT_FAIL("clrt_shade: NULL argument");
+  if (!dptr_rgba8 && !dptr_rgba_f32) CLRT_FAIL("clrt_shade: no output buffer");
+  CLRT_CUDA(cudaSetDevice(ctx->device));
+  return shade_launch(ctx, scene, *h_camera, (const clrt_contact*)dptr_contacts, n, (const clrt_contact*)dptr_shadow_contacts,
+                      (uint32_t*)dptr_rgba8, (float4*)dptr_rgba_f32);
+}
+
+extern "C" int clrt_frame_untile(clrt_ctx* ctx, const void* dptr_stripes, uint32_t resX, uint32_t resY, uint32_t nranks, void* dptr_raster_rgba8) {
+  if (!ctx || !dptr_stripes || !dptr_raster_rgba8 || !nranks) CLRT_FAIL("clrt_frame_untile: bad argument");
+  CLRT_CUDA(cudaSetDevice(ctx->device));
+  const TileGrid g = make_tile_grid(resX, resY);
+  if (!g.tiles) return 0;
+  untile_kernel<<<g.tiles, 256, 0, ctx->stream>>>((const uint32_t*)dptr_stripes, resX, resY, nranks, (uint32_t*)dptr_raster_rgba8);
+  CLRT_CHECK_LAUNCH();
+  return 0;
+}

@@ -1,0 +1,216 @@
+// trace.cu — BVH traversal + intersection: BVHManager::generateContacts (R/src/CLRayTracerEngine/BVHManager.cpp:234-329),
+// kernels generateContacts / generateContacts2 (R/src/CLRayTracerEngine/BVHKernels.cl:84-117) ->
+// bvh_generate_contact (R/Include/CLData/AccelerationStructs/BVH.h:344-408).
+//
+// Design (B200, no RT cores; latency/divergence bound, not HBM or tensor bound):
+//  * persistent warps: the grid is sized to the resident capacity of the 148 SMs; every warp pulls 8x4-pixel packets
+//    (primary) or 32-ray packets (generic) from one atomic counter -> dynamic work stealing inside the GPU, and the
+//    unit the image-space multi-GPU stripes are made of (32x8-pixel tiles = 8 packets, tile t owned by rank t % nranks).
+//  * 64-byte TraceNode per inner node (both child boxes + child ids, four 16-byte loads) instead of the reference's
+//    48-byte node + two 32-byte child-box fetches from the children's records; 48-byte 16-byte-aligned triangles
+//    instead of the per-fetch header walk of the packed scene.
+//  * FAST policy: leaf children are intersected as soon as their box is accepted (so duplicate-key chains never
+//    touch the stack), the nearer inner child is entered first and a child whose entry t exceeds the current best
+//    is culled.  The stack only ever holds inner nodes with strictly growing key prefixes -> at most 32 entries
+//    (the "short stack"), kept in local memory that stays L1 resident.
+//  * REFERENCE_ORDER policy: child A before child B, no culling, leaves go through the stack — the reference's
+//    exact visiting order, hence bit-identical contacts including the winners of exact ties.  Parity vehicle.
+//  Box validity is the reference's in both policies: `t > 0 || origin inside` with the compare-select slab test.
+#include "common.cuh"
+#include "rtmath.cuh"
+
+namespace {
+
+constexpr int TRACE_THREADS = 128;
+constexpr int FAST_STACK = 40;
+constexpr int REF_STACK = 96;
+constexpr uint32_t SENTINEL = 0xFFFFFFFFu;
+
+struct Hit { float t; uint32_t tri; };
+
+__device__ __forceinline__ void test_triangle(const clrt_triangle* __restrict__ tris, uint32_t id, Vec3 o, Vec3 d, Hit& h) {
+  const float4* p = reinterpret_cast<const float4*>(tris + id);
+  const float4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
+  const float t = triangle_intersect(v3(a.x, a.y, a.z), v3(b.x, b.y, b.z), v3(c.x, c.y, c.z), o, d);
+  if (t > 0.0f && t < h.t) { h.t = t; h.tri = id; }     // BVH.h:392: strict, first tested wins exact ties
+}
+
+template <bool REF_ORDER>
+__device__ __forceinline__ Hit traverse(const TraceNode* __restrict__ tnodes, const clrt_triangle* __restrict__ tris,
+                                        uint32_t n, Vec3 o, Vec3 d) {
+  Hit h; h.t = RT_FLT_MAX; h.tri = SENTINEL;
+  if (n == 0) return h;
+  if (n == 1) { test_triangle(tris, 0, o, d, h); return h; }    // the reference reads past its node buffer here
+  const Vec3 inv = v3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+  uint32_t stack[REF_ORDER ? REF_STACK : FAST_STACK];
+  int sp = 0;
+  stack[sp++] = SENTINEL;
+  uint32_t cur = n;                                             // root = slot N (BVHManager.cpp:254)
+  do {
+    if (cur >= n) {
+      const float4* p = reinterpret_cast<const float4*>(tnodes + (cur - n));
+      const float4 q0 = __ldg(p), q1 = __ldg(p + 1), q2 = __ldg(p + 2);
+      const uint4 q3 = __ldg(reinterpret_cast<const uint4*>(p + 3));
+      const float tA = aabb_intersect(q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, o, inv);
+      const float tB = aabb_intersect(q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, o, inv);
+      bool aValid = tA > 0.0f || point_inside(q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, o);
+      bool bValid = tB > 0.0f || point_inside(q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, o);
+      const uint32_t cA = q3.x, cB = q3.y;
+      if (REF_ORDER) {
+        if (aValid && bValid) { cur = cA; if (sp < REF_STACK) stack[sp++] = cB; }
+        else if (aValid) cur = cA;
+        else if (bValid) cur = cB;
+        else cur = stack[--sp];
+      } else {
+        if (aValid && cA < n) { if (!(tA > h.t)) test_triangle(tris, cA, o, d, h); aValid = false; }
+        if (bValid && cB < n) { if (!(tB > h.t)) test_triangle(tris, cB, o, d, h); bValid = false; }
+        aValid = aValid && !(tA > h.t);
+        bValid = bValid && !(tB > h.t);
+        if (aValid && bValid) {
+          const bool bNear = tB < tA;
+          cur = bNear ? cB : cA;
+          if (sp < FAST_STACK) stack[sp++] = bNear ? cA : cB;
+        }
+        else if (aValid) cur = cA;
+        else if (bValid) cur = cB;
+        else cur = stack[--sp];
+      }
+    } else {
+      test_triangle(tris, cur, o, d, h);
+      cur = stack[--sp];
+    }
+  } while (cur != SENTINEL);
+  return h;
+}
+
+__device__ __forceinline__ void write_contact(clrt_contact* __restrict__ out, uint32_t slot, uint32_t pixelIndex, const Hit& h,
+                                              const clrt_triangle* __restrict__ tris) {
+  uint4 head = make_uint4(pixelIndex, 0u, SENTINEL, 0u);
+  float4 nd = make_float4(0.0f, 0.0f, 0.0f, 0.0f);                 // miss: contactDist = 0 (BVH.h:402-406)
+  if (h.tri != SENTINEL) {
+    const float4* p = reinterpret_cast<const float4*>(tris + h.tri);
+    const float4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
+    const Vec3 nrm = triangle_normal(v3(a.x, a.y, a.z), v3(b.x, b.y, b.z), v3(c.x, c.y, c.z));
+    nd = make_float4(nrm.x, nrm.y, nrm.z, h.t);
+    head.y = __float_as_uint(a.w);                                  // MeshHeader.materialIndex
+    head.z = h.tri;                                                 // pad[0] = primitive id (Q11)
+  }
+  uint4* o = reinterpret_cast<uint4*>(out + slot);
+  __stcs(o, head);
+  __stcs(reinterpret_cast<float4*>(o) + 1, nd);
+}
+
+// Primary rays.  Work unit: 8x4-pixel packet; 8 packets form a 32x8 tile; local tile lt of this rank is global
+// tile rank + lt*nranks.  raster != 0: contact goes to out[pixelIndex] (the reference's output[c.pixelIndex] = c);
+// raster == 0: stripe order, slot = lt*256 + y*32 + x, out-of-image slots get pixelIndex = UINT_MAX.
+template <bool REF_ORDER>
+__global__ void __launch_bounds__(TRACE_THREADS)
+trace_primary_kernel(const clrt_camera cam, const TraceNode* __restrict__ tnodes,
+                     const clrt_triangle* __restrict__ tris, uint32_t n, clrt_contact* __restrict__ out,
+                     uint32_t rank, uint32_t nranks, int raster, uint32_t* __restrict__ counter) {
+  const TileGrid g = make_tile_grid(cam.resX, cam.resY);
+  const uint32_t packets = stripe_tile_count(g.tiles, rank, nranks) * 8u;
+  const int lane = threadIdx.x & 31;
+  while (true) {
+    uint32_t pk = 0;
+    if (lane == 0) pk = atomicAdd(counter, 1u);
+    pk = __shfl_sync(0xffffffffu, pk, 0);
+    if (pk >= packets) break;
+    const uint32_t lt = pk >> 3, sub = pk & 7u;
+    const uint32_t gt = rank + lt * nranks;
+    const uint32_t tx = (gt % g.tilesX) * CLRT_TILE_W + (sub & 3u) * 8u + (lane & 7);
+    const uint32_t ty = (gt / g.tilesX) * CLRT_TILE_H + (sub >> 2) * 4u + (lane >> 3);
+    const uint32_t inTile = ((sub >> 2) * 4u + (lane >> 3)) * CLRT_TILE_W + (sub & 3u) * 8u + (lane & 7);
+    const bool inside = tx < cam.resX && ty < cam.resY;
+    const uint32_t pixel = ty * cam.resX + tx;
+    if (inside) {
+      Vec3 o, d;
+      generate_ray(cam, pixel, o, d);
+      const Hit h = traverse<REF_ORDER>(tnodes, tris, n, o, d);
+      write_contact(out, raster ? pixel : lt * CLRT_TILE_PIXELS + inTile, pixel, h, tris);
+    } else if (!raster) {
+      Hit h; h.t = RT_FLT_MAX; h.tri = SENTINEL;
+      write_contact(out, lt * CLRT_TILE_PIXELS + inTile, SENTINEL, h, tris);
+    }
+  }
+}
+
+// Generic rays (generateContacts2): contact i for ray i, pixelIndex = i.  A ray with a zero direction cannot hit
+// anything in the reference either (det == 0 for every triangle); it is skipped without traversal.
+template <bool REF_ORDER>
+__global__ void __launch_bounds__(TRACE_THREADS)
+trace_rays_kernel(const clrt_ray* __restrict__ rays, uint32_t count, const TraceNode* __restrict__ tnodes,
+                  const clrt_triangle* __restrict__ tris, uint32_t n, clrt_contact* __restrict__ out,
+                  uint32_t* __restrict__ counter) {
+  const int lane = threadIdx.x & 31;
+  const uint32_t packets = (count + 31u) / 32u;
+  while (true) {
+    uint32_t pk = 0;
+    if (lane == 0) pk = atomicAdd(counter, 1u);
+    pk = __shfl_sync(0xffffffffu, pk, 0);
+    if (pk >= packets) break;
+    const uint32_t i = pk * 32u + lane;
+    if (i >= count) continue;
+    const float4* p = reinterpret_cast<const float4*>(rays + i);
+    const float4 ro = __ldcs(p + 1), rd = __ldcs(p + 2);
+    Hit h; h.t = RT_FLT_MAX; h.tri = SENTINEL;
+    if (!(rd.x == 0.0f && rd.y == 0.0f && rd.z == 0.0f))
+      h = traverse<REF_ORDER>(tnodes, tris, n, v3(ro.x, ro.y, ro.z), v3(rd.x, rd.y, rd.z));
+    write_contact(out, i, i, h, tris);
+  }
+}
+
+template <typename K>
+int persistent_grid(clrt_ctx* ctx, K kernel, int threads, unsigned* grid) {
+  int per_sm = 0;
+  CLRT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, 0));
+  if (per_sm < 1) per_sm = 1;
+  *grid = (unsigned)(ctx->sm_count * per_sm);
+  return 0;
+}
+
+} // namespace
+
+int bvh_trace_primary(clrt_accel* a, const clrt_camera& cam, clrt_contact* out, uint32_t rank, uint32_t nranks) {
+  const uint32_t resX = cam.resX, resY = cam.resY;
+  clrt_ctx* ctx = a->ctx;
+  if (!a->built) CLRT_FAIL("generateContacts: the BVH was not constructed");
+  const bool raster = (nranks == 0);                 // nranks == 0: whole frame, raster-ordered output
+  if (raster) { rank = 0; nranks = 1; }
+  const TileGrid g = make_tile_grid(resX, resY);
+  const uint32_t packets = stripe_tile_count(g.tiles, rank, nranks) * 8u;
+  if (!packets) return 0;
+  CLRT_CUDA(cudaMemsetAsync(a->d_tile_counter, 0, 4, ctx->stream));
+  unsigned grid = 0;
+  if (a->trace_mode == CLRT_TRACE_REFERENCE_ORDER) {
+    CLRT_TRY(persistent_grid(ctx, trace_primary_kernel<true>, TRACE_THREADS, &grid));
+    grid = min(grid, (packets + 3) / 4);
+    trace_primary_kernel<true><<<grid, TRACE_THREADS, 0, ctx->stream>>>(cam, a->d_tnodes, a->scene->d_tris, a->n, out, rank, nranks, raster, a->d_tile_counter);
+  } else {
+    CLRT_TRY(persistent_grid(ctx, trace_primary_kernel<false>, TRACE_THREADS, &grid));
+    grid = min(grid, (packets + 3) / 4);
+    trace_primary_kernel<false><<<grid, TRACE_THREADS, 0, ctx->stream>>>(cam, a->d_tnodes, a->scene->d_tris, a->n, out, rank, nranks, raster, a->d_tile_counter);
+  }
+  CLRT_CHECK_LAUNCH();
+  return 0;
+}
+
+int bvh_trace_rays(clrt_accel* a, const clrt_ray* rays, clrt_contact* out, uint32_t count) {
+  clrt_ctx* ctx = a->ctx;
+  if (!a->built) CLRT_FAIL("generateContacts: the BVH was not constructed");
+  if (!count) return 0;
+  const uint32_t packets = (count + 31u) / 32u;
+  CLRT_CUDA(cudaMemsetAsync(a->d_tile_counter, 0, 4, ctx->stream));
+  unsigned grid = 0;
+  if (a->trace_mode == CLRT_TRACE_REFERENCE_ORDER) {
+    CLRT_TRY(persistent_grid(ctx, trace_rays_kernel<true>, TRACE_THREADS, &grid));
+    grid = min(grid, (packets + 3) / 4);
+    trace_rays_kernel<true><<<grid, TRACE_THREADS, 0, ctx->stream>>>(rays, count, a->d_tnodes, a->scene->d_tris, a->n, out, a->d_tile_counter);
+  } else {
+    CLRT_TRY(persistent_grid(ctx, trace_rays_kernel<false>, TRACE_THREADS, &grid));
+    grid = min(grid, (packets + 3) / 4);
+    trace_rays_kernel<false><<<grid, TRACE_THREADS, 0, ctx->stream>>>(rays, count, a->d_tnodes, a->scene->d_tris, a->n, out, a->d_tile_counter);
+  }
+  CLRT_CHECK_LAUNCH();
+  return 0;
+}
