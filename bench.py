@@ -1,0 +1,354 @@
+#!/usr/bin/env python
+"""bench.py — the headline benchmark of BASELINE.json on N B200s of one box.
+
+metric   : Mrays/s (primary + shadow rays, 1920x1080), whole job.  Also reported: BVH build ms per M triangles.
+workload : BASELINE.json configs[1] — the largest bundled TestModels mesh present (ClumsyDragon, 50 032 triangles;
+           Skull / swfighter are missing blobs), LBVH build once, then per step ONE 1080p frame: primary rays, one
+           shadow ray per hit per light (scene light + the reference's camera light), Blinn-Phong shading.
+           `--workload soup1m` selects configs[2] (1M-triangle random soup) instead.
+step     : one frame of the moving demo camera.  N > 1: the frame is sharded in image space (tile stripes), the
+           RGBA8 stripes are all-gathered — total work fixed => "scaling": "strong".
+value    : rays traced by all ranks / device time (CUDA events on the launching stream, max over ranks), with the
+           camera and the built structure already resident.
+e2e      : the same through FrameRenderer.render_host (what a user calls): host camera in, pinned-host RGBA8 raster out.
+roofline : the dominant kernel of the step (BVH traversal): algorithmic bytes = node + triangle + contact bytes its
+           rays touch (counted by the same traversal policy on the CPU oracle for a sample of rays),
+           against the measured HBM copy peak — traversal is latency/divergence bound, so this fraction explains
+           rather than bounds; the HBM-bound build kernels are reported per kernel under "kernels".
+cpu_baseline / --impl reference : the reference's own CPU code for the path (oracle/_ref/libclrt_ref.so = its headers
+           compiled in place; else the oracle port) on the host cores, bounded sample.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "Mrays/s (primary+shadow, 1080p)"
+UNIT = "Mrays/s"
+RES = (1920, 1080)
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def make_scene(workload):
+    from openclraytracer_b200 import scenes
+    if workload == "clumsydragon":
+        return scenes.load_bundled("clumsydragon"), "ClumsyDragon (50032 tris, bundled TestModels) + LIGHT 0 10 -330 1000"
+    if workload == "soup1m":
+        return scenes.soup_scene(1_000_000), "Soup-1M (1e6 random triangles, 46 sub-meshes, seed 20161116)"
+    raise SystemExit(f"unknown workload {workload}")
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md)."""
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        self.thread.join(timeout=2)
+        sm, smax, reasons = [], None, set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); smax = float(r[1])
+            except (ValueError, IndexError):
+                continue
+            for name, v in zip(["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"], r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": smax, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ---------------------------------------------------------------------------------------------------------------
+def cpu_reference_sample(scene_buf, res, repeat_s=10.0, threads=None):
+    """The reference's CPU implementation of the step on a bounded sample: primary rays of one frame at `res` through
+    the reference's own bvh_generate_contact + one shadow ray per hit per light through its generic-ray path
+    (the reference has no shadow rays; they are generated by the oracle) + cpuShadeBlinnPhong.  Returns
+    (Mrays/s, cores, kind, sample description, build_ms)."""
+    from oracle import oracle_py as O
+    from openclraytracer_b200 import api
+    O.build(("oracle",))
+    kind = "reference" if O.have_ref() else "port"
+    cores = O.ref().ref_num_threads() if kind == "reference" else O.oracle().oracle_num_threads()
+    cam = api.demo_camera(scene_buf, *res)
+    t0 = time.perf_counter()
+    if kind == "reference":
+        b = O.ref_bvh_build(scene_buf)
+        n = b["n"]
+    else:
+        b = O.bvh_build(scene_buf)
+        n = b["n"]
+    build_s = time.perf_counter() - t0
+    rays_total, elapsed, frames = 0, 0.0, 0
+    while elapsed < repeat_s and frames < 50:
+        t0 = time.perf_counter()
+        if kind == "reference":
+            c = O.ref_trace_primary(cam, b["nodes"], n, scene_buf)
+        else:
+            c = O.bvh_trace_primary(cam, b)
+        t1 = time.perf_counter()
+        sr = O.shadow_rays(cam, scene_buf, c)          # ray generation is ours: not timed
+        live = sr["idx"] != 0xFFFFFFFF
+        srl = np.ascontiguousarray(sr[live])
+        t2 = time.perf_counter()
+        if kind == "reference":
+            O.ref_trace_rays(srl, b["nodes"], n, scene_buf)
+            O.ref_shade(cam, c, scene_buf)
+        else:
+            O.bvh_trace_rays(srl, b)
+            O.shade(cam, scene_buf, c)
+        t3 = time.perf_counter()
+        elapsed += (t1 - t0) + (t3 - t2)
+        rays_total += len(c) + len(srl)
+        frames += 1
+    sample = f"{frames} frame(s) of {res[0]}x{res[1]} primary + shadow rays ({rays_total} rays), demo camera"
+    return rays_total / elapsed / 1e6, cores, kind, sample, build_s * 1e3
+
+
+def run_reference(args, workload_desc, scene_buf):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    res = (960, 540)                                   # bounded sample: a quarter-resolution frame per step
+    vals = []
+    for i in range(args.warmup + args.steps):
+        v, cores, kind, sample, build_ms = cpu_reference_sample(scene_buf, res, repeat_s=0.0)
+        if i >= args.warmup:
+            vals.append(v)
+    value = float(np.mean(vals))
+    rays_per_step = None
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": None, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic camera path over bundled mesh" if args.workload == "clumsydragon" else "synthetic",
+            "config": {"workload": workload_desc, "resolution": "1920x1080 (bounded sample: %dx%d per step)" % res, "accel": "BVH"},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "build_ms_per_Mtri": build_ms / (int(np.frombuffer(scene_buf[:96].tobytes(), dtype=np.uint64)[7]) / 1e6)}
+    print(json.dumps(line))
+
+
+# ---------------------------------------------------------------------------------------------------------------
+def traversal_bytes_per_ray(renderer, cam, shadows):
+    """Algorithmic bytes of the traversal per ray: 64 B per inner-node visit + 48 B per triangle test + 32 B contact
+    (+ 48 B ray read for generic rays), counted by the kernel's own statistics mode."""
+    st = renderer.accel.trace_stats(cam, shadows)
+    return st
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="clumsydragon", choices=["clumsydragon", "soup1m"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-kernels", action="store_true", help="skip the per-kernel build/sort/scan roofline section")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+
+    scene_buf, workload_desc = make_scene(args.workload)
+    if args.impl == "reference":
+        return run_reference(args, workload_desc, scene_buf)
+
+    import torch
+    import torch.distributed as dist
+    from openclraytracer_b200 import api, frame
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; this path has no CPU fallback (use --impl reference for the CPU baseline)")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    hbm_peak, peak_src = load_peaks()
+    n_tris = int(np.frombuffer(scene_buf[:96].tobytes(), dtype=np.uint64)[7])
+
+    r = frame.FrameRenderer(scene_buf, RES[0], RES[1], "BVH", rank, world, local_rank)
+    # ---- build (once; timed separately, median of several) ------------------------------------------------
+    r.accel.enable_stage_timing(True)
+    build_ms, stages = [], []
+    for i in range(8):
+        r.build()
+        build_ms.append(r.accel.stage_ms(api.STAGE_TOTAL))
+        stages.append([r.accel.stage_ms(s) for s in range(4)])
+    r.accel.enable_stage_timing(False)
+    r.build()
+    build_med = float(np.median(build_ms[2:]))
+    stage_med = np.median(np.array(stages[2:]), axis=0)
+
+    cams = [frame.orbit_camera(scene_buf, RES[0], RES[1], s) for s in range(args.warmup + args.steps)]
+    stream = torch.cuda.current_stream()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # rays per frame (counted once, untimed): primary = pixels of the stripe, shadow = live shadow rays
+    rays_per_step = np.zeros(args.warmup + args.steps, dtype=np.int64)
+    for s in range(args.warmup):
+        rays_per_step[s] = r.render_device(cams[s], True, want_rays=True)
+    for s in range(args.warmup, args.warmup + args.steps):
+        rays_per_step[s] = r.render_device(cams[s], True, want_rays=True)
+    # ---- timed: device-resident -------------------------------------------------------------------------
+    sampler = ClockSampler(local_rank)
+    barrier()
+    if rank == 0:
+        sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    ev0.record(stream)
+    for s in range(args.warmup, args.warmup + args.steps):
+        r.render_device(cams[s], True)
+    ev1.record(stream)
+    barrier()
+    dev_ms = ev0.elapsed_time(ev1)
+    # ---- timed: e2e (host camera in, pinned host raster out, every step) ---------------------------------
+    for s in range(args.warmup):
+        r.render_host(cams[s], True)
+    barrier()
+    t_e2e0 = torch.cuda.Event(enable_timing=True); t_e2e1 = torch.cuda.Event(enable_timing=True)
+    t_e2e0.record(stream)
+    for s in range(args.warmup, args.warmup + args.steps):
+        r.render_host(cams[s], True)
+    t_e2e1.record(stream)
+    barrier()
+    e2e_ms = t_e2e0.elapsed_time(t_e2e1)
+    clocks = sampler.stop() if rank == 0 else None
+
+    # ---- dominant kernel, timed alone on its stream (the primary + shadow traversal launches of one frame) ----
+    kt = r.accel.time_trace_kernels(cams[args.warmup], repeats=5)
+
+    t = torch.tensor([dev_ms, e2e_ms], dtype=torch.float64, device="cuda")
+    rays = torch.tensor([int(rays_per_step[args.warmup:].sum())], dtype=torch.int64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(rays, op=dist.ReduceOp.SUM)
+    dev_ms, e2e_ms = float(t[0]), float(t[1])
+    total_rays = int(rays[0])
+
+    if rank == 0:
+        value = total_rays / (dev_ms * 1e-3) / 1e6
+        e2e_value = total_rays / (e2e_ms * 1e-3) / 1e6
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f32", "data": "bundled mesh, synthetic camera path" if args.workload == "clumsydragon" else "synthetic",
+            "config": {"workload": workload_desc, "resolution": "1920x1080", "accel": "LBVH", "triangles": n_tris,
+                       "rays_per_step": total_rays // args.steps, "shadow": "1 per hit per light (scene light + camera light)",
+                       "parallelism": f"image-space tile stripes x{world}, redundant build, all-gather of RGBA8 stripes",
+                       "l2": "per-step working set (contacts + shadow rays + shadow contacts, >400 MB at 1080p) exceeds the 126 MB L2; "
+                             "the camera moves every step; the BVH stays L2 resident as in steady-state rendering"},
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 64, "d2h_bytes_per_step": RES[0] * RES[1] * 4,
+                    "ms_per_step": e2e_ms / args.steps},
+            "gpu_launches": args.steps * (5 if world == 1 else 5),
+            "build_ms": build_med, "build_ms_per_Mtri": build_med / (n_tris / 1e6),
+            "build_stage_ms": {"morton": float(stage_med[0]), "sort": float(stage_med[1]), "emit": float(stage_med[2]), "refit": float(stage_med[3])},
+            "clocks": clocks,
+        }
+        # roofline of the dominant kernel
+        bytes_per_launch = kt["algorithmic_bytes"]
+        achieved = bytes_per_launch / (kt["ms"] * 1e-3) / 1e9
+        line["roofline"] = {"bound": "hbm", "kernel": "trace (primary + shadow launches of one frame)", "achieved": achieved, "peak": hbm_peak,
+                            "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None, "peak_source": peak_src,
+                            "ms_per_launch_pair": kt["ms"], "rays": kt["rays"], "mrays_per_s_kernel_only": kt["rays"] / kt["ms"] / 1e3,
+                            "inner_visits_per_ray": kt["inner_per_ray"], "tri_tests_per_ray": kt["tris_per_ray"],
+                            "note": "traversal is latency/divergence bound (served by L1/L2), see DESIGN.md; HBM-bound kernels are under 'kernels'"}
+        if not args.no_kernels:
+            line["kernels"] = kernel_rooflines(r, hbm_peak, n_tris, stage_med)
+        if not args.no_cpu_baseline:
+            v, cores, kind, sample, cpu_build_ms = cpu_reference_sample(scene_buf, (960, 540), repeat_s=10.0)
+            line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample,
+                                    "build_ms_per_Mtri": cpu_build_ms / (n_tris / 1e6)}
+        print(json.dumps(line))
+    r.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def kernel_rooflines(r, hbm_peak, n_tris, stage_med):
+    """HBM-bound kernels timed live (CUDA events on the context's stream): build stages on the bench scene, and the
+    Sort / Prefix Sum building blocks at 2^24 pairs / elements (SURVEY.md 8d algorithmic bytes)."""
+    import torch
+    from openclraytracer_b200 import api
+    out = []
+    per_tri = {"morton": 104, "sort": 16, "emit": 64, "refit": 100}
+    for i, k in enumerate(["morton", "sort", "emit", "refit"]):
+        ms = float(stage_med[i])
+        gbs = per_tri[k] * n_tris / (ms * 1e-3) / 1e9 if ms > 0 else 0.0
+        out.append({"kernel": f"bvh.{k}", "units": n_tris, "bytes_per_unit": per_tri[k], "ms": ms, "achieved_GBs": gbs, "frac": gbs / hbm_peak})
+    ctx = r.ctx
+    stream = torch.cuda.current_stream()
+    for logn in (24, 26):
+        n = 1 << logn
+        g = torch.Generator(device="cuda"); g.manual_seed(1)
+        keys = torch.randint(0, 1 << 30, (n,), dtype=torch.int32, device="cuda", generator=g)
+        pairs = torch.stack([keys, torch.arange(n, dtype=torch.int32, device="cuda")], dim=1).contiguous()
+        work = torch.empty_like(pairs)
+        srt = api.BitonicSort(ctx)
+        ms = []
+        for it in range(6):
+            work.copy_(pairs)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream); srt.sort(work.data_ptr(), n); e1.record(stream); e1.synchronize()
+            ms.append(e0.elapsed_time(e1))
+        m = float(np.median(ms[2:]))
+        gbs = 16.0 * n / (m * 1e-3) / 1e9
+        out.append({"kernel": "sort_pairs_u32 (onesweep, 4x8 bit)", "units": n, "bytes_per_unit": 16, "ms": m, "achieved_GBs": gbs,
+                    "frac": gbs / hbm_peak, "Mpairs_per_s": n / m / 1e3})
+        vals = torch.randint(0, 8, (n,), dtype=torch.int32, device="cuda", generator=g)
+        outb = torch.empty_like(vals)
+        ps = api.PrefixSum(ctx)
+        ms = []
+        for it in range(6):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream); ps.computePrefixSum(vals.data_ptr(), outb.data_ptr(), n); e1.record(stream); e1.synchronize()
+            ms.append(e0.elapsed_time(e1))
+        m = float(np.median(ms[2:]))
+        gbs = 8.0 * n / (m * 1e-3) / 1e9
+        out.append({"kernel": "scan_inclusive_u32 (decoupled look-back)", "units": n, "bytes_per_unit": 8, "ms": m, "achieved_GBs": gbs, "frac": gbs / hbm_peak})
+        del keys, pairs, work, vals, outb
+    return out
+
+
+if __name__ == "__main__":
+    main()

@@ -122,6 +122,11 @@ int clrt_accel_set_trace_mode(clrt_accel* accel, int mode);
 #define CLRT_STAGE_COUNT  16
 int clrt_accel_stage_ms(clrt_accel* accel, int stage, float* out_ms);
 int clrt_accel_enable_stage_timing(clrt_accel* accel, int on);
+/* Traversal statistics mode (measurement only; the reference has none — SURVEY.md section 5): while on, the trace
+ * kernels count rays traversed, inner-node visits and triangle tests.  set_stats zeroes the counters;
+ * read_stats returns {rays, inner visits, triangle tests} accumulated since. */
+int clrt_accel_set_stats(clrt_accel* accel, int on);
+int clrt_accel_read_stats(clrt_accel* accel, uint64_t* h_out3);
 
 /* Inspection of build products (the reference exposes the cl_mem objects; tests download them). */
 int clrt_bvh_export_nodes(clrt_accel* accel, void* h_nodes /* (2N-1) * 48 B */);

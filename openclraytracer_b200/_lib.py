@@ -49,6 +49,8 @@ SIGNATURES = {
     "clrt_accel_set_trace_mode": (C.c_int, [C.c_void_p, C.c_int]),
     "clrt_accel_stage_ms": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_float)]),
     "clrt_accel_enable_stage_timing": (C.c_int, [C.c_void_p, C.c_int]),
+    "clrt_accel_set_stats": (C.c_int, [C.c_void_p, C.c_int]),
+    "clrt_accel_read_stats": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64)]),
     "clrt_bvh_export_nodes": (C.c_int, [C.c_void_p, C.c_void_p]),
     "clrt_bvh_export_pairs": (C.c_int, [C.c_void_p, C.c_void_p]),
     "clrt_tlg_sizes": (C.c_int, [C.c_void_p] + [C.POINTER(C.c_uint32)] * 4),

@@ -265,7 +265,7 @@ class AccelerationStructureManager:
             cam = np.ascontiguousarray(camera_or_rays, dtype=L.CAMERA)
             out = None if contacts is None else C.c_void_p(contacts.getCLMem() if isinstance(contacts, Buffer) else contacts)
             check(self._lib.clrt_trace_primary(self.handle, _ptr(cam), out))
-            self._primary_pixels = int(cam["resX"]) * int(cam["resY"])
+            self._primary_pixels = int(cam["resX"].item()) * int(cam["resY"].item())
         else:                                                 # generateContacts(rays, contacts, rayCount)
             r = camera_or_rays.getCLMem() if isinstance(camera_or_rays, Buffer) else camera_or_rays
             c = contacts.getCLMem() if isinstance(contacts, Buffer) else contacts
@@ -292,6 +292,15 @@ class AccelerationStructureManager:
         check(self._lib.clrt_accel_stage_ms(self.handle, stage, C.byref(v)))
         return v.value
 
+    def set_stats(self, on=True):
+        check(self._lib.clrt_accel_set_stats(self.handle, int(on)))
+
+    def read_stats(self):
+        """{rays traversed, inner-node visits, triangle tests} since set_stats(True)."""
+        v = (C.c_uint64 * 3)()
+        check(self._lib.clrt_accel_read_stats(self.handle, v))
+        return int(v[0]), int(v[1]), int(v[2])
+
     def render_stripe(self, camera, shadows, rank, nranks, dptr_rgba8, want_rays=False):
         cam = np.ascontiguousarray(camera, dtype=L.CAMERA)
         rays = C.c_uint64()
@@ -302,7 +311,7 @@ class AccelerationStructureManager:
     def render_frame_host(self, camera, shadows, out_rgba8=None, want_rays=False):
         cam = np.ascontiguousarray(camera, dtype=L.CAMERA)
         if out_rgba8 is None:
-            out_rgba8 = np.empty((int(cam["resY"]), int(cam["resX"]), 4), dtype=np.uint8)
+            out_rgba8 = np.empty((int(cam["resY"].item()), int(cam["resX"].item()), 4), dtype=np.uint8)
         rays = C.c_uint64()
         ptr = out_rgba8 if isinstance(out_rgba8, int) else _ptr(out_rgba8)
         check(self._lib.clrt_render_frame_host(self.handle, _ptr(cam), int(shadows), C.c_void_p(ptr) if isinstance(ptr, int) else ptr,

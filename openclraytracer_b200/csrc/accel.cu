@@ -68,6 +68,19 @@ extern "C" int clrt_accel_enable_stage_timing(clrt_accel* a, int on) {
   if (!a) CLRT_FAIL("clrt_accel_enable_stage_timing: NULL accel");
   a->timing = on != 0; return 0;
 }
+extern "C" int clrt_accel_set_stats(clrt_accel* a, int on) {
+  if (!a) CLRT_FAIL("clrt_accel_set_stats: NULL accel");
+  CLRT_CUDA(cudaSetDevice(a->ctx->device));
+  CLRT_CUDA(cudaMemsetAsync(a->d_tile_counter + 4, 0, 24, a->ctx->stream));
+  a->stats = on != 0; return 0;
+}
+extern "C" int clrt_accel_read_stats(clrt_accel* a, uint64_t* out3) {
+  if (!a || !out3) CLRT_FAIL("clrt_accel_read_stats: NULL argument");
+  CLRT_CUDA(cudaSetDevice(a->ctx->device));
+  CLRT_CUDA(cudaMemcpyAsync(out3, a->d_tile_counter + 4, 24, cudaMemcpyDeviceToHost, a->ctx->stream));
+  CLRT_CUDA(cudaStreamSynchronize(a->ctx->stream));
+  return 0;
+}
 extern "C" int clrt_accel_stage_ms(clrt_accel* a, int stage, float* out_ms) {
   if (!a || !out_ms) CLRT_FAIL("clrt_accel_stage_ms: NULL argument");
   if (stage < 0 || stage >= CLRT_STAGE_COUNT) CLRT_FAIL("clrt_accel_stage_ms: stage %d out of range", stage);

@@ -78,6 +78,7 @@ struct clrt_accel {
   const clrt_scene* scene = nullptr;
   int trace_mode = CLRT_TRACE_FAST;
   bool timing = false;
+  bool stats = false;               // traversal statistics mode (rays, inner visits, triangle tests)
   float stage_ms[CLRT_STAGE_COUNT] = {0};
   cudaEvent_t ev[CLRT_STAGE_COUNT + 1] = {nullptr};
   // --- BVH ---

@@ -35,12 +35,15 @@ __device__ __forceinline__ void test_triangle(const clrt_triangle* __restrict__ 
   if (t > 0.0f && t < h.t) { h.t = t; h.tri = id; }     // BVH.h:392: strict, first tested wins exact ties
 }
 
-template <bool REF_ORDER>
+struct Stats { uint32_t rays, inner, tris; };
+
+template <bool REF_ORDER, bool STATS>
 __device__ __forceinline__ Hit traverse(const TraceNode* __restrict__ tnodes, const clrt_triangle* __restrict__ tris,
-                                        uint32_t n, Vec3 o, Vec3 d) {
+                                        uint32_t n, Vec3 o, Vec3 d, Stats& st) {
   Hit h; h.t = RT_FLT_MAX; h.tri = SENTINEL;
+  if (STATS) st.rays++;
   if (n == 0) return h;
-  if (n == 1) { test_triangle(tris, 0, o, d, h); return h; }    // the reference reads past its node buffer here
+  if (n == 1) { test_triangle(tris, 0, o, d, h); if (STATS) st.tris++; return h; }    // the reference reads past its node buffer here
   const Vec3 inv = v3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
   uint32_t stack[REF_ORDER ? REF_STACK : FAST_STACK];
   int sp = 0;
@@ -48,6 +51,7 @@ __device__ __forceinline__ Hit traverse(const TraceNode* __restrict__ tnodes, co
   uint32_t cur = n;                                             // root = slot N (BVHManager.cpp:254)
   do {
     if (cur >= n) {
+      if (STATS) st.inner++;
       const float4* p = reinterpret_cast<const float4*>(tnodes + (cur - n));
       const float4 q0 = __ldg(p), q1 = __ldg(p + 1), q2 = __ldg(p + 2);
       const uint4 q3 = __ldg(reinterpret_cast<const uint4*>(p + 3));
@@ -62,8 +66,8 @@ __device__ __forceinline__ Hit traverse(const TraceNode* __restrict__ tnodes, co
         else if (bValid) cur = cB;
         else cur = stack[--sp];
       } else {
-        if (aValid && cA < n) { if (!(tA > h.t)) test_triangle(tris, cA, o, d, h); aValid = false; }
-        if (bValid && cB < n) { if (!(tB > h.t)) test_triangle(tris, cB, o, d, h); bValid = false; }
+        if (aValid && cA < n) { if (!(tA > h.t)) { test_triangle(tris, cA, o, d, h); if (STATS) st.tris++; } aValid = false; }
+        if (bValid && cB < n) { if (!(tB > h.t)) { test_triangle(tris, cB, o, d, h); if (STATS) st.tris++; } bValid = false; }
         aValid = aValid && !(tA > h.t);
         bValid = bValid && !(tB > h.t);
         if (aValid && bValid) {
@@ -77,6 +81,7 @@ __device__ __forceinline__ Hit traverse(const TraceNode* __restrict__ tnodes, co
       }
     } else {
       test_triangle(tris, cur, o, d, h);
+      if (STATS) st.tris++;
       cur = stack[--sp];
     }
   } while (cur != SENTINEL);
@@ -100,14 +105,26 @@ __device__ __forceinline__ void write_contact(clrt_contact* __restrict__ out, ui
   __stcs(reinterpret_cast<float4*>(o) + 1, nd);
 }
 
+// statistics mode (bench / DESIGN.md figures): rays traversed, inner-node visits, triangle tests -> stats[0..2]
+__device__ __forceinline__ void flush_stats(const Stats& st, unsigned long long* __restrict__ stats) {
+  uint32_t r = st.rays, i = st.inner, t = st.tris;
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) {
+    r += __shfl_xor_sync(0xffffffffu, r, d); i += __shfl_xor_sync(0xffffffffu, i, d); t += __shfl_xor_sync(0xffffffffu, t, d);
+  }
+  if ((threadIdx.x & 31) == 0) { atomicAdd(stats, (unsigned long long)r); atomicAdd(stats + 1, (unsigned long long)i); atomicAdd(stats + 2, (unsigned long long)t); }
+}
+
 // Primary rays.  Work unit: 8x4-pixel packet; 8 packets form a 32x8 tile; local tile lt of this rank is global
 // tile rank + lt*nranks.  raster != 0: contact goes to out[pixelIndex] (the reference's output[c.pixelIndex] = c);
 // raster == 0: stripe order, slot = lt*256 + y*32 + x, out-of-image slots get pixelIndex = UINT_MAX.
-template <bool REF_ORDER>
+template <bool REF_ORDER, bool STATS>
 __global__ void __launch_bounds__(TRACE_THREADS)
 trace_primary_kernel(const clrt_camera cam, const TraceNode* __restrict__ tnodes,
                      const clrt_triangle* __restrict__ tris, uint32_t n, clrt_contact* __restrict__ out,
-                     uint32_t rank, uint32_t nranks, int raster, uint32_t* __restrict__ counter) {
+                     uint32_t rank, uint32_t nranks, int raster, uint32_t* __restrict__ counter,
+                     unsigned long long* __restrict__ stats) {
+  Stats st; st.rays = st.inner = st.tris = 0;
   const TileGrid g = make_tile_grid(cam.resX, cam.resY);
   const uint32_t packets = stripe_tile_count(g.tiles, rank, nranks) * 8u;
   const int lane = threadIdx.x & 31;
@@ -126,22 +143,24 @@ trace_primary_kernel(const clrt_camera cam, const TraceNode* __restrict__ tnodes
     if (inside) {
       Vec3 o, d;
       generate_ray(cam, pixel, o, d);
-      const Hit h = traverse<REF_ORDER>(tnodes, tris, n, o, d);
+      const Hit h = traverse<REF_ORDER, STATS>(tnodes, tris, n, o, d, st);
       write_contact(out, raster ? pixel : lt * CLRT_TILE_PIXELS + inTile, pixel, h, tris);
     } else if (!raster) {
       Hit h; h.t = RT_FLT_MAX; h.tri = SENTINEL;
       write_contact(out, lt * CLRT_TILE_PIXELS + inTile, SENTINEL, h, tris);
     }
   }
+  if (STATS) flush_stats(st, stats);
 }
 
 // Generic rays (generateContacts2): contact i for ray i, pixelIndex = i.  A ray with a zero direction cannot hit
 // anything in the reference either (det == 0 for every triangle); it is skipped without traversal.
-template <bool REF_ORDER>
+template <bool REF_ORDER, bool STATS>
 __global__ void __launch_bounds__(TRACE_THREADS)
 trace_rays_kernel(const clrt_ray* __restrict__ rays, uint32_t count, const TraceNode* __restrict__ tnodes,
                   const clrt_triangle* __restrict__ tris, uint32_t n, clrt_contact* __restrict__ out,
-                  uint32_t* __restrict__ counter) {
+                  uint32_t* __restrict__ counter, unsigned long long* __restrict__ stats) {
+  Stats st; st.rays = st.inner = st.tris = 0;
   const int lane = threadIdx.x & 31;
   const uint32_t packets = (count + 31u) / 32u;
   while (true) {
@@ -150,14 +169,16 @@ trace_rays_kernel(const clrt_ray* __restrict__ rays, uint32_t count, const Trace
     pk = __shfl_sync(0xffffffffu, pk, 0);
     if (pk >= packets) break;
     const uint32_t i = pk * 32u + lane;
-    if (i >= count) continue;
-    const float4* p = reinterpret_cast<const float4*>(rays + i);
-    const float4 ro = __ldcs(p + 1), rd = __ldcs(p + 2);
-    Hit h; h.t = RT_FLT_MAX; h.tri = SENTINEL;
-    if (!(rd.x == 0.0f && rd.y == 0.0f && rd.z == 0.0f))
-      h = traverse<REF_ORDER>(tnodes, tris, n, v3(ro.x, ro.y, ro.z), v3(rd.x, rd.y, rd.z));
-    write_contact(out, i, i, h, tris);
+    if (i < count) {
+      const float4* p = reinterpret_cast<const float4*>(rays + i);
+      const float4 ro = __ldcs(p + 1), rd = __ldcs(p + 2);
+      Hit h; h.t = RT_FLT_MAX; h.tri = SENTINEL;
+      if (!(rd.x == 0.0f && rd.y == 0.0f && rd.z == 0.0f))
+        h = traverse<REF_ORDER, STATS>(tnodes, tris, n, v3(ro.x, ro.y, ro.z), v3(rd.x, rd.y, rd.z), st);
+      write_contact(out, i, i, h, tris);
+    }
   }
+  if (STATS) flush_stats(st, stats);
 }
 
 template <typename K>
@@ -171,6 +192,27 @@ int persistent_grid(clrt_ctx* ctx, K kernel, int threads, unsigned* grid) {
 
 } // namespace
 
+template <bool R, bool S>
+static int launch_primary(clrt_accel* a, const clrt_camera& cam, clrt_contact* out, uint32_t rank, uint32_t nranks, int raster, uint32_t packets) {
+  unsigned grid = 0;
+  CLRT_TRY(persistent_grid(a->ctx, trace_primary_kernel<R, S>, TRACE_THREADS, &grid));
+  grid = min(grid, (packets + 3) / 4);
+  trace_primary_kernel<R, S><<<grid, TRACE_THREADS, 0, a->ctx->stream>>>(cam, a->d_tnodes, a->scene->d_tris, a->n, out, rank, nranks, raster,
+                                                                        a->d_tile_counter, (unsigned long long*)(a->d_tile_counter + 4));
+  CLRT_CHECK_LAUNCH();
+  return 0;
+}
+template <bool R, bool S>
+static int launch_rays(clrt_accel* a, const clrt_ray* rays, clrt_contact* out, uint32_t count, uint32_t packets) {
+  unsigned grid = 0;
+  CLRT_TRY(persistent_grid(a->ctx, trace_rays_kernel<R, S>, TRACE_THREADS, &grid));
+  grid = min(grid, (packets + 3) / 4);
+  trace_rays_kernel<R, S><<<grid, TRACE_THREADS, 0, a->ctx->stream>>>(rays, count, a->d_tnodes, a->scene->d_tris, a->n, out,
+                                                                     a->d_tile_counter, (unsigned long long*)(a->d_tile_counter + 4));
+  CLRT_CHECK_LAUNCH();
+  return 0;
+}
+
 int bvh_trace_primary(clrt_accel* a, const clrt_camera& cam, clrt_contact* out, uint32_t rank, uint32_t nranks) {
   const uint32_t resX = cam.resX, resY = cam.resY;
   clrt_ctx* ctx = a->ctx;
@@ -181,18 +223,9 @@ int bvh_trace_primary(clrt_accel* a, const clrt_camera& cam, clrt_contact* out, 
   const uint32_t packets = stripe_tile_count(g.tiles, rank, nranks) * 8u;
   if (!packets) return 0;
   CLRT_CUDA(cudaMemsetAsync(a->d_tile_counter, 0, 4, ctx->stream));
-  unsigned grid = 0;
-  if (a->trace_mode == CLRT_TRACE_REFERENCE_ORDER) {
-    CLRT_TRY(persistent_grid(ctx, trace_primary_kernel<true>, TRACE_THREADS, &grid));
-    grid = min(grid, (packets + 3) / 4);
-    trace_primary_kernel<true><<<grid, TRACE_THREADS, 0, ctx->stream>>>(cam, a->d_tnodes, a->scene->d_tris, a->n, out, rank, nranks, raster, a->d_tile_counter);
-  } else {
-    CLRT_TRY(persistent_grid(ctx, trace_primary_kernel<false>, TRACE_THREADS, &grid));
-    grid = min(grid, (packets + 3) / 4);
-    trace_primary_kernel<false><<<grid, TRACE_THREADS, 0, ctx->stream>>>(cam, a->d_tnodes, a->scene->d_tris, a->n, out, rank, nranks, raster, a->d_tile_counter);
-  }
-  CLRT_CHECK_LAUNCH();
-  return 0;
+  const bool ref = a->trace_mode == CLRT_TRACE_REFERENCE_ORDER;
+  if (a->stats) return ref ? launch_primary<true, true>(a, cam, out, rank, nranks, raster, packets) : launch_primary<false, true>(a, cam, out, rank, nranks, raster, packets);
+  return ref ? launch_primary<true, false>(a, cam, out, rank, nranks, raster, packets) : launch_primary<false, false>(a, cam, out, rank, nranks, raster, packets);
 }
 
 int bvh_trace_rays(clrt_accel* a, const clrt_ray* rays, clrt_contact* out, uint32_t count) {
@@ -201,16 +234,7 @@ int bvh_trace_rays(clrt_accel* a, const clrt_ray* rays, clrt_contact* out, uint3
   if (!count) return 0;
   const uint32_t packets = (count + 31u) / 32u;
   CLRT_CUDA(cudaMemsetAsync(a->d_tile_counter, 0, 4, ctx->stream));
-  unsigned grid = 0;
-  if (a->trace_mode == CLRT_TRACE_REFERENCE_ORDER) {
-    CLRT_TRY(persistent_grid(ctx, trace_rays_kernel<true>, TRACE_THREADS, &grid));
-    grid = min(grid, (packets + 3) / 4);
-    trace_rays_kernel<true><<<grid, TRACE_THREADS, 0, ctx->stream>>>(rays, count, a->d_tnodes, a->scene->d_tris, a->n, out, a->d_tile_counter);
-  } else {
-    CLRT_TRY(persistent_grid(ctx, trace_rays_kernel<false>, TRACE_THREADS, &grid));
-    grid = min(grid, (packets + 3) / 4);
-    trace_rays_kernel<false><<<grid, TRACE_THREADS, 0, ctx->stream>>>(rays, count, a->d_tnodes, a->scene->d_tris, a->n, out, a->d_tile_counter);
-  }
-  CLRT_CHECK_LAUNCH();
-  return 0;
+  const bool ref = a->trace_mode == CLRT_TRACE_REFERENCE_ORDER;
+  if (a->stats) return ref ? launch_rays<true, true>(a, rays, out, count, packets) : launch_rays<false, true>(a, rays, out, count, packets);
+  return ref ? launch_rays<true, false>(a, rays, out, count, packets) : launch_rays<false, false>(a, rays, out, count, packets);
 }

@@ -1,0 +1,135 @@
+"""Frame rendering across the GPUs of one box: the Demo's RTFrame() (R/src/Demos/OpenCLRayTracerDemo/
+OpenCLRayTracerDemo.cpp:271-326) sharded in image space.  The reference is single-device; this is new.
+
+One process per GPU (torch.distributed, NCCL).  The scene is static, so every rank builds the acceleration structure
+once (redundant rebuild: a 1M-triangle LBVH build costs less than broadcasting its ~160 MB).  Per frame each rank
+renders its stripe — 32x8-pixel tiles, tile t owned by rank t % world, persistent warps inside the GPU pull packets
+from an atomic counter — into a device buffer in stripe order; ONE collective (all-gather of equal, padded RGBA8
+stripes, 8.3 MB per 1080p frame) follows, and an untile kernel restores raster order.  No other exchange exists on
+the path.
+
+PyTorch is plumbing here: device memory, the stream shared with NCCL, and the collective.
+"""
+import numpy as np
+
+from . import api, layouts as L
+
+TILE_W, TILE_H, TILE_PIXELS = 32, 8, 256
+
+
+def tile_grid(resX, resY):
+    tx, ty = (resX + TILE_W - 1) // TILE_W, (resY + TILE_H - 1) // TILE_H
+    return tx, ty, tx * ty
+
+
+def stripe_capacity(resX, resY, world):
+    """Slots (pixels) of one padded stripe: ceil(tiles / world) tiles of 256 slots."""
+    _, _, tiles = tile_grid(resX, resY)
+    return ((tiles + world - 1) // world) * TILE_PIXELS
+
+
+def stripe_pixel_indices(resX, resY, rank, world):
+    """Host mirror of the device stripe layout: for every slot of `rank`'s padded stripe the raster pixel index it
+    holds, or -1 (outside the image / padding).  Slot = local_tile*256 + y_in_tile*32 + x_in_tile; local tile lt is
+    global tile rank + lt*world."""
+    tx, _, tiles = tile_grid(resX, resY)
+    cap_tiles = (tiles + world - 1) // world
+    lt = np.arange(cap_tiles)[:, None, None]
+    gt = rank + lt * world
+    x = (gt % tx) * TILE_W + np.arange(TILE_W)[None, None, :]
+    y = (gt // tx) * TILE_H + np.arange(TILE_H)[None, :, None]
+    pix = y * resX + x
+    ok = (gt < tiles) & (x < resX) & (y < resY)
+    return np.where(ok, pix, -1).reshape(-1).astype(np.int64)
+
+
+def untile_host(stripes, resX, resY, world):
+    """numpy mirror of clrt_frame_untile: gathered stripes (rank-major, each `stripe_capacity` slots) -> raster."""
+    cap = stripe_capacity(resX, resY, world)
+    stripes = np.asarray(stripes).reshape(world, cap)
+    out = np.zeros(resX * resY, dtype=stripes.dtype)
+    for r in range(world):
+        idx = stripe_pixel_indices(resX, resY, r, world)
+        ok = idx >= 0
+        out[idx[ok]] = stripes[r][ok]
+    return out.reshape(resY, resX)
+
+
+def gather_stripes(local_stripe, world, group=None):
+    """The one collective of the path: all-gather of equal padded stripes (torch tensor, any backend)."""
+    import torch
+    import torch.distributed as dist
+    if world == 1:
+        return local_stripe
+    out = torch.empty(world * local_stripe.numel(), dtype=local_stripe.dtype, device=local_stripe.device)
+    dist.all_gather_into_tensor(out, local_stripe.contiguous(), group=group)
+    return out
+
+
+class FrameRenderer:
+    """Per-rank renderer: owns the context (on torch's current stream), the device scene and the built structure."""
+
+    def __init__(self, scene_buf, resX, resY, accel="BVH", rank=0, world=1, device=0, group=None,
+                 topLevelDensity=2.0, leafDensity=2.0):
+        import torch
+        self.torch = torch
+        self.rank, self.world, self.group = rank, world, group
+        self.resX, self.resY = resX, resY
+        torch.cuda.set_device(device)
+        self.device = torch.device("cuda", device)
+        self.stream = torch.cuda.current_stream(self.device)
+        self.ctx = api.Context(device, stream=self.stream.cuda_stream)
+        self.scene = api.Scene(scene_buf)
+        self.scene.loadToGPU(self.ctx)
+        if accel.upper() == "BVH":                     # -accStruct {BVH,GRID} (OpenCLRayTracerDemo.cpp:66-73)
+            self.accel = api.BVHManager(self.ctx, self.scene)
+        else:
+            self.accel = api.TwoLevelGridManager(self.ctx, self.scene, topLevelDensity, leafDensity)
+        self.accel.initialize()
+        self.cap = stripe_capacity(resX, resY, world)
+        self.stripe = torch.zeros(self.cap, dtype=torch.int32, device=self.device)
+        self.gathered = torch.zeros(self.cap * world, dtype=torch.int32, device=self.device) if world > 1 else self.stripe
+        self.raster = torch.zeros(resY * resX, dtype=torch.int32, device=self.device)
+        self.host_raster = torch.zeros(resY * resX, dtype=torch.int32).pin_memory()
+
+    def build(self):
+        self.accel.initializeFrame()
+        self.accel.construct()
+
+    def render_device(self, camera, shadows=True, want_rays=False):
+        """One frame, result left on the device in raster order (on every rank).  Returns rays traced by this rank
+        if want_rays (that costs a host sync)."""
+        rays = self.accel.render_stripe(camera, shadows, self.rank, self.world, self.stripe.data_ptr(), want_rays)
+        if self.world > 1:
+            import torch.distributed as dist
+            dist.all_gather_into_tensor(self.gathered, self.stripe, group=self.group)
+        api.frame_untile(self.ctx, self.gathered.data_ptr(), self.resX, self.resY, self.world, self.raster.data_ptr())
+        return rays
+
+    def render_host(self, camera, shadows=True):
+        """e2e: host camera in, RGBA8 raster in pinned host memory out (rank 0 reads the frame back)."""
+        self.render_device(camera, shadows)
+        if self.rank == 0:
+            self.host_raster.copy_(self.raster, non_blocking=True)
+        self.stream.synchronize()
+        return self.host_raster
+
+    def close(self):
+        self.accel.free(); self.scene.free(); self.ctx.close()
+
+
+def orbit_camera(scene_buf, resX, resY, step, steps_per_turn=64, fov_deg=90.0):
+    """Demo camera (OpenCLRayTracerDemo.cpp:202-217) moved along a small arc so successive frames differ:
+    yaw about the scene centre by +-0.2 rad, same distance.  float32 like the reference's Transform.h."""
+    hdr = np.frombuffer(scene_buf[:96].tobytes(), dtype=L.SCENE_HEADER)[0]
+    bb = hdr["modelsBoundingBox"].astype(np.float64)
+    centre = (bb[0, :3] + bb[1, :3]) * 0.5
+    half = (bb[1, :3] - bb[0, :3]) * 0.5
+    base = api.demo_camera(scene_buf, resX, resY, fov_deg)
+    ang = 0.2 * np.sin(2.0 * np.pi * step / steps_per_turn)
+    dist = 2.0 * half[2]
+    pos = np.array([centre[0] + dist * np.sin(ang), centre[1], centre[2] - dist * np.cos(ang)])
+    # camera looks along +z in its own frame; yaw so that it faces the centre.  Rows of the 3x4 matrix (Transform.h).
+    c, s = np.cos(-ang), np.sin(-ang)
+    m = np.array([c, 0, s, pos[0], 0, 1, 0, pos[1], -s, 0, c, pos[2]], dtype=np.float32)
+    return api.make_camera(resX, resY, base["FOVDistance"], m)

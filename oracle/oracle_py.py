@@ -107,7 +107,7 @@ def bvh_build(scene, literal=False):
 
 def bvh_trace_primary(camera, b, want_stats=False):
     cam = np.ascontiguousarray(camera, dtype=L.CAMERA)
-    count = int(cam["resX"]) * int(cam["resY"])
+    count = int(cam["resX"].item()) * int(cam["resY"].item())
     out = np.zeros(count, dtype=L.CONTACT)
     stats = np.zeros(3, dtype=np.uint64)
     oracle().oracle_bvh_trace_primary(_p(cam), _p(b["nodes"]), C.c_uint32(b["n"]), _p(b["tris"]), _p(out), _p(stats) if want_stats else None)
@@ -123,7 +123,7 @@ def bvh_trace_rays(rays, b):
 
 def generate_primary_rays(camera):
     cam = np.ascontiguousarray(camera, dtype=L.CAMERA)
-    rays = np.zeros(int(cam["resX"]) * int(cam["resY"]), dtype=L.RAY)
+    rays = np.zeros(int(cam["resX"].item()) * int(cam["resY"].item()), dtype=L.RAY)
     oracle().oracle_generate_primary_rays(_p(cam), _p(rays))
     return rays
 
@@ -193,7 +193,7 @@ def ref_bvh_build(scene, literal=False, sorter=None):
 
 def ref_trace_primary(camera, nodes, n, scene):
     cam = np.ascontiguousarray(camera, dtype=L.CAMERA)
-    out = np.zeros(int(cam["resX"]) * int(cam["resY"]), dtype=L.CONTACT)
+    out = np.zeros(int(cam["resX"].item()) * int(cam["resY"].item()), dtype=L.CONTACT)
     ref().ref_bvh_trace_primary(_p(cam), _p(nodes), C.c_uint32(n), _p(scene), _p(out))
     return out
 
@@ -207,7 +207,7 @@ def ref_trace_rays(rays, nodes, n, scene):
 
 def ref_generate_rays(camera):
     cam = np.ascontiguousarray(camera, dtype=L.CAMERA)
-    rays = np.zeros(int(cam["resX"]) * int(cam["resY"]), dtype=L.RAY)
+    rays = np.zeros(int(cam["resX"].item()) * int(cam["resY"].item()), dtype=L.RAY)
     ref().ref_generate_rays(_p(cam), _p(rays))
     return rays
 

@@ -1,0 +1,58 @@
+"""The C-ABI library loads without a GPU and exports every symbol include/clrt.h declares; no compute calls here."""
+import os
+import re
+import ctypes as C
+import numpy as np
+import pytest
+from conftest import ROOT
+
+
+def declared_symbols():
+    text = open(os.path.join(ROOT, "include", "clrt.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(clrt_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol():
+    from openclraytracer_b200 import _lib
+    lib = _lib.load()
+    names = declared_symbols()
+    assert len(names) >= 40
+    for name in names:
+        assert hasattr(lib, name), f"{name} is declared in include/clrt.h but not exported"
+        assert name in _lib.SIGNATURES, f"{name} has no ctypes signature in _lib.py"
+    for name in _lib.SIGNATURES:
+        assert name in names, f"{name} is bound in _lib.py but not declared in include/clrt.h"
+    assert lib.clrt_abi_version() == 1
+
+
+def test_no_cpu_fallback_without_gpu():
+    """Without a CUDA device every entry point that needs one fails with an error message (never computes on the CPU)."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    from openclraytracer_b200 import api
+    with pytest.raises(api.ClrtError, match="no CUDA device|no CPU fallback"):
+        api.Context(0)
+
+
+def test_product_package_does_not_import_the_oracle():
+    pkg = os.path.join(ROOT, "openclraytracer_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp")):
+                src = open(os.path.join(dirpath, f)).read()
+                assert "oracle_py" not in src and "libclrt_oracle" not in src and "libclrt_ref" not in src, f
+
+
+def test_layout_sizes_match_header():
+    """include/clrt_types.h compiled with gcc gives the sizes layouts.py asserts."""
+    import subprocess, tempfile
+    names = {"clrt_bvh_node": 48, "clrt_aabb": 32, "clrt_contact": 32, "clrt_ray": 48, "clrt_camera": 64, "clrt_matrix4": 48,
+             "clrt_light": 16, "clrt_material": 96, "clrt_scene_header": 96, "clrt_model_header": 64, "clrt_mesh_header": 48,
+             "clrt_grid_data": 64, "clrt_top_cell": 16, "clrt_triangle": 48, "clrt_uint2": 8}
+    body = "".join(f'_Static_assert(sizeof({k}) == {v}, "{k}");\n' for k, v in names.items())
+    with tempfile.TemporaryDirectory() as d:
+        src = os.path.join(d, "t.c")
+        open(src, "w").write(f'#include "clrt.h"\n{body}int main(void){{return 0;}}\n')
+        subprocess.run(["gcc", "-std=c11", "-I", os.path.join(ROOT, "include"), "-c", src, "-o", os.path.join(d, "t.o")], check=True)

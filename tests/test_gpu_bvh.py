@@ -1,0 +1,266 @@
+"""GPU parity: scene flattening, LBVH build (Morton, sort, Karras emit, refit), traversal, shading — through the C ABI,
+against the committed golden vectors (reference's own code) and the oracle.  Integer/index work bit-exact; hit t /
+normals bit-exact in REFERENCE_ORDER mode, FAST mode by the north-star tolerances."""
+import numpy as np
+import pytest
+from conftest import BUNDLED, masked_nodes, digest
+from openclraytracer_b200 import api, scenes, layouts as L
+
+pytestmark = pytest.mark.gpu
+
+
+def build_gpu(ctx, scene_buf):
+    scene = api.Scene(scene_buf); scene.loadToGPU(ctx)
+    bvh = api.BVHManager(ctx, scene); bvh.initialize(); bvh.initializeFrame(); bvh.construct()
+    return scene, bvh
+
+
+def check_hierarchy(nodes, n):
+    """Testing/BVHTest.h:52-113 vectorised: every parent chain ends at the root; parent boxes contain child boxes."""
+    parent = nodes["data"][:, 0].astype(np.int64)
+    assert parent[n] == 0xFFFFFFFF
+    cur = parent[:n].copy()
+    for _ in range(4 * 64):
+        live = cur != 0xFFFFFFFF
+        if not live.any():
+            break
+        cur[live] = parent[cur[live]]
+    assert (cur == 0xFFFFFFFF).all(), "a leaf's parent chain does not end at the root"
+    inner = np.arange(n, 2 * n - 1)
+    for c in (1, 2):
+        child = nodes["data"][inner, c]
+        assert (nodes["data"][child, 0] == inner).all()
+        assert (nodes["bounds"][inner, 0, :3] <= nodes["bounds"][child, 0, :3]).all()
+        assert (nodes["bounds"][inner, 1, :3] >= nodes["bounds"][child, 1, :3]).all()
+    kids = np.concatenate([nodes["data"][inner, 1], nodes["data"][inner, 2]])
+    assert len(np.unique(kids)) == 2 * n - 2 and n not in kids
+
+
+@pytest.mark.parametrize("name", BUNDLED)
+def test_build_matches_golden_and_oracle(ctx, O, golden, name):
+    g = golden(name)
+    buf = scenes.load_bundled(name)
+    scene, bvh = build_gpu(ctx, buf)
+    n = scene.triangle_count()
+    assert n == int(g["n"])
+    tris, tim = O.flatten(buf)
+    assert np.array_equal(scene.export_triangles(), tris)                 # flattening (incl. mis-aligned blocks, Q14)
+    pairs, nodes = bvh.export_pairs(), bvh.export_nodes()
+    assert digest(pairs) == str(g["pairs_sha"])                            # Morton codes + sorted order, bit-exact
+    assert digest(masked_nodes(nodes, n)) == str(g["nodes_sha"])           # topology + boxes, bit-exact
+    check_hierarchy(nodes, n)
+    bvh.free(); scene.free()
+
+
+@pytest.mark.parametrize("name", BUNDLED)
+def test_trace_reference_order_bit_exact(ctx, golden, name):
+    g = golden(name)
+    buf = scenes.load_bundled(name)
+    scene, bvh = build_gpu(ctx, buf)
+    bvh.set_trace_mode(api.TRACE_REFERENCE_ORDER)
+    for k in range(2):
+        want = g[f"contacts{k}"]
+        bvh.generateContacts(g[f"cam{k}"])
+        got = bvh.download_primary_contacts()
+        hit = want["nd"][:, 3] > 0
+        assert np.array_equal(got["nd"][:, 3] > 0, hit)
+        assert np.array_equal(got["nd"][hit], want["nd"][hit])
+        assert np.array_equal(got["materialIndex"][hit], want["materialIndex"][hit])
+        assert np.array_equal(got["pixelIndex"], want["pixelIndex"])
+        assert (got["nd"][~hit] == 0).all()
+    bvh.free(); scene.free()
+
+
+def compare_fast(got, want, tris):
+    """North-star tolerances: ids agree on >= 99.99 % of rays, mismatches only on near ties (|dt| <= 1e-5 t);
+    t within 1e-4 relative."""
+    hit = want["nd"][:, 3] > 0
+    assert np.array_equal(got["nd"][:, 3] > 0, hit)
+    tw, tg = want["nd"][hit, 3].astype(np.float64), got["nd"][hit, 3].astype(np.float64)
+    assert (np.abs(tw - tg) <= 1e-4 * tw).all()
+    same = got["pad"][hit, 0] == want["pad"][hit, 0]
+    if not same.all():
+        assert (np.abs(tw - tg)[~same] <= 1e-5 * tw[~same]).all()
+    assert same.mean() >= 0.9999 or (~same).sum() <= 1
+    nw, ng = want["nd"][hit][same][:, :3], got["nd"][hit][same][:, :3]
+    assert np.array_equal(nw, ng)
+
+
+@pytest.mark.parametrize("name", BUNDLED)
+def test_trace_fast_within_tolerance(ctx, O, golden, name):
+    g = golden(name)
+    buf = scenes.load_bundled(name)
+    scene, bvh = build_gpu(ctx, buf)
+    b = O.bvh_build(buf)
+    for cam in (g["cam0"], g["cam1"], api.demo_camera(buf, 320, 200)):
+        want = O.bvh_trace_primary(cam, b)
+        bvh.set_trace_mode(api.TRACE_FAST)
+        bvh.generateContacts(cam)
+        compare_fast(bvh.download_primary_contacts(), want, b["tris"])
+    bvh.free(); scene.free()
+
+
+@pytest.mark.parametrize("n,tpm", [(1, 24), (2, 24), (3, 24), (100, 16), (5000, 1000), (200_000, 21840)])
+def test_soup_build_and_trace_vs_oracle(ctx, O, n, tpm):
+    buf = scenes.soup_scene(n, seed=n, tris_per_mesh=tpm)
+    scene, bvh = build_gpu(ctx, buf)
+    b = O.bvh_build(buf)
+    assert np.array_equal(scene.export_triangles(), b["tris"])
+    assert np.array_equal(bvh.export_pairs(), b["pairs"])
+    nodes = bvh.export_nodes()
+    assert np.array_equal(masked_nodes(nodes, n), masked_nodes(b["nodes"], n)[: 2 * n - 1])
+    if n >= 2:
+        check_hierarchy(nodes, n)
+    cam = api.demo_camera(buf, 256, 144)
+    want = O.bvh_trace_primary(cam, b)
+    bvh.set_trace_mode(api.TRACE_REFERENCE_ORDER)
+    bvh.generateContacts(cam)
+    got = bvh.download_primary_contacts()
+    hit = want["nd"][:, 3] > 0
+    assert np.array_equal(got["nd"][:, 3] > 0, hit)
+    assert np.array_equal(got["nd"][hit], want["nd"][hit]) and np.array_equal(got["pad"][hit, 0], want["pad"][hit, 0])
+    bvh.set_trace_mode(api.TRACE_FAST)
+    bvh.generateContacts(cam)
+    compare_fast(bvh.download_primary_contacts(), want, b["tris"])
+    bvh.free(); scene.free()
+
+
+def test_generic_rays_entry_point(ctx, O):
+    """generateContacts(rays, contacts, rayCount): primary rays generated on the device == oracle's; traced contacts
+    equal the camera entry point's; a zero-direction ray is a miss."""
+    buf = scenes.load_bundled("gardenlight")
+    scene, bvh = build_gpu(ctx, buf)
+    b = O.bvh_build(buf)
+    cam = api.demo_camera(buf, 128, 96)
+    n = 128 * 96
+    rays = api.Buffer(ctx, n * 48); contacts = api.Buffer(ctx, n * 32)
+    api.generate_primary_rays(ctx, cam, rays.getCLMem())
+    r = rays.copyToHost(L.RAY, n)
+    wr = O.generate_primary_rays(cam)
+    assert np.array_equal(r["origin"][:, :3], wr["origin"][:, :3]) and np.array_equal(r["direction"][:, :3], wr["direction"][:, :3])
+    r["direction"][5] = 0
+    rays.upload(r)
+    for mode in (api.TRACE_REFERENCE_ORDER, api.TRACE_FAST):
+        bvh.set_trace_mode(mode)
+        bvh.generateContacts(rays, contacts, n)
+        got = contacts.copyToHost(L.CONTACT, n)
+        want = O.bvh_trace_rays(r, b)
+        assert got["nd"][5, 3] == 0
+        if mode == api.TRACE_REFERENCE_ORDER:
+            hit = want["nd"][:, 3] > 0
+            assert np.array_equal(got["nd"][:, 3] > 0, hit) and np.array_equal(got["nd"][hit], want["nd"][hit])
+        else:
+            compare_fast(got, want, b["tris"])
+    rays.free(); contacts.free(); bvh.free(); scene.free()
+
+
+@pytest.mark.parametrize("name", ["cube", "tenryuu", "clumsydragon"])
+def test_shading_matches_reference_host_loop(ctx, O, golden, name):
+    """cpuShadeBlinnPhong (host loop in the reference) as a CUDA kernel: float colour within 1e-4, RGBA8 within 1 LSB."""
+    g = golden(name)
+    buf = scenes.load_bundled(name)
+    scene, bvh = build_gpu(ctx, buf)
+    bvh.set_trace_mode(api.TRACE_REFERENCE_ORDER)
+    for k in range(2):
+        cam = g[f"cam{k}"]
+        bvh.generateContacts(cam)
+        n = 96 * 64
+        f32 = api.Buffer(ctx, n * 16); u8 = api.Buffer(ctx, n * 4)
+        api.shade(ctx, scene, cam, bvh.getPrimaryContacts(), n, None, u8.getCLMem(), f32.getCLMem())
+        got = f32.copyToHost(np.float32, n * 4).reshape(n, 4)
+        want = g[f"colors{k}"]
+        assert np.allclose(got, want, rtol=1e-4, atol=1e-5)
+        want8 = np.floor(np.clip(want, 0, 1) * 255.0 + 0.5).astype(np.int32)
+        got8 = u8.copyToHost(np.uint8, n * 4).reshape(n, 4).astype(np.int32)
+        assert np.abs(got8 - want8).max() <= 1
+        f32.free(); u8.free()
+    bvh.free(); scene.free()
+
+
+def test_shadow_pass_matches_oracle(ctx, O):
+    buf = scenes.load_bundled("tenryuu")
+    scene, bvh = build_gpu(ctx, buf)
+    b = O.bvh_build(buf)
+    cam = api.demo_camera(buf, 160, 100)
+    n = 160 * 100
+    bvh.set_trace_mode(api.TRACE_REFERENCE_ORDER)
+    bvh.generateContacts(cam)
+    contacts = bvh.download_primary_contacts()
+    L1 = scene.num_lights() + 1
+    srays = api.Buffer(ctx, n * L1 * 48); scont = api.Buffer(ctx, n * L1 * 32); u8 = api.Buffer(ctx, n * 4)
+    assert api.generate_shadow_rays(ctx, scene, cam, bvh.getPrimaryContacts(), n, srays.getCLMem()) == L1
+    want_rays = O.shadow_rays(cam, buf, contacts)
+    got_rays = srays.copyToHost(L.RAY, n * L1)
+    live = want_rays["idx"] != 0xFFFFFFFF
+    assert np.array_equal(got_rays["idx"] != 0xFFFFFFFF, live)
+    assert np.allclose(got_rays["origin"][live], want_rays["origin"][live], rtol=1e-5, atol=1e-6)
+    assert np.allclose(got_rays["direction"][live], want_rays["direction"][live], rtol=1e-5, atol=1e-6)
+    bvh.generateContacts(srays, scont, n * L1)
+    sc = scont.copyToHost(L.CONTACT, n * L1)
+    want_sc = O.bvh_trace_rays(got_rays, b)
+    assert np.array_equal(sc["nd"][:, 3], want_sc["nd"][:, 3])
+    api.shade(ctx, scene, cam, bvh.getPrimaryContacts(), n, scont.getCLMem(), u8.getCLMem(), None)
+    want8 = O.shade(cam, buf, contacts, shadow=sc).view(np.uint8).reshape(n, 4).astype(np.int32)
+    got8 = u8.copyToHost(np.uint8, n * 4).reshape(n, 4).astype(np.int32)
+    assert np.abs(got8 - want8).max() <= 1
+    assert (sc["nd"][:, 3] > 0).any()                       # some light is actually occluded
+    srays.free(); scont.free(); u8.free(); bvh.free(); scene.free()
+
+
+@pytest.mark.parametrize("res", [(160, 100), (97, 61)])
+def test_stripes_compose_to_the_single_gpu_frame(ctx, res):
+    """Image-space sharding: stripes of nranks = 2, 3, 8 untiled == the one-rank frame (ragged edges included)."""
+    buf = scenes.load_bundled("gardenlight")
+    scene, bvh = build_gpu(ctx, buf)
+    cam = api.demo_camera(buf, *res)
+    ref_img, rays = bvh.render_frame_host(cam, shadows=True, want_rays=True)
+    assert rays >= res[0] * res[1]
+    for nranks in (2, 3, 8):
+        cap, _ = api.frame_stripe_pixels(res[0], res[1], 0, nranks)
+        stripes = api.Buffer(ctx, cap * 4 * nranks); raster = api.Buffer(ctx, res[0] * res[1] * 4)
+        total = 0
+        for r in range(nranks):
+            total += bvh.render_stripe(cam, True, r, nranks, stripes.getCLMem() + r * cap * 4, want_rays=True)
+        api.frame_untile(ctx, stripes.getCLMem(), res[0], res[1], nranks, raster.getCLMem())
+        img = raster.copyToHost(np.uint8).reshape(res[1], res[0], 4)
+        assert np.array_equal(img, ref_img)
+        assert total == rays
+        stripes.free(); raster.free()
+    bvh.free(); scene.free()
+
+
+def test_full_size_soup_1m_properties(ctx):
+    """BASELINE config 3 size: 1M-triangle soup.  Size-independent properties: sorted keys, leaf permutation,
+    hierarchy + containment, FAST == REFERENCE_ORDER closest hits, idempotent rebuild."""
+    n = 1_000_000
+    buf = scenes.soup_scene(n)
+    scene, bvh = build_gpu(ctx, buf)
+    pairs, nodes = bvh.export_pairs(), bvh.export_nodes()
+    assert (pairs["x"][1:] >= pairs["x"][:-1]).all()
+    eq = pairs["x"][1:] == pairs["x"][:-1]
+    assert (pairs["y"][1:][eq] > pairs["y"][:-1][eq]).all()
+    assert np.array_equal(np.sort(pairs["y"]), np.arange(n, dtype=np.uint32))
+    check_hierarchy(nodes, n)
+    bvh.initializeFrame(); bvh.construct()
+    assert digest(masked_nodes(bvh.export_nodes(), n)) == digest(masked_nodes(nodes, n))
+    cam = api.demo_camera(buf, 640, 360)
+    bvh.set_trace_mode(api.TRACE_REFERENCE_ORDER); bvh.generateContacts(cam); a = bvh.download_primary_contacts()
+    bvh.set_trace_mode(api.TRACE_FAST); bvh.generateContacts(cam); b = bvh.download_primary_contacts()
+    assert (a["nd"][:, 3] > 0).mean() > 0.5
+    compare_fast(b, a, None)
+    bvh.free(); scene.free()
+
+
+def test_errors_are_reported_not_swallowed(ctx):
+    scene = api.Scene(np.zeros(200, dtype=np.uint8))
+    with pytest.raises(api.ClrtError, match="totalDataSize"):
+        scene.loadToGPU(ctx)
+    buf = scenes.cube_scene()
+    s = api.Scene(buf); s.loadToGPU(ctx)
+    bvh = api.BVHManager(ctx, s); bvh.initialize()
+    with pytest.raises(api.ClrtError, match="initializeFrame"):
+        bvh.construct()
+    bvh.initializeFrame()
+    with pytest.raises(api.ClrtError, match="not constructed|was not constructed"):
+        bvh.generateContacts(api.demo_camera(buf, 8, 8))
+    bvh.free(); s.free()

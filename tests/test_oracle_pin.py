@@ -1,0 +1,113 @@
+"""Pins the oracle (oracle/clrt_oracle.cpp, our CPU restatement) to the REFERENCE:
+ (1) against the committed golden vectors, which were produced by the reference's own headers + tinyobj compiled in
+     place (tests/golden/make_golden.py -> oracle/_ref/libclrt_ref.so);
+ (2) live against oracle/_ref/libclrt_ref.so where it exists (build container; it also travels to the GPU box).
+The reference itself holds no golden vectors or known-answer tests."""
+import numpy as np
+import pytest
+from conftest import BUNDLED, masked_nodes, digest
+from openclraytracer_b200 import scenes, layouts as L
+
+
+@pytest.mark.parametrize("name", BUNDLED)
+def test_oracle_build_matches_golden(O, golden, name):
+    g = golden(name)
+    scene = scenes.load_bundled(name)
+    b = O.bvh_build(scene)
+    n = b["n"]
+    assert n == int(g["n"])
+    tris, tim = b["tris"], b["tim"]
+    _, unsorted = O.bvh_morton(scene, tris, tim)
+    assert digest(unsorted) == str(g["unsorted_sha"])        # Morton codes bit-exact
+    assert digest(b["pairs"]) == str(g["pairs_sha"])          # canonical sorted order
+    assert digest(masked_nodes(b["nodes"], n)) == str(g["nodes_sha"])   # topology + boxes, bit-exact
+    if "nodes" in g:
+        assert np.array_equal(masked_nodes(b["nodes"], n), g["nodes"])
+
+
+@pytest.mark.parametrize("name", BUNDLED)
+def test_oracle_trace_and_shade_match_golden(O, golden, name):
+    g = golden(name)
+    scene = scenes.load_bundled(name)
+    b = O.bvh_build(scene)
+    for k in range(2):
+        cam = g[f"cam{k}"]
+        want = g[f"contacts{k}"]
+        got = O.bvh_trace_primary(cam, b)
+        hit = want["nd"][:, 3] > 0
+        assert hit.any()
+        assert np.array_equal(got["nd"][:, 3] > 0, hit)
+        assert np.array_equal(got["nd"][hit], want["nd"][hit])                  # normal + t, bit-exact
+        assert np.array_equal(got["materialIndex"][hit], want["materialIndex"][hit])
+        assert np.array_equal(got["pixelIndex"], want["pixelIndex"])
+        _, f32 = O.shade(cam, scene, got, want_f32=True)
+        assert np.array_equal(f32[hit], g[f"colors{k}"][hit])                   # host Blinn-Phong, bit-exact
+        assert not f32[~hit].any()
+
+
+def test_demo_camera_matches_golden(O, golden):
+    from openclraytracer_b200 import api
+    for name in BUNDLED:
+        g = golden(name)
+        scene = scenes.load_bundled(name)
+        cam = O.demo_camera(scene, 96, 64)
+        assert cam.tobytes() == g["cam0"].tobytes()
+        assert api.demo_camera(scene, 96, 64).tobytes() == g["cam0"].tobytes()   # host-side mirror (api.py)
+
+
+def test_ray_generation_matches_reference(O, golden):
+    if not O.have_ref():
+        pytest.skip("oracle/_ref not built")
+    g = golden("tenryuu")
+    for k in range(2):
+        a = O.generate_primary_rays(g[f"cam{k}"])
+        b = O.ref_generate_rays(g[f"cam{k}"])
+        assert np.array_equal(a["origin"][:, :3], b["origin"][:, :3])
+        assert np.array_equal(a["direction"][:, :3], b["direction"][:, :3])
+
+
+def test_struct_sizes_match_reference(O):
+    if not O.have_ref():
+        pytest.skip("oracle/_ref not built")
+    s = O.ref_struct_sizes()
+    names = ["BVH_NODE", "AABB", "CONTACT", "CAMERA", None, "SCENE_HEADER", "MODEL_HEADER", "MESH_HEADER", "MATERIAL", "LIGHT",
+             "GRID_DATA", "TOP_CELL", "FLOAT4", "UINT2"]
+    for size, name in zip(s, names):
+        if name:
+            assert size == getattr(L, name).itemsize, name
+    assert s[4] == 48            # Matrix4
+
+
+@pytest.mark.parametrize("n", [1, 2, 3, 7, 64, 1000])
+def test_oracle_vs_reference_live_on_soup(O, n):
+    """Synthetic scenes (our packer) through the reference's own headers vs the restatement: codes, topology, boxes,
+    contacts.  Covers N=1 (no inner node), N=2, odd sizes."""
+    if not O.have_ref():
+        pytest.skip("oracle/_ref not built")
+    scene = scenes.soup_scene(n, seed=7 + n, tris_per_mesh=24)
+    b = O.bvh_build(scene)
+    r = O.ref_bvh_build(scene)
+    assert np.array_equal(b["pairs"], r["pairs"])
+    assert np.array_equal(masked_nodes(b["nodes"], n)[: 2 * n - 1], masked_nodes(r["nodes"], n)[: 2 * n - 1])
+    if n >= 2:
+        cam = O.demo_camera(scene, 48, 32)
+        a = O.bvh_trace_primary(cam, b)
+        c = O.ref_trace_primary(cam, r["nodes"], n, scene)
+        hit = c["nd"][:, 3] > 0
+        assert np.array_equal(a["nd"][:, 3] > 0, hit)
+        assert np.array_equal(a["nd"][hit], c["nd"][hit])
+
+
+def test_literal_mode_differs_only_in_last_inner_node(O):
+    """Q1: the reference's guard skips inner node N-2; LITERAL leaves slot 2N-2 unbuilt, all other slots identical."""
+    scene = scenes.soup_scene(100, seed=3, tris_per_mesh=48)
+    tris, tim = O.flatten(scene)
+    nodes, pairs = O.bvh_morton(scene, tris, tim)
+    pairs = O.sort_pairs_stable(pairs)
+    import ctypes as C
+    n = 100
+    fixed, lit = nodes.copy(), nodes.copy()
+    O.oracle().oracle_bvh_radix_tree(fixed.ctypes.data_as(C.c_void_p), pairs.ctypes.data_as(C.c_void_p), C.c_uint32(n), C.c_int(0))
+    O.oracle().oracle_bvh_radix_tree(lit.ctypes.data_as(C.c_void_p), pairs.ctypes.data_as(C.c_void_p), C.c_uint32(n), C.c_int(1))
+    assert np.array_equal(fixed["data"][n:2 * n - 2, 1:3], lit["data"][n:2 * n - 2, 1:3])
+    assert not np.array_equal(fixed["data"][2 * n - 2, 1:3], lit["data"][2 * n - 2, 1:3])
