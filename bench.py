@@ -34,6 +34,7 @@ sys.path.insert(0, ROOT)
 METRIC = "Mrays/s (primary+shadow, 1080p)"
 UNIT = "Mrays/s"
 RES = (1920, 1080)
+DATA = {"clumsydragon": "bundled mesh, synthetic camera path", "soup1m": "synthetic"}
 
 
 def load_peaks():
@@ -96,79 +97,110 @@ class ClockSampler:
 
 
 # ---------------------------------------------------------------------------------------------------------------
-def cpu_reference_sample(scene_buf, res, repeat_s=10.0, threads=None):
-    """The reference's CPU implementation of the step on a bounded sample: primary rays of one frame at `res` through
-    the reference's own bvh_generate_contact + one shadow ray per hit per light through its generic-ray path
-    (the reference has no shadow rays; they are generated by the oracle) + cpuShadeBlinnPhong.  Returns
-    (Mrays/s, cores, kind, sample description, build_ms)."""
-    from oracle import oracle_py as O
-    from openclraytracer_b200 import api
-    O.build(("oracle",))
-    kind = "reference" if O.have_ref() else "port"
-    cores = O.ref().ref_num_threads() if kind == "reference" else O.oracle().oracle_num_threads()
-    cam = api.demo_camera(scene_buf, *res)
-    t0 = time.perf_counter()
-    if kind == "reference":
-        b = O.ref_bvh_build(scene_buf)
-        n = b["n"]
-    else:
-        b = O.bvh_build(scene_buf)
-        n = b["n"]
-    build_s = time.perf_counter() - t0
-    rays_total, elapsed, frames = 0, 0.0, 0
-    while elapsed < repeat_s and frames < 50:
+class CpuReference:
+    """The reference's CPU implementation of the step: primary rays through the reference's own bvh_generate_contact,
+    one shadow ray per hit per light through its generic-ray path (the reference has no shadow rays; they are
+    generated by the oracle, untimed), cpuShadeBlinnPhong.  oracle/_ref/libclrt_ref.so (the reference's headers compiled
+    in place, OpenMP over work-items) when present ("reference"), else the oracle port ("port")."""
+
+    def __init__(self, scene_buf):
+        from oracle import oracle_py as O
+        O.build(("oracle",))
+        self.O, self.scene = O, scene_buf
+        self.kind = "reference" if O.have_ref() else "port"
+        self.cores = O.ref().ref_num_threads() if self.kind == "reference" else O.oracle().oracle_num_threads()
         t0 = time.perf_counter()
-        if kind == "reference":
-            c = O.ref_trace_primary(cam, b["nodes"], n, scene_buf)
-        else:
-            c = O.bvh_trace_primary(cam, b)
+        self.b = O.ref_bvh_build(scene_buf) if self.kind == "reference" else O.bvh_build(scene_buf)
+        self.build_ms = (time.perf_counter() - t0) * 1e3
+        self.n = self.b["n"]
+
+    def frame(self, cam):
+        """-> (rays traced, seconds)"""
+        O, b, n, scene = self.O, self.b, self.n, self.scene
+        t0 = time.perf_counter()
+        c = O.ref_trace_primary(cam, b["nodes"], n, scene) if self.kind == "reference" else O.bvh_trace_primary(cam, b)
         t1 = time.perf_counter()
-        sr = O.shadow_rays(cam, scene_buf, c)          # ray generation is ours: not timed
-        live = sr["idx"] != 0xFFFFFFFF
-        srl = np.ascontiguousarray(sr[live])
+        sr = O.shadow_rays(cam, scene, c)
+        srl = np.ascontiguousarray(sr[sr["idx"] != 0xFFFFFFFF])
         t2 = time.perf_counter()
-        if kind == "reference":
-            O.ref_trace_rays(srl, b["nodes"], n, scene_buf)
-            O.ref_shade(cam, c, scene_buf)
+        if self.kind == "reference":
+            O.ref_trace_rays(srl, b["nodes"], n, scene); O.ref_shade(cam, c, scene)
         else:
-            O.bvh_trace_rays(srl, b)
-            O.shade(cam, scene_buf, c)
+            O.bvh_trace_rays(srl, b); O.shade(cam, scene, c)
         t3 = time.perf_counter()
-        elapsed += (t1 - t0) + (t3 - t2)
-        rays_total += len(c) + len(srl)
-        frames += 1
-    sample = f"{frames} frame(s) of {res[0]}x{res[1]} primary + shadow rays ({rays_total} rays), demo camera"
-    return rays_total / elapsed / 1e6, cores, kind, sample, build_s * 1e3
+        return len(c) + len(srl), (t1 - t0) + (t3 - t2)
 
 
-def run_reference(args, workload_desc, scene_buf):
-    rank = int(os.environ.get("RANK", "0"))
-    if rank != 0:
+def cpu_baseline(scene_buf, res, budget_s=12.0):
+    from openclraytracer_b200 import frame
+    ref = CpuReference(scene_buf)
+    rays, secs, frames = 0, 0.0, 0
+    while frames < 1 or (secs < budget_s and frames < 64):
+        r, s = ref.frame(frame.orbit_camera(scene_buf, res[0], res[1], frames))
+        rays += r; secs += s; frames += 1
+    sample = f"{frames} frame(s) of {res[0]}x{res[1]} primary+shadow rays ({rays} rays) on the bench camera path"
+    return rays / secs / 1e6, ref, sample
+
+
+def run_reference(args, workload_desc, scene_buf, n_tris):
+    """--impl reference: the reference's own CPU implementation on the host cores, same metric/config; each step is a
+    bounded sample (one 960x540 frame of the same camera path).  Rank 0 only."""
+    if int(os.environ.get("RANK", "0")) != 0:
         return
-    res = (960, 540)                                   # bounded sample: a quarter-resolution frame per step
-    vals = []
+    from openclraytracer_b200 import frame
+    res = (960, 540)
+    ref = CpuReference(scene_buf)
+    rays, secs = 0, 0.0
     for i in range(args.warmup + args.steps):
-        v, cores, kind, sample, build_ms = cpu_reference_sample(scene_buf, res, repeat_s=0.0)
+        r, s = ref.frame(frame.orbit_camera(scene_buf, res[0], res[1], i))
         if i >= args.warmup:
-            vals.append(v)
-    value = float(np.mean(vals))
-    rays_per_step = None
+            rays += r; secs += s
+    value = rays / secs / 1e6
+    sample = f"{args.steps} frame(s) of {res[0]}x{res[1]} primary+shadow rays ({rays} rays) on the bench camera path"
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": None, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-            "dtype": "f32", "data": "synthetic camera path over bundled mesh" if args.workload == "clumsydragon" else "synthetic",
-            "config": {"workload": workload_desc, "resolution": "1920x1080 (bounded sample: %dx%d per step)" % res, "accel": "BVH"},
-            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
+            "warmup": args.warmup, "ms_per_step": secs / args.steps * 1e3, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f32", "data": DATA[args.workload],
+            "config": {"workload": workload_desc, "resolution": "1920x1080 (bounded sample: %dx%d per step)" % res, "accel": "LBVH",
+                       "triangles": n_tris},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": ref.cores, "kind": ref.kind, "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-            "build_ms_per_Mtri": build_ms / (int(np.frombuffer(scene_buf[:96].tobytes(), dtype=np.uint64)[7]) / 1e6)}
+            "build_ms_per_Mtri": ref.build_ms / (n_tris / 1e6)}
     print(json.dumps(line))
 
 
 # ---------------------------------------------------------------------------------------------------------------
-def traversal_bytes_per_ray(renderer, cam, shadows):
-    """Algorithmic bytes of the traversal per ray: 64 B per inner-node visit + 48 B per triangle test + 32 B contact
-    (+ 48 B ray read for generic rays), counted by the kernel's own statistics mode."""
-    st = renderer.accel.trace_stats(cam, shadows)
-    return st
+def time_trace_kernels(r, cam, repeats=5):
+    """The dominant kernel alone: the two traversal launches of one frame (primary rays via the camera entry, shadow
+    rays via the generic-ray entry) timed with CUDA events on the launching stream; algorithmic bytes from the
+    kernel's statistics mode: 64 B per inner-node visit + 48 B per triangle test + 32 B per contact written
+    + 48 B per generic ray read."""
+    import torch
+    from openclraytracer_b200 import api
+    a, ctx, scene = r.accel, r.ctx, r.scene
+    n = r.resX * r.resY
+    L1 = scene.num_lights() + 1
+    contacts = torch.empty(n * 32, dtype=torch.uint8, device="cuda")
+    srays = torch.empty(n * L1 * 48, dtype=torch.uint8, device="cuda")
+    scont = torch.empty(n * L1 * 32, dtype=torch.uint8, device="cuda")
+    torch.cuda.synchronize()
+    stream = r.stream
+    a.set_stats(True)
+    a.generateContacts(cam, contacts.data_ptr())
+    api.generate_shadow_rays(ctx, scene, cam, contacts.data_ptr(), n, srays.data_ptr())
+    a.generateContacts(srays.data_ptr(), scont.data_ptr(), n * L1)
+    rays, inner, tris = a.read_stats()
+    a.set_stats(False)
+    ms = []
+    for _ in range(repeats + 2):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        a.generateContacts(cam, contacts.data_ptr())
+        a.generateContacts(srays.data_ptr(), scont.data_ptr(), n * L1)
+        e1.record(stream); e1.synchronize()
+        ms.append(e0.elapsed_time(e1))
+    m = float(np.median(ms[2:]))
+    alg = inner * 64 + tris * 48 + (n + n * L1) * 32 + n * L1 * 48
+    return {"ms": m, "rays": rays, "algorithmic_bytes": alg, "inner_per_ray": inner / max(rays, 1), "tris_per_ray": tris / max(rays, 1)}
 
 
 def main():
@@ -184,8 +216,9 @@ def main():
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
 
     scene_buf, workload_desc = make_scene(args.workload)
+    n_tris = int(np.frombuffer(scene_buf[:96].tobytes(), dtype=np.uint64)[7])
     if args.impl == "reference":
-        return run_reference(args, workload_desc, scene_buf)
+        return run_reference(args, workload_desc, scene_buf, n_tris)
 
     import torch
     import torch.distributed as dist
@@ -200,7 +233,6 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     hbm_peak, peak_src = load_peaks()
-    n_tris = int(np.frombuffer(scene_buf[:96].tobytes(), dtype=np.uint64)[7])
 
     r = frame.FrameRenderer(scene_buf, RES[0], RES[1], "BVH", rank, world, local_rank)
     # ---- build (once; timed separately, median of several) ------------------------------------------------
@@ -216,7 +248,7 @@ def main():
     stage_med = np.median(np.array(stages[2:]), axis=0)
 
     cams = [frame.orbit_camera(scene_buf, RES[0], RES[1], s) for s in range(args.warmup + args.steps)]
-    stream = torch.cuda.current_stream()
+    stream = r.stream
 
     def barrier():
         if world > 1:
@@ -256,7 +288,7 @@ def main():
     clocks = sampler.stop() if rank == 0 else None
 
     # ---- dominant kernel, timed alone on its stream (the primary + shadow traversal launches of one frame) ----
-    kt = r.accel.time_trace_kernels(cams[args.warmup], repeats=5)
+    kt = time_trace_kernels(r, cams[args.warmup], repeats=5)
 
     t = torch.tensor([dev_ms, e2e_ms], dtype=torch.float64, device="cuda")
     rays = torch.tensor([int(rays_per_step[args.warmup:].sum())], dtype=torch.int64, device="cuda")
@@ -272,7 +304,7 @@ def main():
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-            "dtype": "f32", "data": "bundled mesh, synthetic camera path" if args.workload == "clumsydragon" else "synthetic",
+            "dtype": "f32", "data": DATA[args.workload],
             "config": {"workload": workload_desc, "resolution": "1920x1080", "accel": "LBVH", "triangles": n_tris,
                        "rays_per_step": total_rays // args.steps, "shadow": "1 per hit per light (scene light + camera light)",
                        "parallelism": f"image-space tile stripes x{world}, redundant build, all-gather of RGBA8 stripes",
@@ -296,9 +328,9 @@ def main():
         if not args.no_kernels:
             line["kernels"] = kernel_rooflines(r, hbm_peak, n_tris, stage_med)
         if not args.no_cpu_baseline:
-            v, cores, kind, sample, cpu_build_ms = cpu_reference_sample(scene_buf, (960, 540), repeat_s=10.0)
-            line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample,
-                                    "build_ms_per_Mtri": cpu_build_ms / (n_tris / 1e6)}
+            v, ref, sample = cpu_baseline(scene_buf, (960, 540))
+            line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": ref.cores, "kind": ref.kind, "sample": sample,
+                                    "build_ms_per_Mtri": ref.build_ms / (n_tris / 1e6)}
         print(json.dumps(line))
     r.close()
     if world > 1:
@@ -317,36 +349,37 @@ def kernel_rooflines(r, hbm_peak, n_tris, stage_med):
         gbs = per_tri[k] * n_tris / (ms * 1e-3) / 1e9 if ms > 0 else 0.0
         out.append({"kernel": f"bvh.{k}", "units": n_tris, "bytes_per_unit": per_tri[k], "ms": ms, "achieved_GBs": gbs, "frac": gbs / hbm_peak})
     ctx = r.ctx
-    stream = torch.cuda.current_stream()
-    for logn in (24, 26):
-        n = 1 << logn
-        g = torch.Generator(device="cuda"); g.manual_seed(1)
-        keys = torch.randint(0, 1 << 30, (n,), dtype=torch.int32, device="cuda", generator=g)
-        pairs = torch.stack([keys, torch.arange(n, dtype=torch.int32, device="cuda")], dim=1).contiguous()
-        work = torch.empty_like(pairs)
-        srt = api.BitonicSort(ctx)
-        ms = []
-        for it in range(6):
-            work.copy_(pairs)
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record(stream); srt.sort(work.data_ptr(), n); e1.record(stream); e1.synchronize()
-            ms.append(e0.elapsed_time(e1))
-        m = float(np.median(ms[2:]))
-        gbs = 16.0 * n / (m * 1e-3) / 1e9
-        out.append({"kernel": "sort_pairs_u32 (onesweep, 4x8 bit)", "units": n, "bytes_per_unit": 16, "ms": m, "achieved_GBs": gbs,
-                    "frac": gbs / hbm_peak, "Mpairs_per_s": n / m / 1e3})
-        vals = torch.randint(0, 8, (n,), dtype=torch.int32, device="cuda", generator=g)
-        outb = torch.empty_like(vals)
-        ps = api.PrefixSum(ctx)
-        ms = []
-        for it in range(6):
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record(stream); ps.computePrefixSum(vals.data_ptr(), outb.data_ptr(), n); e1.record(stream); e1.synchronize()
-            ms.append(e0.elapsed_time(e1))
-        m = float(np.median(ms[2:]))
-        gbs = 8.0 * n / (m * 1e-3) / 1e9
-        out.append({"kernel": "scan_inclusive_u32 (decoupled look-back)", "units": n, "bytes_per_unit": 8, "ms": m, "achieved_GBs": gbs, "frac": gbs / hbm_peak})
-        del keys, pairs, work, vals, outb
+    stream = r.stream
+    with torch.cuda.stream(stream):
+        for logn in (24, 26):
+            n = 1 << logn
+            g = torch.Generator(device="cuda"); g.manual_seed(1)
+            keys = torch.randint(0, 1 << 30, (n,), dtype=torch.int32, device="cuda", generator=g)
+            pairs = torch.stack([keys, torch.arange(n, dtype=torch.int32, device="cuda")], dim=1).contiguous()
+            work = torch.empty_like(pairs)
+            srt = api.BitonicSort(ctx)
+            ms = []
+            for it in range(6):
+                work.copy_(pairs)
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(stream); srt.sort(work.data_ptr(), n); e1.record(stream); e1.synchronize()
+                ms.append(e0.elapsed_time(e1))
+            m = float(np.median(ms[2:]))
+            gbs = 16.0 * n / (m * 1e-3) / 1e9
+            out.append({"kernel": "sort_pairs_u32 (onesweep, 4x8 bit)", "units": n, "bytes_per_unit": 16, "ms": m, "achieved_GBs": gbs,
+                        "frac": gbs / hbm_peak, "Mpairs_per_s": n / m / 1e3})
+            vals = torch.randint(0, 8, (n,), dtype=torch.int32, device="cuda", generator=g)
+            outb = torch.empty_like(vals)
+            ps = api.PrefixSum(ctx)
+            ms = []
+            for it in range(6):
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(stream); ps.computePrefixSum(vals.data_ptr(), outb.data_ptr(), n); e1.record(stream); e1.synchronize()
+                ms.append(e0.elapsed_time(e1))
+            m = float(np.median(ms[2:]))
+            gbs = 8.0 * n / (m * 1e-3) / 1e9
+            out.append({"kernel": "scan_inclusive_u32 (decoupled look-back)", "units": n, "bytes_per_unit": 8, "ms": m, "achieved_GBs": gbs, "frac": gbs / hbm_peak})
+            del keys, pairs, work, vals, outb
     return out
 
 

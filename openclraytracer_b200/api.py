@@ -12,6 +12,7 @@ Errors: the reference returns Result + fills Errata&; here a failed call raises 
 The C++ shim with the literal signatures lives in include/clrt/; this module is the Python face used by tests and bench.
 """
 import ctypes as C
+import weakref
 import numpy as np
 from . import _lib
 from . import layouts as L
@@ -35,6 +36,10 @@ class Context:
         check(self._lib.clrt_ctx_create(int(device), C.c_void_p(stream) if stream else None, C.byref(h)))
         self.handle = h
         self.device = device
+        self._children = weakref.WeakSet()      # buffers / scenes / managers created on this context
+
+    def _adopt(self, child):
+        self._children.add(child)
 
     def finish(self):                      # CLExecutionContext::finishQueue
         check(self._lib.clrt_ctx_sync(self.handle))
@@ -69,7 +74,11 @@ class Context:
         return self.device_info(0)
 
     def close(self):
+        """Frees everything still alive on this context first (handles keep a raw pointer to their context)."""
         if self.handle:
+            kids = list(self._children)
+            for k in sorted(kids, key=lambda k: 0 if isinstance(k, AccelerationStructureManager) else 1):
+                k.free()
             self._lib.clrt_ctx_destroy(self.handle)
             self.handle = None
 
@@ -94,6 +103,7 @@ class Buffer:
             src = _ptr(source)
         check(self._lib.clrt_buf_alloc(context.handle, size, src, C.byref(h)))
         self.handle = h
+        context._adopt(self)
 
     @classmethod
     def from_array(cls, context, arr):
@@ -189,6 +199,7 @@ class Scene:
         h = C.c_void_p()
         check(self._lib.clrt_scene_upload(context.handle, _ptr(self._host), self._host.nbytes, C.byref(h)))
         self.handle, self.context = h, context
+        context._adopt(self)
 
     def getDeviceSceneData(self):
         return self._lib.clrt_scene_dptr(self.handle)
@@ -335,6 +346,7 @@ class BVHManager(AccelerationStructureManager):
         h = C.c_void_p()
         check(self._lib.clrt_bvh_create(self.context.handle, self.scene.handle, C.byref(h)))
         self.handle = h
+        self.context._adopt(self)
 
     def export_nodes(self):
         n = self.scene.triangle_count()
@@ -369,6 +381,7 @@ class TwoLevelGridManager(AccelerationStructureManager):
         h = C.c_void_p()
         check(self._lib.clrt_tlg_create(self.context.handle, self.scene.handle, self._top, self._leaf, C.byref(h)))
         self.handle = h
+        self.context._adopt(self)
 
     def sizes(self):
         v = [C.c_uint32() for _ in range(4)]

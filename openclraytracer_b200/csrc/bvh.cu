@@ -126,11 +126,26 @@ __device__ __forceinline__ int2 determine_range(const uint2* __restrict__ list, 
 // Writes: own children (data[1], data[2]; data[3] = 0), parent links of both children, root parent = UINT_MAX.
 // The inner box is NOT written here: refit merges (childA, childB, init box) and writes the result, which is what
 // the reference's fill (BVH.h:309-310) followed by merge3 (:333) leaves in memory.
+// Also here (ours): the traversal-side products that depend only on the sorted order —
+//   tris_sorted[p] = triangle of the leaf at sorted position p (v1.w := original triangle id), so that leaves that are
+//   neighbours in the tree are neighbours in memory, and TraceNode child ids (leaf -> sorted position p, inner -> N + i).
+// Leaf ids in sorted-position space make "smaller id" == "visited earlier by the reference's A-before-B traversal",
+// which is the tie-break the FAST traversal uses to pick the reference's winner on exact ties.
 __global__ void __launch_bounds__(256)
-karras_emit_kernel(const clrt_uint2* __restrict__ pairs_, uint32_t n, clrt_bvh_node* __restrict__ nodes) {
+karras_emit_kernel(const clrt_uint2* __restrict__ pairs_, uint32_t n, clrt_bvh_node* __restrict__ nodes,
+                   const clrt_triangle* __restrict__ tris, clrt_triangle* __restrict__ tris_sorted, TraceNode* __restrict__ tnodes) {
   const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx + 1 >= n) return;
+  if (idx >= n) return;
   const uint2* list = reinterpret_cast<const uint2*>(pairs_);
+  {
+    const uint32_t leaf = list[idx].y;
+    const float4* src = reinterpret_cast<const float4*>(tris + leaf);
+    float4 a = __ldg(src), b = __ldg(src + 1), c = __ldg(src + 2);
+    b.w = __uint_as_float(leaf);
+    float4* dst = reinterpret_cast<float4*>(tris_sorted + idx);
+    dst[0] = a; dst[1] = b; dst[2] = c;
+  }
+  if (idx + 1 >= n) return;
   const int2 range = determine_range(list, (int)idx, n);
   const int split = find_split(list, range.x, range.y);
   const uint32_t self = idx + n;
@@ -143,6 +158,8 @@ karras_emit_kernel(const clrt_uint2* __restrict__ pairs_, uint32_t n, clrt_bvh_n
   d[1] = child_A; d[2] = child_B; d[3] = 0u;
   nodes[child_A].data[0] = self;
   nodes[child_B].data[0] = self;
+  reinterpret_cast<uint4*>(tnodes + idx)[3] = make_uint4(aIsLeaf ? (uint32_t)split : (uint32_t)split + n,
+                                                         bIsLeaf ? (uint32_t)split + 1u : (uint32_t)split + 1u + n, 0u, 0u);
 }
 
 // ---- stage 4: bottom-up refit with per-node arrival counters ---------------------------------------------------
@@ -175,7 +192,6 @@ refit_atomic_kernel(clrt_bvh_node* __restrict__ nodes, uint32_t* __restrict__ co
     __stcg(tn,     make_float4(a0.x, a0.y, a0.z, a1.x));
     __stcg(tn + 1, make_float4(a1.y, a1.z, b0.x, b0.y));
     __stcg(tn + 2, make_float4(b0.z, b1.x, b1.y, b1.z));
-    __stcg(reinterpret_cast<uint4*>(tn + 3), make_uint4(cA, cB, 0u, 0u));
     current = d.x;
   }
 }
@@ -191,12 +207,13 @@ int bvh_init_frame(clrt_accel* a) {
   a->pairs_items = pow2ceil_u32(n ? n : 1);                  // the reference pads to 2^k for its bitonic sort (BVHManager.cpp:129-131)
   const size_t nodes_bytes = (size_t)(n ? 2 * (size_t)n - 1 : 1) * sizeof(clrt_bvh_node);
   if (nodes_bytes > a->nodes_cap || (size_t)a->pairs_items * 8 > a->pairs_cap || (size_t)n * 4 > a->counters_cap ||
-      (size_t)n * sizeof(TraceNode) > a->tnodes_cap)
+      (size_t)n * sizeof(TraceNode) > a->tnodes_cap || (size_t)n * sizeof(clrt_triangle) > a->tris_sorted_cap)
     CLRT_CUDA(cudaStreamSynchronize(ctx->stream));
   CLRT_TRY(clrt_grow((void**)&a->d_nodes, &a->nodes_cap, nodes_bytes));
   CLRT_TRY(clrt_grow((void**)&a->d_pairs, &a->pairs_cap, (size_t)a->pairs_items * 8));
   CLRT_TRY(clrt_grow((void**)&a->d_counters, &a->counters_cap, (size_t)(n ? n : 1) * 4));
   CLRT_TRY(clrt_grow((void**)&a->d_tnodes, &a->tnodes_cap, (size_t)(n ? n : 1) * sizeof(TraceNode)));
+  CLRT_TRY(clrt_grow((void**)&a->d_tris_sorted, &a->tris_sorted_cap, (size_t)(n ? n : 1) * sizeof(clrt_triangle)));
   // fills of initializeFrame (BVHManager.cpp:138-147): pairs = (UINT_MAX,UINT_MAX), counters = 0
   CLRT_CUDA(cudaMemsetAsync(a->d_pairs, 0xFF, (size_t)a->pairs_items * 8, ctx->stream));
   CLRT_CUDA(cudaMemsetAsync(a->d_counters, 0, (size_t)(n ? n : 1) * 4, ctx->stream));
@@ -221,8 +238,8 @@ int bvh_construct(clrt_accel* a) {
   // reference's sort over 2^k items leaves it.  Morton keys have 30 bits.
   CLRT_TRY(sort_pairs_radix(ctx, a->d_pairs, n, 30));
   if (tm) CLRT_CUDA(cudaEventRecord(a->ev[2], s));
-  if (n > 1) {
-    karras_emit_kernel<<<(n - 1 + 255) / 256, 256, 0, s>>>(a->d_pairs, n, a->d_nodes);
+  if (n) {
+    karras_emit_kernel<<<(n + 255) / 256, 256, 0, s>>>(a->d_pairs, n, a->d_nodes, a->scene->d_tris, a->d_tris_sorted, a->d_tnodes);
     CLRT_CHECK_LAUNCH();
   }
   if (tm) CLRT_CUDA(cudaEventRecord(a->ev[3], s));

@@ -26,13 +26,19 @@ constexpr int FAST_STACK = 40;
 constexpr int REF_STACK = 96;
 constexpr uint32_t SENTINEL = 0xFFFFFFFFu;
 
-struct Hit { float t; uint32_t tri; };
+// `tri` is the leaf's SORTED POSITION (index into tris_sorted).  The reference's unordered A-before-B traversal tests
+// leaves in ascending sorted position and accepts `0 < t < best` (BVH.h:392), so among exact ties its winner is the
+// smallest position: ORDERED == false relies on visiting order (REFERENCE_ORDER policy), ORDERED == true applies the
+// same rule explicitly so that a reordered traversal returns the same triangle.
+struct Hit { float t; uint32_t tri; float cull; };
+constexpr float CULL_SLACK = 1.00001f;   // boxes are culled against best_t * (1 + 1e-5): slab-t vs triangle-t rounding never hides a tie
 
+template <bool ORDERED>
 __device__ __forceinline__ void test_triangle(const clrt_triangle* __restrict__ tris, uint32_t id, Vec3 o, Vec3 d, Hit& h) {
   const float4* p = reinterpret_cast<const float4*>(tris + id);
   const float4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
   const float t = triangle_intersect(v3(a.x, a.y, a.z), v3(b.x, b.y, b.z), v3(c.x, c.y, c.z), o, d);
-  if (t > 0.0f && t < h.t) { h.t = t; h.tri = id; }     // BVH.h:392: strict, first tested wins exact ties
+  if (t > 0.0f && (t < h.t || (ORDERED && t == h.t && id < h.tri))) { h.t = t; h.tri = id; h.cull = t * CULL_SLACK; }
 }
 
 struct Stats { uint32_t rays, inner, tris; };
@@ -40,10 +46,10 @@ struct Stats { uint32_t rays, inner, tris; };
 template <bool REF_ORDER, bool STATS>
 __device__ __forceinline__ Hit traverse(const TraceNode* __restrict__ tnodes, const clrt_triangle* __restrict__ tris,
                                         uint32_t n, Vec3 o, Vec3 d, Stats& st) {
-  Hit h; h.t = RT_FLT_MAX; h.tri = SENTINEL;
+  Hit h; h.t = RT_FLT_MAX; h.tri = SENTINEL; h.cull = RT_FLT_MAX;
   if (STATS) st.rays++;
   if (n == 0) return h;
-  if (n == 1) { test_triangle(tris, 0, o, d, h); if (STATS) st.tris++; return h; }    // the reference reads past its node buffer here
+  if (n == 1) { test_triangle<false>(tris, 0, o, d, h); if (STATS) st.tris++; return h; }    // the reference reads past its node buffer here
   const Vec3 inv = v3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
   uint32_t stack[REF_ORDER ? REF_STACK : FAST_STACK];
   int sp = 0;
@@ -66,10 +72,10 @@ __device__ __forceinline__ Hit traverse(const TraceNode* __restrict__ tnodes, co
         else if (bValid) cur = cB;
         else cur = stack[--sp];
       } else {
-        if (aValid && cA < n) { if (!(tA > h.t)) { test_triangle(tris, cA, o, d, h); if (STATS) st.tris++; } aValid = false; }
-        if (bValid && cB < n) { if (!(tB > h.t)) { test_triangle(tris, cB, o, d, h); if (STATS) st.tris++; } bValid = false; }
-        aValid = aValid && !(tA > h.t);
-        bValid = bValid && !(tB > h.t);
+        if (aValid && cA < n) { if (!(tA > h.cull)) { test_triangle<true>(tris, cA, o, d, h); if (STATS) st.tris++; } aValid = false; }
+        if (bValid && cB < n) { if (!(tB > h.cull)) { test_triangle<true>(tris, cB, o, d, h); if (STATS) st.tris++; } bValid = false; }
+        aValid = aValid && !(tA > h.cull);
+        bValid = bValid && !(tB > h.cull);
         if (aValid && bValid) {
           const bool bNear = tB < tA;
           cur = bNear ? cB : cA;
@@ -80,7 +86,7 @@ __device__ __forceinline__ Hit traverse(const TraceNode* __restrict__ tnodes, co
         else cur = stack[--sp];
       }
     } else {
-      test_triangle(tris, cur, o, d, h);
+      test_triangle<false>(tris, cur, o, d, h);
       if (STATS) st.tris++;
       cur = stack[--sp];
     }
@@ -98,7 +104,7 @@ __device__ __forceinline__ void write_contact(clrt_contact* __restrict__ out, ui
     const Vec3 nrm = triangle_normal(v3(a.x, a.y, a.z), v3(b.x, b.y, b.z), v3(c.x, c.y, c.z));
     nd = make_float4(nrm.x, nrm.y, nrm.z, h.t);
     head.y = __float_as_uint(a.w);                                  // MeshHeader.materialIndex
-    head.z = h.tri;                                                 // pad[0] = primitive id (Q11)
+    head.z = __float_as_uint(b.w);                                  // pad[0] = primitive (global triangle) id (Q11)
   }
   uint4* o = reinterpret_cast<uint4*>(out + slot);
   __stcs(o, head);
@@ -146,7 +152,7 @@ trace_primary_kernel(const clrt_camera cam, const TraceNode* __restrict__ tnodes
       const Hit h = traverse<REF_ORDER, STATS>(tnodes, tris, n, o, d, st);
       write_contact(out, raster ? pixel : lt * CLRT_TILE_PIXELS + inTile, pixel, h, tris);
     } else if (!raster) {
-      Hit h; h.t = RT_FLT_MAX; h.tri = SENTINEL;
+      Hit h; h.t = RT_FLT_MAX; h.tri = SENTINEL; h.cull = RT_FLT_MAX;
       write_contact(out, lt * CLRT_TILE_PIXELS + inTile, SENTINEL, h, tris);
     }
   }
@@ -172,7 +178,7 @@ trace_rays_kernel(const clrt_ray* __restrict__ rays, uint32_t count, const Trace
     if (i < count) {
       const float4* p = reinterpret_cast<const float4*>(rays + i);
       const float4 ro = __ldcs(p + 1), rd = __ldcs(p + 2);
-      Hit h; h.t = RT_FLT_MAX; h.tri = SENTINEL;
+      Hit h; h.t = RT_FLT_MAX; h.tri = SENTINEL; h.cull = RT_FLT_MAX;
       if (!(rd.x == 0.0f && rd.y == 0.0f && rd.z == 0.0f))
         h = traverse<REF_ORDER, STATS>(tnodes, tris, n, v3(ro.x, ro.y, ro.z), v3(rd.x, rd.y, rd.z), st);
       write_contact(out, i, i, h, tris);
@@ -197,7 +203,7 @@ static int launch_primary(clrt_accel* a, const clrt_camera& cam, clrt_contact* o
   unsigned grid = 0;
   CLRT_TRY(persistent_grid(a->ctx, trace_primary_kernel<R, S>, TRACE_THREADS, &grid));
   grid = min(grid, (packets + 3) / 4);
-  trace_primary_kernel<R, S><<<grid, TRACE_THREADS, 0, a->ctx->stream>>>(cam, a->d_tnodes, a->scene->d_tris, a->n, out, rank, nranks, raster,
+  trace_primary_kernel<R, S><<<grid, TRACE_THREADS, 0, a->ctx->stream>>>(cam, a->d_tnodes, a->d_tris_sorted, a->n, out, rank, nranks, raster,
                                                                         a->d_tile_counter, (unsigned long long*)(a->d_tile_counter + 4));
   CLRT_CHECK_LAUNCH();
   return 0;
@@ -207,7 +213,7 @@ static int launch_rays(clrt_accel* a, const clrt_ray* rays, clrt_contact* out, u
   unsigned grid = 0;
   CLRT_TRY(persistent_grid(a->ctx, trace_rays_kernel<R, S>, TRACE_THREADS, &grid));
   grid = min(grid, (packets + 3) / 4);
-  trace_rays_kernel<R, S><<<grid, TRACE_THREADS, 0, a->ctx->stream>>>(rays, count, a->d_tnodes, a->scene->d_tris, a->n, out,
+  trace_rays_kernel<R, S><<<grid, TRACE_THREADS, 0, a->ctx->stream>>>(rays, count, a->d_tnodes, a->d_tris_sorted, a->n, out,
                                                                      a->d_tile_counter, (unsigned long long*)(a->d_tile_counter + 4));
   CLRT_CHECK_LAUNCH();
   return 0;

@@ -77,7 +77,10 @@ class FrameRenderer:
         self.resX, self.resY = resX, resY
         torch.cuda.set_device(device)
         self.device = torch.device("cuda", device)
-        self.stream = torch.cuda.current_stream(self.device)
+        # one stream for everything of this renderer: our kernels (the context borrows it), torch's copies and NCCL's
+        # ordering (torch orders the collective after/before work on the stream that is current when it is issued)
+        self.stream = torch.cuda.Stream(self.device)
+        assert self.stream.cuda_stream != 0
         self.ctx = api.Context(device, stream=self.stream.cuda_stream)
         self.scene = api.Scene(scene_buf)
         self.scene.loadToGPU(self.ctx)
@@ -87,6 +90,7 @@ class FrameRenderer:
             self.accel = api.TwoLevelGridManager(self.ctx, self.scene, topLevelDensity, leafDensity)
         self.accel.initialize()
         self.cap = stripe_capacity(resX, resY, world)
+        torch.cuda.synchronize()
         self.stripe = torch.zeros(self.cap, dtype=torch.int32, device=self.device)
         self.gathered = torch.zeros(self.cap * world, dtype=torch.int32, device=self.device) if world > 1 else self.stripe
         self.raster = torch.zeros(resY * resX, dtype=torch.int32, device=self.device)
@@ -99,18 +103,20 @@ class FrameRenderer:
     def render_device(self, camera, shadows=True, want_rays=False):
         """One frame, result left on the device in raster order (on every rank).  Returns rays traced by this rank
         if want_rays (that costs a host sync)."""
-        rays = self.accel.render_stripe(camera, shadows, self.rank, self.world, self.stripe.data_ptr(), want_rays)
-        if self.world > 1:
-            import torch.distributed as dist
-            dist.all_gather_into_tensor(self.gathered, self.stripe, group=self.group)
-        api.frame_untile(self.ctx, self.gathered.data_ptr(), self.resX, self.resY, self.world, self.raster.data_ptr())
+        with self.torch.cuda.stream(self.stream):
+            rays = self.accel.render_stripe(camera, shadows, self.rank, self.world, self.stripe.data_ptr(), want_rays)
+            if self.world > 1:
+                import torch.distributed as dist
+                dist.all_gather_into_tensor(self.gathered, self.stripe, group=self.group)
+            api.frame_untile(self.ctx, self.gathered.data_ptr(), self.resX, self.resY, self.world, self.raster.data_ptr())
         return rays
 
     def render_host(self, camera, shadows=True):
         """e2e: host camera in, RGBA8 raster in pinned host memory out (rank 0 reads the frame back)."""
         self.render_device(camera, shadows)
-        if self.rank == 0:
-            self.host_raster.copy_(self.raster, non_blocking=True)
+        with self.torch.cuda.stream(self.stream):
+            if self.rank == 0:
+                self.host_raster.copy_(self.raster, non_blocking=True)
         self.stream.synchronize()
         return self.host_raster
 

@@ -246,7 +246,7 @@ def test_full_size_soup_1m_properties(ctx):
     cam = api.demo_camera(buf, 640, 360)
     bvh.set_trace_mode(api.TRACE_REFERENCE_ORDER); bvh.generateContacts(cam); a = bvh.download_primary_contacts()
     bvh.set_trace_mode(api.TRACE_FAST); bvh.generateContacts(cam); b = bvh.download_primary_contacts()
-    assert (a["nd"][:, 3] > 0).mean() > 0.5
+    assert (a["nd"][:, 3] > 0).mean() > 0.2
     compare_fast(b, a, None)
     bvh.free(); scene.free()
 
