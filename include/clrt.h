@@ -119,6 +119,13 @@ int clrt_accel_set_trace_mode(clrt_accel* accel, int mode);
 #define CLRT_STAGE_EMIT   2
 #define CLRT_STAGE_REFIT  3
 #define CLRT_STAGE_TOTAL  4
+/* Two-Level Grid stages (TwoLevelGridManager.cpp:207-469): count+scan, top pairs (scatter+sort+ranges), leaf cells,
+ * leaf-pair count+scan, leaf pairs (exact scatter+sort+ranges). */
+#define CLRT_STAGE_TLG_COUNT_TOP  8
+#define CLRT_STAGE_TLG_TOP_PAIRS  9
+#define CLRT_STAGE_TLG_LEAF_CELLS 10
+#define CLRT_STAGE_TLG_LEAF_COUNT 11
+#define CLRT_STAGE_TLG_LEAF_PAIRS 12
 #define CLRT_STAGE_COUNT  16
 int clrt_accel_stage_ms(clrt_accel* accel, int stage, float* out_ms);
 int clrt_accel_enable_stage_timing(clrt_accel* accel, int on);

@@ -230,3 +230,51 @@ def ref_shade(camera, contacts, scene):
     out = np.zeros((len(contacts), 4), dtype=np.float32)
     ref().ref_shade(_p(cam), _p(contacts), C.c_uint32(len(contacts)), _p(scene), _p(out))
     return out
+
+
+# ---- Two-Level Grid through the reference's own functions (oracle/_ref) -------------------------------------------
+class RefTlg:
+    """ref_tlg_build: the reference's TwoLevelGrid.h functions in the manager's launch order (FIXED semantics of
+    SURVEY.md Q17/Q18/Q21 unless literal)."""
+
+    def __init__(self, scene, topLevelDensity=2.0, leafDensity=2.0, literal=False):
+        r = ref()
+        r.ref_tlg_build.restype = C.c_void_p
+        self.scene = np.ascontiguousarray(scene)
+        self.h = C.c_void_p(r.ref_tlg_build(_p(self.scene), C.c_float(topLevelDensity), C.c_float(leafDensity), C.c_int(int(literal))))
+
+    def sizes(self):
+        out = np.zeros(4, dtype=np.uint32)
+        ref().ref_tlg_sizes(self.h, _p(out))
+        return tuple(int(x) for x in out)
+
+    def export(self):
+        tc, tp, lc, lp = self.sizes()
+        grid = np.zeros(1, dtype=L.GRID_DATA)
+        cells = np.zeros(tc, dtype=L.TOP_CELL); tr = np.zeros(tc, dtype=L.UINT2); tpairs = np.zeros(tp, dtype=L.UINT2)
+        lr = np.zeros(lc, dtype=L.UINT2); lpairs = np.zeros(lp, dtype=L.UINT2)
+        ref().ref_tlg_export(self.h, _p(grid), _p(cells), _p(tr), _p(tpairs), _p(lr), _p(lpairs))
+        return dict(grid=grid[0], top_cells=cells, top_ranges=tr, top_pairs=tpairs, leaf_ranges=lr, leaf_pairs=lpairs)
+
+    def trace_primary(self, camera):
+        cam = np.ascontiguousarray(camera, dtype=L.CAMERA)
+        out = np.zeros(int(cam["resX"].item()) * int(cam["resY"].item()), dtype=L.CONTACT)
+        ref().ref_tlg_trace_primary(self.h, _p(cam), _p(self.scene), _p(out))
+        return out
+
+    def trace_rays(self, rays):
+        rays = np.ascontiguousarray(rays, dtype=L.RAY)
+        out = np.zeros(len(rays), dtype=L.CONTACT)
+        ref().ref_tlg_trace_rays(self.h, _p(rays), C.c_uint32(len(rays)), _p(self.scene), _p(out))
+        return out
+
+    def free(self):
+        if self.h:
+            ref().ref_tlg_free(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass

@@ -49,7 +49,12 @@
 static inline float clrt_cl_sign(float v) { return v > 0.0f ? 1.0f : (v < 0.0f ? -1.0f : (v == 0.0f ? v : 0.0f)); }
 #define sign(n) clrt_cl_sign(n)
 #include <CLData/AccelerationStructs/BVH.h>
+// Q20: `pow` in calcLeafCellResolution (TwoLevelGrid.h:199-205) is implementation defined on the OpenCL device and its result
+// is truncated to a cell count; both sides of the parity check evaluate it in double and round to float once.
+static inline float clrt_ref_pow(float x, float y) { return (float)::pow((double)x, (double)y); }
+#define pow(x, y) clrt_ref_pow((x), (y))
 #include <CLData/AccelerationStructs/TwoLevelGrid.h>
+#undef pow
 #include <CLData/Shading.h>
 #undef _WIN32
 // ----------------------------------------------------------------------------------------------
@@ -261,6 +266,131 @@ void ref_shade(const uint8_t* camera, const uint8_t* contacts, uint32_t count, c
       cpuShadeBlinnPhong(&cam, &c, (char*)scene, color);
       memcpy(colors4 + 4 * (size_t)c.pixelIndex, &color, 16);
     }
+  }
+}
+
+// ---- Two-Level Grid ---------------------------------------------------------------------------------------------
+// Reference code called as-is: prepareGridData (TwoLevelGrid.h:102-124), writePairs (:173-190), fillTopLevelCell
+// (:215-225), countLeafPairs (:295-315), writeLeafPairs (:378-403), tlg_generate_contact (:557-678).
+// Restated here (host code that needs OpenCL/boost): TwoLevelGridManager::getResolution/calculateGridData
+// (TwoLevelGridManager.cpp:566-600), the construct() sequence (:207-469), the scan (PrefixSum.cpp, inclusive) and the two
+// range-extraction kernels (TwoLevelGridKernels.cl:71-116,179-221) with the FIXED semantics of SURVEY.md Q17/Q18/Q21:
+// every triangle takes part; range[c] = [first, one-past-last) over the REAL pairs; buffers zero-initialised; the sort is
+// the canonical stable one.  literal != 0 keeps Q17 (the last triangle is skipped by count and scatter).
+struct RefTlg {
+  GridData grid;
+  std::vector<TopLevelCell> cells;
+  std::vector<CL_UINT2> topRanges, topPairs, leafRanges, leafPairs;   // pairs: real ones only, sorted
+  uint32_t leafCells;
+};
+
+static void ref_extract_ranges(const std::vector<CL_UINT2>& sorted, std::vector<CL_UINT2>& ranges) {
+  const size_t n = sorted.size();
+  for (size_t i = 0; i + 1 < n; i++) {
+    const CL_UINT thisOne = sorted[i].x, right = sorted[i + 1].x;
+    if (right > thisOne) { ranges[thisOne].y = (CL_UINT)(i + 1); ranges[right].x = (CL_UINT)(i + 1); }
+  }
+  if (n) ranges[sorted[n - 1].x].y = (CL_UINT)n;                       // FIXED: one past the last (the reference writes n-1)
+}
+static void ref_stable_sort(std::vector<CL_UINT2>& v) {
+  std::stable_sort(v.begin(), v.end(), [](const CL_UINT2& a, const CL_UINT2& b) { return a.x < b.x; });
+}
+
+void* ref_tlg_build(const uint8_t* sceneRaw, float topLevelDensity, float leafDensity, int literal) {
+  const char* scene = (const char*)sceneRaw;
+  const SceneHeader* sh = SCENE_HEADER(scene);
+  RefTlg* t = new RefTlg();
+  // getResolution + calculateGridData (TwoLevelGridManager.cpp:566-600)
+  {
+    struct AABB bounds = sh->modelsBoundingBox;
+    float deltaX = bounds.bounds[1].x - bounds.bounds[0].x;
+    float deltaY = bounds.bounds[1].y - bounds.bounds[0].y;
+    float deltaZ = bounds.bounds[1].z - bounds.bounds[0].z;
+    float volume = boxVolume(bounds);
+    float prims = sh->totalNumberOfTriangles;
+    float a = clrt_ref_pow(topLevelDensity * prims / volume, oneThird);
+    memset(&t->grid, 0, sizeof t->grid);
+    t->grid.box = bounds;
+    t->grid.resX = deltaX * a; t->grid.resY = deltaY * a; t->grid.resZ = deltaZ * a;
+    t->grid.stepX = (bounds.bounds[1].x - bounds.bounds[0].x) / t->grid.resX;
+    t->grid.stepY = (bounds.bounds[1].y - bounds.bounds[0].y) / t->grid.resY;
+    t->grid.stepZ = (bounds.bounds[1].z - bounds.bounds[0].z) / t->grid.resZ;
+    t->grid.leafDensity = leafDensity;
+  }
+  const uint32_t n = (uint32_t)sh->totalNumberOfTriangles;
+  const uint32_t cellsCount = t->grid.resX * t->grid.resY * t->grid.resZ;
+  if (cellsCount == 0) { t->leafCells = 0; return t; }
+  const uint32_t tris = literal ? n - 1 : n;                                 // Q17
+  std::vector<CL_UINT> counters(n, 0), scan(n, 0);
+  for (uint32_t i = 0; i < tris; i++) prepareGridData(scene, i, &t->grid, counters.data());       // TwoLevelGridKernels.cl:43-51
+  { CL_UINT run = 0; for (uint32_t i = 0; i < n; i++) { run += counters[i]; scan[i] = run; } }   // inclusive (Q23)
+  const uint32_t pairsCount = n ? scan[n - 1] : 0;
+  t->topPairs.assign(pairsCount, CL_UINT2());
+  for (auto& p : t->topPairs) p.x = p.y = UINT_MAX;
+  for (uint32_t i = 0; i < tris; i++) writePairs(scene, i, &t->grid, scan.data(), counters.data(), t->topPairs.data());   // :56-66
+  ref_stable_sort(t->topPairs);
+  t->topRanges.assign(cellsCount, CL_UINT2()); for (auto& r : t->topRanges) r.x = r.y = 0;
+  ref_extract_ranges(t->topPairs, t->topRanges);
+  t->cells.assign(cellsCount, TopLevelCell()); memset(t->cells.data(), 0, cellsCount * sizeof(TopLevelCell));
+  std::vector<CL_UINT> leafCounts(cellsCount, 0), leafScan(cellsCount, 0);
+  for (uint32_t c = 0; c < cellsCount; c++) fillTopLevelCell(t->topRanges.data(), leafCounts.data(), t->cells.data(), &t->grid, c);   // :121-127
+  { CL_UINT run = 0; for (uint32_t c = 0; c < cellsCount; c++) { run += leafCounts[c]; leafScan[c] = run; } }
+  t->leafCells = leafScan[cellsCount - 1];
+  for (uint32_t c = 1; c < cellsCount; c++) t->cells[c].firstLeafIdx = leafScan[c - 1];        // :132-139
+  std::vector<CL_UINT> lcount(pairsCount, 0), lscan(pairsCount, 0);
+  #pragma omp parallel for schedule(dynamic, 64)
+  for (long p = 0; p < (long)pairsCount; p++)
+    lcount[p] = countLeafPairs(scene, t->topPairs.data(), (CL_UINT)p, &t->grid, t->cells.data());                         // :144-157
+  { CL_UINT run = 0; for (uint32_t p = 0; p < pairsCount; p++) { run += lcount[p]; lscan[p] = run; } }
+  const uint32_t leafPairsCap = pairsCount ? lscan[pairsCount - 1] : 0;
+  std::vector<CL_UINT2> lp(leafPairsCap);
+  for (auto& p : lp) p.x = p.y = UINT_MAX;
+  #pragma omp parallel for schedule(dynamic, 64)
+  for (long p = 0; p < (long)pairsCount; p++)
+    writeLeafPairs(scene, t->topPairs.data(), t->cells.data(), (CL_UINT)p, &t->grid, lscan.data(), lcount.data(), lp.data());   // :162-174
+  ref_stable_sort(lp);
+  size_t real = 0; while (real < lp.size() && lp[real].x != UINT_MAX) real++;    // Q19: gaps (UINT_MAX) sort last
+  lp.resize(real);
+  t->leafPairs.swap(lp);
+  t->leafRanges.assign(t->leafCells, CL_UINT2()); for (auto& r : t->leafRanges) r.x = r.y = 0;   // Q21: cleared
+  ref_extract_ranges(t->leafPairs, t->leafRanges);
+  return t;
+}
+void ref_tlg_free(void* h) { delete (RefTlg*)h; }
+void ref_tlg_sizes(void* h, uint32_t* out4) {
+  RefTlg* t = (RefTlg*)h;
+  out4[0] = (uint32_t)t->cells.size(); out4[1] = (uint32_t)t->topPairs.size(); out4[2] = t->leafCells; out4[3] = (uint32_t)t->leafPairs.size();
+}
+void ref_tlg_export(void* h, uint8_t* grid, uint8_t* cells, uint8_t* topRanges, uint8_t* topPairs, uint8_t* leafRanges, uint8_t* leafPairs) {
+  RefTlg* t = (RefTlg*)h;
+  memcpy(grid, &t->grid, sizeof(GridData));
+  if (t->cells.size()) { memcpy(cells, t->cells.data(), t->cells.size() * 16); memcpy(topRanges, t->topRanges.data(), t->topRanges.size() * 8); }
+  if (t->topPairs.size()) memcpy(topPairs, t->topPairs.data(), t->topPairs.size() * 8);
+  if (t->leafRanges.size()) memcpy(leafRanges, t->leafRanges.data(), t->leafRanges.size() * 8);
+  if (t->leafPairs.size()) memcpy(leafPairs, t->leafPairs.data(), t->leafPairs.size() * 8);
+}
+// TwoLevelGridKernels.cl:228-246 / :251-267
+void ref_tlg_trace_primary(void* h, const uint8_t* camera, const uint8_t* scene, uint8_t* contacts) {
+  RefTlg* t = (RefTlg*)h;
+  struct Camera cam; memcpy(&cam, camera, sizeof cam);
+  const long rays = (long)cam.resX * cam.resY;
+  #pragma omp parallel for schedule(dynamic, 256)
+  for (long i = 0; i < rays; i++) {
+    const struct Ray r = generateRay(&cam, (CL_UINT)i);
+    struct Contact c = tlg_generate_contact(r, (const char*)scene, &t->grid, t->cells.data(), t->leafRanges.data(), t->leafPairs.data());
+    c.pixelIndex = (CL_UINT)i;
+    memcpy(contacts + 32 * i, &c, 32);
+  }
+}
+void ref_tlg_trace_rays(void* h, const uint8_t* rays48, uint32_t rayCount, const uint8_t* scene, uint8_t* contacts) {
+  RefTlg* t = (RefTlg*)h;
+  #pragma omp parallel for schedule(dynamic, 256)
+  for (long i = 0; i < (long)rayCount; i++) {
+    struct Ray r; memset(&r, 0, sizeof r);
+    memcpy(&r.idx, rays48 + 48 * i, 4); memcpy(&r.origin, rays48 + 48 * i + 16, 16); memcpy(&r.direction, rays48 + 48 * i + 32, 16);
+    struct Contact c = tlg_generate_contact(r, (const char*)scene, &t->grid, t->cells.data(), t->leafRanges.data(), t->leafPairs.data());
+    c.pixelIndex = (CL_UINT)i;
+    memcpy(contacts + 32 * i, &c, 32);
   }
 }
 

@@ -70,6 +70,23 @@ def main():
             out[f"contacts{k}"] = c
             out[f"colors{k}"] = O.ref_shade(cam, c, scene)
         np.savez_compressed(os.path.join(HERE, f"bvh_{name}.npz"), **out)
+        # Two-Level Grid (densities 2.0 / 2.0, the reference's defaults): cell lists as digests (+ full arrays when small),
+        # contacts for the same two cameras, all from the reference's own TwoLevelGrid.h functions.
+        t = O.RefTlg(scene)
+        e = t.export()
+        tl = dict(sizes=np.array(t.sizes(), dtype=np.uint32), grid=e["grid"])
+        for k in ("top_cells", "top_ranges", "top_pairs", "leaf_ranges", "leaf_pairs"):
+            tl[k + "_sha"] = digest(e[k])
+            if n <= 400:
+                tl[k] = e[k]
+        for k, cam in enumerate(cams):
+            c = t.trace_primary(cam)
+            miss = c["nd"][:, 3] <= 0
+            c["nd"][miss] = 0
+            tl[f"cam{k}"] = cam
+            tl[f"contacts{k}"] = c
+        np.savez_compressed(os.path.join(HERE, f"tlg_{name}.npz"), **tl)
+        t.free()
         print(name, n, len(scene), [int((out[f'contacts{k}']['nd'][:, 3] > 0).sum()) for k in range(2)])
 
 
