@@ -131,9 +131,9 @@ int clrt_accel_stage_ms(clrt_accel* accel, int stage, float* out_ms);
 int clrt_accel_enable_stage_timing(clrt_accel* accel, int on);
 /* Traversal statistics mode (measurement only; the reference has none — SURVEY.md section 5): while on, the trace
  * kernels count rays traversed, inner-node visits and triangle tests.  set_stats zeroes the counters;
- * read_stats returns {rays, inner visits, triangle tests} accumulated since. */
+ * read_stats returns {rays, inner-node visits, triangle tests, leaf-box tests inside equal-key runs} accumulated since. */
 int clrt_accel_set_stats(clrt_accel* accel, int on);
-int clrt_accel_read_stats(clrt_accel* accel, uint64_t* h_out3);
+int clrt_accel_read_stats(clrt_accel* accel, uint64_t* h_out4);
 
 /* Inspection of build products (the reference exposes the cl_mem objects; tests download them). */
 int clrt_bvh_export_nodes(clrt_accel* accel, void* h_nodes /* (2N-1) * 48 B */);
@@ -157,6 +157,11 @@ int clrt_shade(clrt_ctx* ctx, const clrt_scene* scene, const clrt_camera* h_came
                uint32_t n, const void* dptr_shadow_contacts, void* dptr_rgba8 /* may be NULL */,
                void* dptr_rgba_f32 /* may be NULL */);
 
+/* Shadow pass + Blinn-Phong in ONE kernel over n contacts (BVH only): per contact and light an occlusion query along the
+ * shadow ray clrt_generate_shadow_rays would build, then the shading of clrt_shade -> RGBA8.  Same pixels as the
+ * three-call pipeline, without materialising rays and shadow contacts. */
+int clrt_shadow_shade(clrt_accel* accel, const clrt_camera* h_camera, const void* dptr_contacts, uint32_t n, void* dptr_rgba8);
+
 /* ---- frame: RTFrame() (OpenCLRayTracerDemo.cpp:271-326) as one call; the image-space shard entry -------
  * Renders the pixels of stripe `rank` of `nranks` (32x8-pixel tiles, tile t owned by rank t % nranks; inside the
  * GPU persistent CTAs pull tiles from an atomic counter) into dptr_rgba8 in STRIPE order (tile-major, 256 px per
@@ -165,6 +170,9 @@ int clrt_shade(clrt_ctx* ctx, const clrt_scene* scene, const clrt_camera* h_came
 int clrt_frame_stripe_pixels(uint32_t resX, uint32_t resY, uint32_t rank, uint32_t nranks, uint32_t* out_pixels, uint32_t* out_tiles);
 int clrt_render_stripe(clrt_accel* accel, const clrt_camera* h_camera, int shadows, uint32_t rank, uint32_t nranks,
                        void* dptr_rgba8, uint64_t* out_rays);
+/* The frame entry points fuse the shadow pass with the shading on a BVH (occlusion queries inside one kernel).  on == 0
+ * forces the three-call pipeline (clrt_generate_shadow_rays -> clrt_trace_rays -> clrt_shade); pixels are identical. */
+int clrt_accel_set_fused_shadows(clrt_accel* accel, int on);
 int clrt_frame_untile(clrt_ctx* ctx, const void* dptr_stripes, uint32_t resX, uint32_t resY, uint32_t nranks, void* dptr_raster_rgba8);
 /* Whole frame with HOST output: upload camera, trace, (shadow,) shade, download RGBA8 raster — the e2e path. */
 int clrt_render_frame_host(clrt_accel* accel, const clrt_camera* h_camera, int shadows, void* h_rgba8, uint64_t* out_rays);

@@ -49,6 +49,7 @@ SIGNATURES = {
     "clrt_accel_set_trace_mode": (C.c_int, [C.c_void_p, C.c_int]),
     "clrt_accel_stage_ms": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_float)]),
     "clrt_accel_enable_stage_timing": (C.c_int, [C.c_void_p, C.c_int]),
+    "clrt_accel_set_fused_shadows": (C.c_int, [C.c_void_p, C.c_int]),
     "clrt_accel_set_stats": (C.c_int, [C.c_void_p, C.c_int]),
     "clrt_accel_read_stats": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64)]),
     "clrt_bvh_export_nodes": (C.c_int, [C.c_void_p, C.c_void_p]),
@@ -58,6 +59,7 @@ SIGNATURES = {
     "clrt_generate_primary_rays": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
     "clrt_generate_shadow_rays": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.POINTER(C.c_uint32)]),
     "clrt_shade": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "clrt_shadow_shade": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]),
     "clrt_frame_stripe_pixels": (C.c_int, [C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
     "clrt_render_stripe": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_uint32, C.c_uint32, C.c_void_p, C.POINTER(C.c_uint64)]),
     "clrt_frame_untile": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_void_p]),

@@ -303,14 +303,21 @@ class AccelerationStructureManager:
         check(self._lib.clrt_accel_stage_ms(self.handle, stage, C.byref(v)))
         return v.value
 
+    def shadow_shade(self, camera, dptr_contacts, n, dptr_rgba8):
+        cam = np.ascontiguousarray(camera, dtype=L.CAMERA)
+        check(self._lib.clrt_shadow_shade(self.handle, _ptr(cam), C.c_void_p(dptr_contacts), n, C.c_void_p(dptr_rgba8)))
+
+    def set_fused_shadows(self, on=True):
+        check(self._lib.clrt_accel_set_fused_shadows(self.handle, int(on)))
+
     def set_stats(self, on=True):
         check(self._lib.clrt_accel_set_stats(self.handle, int(on)))
 
     def read_stats(self):
-        """{rays traversed, inner-node visits, triangle tests} since set_stats(True)."""
-        v = (C.c_uint64 * 3)()
+        """{rays traversed, inner-node visits, triangle tests, run leaf-box tests} since set_stats(True)."""
+        v = (C.c_uint64 * 4)()
         check(self._lib.clrt_accel_read_stats(self.handle, v))
-        return int(v[0]), int(v[1]), int(v[2])
+        return int(v[0]), int(v[1]), int(v[2]), int(v[3])
 
     def render_stripe(self, camera, shadows, rank, nranks, dptr_rgba8, want_rays=False):
         cam = np.ascontiguousarray(camera, dtype=L.CAMERA)

@@ -8,6 +8,9 @@ int shade_launch_shadow_rays(clrt_ctx* ctx, const clrt_scene* scene, const clrt_
 int shade_launch(clrt_ctx* ctx, const clrt_scene* scene, const clrt_camera& cam, const clrt_contact* contacts, uint32_t n,
                  const clrt_contact* shadow, uint32_t* rgba8, float4* rgba_f32);
 
+int bvh_shadow_shade(clrt_accel* a, const clrt_camera& cam, const clrt_contact* contacts, uint32_t count, uint32_t* rgba8,
+                     unsigned long long* d_ray_counter);
+
 static int accel_create(clrt_ctx* ctx, const clrt_scene* scene, AccelKind kind, clrt_accel** out) {
   if (!ctx || !scene || !out) CLRT_FAIL("accel create: NULL argument");
   if (scene->ctx != ctx) CLRT_FAIL("accel create: scene belongs to another context");
@@ -41,6 +44,7 @@ extern "C" int clrt_accel_destroy(clrt_accel* a) {
   if (a->d_counters) cudaFree(a->d_counters);
   if (a->d_tnodes) cudaFree(a->d_tnodes);
   if (a->d_tris_sorted) cudaFree(a->d_tris_sorted);
+  if (a->d_leafbox_sorted) cudaFree(a->d_leafbox_sorted);
   if (a->d_contacts) cudaFree(a->d_contacts);
   if (a->d_frame_scratch) cudaFree(a->d_frame_scratch);
   if (a->d_fb) cudaFree(a->d_fb);
@@ -65,6 +69,10 @@ extern "C" int clrt_accel_set_trace_mode(clrt_accel* a, int mode) {
   if (mode != CLRT_TRACE_FAST && mode != CLRT_TRACE_REFERENCE_ORDER) CLRT_FAIL("clrt_accel_set_trace_mode: unknown mode %d", mode);
   a->trace_mode = mode; return 0;
 }
+extern "C" int clrt_accel_set_fused_shadows(clrt_accel* a, int on) {
+  if (!a) CLRT_FAIL("clrt_accel_set_fused_shadows: NULL accel");
+  a->unfused_shadows = on == 0; return 0;
+}
 extern "C" int clrt_accel_enable_stage_timing(clrt_accel* a, int on) {
   if (!a) CLRT_FAIL("clrt_accel_enable_stage_timing: NULL accel");
   a->timing = on != 0; return 0;
@@ -72,13 +80,13 @@ extern "C" int clrt_accel_enable_stage_timing(clrt_accel* a, int on) {
 extern "C" int clrt_accel_set_stats(clrt_accel* a, int on) {
   if (!a) CLRT_FAIL("clrt_accel_set_stats: NULL accel");
   CLRT_CUDA(cudaSetDevice(a->ctx->device));
-  CLRT_CUDA(cudaMemsetAsync(a->d_tile_counter + 4, 0, 24, a->ctx->stream));
+  CLRT_CUDA(cudaMemsetAsync(a->d_tile_counter + 4, 0, 32, a->ctx->stream));
   a->stats = on != 0; return 0;
 }
 extern "C" int clrt_accel_read_stats(clrt_accel* a, uint64_t* out3) {
   if (!a || !out3) CLRT_FAIL("clrt_accel_read_stats: NULL argument");
   CLRT_CUDA(cudaSetDevice(a->ctx->device));
-  CLRT_CUDA(cudaMemcpyAsync(out3, a->d_tile_counter + 4, 24, cudaMemcpyDeviceToHost, a->ctx->stream));
+  CLRT_CUDA(cudaMemcpyAsync(out3, a->d_tile_counter + 4, 32, cudaMemcpyDeviceToHost, a->ctx->stream));
   CLRT_CUDA(cudaStreamSynchronize(a->ctx->stream));
   return 0;
 }
@@ -119,6 +127,14 @@ extern "C" int clrt_trace_rays(clrt_accel* a, const void* dptr_rays, void* dptr_
                               : tlg_trace_rays(a, (const clrt_ray*)dptr_rays, (clrt_contact*)dptr_contacts, ray_count);
 }
 
+// Shadow pass fused with the shading over an arbitrary contact buffer (BVH only).
+extern "C" int clrt_shadow_shade(clrt_accel* a, const clrt_camera* h_camera, const void* dptr_contacts, uint32_t n, void* dptr_rgba8) {
+  if (!a || !h_camera || (n && (!dptr_contacts || !dptr_rgba8))) CLRT_FAIL("clrt_shadow_shade: NULL argument");
+  if (a->kind != ACCEL_BVH) CLRT_FAIL("clrt_shadow_shade: the fused shadow pass exists for the BVH only");
+  CLRT_CUDA(cudaSetDevice(a->ctx->device));
+  return bvh_shadow_shade(a, *h_camera, (const clrt_contact*)dptr_contacts, n, (uint32_t*)dptr_rgba8, nullptr);
+}
+
 // ---- frame ---------------------------------------------------------------------------------------------
 extern "C" int clrt_frame_stripe_pixels(uint32_t resX, uint32_t resY, uint32_t rank, uint32_t nranks, uint32_t* out_pixels, uint32_t* out_tiles) {
   if (!nranks || rank >= nranks) CLRT_FAIL("clrt_frame_stripe_pixels: rank %u of %u", rank, nranks);
@@ -140,9 +156,12 @@ extern "C" int clrt_render_stripe(clrt_accel* a, const clrt_camera* h_camera, in
   const uint32_t tiles = stripe_tile_count(g.tiles, rank, nranks);
   const uint32_t slots = tiles * CLRT_TILE_PIXELS;
   const uint32_t L1 = a->scene->n_lights + 1;
+  // BVH: the shadow pass is fused with the shading (occlusion queries, no ray / shadow-contact buffers); the grid keeps
+  // the three-kernel pipeline through the generic-ray entry point.
+  const bool fused = shadows && a->kind == ACCEL_BVH && L1 <= 32 && !a->unfused_shadows;
   const size_t contacts_bytes = (size_t)slots * sizeof(clrt_contact);
-  const size_t srays_bytes = shadows ? (size_t)slots * L1 * sizeof(clrt_ray) : 0;
-  const size_t scont_bytes = shadows ? (size_t)slots * L1 * sizeof(clrt_contact) : 0;
+  const size_t srays_bytes = (shadows && !fused) ? (size_t)slots * L1 * sizeof(clrt_ray) : 0;
+  const size_t scont_bytes = (shadows && !fused) ? (size_t)slots * L1 * sizeof(clrt_contact) : 0;
   const size_t total = contacts_bytes + srays_bytes + scont_bytes + 64;
   if (total > a->frame_scratch_cap) {
     CLRT_CUDA(cudaStreamSynchronize(ctx->stream));
@@ -155,12 +174,15 @@ extern "C" int clrt_render_stripe(clrt_accel* a, const clrt_camera* h_camera, in
   unsigned long long* counter = (unsigned long long*)(base + contacts_bytes + srays_bytes + scont_bytes);
   if (slots) {
     CLRT_TRY(accel_trace_primary(a, cam, contacts, rank, nranks));
-    if (shadows) {
+    if (fused) {
+      CLRT_CUDA(cudaMemsetAsync(counter, 0, 8, ctx->stream));
+      CLRT_TRY(bvh_shadow_shade(a, cam, contacts, slots, (uint32_t*)dptr_rgba8, out_rays ? counter : nullptr));
+    } else if (shadows) {
       CLRT_CUDA(cudaMemsetAsync(counter, 0, 8, ctx->stream));
       CLRT_TRY(shade_launch_shadow_rays(ctx, a->scene, cam, contacts, slots, srays, out_rays ? counter : nullptr));
       CLRT_TRY(a->kind == ACCEL_BVH ? bvh_trace_rays(a, srays, scont, slots * L1) : tlg_trace_rays(a, srays, scont, slots * L1));
     }
-    CLRT_TRY(shade_launch(ctx, a->scene, cam, contacts, slots, shadows ? scont : nullptr, (uint32_t*)dptr_rgba8, nullptr));
+    if (!fused) CLRT_TRY(shade_launch(ctx, a->scene, cam, contacts, slots, shadows ? scont : nullptr, (uint32_t*)dptr_rgba8, nullptr));
   }
   if (out_rays) {
     // primary rays = pixels of this stripe that lie inside the image; shadow rays = live rays counted on the device

@@ -133,7 +133,8 @@ __device__ __forceinline__ int2 determine_range(const uint2* __restrict__ list, 
 // which is the tie-break the FAST traversal uses to pick the reference's winner on exact ties.
 __global__ void __launch_bounds__(256)
 karras_emit_kernel(const clrt_uint2* __restrict__ pairs_, uint32_t n, clrt_bvh_node* __restrict__ nodes,
-                   const clrt_triangle* __restrict__ tris, clrt_triangle* __restrict__ tris_sorted, TraceNode* __restrict__ tnodes) {
+                   const clrt_triangle* __restrict__ tris, clrt_triangle* __restrict__ tris_sorted, float4* __restrict__ leafbox_sorted,
+                   TraceNode* __restrict__ tnodes) {
   const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= n) return;
   const uint2* list = reinterpret_cast<const uint2*>(pairs_);
@@ -144,6 +145,8 @@ karras_emit_kernel(const clrt_uint2* __restrict__ pairs_, uint32_t n, clrt_bvh_n
     b.w = __uint_as_float(leaf);
     float4* dst = reinterpret_cast<float4*>(tris_sorted + idx);
     dst[0] = a; dst[1] = b; dst[2] = c;
+    const float4* lb = reinterpret_cast<const float4*>(nodes + leaf) + 1;      // leaf box written by morton_leaves_kernel
+    leafbox_sorted[2 * (size_t)idx] = lb[0]; leafbox_sorted[2 * (size_t)idx + 1] = lb[1];
   }
   if (idx + 1 >= n) return;
   const int2 range = determine_range(list, (int)idx, n);
@@ -158,8 +161,15 @@ karras_emit_kernel(const clrt_uint2* __restrict__ pairs_, uint32_t n, clrt_bvh_n
   d[1] = child_A; d[2] = child_B; d[3] = 0u;
   nodes[child_A].data[0] = self;
   nodes[child_B].data[0] = self;
+  // Equal-key runs (the reference's right-leaning chains, Q8): an inner child whose whole range carries one key is a
+  // chain of its leaves in sorted order.  The traversal may treat it as ONE multi-triangle leaf [start, start+count):
+  // pad0 = start of child A's run, pad1 = countA | countB << 16 (0 = not a run; child B's run starts at split+1).
+  uint32_t cntA = 0, cntB = 0;
+  if (!aIsLeaf && list[range.x].x == list[split].x) { cntA = (uint32_t)(split - range.x + 1); if (cntA > 0xFFFFu) cntA = 0; }
+  if (!bIsLeaf && list[split + 1].x == list[range.y].x) { cntB = (uint32_t)(range.y - split); if (cntB > 0xFFFFu) cntB = 0; }
   reinterpret_cast<uint4*>(tnodes + idx)[3] = make_uint4(aIsLeaf ? (uint32_t)split : (uint32_t)split + n,
-                                                         bIsLeaf ? (uint32_t)split + 1u : (uint32_t)split + 1u + n, 0u, 0u);
+                                                         bIsLeaf ? (uint32_t)split + 1u : (uint32_t)split + 1u + n,
+                                                         (uint32_t)range.x, cntA | (cntB << 16));
 }
 
 // ---- stage 4: bottom-up refit with per-node arrival counters ---------------------------------------------------
@@ -207,13 +217,14 @@ int bvh_init_frame(clrt_accel* a) {
   a->pairs_items = pow2ceil_u32(n ? n : 1);                  // the reference pads to 2^k for its bitonic sort (BVHManager.cpp:129-131)
   const size_t nodes_bytes = (size_t)(n ? 2 * (size_t)n - 1 : 1) * sizeof(clrt_bvh_node);
   if (nodes_bytes > a->nodes_cap || (size_t)a->pairs_items * 8 > a->pairs_cap || (size_t)n * 4 > a->counters_cap ||
-      (size_t)n * sizeof(TraceNode) > a->tnodes_cap || (size_t)n * sizeof(clrt_triangle) > a->tris_sorted_cap)
+      (size_t)n * sizeof(TraceNode) > a->tnodes_cap || (size_t)n * sizeof(clrt_triangle) > a->tris_sorted_cap || (size_t)n * 32 > a->leafbox_cap)
     CLRT_CUDA(cudaStreamSynchronize(ctx->stream));
   CLRT_TRY(clrt_grow((void**)&a->d_nodes, &a->nodes_cap, nodes_bytes));
   CLRT_TRY(clrt_grow((void**)&a->d_pairs, &a->pairs_cap, (size_t)a->pairs_items * 8));
   CLRT_TRY(clrt_grow((void**)&a->d_counters, &a->counters_cap, (size_t)(n ? n : 1) * 4));
   CLRT_TRY(clrt_grow((void**)&a->d_tnodes, &a->tnodes_cap, (size_t)(n ? n : 1) * sizeof(TraceNode)));
   CLRT_TRY(clrt_grow((void**)&a->d_tris_sorted, &a->tris_sorted_cap, (size_t)(n ? n : 1) * sizeof(clrt_triangle)));
+  CLRT_TRY(clrt_grow((void**)&a->d_leafbox_sorted, &a->leafbox_cap, (size_t)(n ? n : 1) * 32));
   // fills of initializeFrame (BVHManager.cpp:138-147): pairs = (UINT_MAX,UINT_MAX), counters = 0
   CLRT_CUDA(cudaMemsetAsync(a->d_pairs, 0xFF, (size_t)a->pairs_items * 8, ctx->stream));
   CLRT_CUDA(cudaMemsetAsync(a->d_counters, 0, (size_t)(n ? n : 1) * 4, ctx->stream));
@@ -239,7 +250,7 @@ int bvh_construct(clrt_accel* a) {
   CLRT_TRY(sort_pairs_radix(ctx, a->d_pairs, n, 30));
   if (tm) CLRT_CUDA(cudaEventRecord(a->ev[2], s));
   if (n) {
-    karras_emit_kernel<<<(n + 255) / 256, 256, 0, s>>>(a->d_pairs, n, a->d_nodes, a->scene->d_tris, a->d_tris_sorted, a->d_tnodes);
+    karras_emit_kernel<<<(n + 255) / 256, 256, 0, s>>>(a->d_pairs, n, a->d_nodes, a->scene->d_tris, a->d_tris_sorted, a->d_leafbox_sorted, a->d_tnodes);
     CLRT_CHECK_LAUNCH();
   }
   if (tm) CLRT_CUDA(cudaEventRecord(a->ev[3], s));

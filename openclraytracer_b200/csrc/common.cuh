@@ -67,7 +67,7 @@ struct __align__(16) TraceNode {
   float ax0, ay0, az0, ax1;   // child A min.xyz, max.x
   float ay1, az1, bx0, by0;   // child A max.yz, child B min.xy
   float bz0, bx1, by1, bz1;   // child B min.z, max.xyz
-  uint32_t childA, childB, pad0, pad1;  // child id < N : leaf (= SORTED POSITION of the leaf), else N + inner node index
+  uint32_t childA, childB, runStartA, runCounts;  // child id < N : leaf (= SORTED POSITION of the leaf), else N + inner node index
 };
 
 enum AccelKind { ACCEL_BVH = 0, ACCEL_TLG = 1 };
@@ -78,6 +78,7 @@ struct clrt_accel {
   const clrt_scene* scene = nullptr;
   int trace_mode = CLRT_TRACE_FAST;
   bool timing = false;
+  bool unfused_shadows = false;     // frame entry points: force the three-kernel shadow pipeline (parity checks)
   bool stats = false;               // traversal statistics mode (rays, inner visits, triangle tests)
   float stage_ms[CLRT_STAGE_COUNT] = {0};
   cudaEvent_t ev[CLRT_STAGE_COUNT + 1] = {nullptr};
@@ -88,6 +89,7 @@ struct clrt_accel {
   uint32_t* d_counters = nullptr; size_t counters_cap = 0;    // N x 4 B
   TraceNode* d_tnodes = nullptr;  size_t tnodes_cap = 0;      // (N-1) x 64 B
   clrt_triangle* d_tris_sorted = nullptr; size_t tris_sorted_cap = 0;   // N x 48 B, sorted-leaf order, v1.w = triangle id
+  float4* d_leafbox_sorted = nullptr; size_t leafbox_cap = 0;           // N x 32 B: leaf boxes (min, max) in sorted-leaf order
   uint32_t pairs_items = 0;
   bool built = false;
   // --- primary contacts / frame scratch ---

@@ -5,13 +5,9 @@
 //  lightEnergyPercentage  R/Include/CLData/Primitives/Light.h:55-58
 // Shadow rays do not exist in the reference (KNOWN_ISSUES_AND_TODO.txt:27-30); they are produced here and traced
 // through the reference's generic-ray entry point (generateContacts(rays, contacts, n)).
-#include "common.cuh"
-#include "rtmath.cuh"
+#include "shade_math.cuh"
 
 namespace {
-
-constexpr float CAMERA_LIGHT_ENERGY = 100000.0f;        // Shading.h:121
-constexpr float SHADOW_EPS_REL = 1.0e-4f;               // shadow-ray origin offset, relative to the primary hit distance
 
 __global__ void __launch_bounds__(256)
 primary_rays_kernel(clrt_camera cam, clrt_ray* __restrict__ rays) {
@@ -22,11 +18,6 @@ primary_rays_kernel(clrt_camera cam, clrt_ray* __restrict__ rays) {
   p[0] = make_uint4(i, 0u, 0u, 0u);
   reinterpret_cast<float4*>(p)[1] = make_float4(o.x, o.y, o.z, 0.0f);
   reinterpret_cast<float4*>(p)[2] = make_float4(d.x, d.y, d.z, 0.0f);
-}
-
-__device__ __forceinline__ Vec3 light_position(const clrt_light* __restrict__ lights, uint32_t n_lights, uint32_t l, Vec3 camPos, float& energy) {
-  if (l < n_lights) { const float4 q = __ldg(reinterpret_cast<const float4*>(lights + l)); energy = q.w; return v3(q.x, q.y, q.z); }
-  energy = CAMERA_LIGHT_ENERGY; return camPos;           // the synthetic camera light (Shading.h:114-126)
 }
 
 // One thread per (contact, light).  Ray index r = c*(L+1)+l.
@@ -44,11 +35,7 @@ shadow_rays_kernel(clrt_camera cam, const clrt_contact* __restrict__ contacts, u
     uint4 h = make_uint4(0xFFFFFFFFu, 0u, 0u, 0u);
     float4 ro = make_float4(0.f, 0.f, 0.f, 0.f), rd = make_float4(0.f, 0.f, 0.f, 0.f);
     if (nd.w > 0.0f && head.x != 0xFFFFFFFFu) {
-      Vec3 o, d; generate_ray(cam, head.x, o, d);
-      const Vec3 P = vadd(o, vscale(d, nd.w));
-      float energy; const Vec3 lp = light_position(lights, n_lights, l, o, energy);
-      const Vec3 dir = vnormalize(vsub(lp, P));
-      const Vec3 org = vadd(P, vscale(dir, SHADOW_EPS_REL * nd.w));
+      Vec3 org, dir; shadow_ray(cam, head.x, nd.w, lights, n_lights, l, org, dir);
       h.x = (uint32_t)r; ro = make_float4(org.x, org.y, org.z, 0.f); rd = make_float4(dir.x, dir.y, dir.z, 0.f);
       live = true;
     }
@@ -57,12 +44,6 @@ shadow_rays_kernel(clrt_camera cam, const clrt_contact* __restrict__ contacts, u
   }
   const unsigned m = __ballot_sync(0xffffffffu, live);
   if ((threadIdx.x & 31) == 0 && m && ray_counter) atomicAdd(ray_counter, (unsigned long long)__popc(m));
-}
-
-__device__ __forceinline__ uint32_t to_u8(float c) {
-  c = (c > 0.0f) ? c : 0.0f;            // NaN -> 0
-  c = (c < 1.0f) ? c : 1.0f;
-  return (uint32_t)(c * 255.0f + 0.5f);
 }
 
 // One thread per contact.
@@ -74,51 +55,14 @@ shade_kernel(clrt_camera cam, const clrt_contact* __restrict__ contacts, uint32_
   if (i >= n) return;
   const uint4 head = __ldcs(reinterpret_cast<const uint4*>(contacts + i));
   const float4 nd = __ldcs(reinterpret_cast<const float4*>(contacts + i) + 1);
-  float4 color = make_float4(0.f, 0.f, 0.f, 0.f);
-  uint32_t packed = 0u;
-  if (nd.w > 0.0f && head.x != 0xFFFFFFFFu) {                      // OpenCLRayTracerDemo.cpp:305
-    // default material (Shading.h:76-86) unless the index is valid (:92-96)
-    Vec3 amb = v3(0.2f, 0.2f, 0.2f), dif = v3(1.f, 1.f, 1.f), spc = v3(1.f, 0.f, 0.f);
-    float shininess = 0.4f;
-    if (head.y < n_materials) {
-      const float4* m = reinterpret_cast<const float4*>(materials + head.y);
-      const float4 a = __ldg(m), d4 = __ldg(m + 1), s4 = __ldg(m + 2), tail = __ldg(m + 5);
-      amb = v3(a.x, a.y, a.z); dif = v3(d4.x, d4.y, d4.z); spc = v3(s4.x, s4.y, s4.z); shininess = tail.x;
-    }
-    Vec3 o, d; generate_ray(cam, head.x, o, d);
-    const Vec3 P = vadd(o, vscale(d, nd.w));
-    const Vec3 N = v3(nd.x, nd.y, nd.z);
-    const Vec3 V = vnormalize(vsub(o, P));
-    float cr = amb.x, cg = amb.y, cb = amb.z;
-    const uint32_t L1 = n_lights + 1;
-    float totalEnergy = 0.0f;
-    for (uint32_t l = 0; l < L1; l++) {
-      float energy; const Vec3 lp = light_position(lights, n_lights, l, o, energy);
-      const float dist = vlength(vsub(lp, P));
-      totalEnergy += rmax(1.0f - dist / energy, 0.0f) * energy;
-    }
-    for (uint32_t l = 0; l < L1; l++) {
-      float energy; const Vec3 lp = light_position(lights, n_lights, l, o, energy);
-      Vec3 Lv = vsub(lp, P);
-      const float dist = vlength(Lv);
-      if (shadow) {                                                // ours: occluded lights add nothing
-        const float st = __ldcs(&shadow[(size_t)i * L1 + l].normalAndintersectionDistance.w);
-        if (st > 0.0f && st < dist - SHADOW_EPS_REL * nd.w) continue;
-      }
-      const float intensity = rmax(1.0f - dist / energy, 0.0f);
-      const float pct = (intensity * energy) / totalEnergy;
-      const float ls = intensity * pct;
-      Lv = vnormalize(Lv);
-      float LdotN = vdot(Lv, N);
-      LdotN = LdotN > 0.0f ? LdotN : 0.0f;
-      cr += dif.x * LdotN * ls; cg += dif.y * LdotN * ls; cb += dif.z * LdotN * ls;
-      const Vec3 R = vnormalize(vsub(vscale(N, 2.0f * LdotN), Lv));
-      const float nSpecular = powf(vdot(R, V), shininess);
-      cr += rmax(spc.x * nSpecular * ls, 0.0f); cg += rmax(spc.y * nSpecular * ls, 0.0f); cb += rmax(spc.z * nSpecular * ls, 0.0f);
-    }
-    color = make_float4(rmin(cr, 1.0f), rmin(cg, 1.0f), rmin(cb, 1.0f), 1.0f);
-    packed = to_u8(color.x) | (to_u8(color.y) << 8) | (to_u8(color.z) << 16) | (255u << 24);
-  }
+  const uint32_t L1 = n_lights + 1;
+  uint32_t packed;
+  const float4 color = shade_contact(cam, head, nd, lights, n_lights, materials, n_materials,
+    [&](uint32_t l, float dist) {                                  // ours: occluded lights add nothing
+      if (!shadow) return false;
+      const float st = __ldcs(&shadow[(size_t)i * L1 + l].normalAndintersectionDistance.w);
+      return st > 0.0f && st < dist - SHADOW_EPS_REL * nd.w;
+    }, packed);
   if (rgba8) __stcs(rgba8 + i, packed);
   if (rgba_f32) __stcs(rgba_f32 + i, color);
 }

@@ -18,6 +18,7 @@
 //  Box validity is the reference's in both policies: `t > 0 || origin inside` with the compare-select slab test.
 #include "common.cuh"
 #include "rtmath.cuh"
+#include "shade_math.cuh"
 
 namespace {
 
@@ -38,15 +39,34 @@ __device__ __forceinline__ void test_triangle(const clrt_triangle* __restrict__ 
   const float4* p = reinterpret_cast<const float4*>(tris + id);
   const float4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
   const float t = triangle_intersect(v3(a.x, a.y, a.z), v3(b.x, b.y, b.z), v3(c.x, c.y, c.z), o, d);
-  if (t > 0.0f && (t < h.t || (ORDERED && t == h.t && id < h.tri))) { h.t = t; h.tri = id; h.cull = t * CULL_SLACK; }
+  if (t > 0.0f && (t < h.t || (ORDERED && t == h.t && h.tri != SENTINEL && id < h.tri))) { h.t = t; h.tri = id; h.cull = t * CULL_SLACK; }
 }
 
-struct Stats { uint32_t rays, inner, tris; };
+struct Stats { uint32_t rays, inner, tris, lboxes; };
 
-template <bool REF_ORDER, bool STATS>
+// An equal-key run [start, start+count) entered as one multi-triangle leaf.  The reference walks the chain node by node:
+// at chain node i it tests the box of leaf i and the box of the remaining suffix, so leaf j is intersected iff its own
+// box and every enclosing suffix box are valid; suffix boxes contain the leaf boxes and the slab test is monotone under
+// box inclusion (also in floating point), hence "leaf box valid" alone selects the same leaves.  Boxes and triangles of
+// a run are contiguous in memory (sorted order) and independent of each other - no pointer chasing.
+template <bool STATS, bool ANYHIT>
+__device__ __forceinline__ void test_run(const clrt_triangle* __restrict__ tris, const float4* __restrict__ leafbox,
+                                         uint32_t start, uint32_t count, Vec3 o, Vec3 d, Vec3 inv, Hit& h, Stats& st) {
+  for (uint32_t p = start; p < start + count; p++) {
+    const float4 lo = __ldg(leafbox + 2 * (size_t)p), hi = __ldg(leafbox + 2 * (size_t)p + 1);
+    if (STATS) st.lboxes++;
+    const float tb = aabb_intersect(lo.x, lo.y, lo.z, hi.x, hi.y, hi.z, o, inv);
+    const bool valid = tb > 0.0f || point_inside(lo.x, lo.y, lo.z, hi.x, hi.y, hi.z, o);
+    if (valid && !(tb > h.cull)) { test_triangle<true>(tris, p, o, d, h); if (STATS) st.tris++; if (ANYHIT && h.tri != SENTINEL) return; }
+  }
+}
+
+// ANYHIT (FAST policy only): returns at the first triangle with 0 < t < tmax - an occlusion query; the answer "some hit
+// below tmax exists" equals "the closest hit is below tmax", which is what the shading's shadow test asks.
+template <bool REF_ORDER, bool STATS, bool ANYHIT = false>
 __device__ __forceinline__ Hit traverse(const TraceNode* __restrict__ tnodes, const clrt_triangle* __restrict__ tris,
-                                        uint32_t n, Vec3 o, Vec3 d, Stats& st) {
-  Hit h; h.t = RT_FLT_MAX; h.tri = SENTINEL; h.cull = RT_FLT_MAX;
+                                        const float4* __restrict__ leafbox, uint32_t n, Vec3 o, Vec3 d, Stats& st, float tmax = RT_FLT_MAX) {
+  Hit h; h.t = tmax; h.tri = SENTINEL; h.cull = ANYHIT ? tmax * CULL_SLACK : RT_FLT_MAX;
   if (STATS) st.rays++;
   if (n == 0) return h;
   if (n == 1) { test_triangle<false>(tris, 0, o, d, h); if (STATS) st.tris++; return h; }    // the reference reads past its node buffer here
@@ -72,8 +92,13 @@ __device__ __forceinline__ Hit traverse(const TraceNode* __restrict__ tnodes, co
         else if (bValid) cur = cB;
         else cur = stack[--sp];
       } else {
+        const uint32_t cntA = q3.w & 0xFFFFu, cntB = q3.w >> 16;
         if (aValid && cA < n) { if (!(tA > h.cull)) { test_triangle<true>(tris, cA, o, d, h); if (STATS) st.tris++; } aValid = false; }
+        else if (aValid && cntA) { if (!(tA > h.cull)) test_run<STATS, ANYHIT>(tris, leafbox, q3.z, cntA, o, d, inv, h, st); aValid = false; }
+        if (ANYHIT && h.tri != SENTINEL) return h;
         if (bValid && cB < n) { if (!(tB > h.cull)) { test_triangle<true>(tris, cB, o, d, h); if (STATS) st.tris++; } bValid = false; }
+        else if (bValid && cntB) { if (!(tB > h.cull)) test_run<STATS, ANYHIT>(tris, leafbox, cB - n, cntB, o, d, inv, h, st); bValid = false; }
+        if (ANYHIT && h.tri != SENTINEL) return h;
         aValid = aValid && !(tA > h.cull);
         bValid = bValid && !(tB > h.cull);
         if (aValid && bValid) {
@@ -113,12 +138,16 @@ __device__ __forceinline__ void write_contact(clrt_contact* __restrict__ out, ui
 
 // statistics mode (bench / DESIGN.md figures): rays traversed, inner-node visits, triangle tests -> stats[0..2]
 __device__ __forceinline__ void flush_stats(const Stats& st, unsigned long long* __restrict__ stats) {
-  uint32_t r = st.rays, i = st.inner, t = st.tris;
+  uint32_t r = st.rays, i = st.inner, t = st.tris, b = st.lboxes;
 #pragma unroll
   for (int d = 16; d > 0; d >>= 1) {
     r += __shfl_xor_sync(0xffffffffu, r, d); i += __shfl_xor_sync(0xffffffffu, i, d); t += __shfl_xor_sync(0xffffffffu, t, d);
+    b += __shfl_xor_sync(0xffffffffu, b, d);
   }
-  if ((threadIdx.x & 31) == 0) { atomicAdd(stats, (unsigned long long)r); atomicAdd(stats + 1, (unsigned long long)i); atomicAdd(stats + 2, (unsigned long long)t); }
+  if ((threadIdx.x & 31) == 0) {
+    atomicAdd(stats, (unsigned long long)r); atomicAdd(stats + 1, (unsigned long long)i); atomicAdd(stats + 2, (unsigned long long)t);
+    atomicAdd(stats + 3, (unsigned long long)b);
+  }
 }
 
 // Primary rays.  Work unit: 8x4-pixel packet; 8 packets form a 32x8 tile; local tile lt of this rank is global
@@ -127,10 +156,10 @@ __device__ __forceinline__ void flush_stats(const Stats& st, unsigned long long*
 template <bool REF_ORDER, bool STATS>
 __global__ void __launch_bounds__(TRACE_THREADS)
 trace_primary_kernel(const clrt_camera cam, const TraceNode* __restrict__ tnodes,
-                     const clrt_triangle* __restrict__ tris, uint32_t n, clrt_contact* __restrict__ out,
+                     const clrt_triangle* __restrict__ tris, const float4* __restrict__ leafbox, uint32_t n, clrt_contact* __restrict__ out,
                      uint32_t rank, uint32_t nranks, int raster, uint32_t* __restrict__ counter,
                      unsigned long long* __restrict__ stats) {
-  Stats st; st.rays = st.inner = st.tris = 0;
+  Stats st; st.rays = st.inner = st.tris = st.lboxes = 0;
   const TileGrid g = make_tile_grid(cam.resX, cam.resY);
   const uint32_t packets = stripe_tile_count(g.tiles, rank, nranks) * 8u;
   const int lane = threadIdx.x & 31;
@@ -149,7 +178,7 @@ trace_primary_kernel(const clrt_camera cam, const TraceNode* __restrict__ tnodes
     if (inside) {
       Vec3 o, d;
       generate_ray(cam, pixel, o, d);
-      const Hit h = traverse<REF_ORDER, STATS>(tnodes, tris, n, o, d, st);
+      const Hit h = traverse<REF_ORDER, STATS>(tnodes, tris, leafbox, n, o, d, st);
       write_contact(out, raster ? pixel : lt * CLRT_TILE_PIXELS + inTile, pixel, h, tris);
     } else if (!raster) {
       Hit h; h.t = RT_FLT_MAX; h.tri = SENTINEL; h.cull = RT_FLT_MAX;
@@ -164,9 +193,9 @@ trace_primary_kernel(const clrt_camera cam, const TraceNode* __restrict__ tnodes
 template <bool REF_ORDER, bool STATS>
 __global__ void __launch_bounds__(TRACE_THREADS)
 trace_rays_kernel(const clrt_ray* __restrict__ rays, uint32_t count, const TraceNode* __restrict__ tnodes,
-                  const clrt_triangle* __restrict__ tris, uint32_t n, clrt_contact* __restrict__ out,
+                  const clrt_triangle* __restrict__ tris, const float4* __restrict__ leafbox, uint32_t n, clrt_contact* __restrict__ out,
                   uint32_t* __restrict__ counter, unsigned long long* __restrict__ stats) {
-  Stats st; st.rays = st.inner = st.tris = 0;
+  Stats st; st.rays = st.inner = st.tris = st.lboxes = 0;
   const int lane = threadIdx.x & 31;
   const uint32_t packets = (count + 31u) / 32u;
   while (true) {
@@ -180,9 +209,59 @@ trace_rays_kernel(const clrt_ray* __restrict__ rays, uint32_t count, const Trace
       const float4 ro = __ldcs(p + 1), rd = __ldcs(p + 2);
       Hit h; h.t = RT_FLT_MAX; h.tri = SENTINEL; h.cull = RT_FLT_MAX;
       if (!(rd.x == 0.0f && rd.y == 0.0f && rd.z == 0.0f))
-        h = traverse<REF_ORDER, STATS>(tnodes, tris, n, v3(ro.x, ro.y, ro.z), v3(rd.x, rd.y, rd.z), st);
+        h = traverse<REF_ORDER, STATS>(tnodes, tris, leafbox, n, v3(ro.x, ro.y, ro.z), v3(rd.x, rd.y, rd.z), st);
       write_contact(out, i, i, h, tris);
     }
+  }
+  if (STATS) flush_stats(st, stats);
+}
+
+// Shadow pass + shading fused (ours; the reference shades on the host and has no shadow rays): one thread per primary
+// contact; for every light an occlusion query (ANYHIT) along the same shadow ray the stand-alone path builds
+// (shade_math.cuh), then Blinn-Phong -> RGBA8.  Same pixels as shadow_rays_kernel + trace_rays_kernel + shade_kernel,
+// without the 48-byte rays and 32-byte shadow contacts ever touching HBM.  Needs L+1 <= 32 lights.
+template <bool STATS>
+__global__ void __launch_bounds__(TRACE_THREADS)
+shadow_shade_kernel(const clrt_camera cam, const clrt_contact* __restrict__ contacts, uint32_t count,
+                    const clrt_light* __restrict__ lights, uint32_t n_lights, const clrt_material* __restrict__ materials, uint32_t n_materials,
+                    const TraceNode* __restrict__ tnodes, const clrt_triangle* __restrict__ tris, const float4* __restrict__ leafbox, uint32_t n,
+                    uint32_t* __restrict__ rgba8, uint32_t* __restrict__ counter, unsigned long long* __restrict__ ray_counter,
+                    unsigned long long* __restrict__ stats) {
+  Stats st; st.rays = st.inner = st.tris = st.lboxes = 0;
+  const int lane = threadIdx.x & 31;
+  const uint32_t packets = (count + 31u) / 32u, L1 = n_lights + 1;
+  uint32_t live_rays = 0;
+  while (true) {
+    uint32_t pk = 0;
+    if (lane == 0) pk = atomicAdd(counter, 1u);
+    pk = __shfl_sync(0xffffffffu, pk, 0);
+    if (pk >= packets) break;
+    const uint32_t i = pk * 32u + lane;
+    if (i < count) {
+      const uint4 head = __ldcs(reinterpret_cast<const uint4*>(contacts + i));
+      const float4 nd = __ldcs(reinterpret_cast<const float4*>(contacts + i) + 1);
+      uint32_t occl = 0;
+      if (nd.w > 0.0f && head.x != SENTINEL) {
+        Vec3 o, d; generate_ray(cam, head.x, o, d);
+        const Vec3 P = vadd(o, vscale(d, nd.w));
+        for (uint32_t l = 0; l < L1; l++) {
+          float energy; const Vec3 lp = light_position(lights, n_lights, l, o, energy);
+          const float dist = vlength(vsub(lp, P));
+          Vec3 org, dir; shadow_ray(cam, head.x, nd.w, lights, n_lights, l, org, dir);
+          const Hit h = traverse<false, STATS, true>(tnodes, tris, leafbox, n, org, dir, st, dist - SHADOW_EPS_REL * nd.w);
+          occl |= (h.tri != SENTINEL ? 1u : 0u) << l;
+        }
+        live_rays += L1;
+      }
+      uint32_t packed;
+      shade_contact(cam, head, nd, lights, n_lights, materials, n_materials, [&](uint32_t l, float) { return ((occl >> l) & 1u) != 0u; }, packed);
+      __stcs(rgba8 + i, packed);
+    }
+  }
+  if (ray_counter) {
+#pragma unroll
+    for (int dd = 16; dd > 0; dd >>= 1) live_rays += __shfl_xor_sync(0xffffffffu, live_rays, dd);
+    if (lane == 0 && live_rays) atomicAdd(ray_counter, (unsigned long long)live_rays);
   }
   if (STATS) flush_stats(st, stats);
 }
@@ -203,7 +282,7 @@ static int launch_primary(clrt_accel* a, const clrt_camera& cam, clrt_contact* o
   unsigned grid = 0;
   CLRT_TRY(persistent_grid(a->ctx, trace_primary_kernel<R, S>, TRACE_THREADS, &grid));
   grid = min(grid, (packets + 3) / 4);
-  trace_primary_kernel<R, S><<<grid, TRACE_THREADS, 0, a->ctx->stream>>>(cam, a->d_tnodes, a->d_tris_sorted, a->n, out, rank, nranks, raster,
+  trace_primary_kernel<R, S><<<grid, TRACE_THREADS, 0, a->ctx->stream>>>(cam, a->d_tnodes, a->d_tris_sorted, a->d_leafbox_sorted, a->n, out, rank, nranks, raster,
                                                                         a->d_tile_counter, (unsigned long long*)(a->d_tile_counter + 4));
   CLRT_CHECK_LAUNCH();
   return 0;
@@ -213,7 +292,7 @@ static int launch_rays(clrt_accel* a, const clrt_ray* rays, clrt_contact* out, u
   unsigned grid = 0;
   CLRT_TRY(persistent_grid(a->ctx, trace_rays_kernel<R, S>, TRACE_THREADS, &grid));
   grid = min(grid, (packets + 3) / 4);
-  trace_rays_kernel<R, S><<<grid, TRACE_THREADS, 0, a->ctx->stream>>>(rays, count, a->d_tnodes, a->d_tris_sorted, a->n, out,
+  trace_rays_kernel<R, S><<<grid, TRACE_THREADS, 0, a->ctx->stream>>>(rays, count, a->d_tnodes, a->d_tris_sorted, a->d_leafbox_sorted, a->n, out,
                                                                      a->d_tile_counter, (unsigned long long*)(a->d_tile_counter + 4));
   CLRT_CHECK_LAUNCH();
   return 0;
@@ -243,4 +322,31 @@ int bvh_trace_rays(clrt_accel* a, const clrt_ray* rays, clrt_contact* out, uint3
   const bool ref = a->trace_mode == CLRT_TRACE_REFERENCE_ORDER;
   if (a->stats) return ref ? launch_rays<true, true>(a, rays, out, count, packets) : launch_rays<false, true>(a, rays, out, count, packets);
   return ref ? launch_rays<true, false>(a, rays, out, count, packets) : launch_rays<false, false>(a, rays, out, count, packets);
+}
+
+// Fused shadow + shade over `count` contacts (BVH only).  d_ray_counter (may be NULL) accumulates the live shadow rays.
+int bvh_shadow_shade(clrt_accel* a, const clrt_camera& cam, const clrt_contact* contacts, uint32_t count, uint32_t* rgba8,
+                     unsigned long long* d_ray_counter) {
+  clrt_ctx* ctx = a->ctx;
+  if (!a->built) CLRT_FAIL("shadow pass: the BVH was not constructed");
+  if (!count) return 0;
+  const clrt_scene* sc = a->scene;
+  if (sc->n_lights + 1 > 32) CLRT_FAIL("fused shadow pass supports at most 31 scene lights");
+  const uint32_t packets = (count + 31u) / 32u;
+  CLRT_CUDA(cudaMemsetAsync(a->d_tile_counter, 0, 4, ctx->stream));
+  unsigned grid = 0;
+  unsigned long long* stats = (unsigned long long*)(a->d_tile_counter + 4);
+  if (a->stats) {
+    CLRT_TRY(persistent_grid(ctx, shadow_shade_kernel<true>, TRACE_THREADS, &grid));
+    grid = min(grid, (packets + 3) / 4);
+    shadow_shade_kernel<true><<<grid, TRACE_THREADS, 0, ctx->stream>>>(cam, contacts, count, sc->d_lights, sc->n_lights, sc->d_materials, sc->n_materials,
+        a->d_tnodes, a->d_tris_sorted, a->d_leafbox_sorted, a->n, rgba8, a->d_tile_counter, d_ray_counter, stats);
+  } else {
+    CLRT_TRY(persistent_grid(ctx, shadow_shade_kernel<false>, TRACE_THREADS, &grid));
+    grid = min(grid, (packets + 3) / 4);
+    shadow_shade_kernel<false><<<grid, TRACE_THREADS, 0, ctx->stream>>>(cam, contacts, count, sc->d_lights, sc->n_lights, sc->d_materials, sc->n_materials,
+        a->d_tnodes, a->d_tris_sorted, a->d_leafbox_sorted, a->n, rgba8, a->d_tile_counter, d_ray_counter, stats);
+  }
+  CLRT_CHECK_LAUNCH();
+  return 0;
 }

@@ -264,3 +264,34 @@ def test_errors_are_reported_not_swallowed(ctx):
     with pytest.raises(api.ClrtError, match="not constructed|was not constructed"):
         bvh.generateContacts(api.demo_camera(buf, 8, 8))
     bvh.free(); s.free()
+
+
+@pytest.mark.parametrize("name", ["tenryuu", "clumsydragon", "soup"])
+def test_fused_shadow_pass_equals_three_kernel_pipeline(ctx, name):
+    """The frame's fused shadow+shade kernel (occlusion queries) gives the pixels and ray counts of
+    generate_shadow_rays -> trace_rays -> shade, bit for bit."""
+    buf = scenes.soup_scene(60_000, seed=5) if name == "soup" else scenes.load_bundled(name)
+    scene, bvh = build_gpu(ctx, buf)
+    for cam in (api.demo_camera(buf, 320, 180), api.demo_camera(buf, 97, 61)):
+        bvh.set_fused_shadows(True)
+        a, ra = bvh.render_frame_host(cam, shadows=True, want_rays=True)
+        a = a.copy()
+        bvh.set_fused_shadows(False)
+        b, rb = bvh.render_frame_host(cam, shadows=True, want_rays=True)
+        assert np.array_equal(a, b) and ra == rb
+        assert (a[..., 3] == 255).any()
+    # stand-alone entry point over the primary contacts
+    cam = api.demo_camera(buf, 160, 90)
+    n = 160 * 90
+    bvh.generateContacts(cam)
+    u8a = api.Buffer(ctx, n * 4); u8b = api.Buffer(ctx, n * 4)
+    bvh.shadow_shade(cam, bvh.getPrimaryContacts(), n, u8a.getCLMem())
+    L1 = scene.num_lights() + 1
+    srays = api.Buffer(ctx, n * L1 * 48); scont = api.Buffer(ctx, n * L1 * 32)
+    api.generate_shadow_rays(ctx, scene, cam, bvh.getPrimaryContacts(), n, srays.getCLMem())
+    bvh.generateContacts(srays, scont, n * L1)
+    api.shade(ctx, scene, cam, bvh.getPrimaryContacts(), n, scont.getCLMem(), u8b.getCLMem(), None)
+    assert np.array_equal(u8a.copyToHost(np.uint32), u8b.copyToHost(np.uint32))
+    for x in (u8a, u8b, srays, scont):
+        x.free()
+    bvh.free(); scene.free()
