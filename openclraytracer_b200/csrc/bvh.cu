@@ -134,7 +134,7 @@ __device__ __forceinline__ int2 determine_range(const uint2* __restrict__ list, 
 __global__ void __launch_bounds__(256)
 karras_emit_kernel(const clrt_uint2* __restrict__ pairs_, uint32_t n, clrt_bvh_node* __restrict__ nodes,
                    const clrt_triangle* __restrict__ tris, clrt_triangle* __restrict__ tris_sorted, float4* __restrict__ leafbox_sorted,
-                   TraceNode* __restrict__ tnodes) {
+                   TraceNode* __restrict__ tnodes, uint32_t* __restrict__ max_run) {
   const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= n) return;
   const uint2* list = reinterpret_cast<const uint2*>(pairs_);
@@ -167,6 +167,7 @@ karras_emit_kernel(const clrt_uint2* __restrict__ pairs_, uint32_t n, clrt_bvh_n
   uint32_t cntA = 0, cntB = 0;
   if (!aIsLeaf && list[range.x].x == list[split].x) { cntA = (uint32_t)(split - range.x + 1); if (cntA > 0xFFFFu) cntA = 0; }
   if (!bIsLeaf && list[split + 1].x == list[range.y].x) { cntB = (uint32_t)(range.y - split); if (cntB > 0xFFFFu) cntB = 0; }
+  if (max(cntA, cntB) >= 2) atomicMax(max_run, max(cntA, cntB));
   reinterpret_cast<uint4*>(tnodes + idx)[3] = make_uint4(aIsLeaf ? (uint32_t)split : (uint32_t)split + n,
                                                          bIsLeaf ? (uint32_t)split + 1u : (uint32_t)split + 1u + n,
                                                          (uint32_t)range.x, cntA | (cntB << 16));
@@ -249,8 +250,9 @@ int bvh_construct(clrt_accel* a) {
   // reference's sort over 2^k items leaves it.  Morton keys have 30 bits.
   CLRT_TRY(sort_pairs_radix(ctx, a->d_pairs, n, 30));
   if (tm) CLRT_CUDA(cudaEventRecord(a->ev[2], s));
+  CLRT_CUDA(cudaMemsetAsync(a->d_tile_counter + 12, 0, 4, s));
   if (n) {
-    karras_emit_kernel<<<(n + 255) / 256, 256, 0, s>>>(a->d_pairs, n, a->d_nodes, a->scene->d_tris, a->d_tris_sorted, a->d_leafbox_sorted, a->d_tnodes);
+    karras_emit_kernel<<<(n + 255) / 256, 256, 0, s>>>(a->d_pairs, n, a->d_nodes, a->scene->d_tris, a->d_tris_sorted, a->d_leafbox_sorted, a->d_tnodes, a->d_tile_counter + 12);
     CLRT_CHECK_LAUNCH();
   }
   if (tm) CLRT_CUDA(cudaEventRecord(a->ev[3], s));
@@ -263,6 +265,14 @@ int bvh_construct(clrt_accel* a) {
     CLRT_CUDA(cudaEventSynchronize(a->ev[4]));
     for (int i = 0; i < 4; i++) CLRT_CUDA(cudaEventElapsedTime(&a->stage_ms[i], a->ev[i], a->ev[i + 1]));
     CLRT_CUDA(cudaEventElapsedTime(&a->stage_ms[CLRT_STAGE_TOTAL], a->ev[0], a->ev[4]));
+  }
+  // longest equal-key run: selects the traversal variant (4-byte read-back; construct() is synchronous in the reference too)
+  {
+    void* pin = nullptr;
+    CLRT_TRY(clrt_ctx_pinned(ctx, 64, &pin));
+    CLRT_CUDA(cudaMemcpyAsync(pin, a->d_tile_counter + 12, 4, cudaMemcpyDeviceToHost, s));
+    CLRT_CUDA(cudaStreamSynchronize(s));
+    a->max_run = *(uint32_t*)pin;
   }
   a->built = true;
   return 0;

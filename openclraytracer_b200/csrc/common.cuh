@@ -91,6 +91,7 @@ struct clrt_accel {
   clrt_triangle* d_tris_sorted = nullptr; size_t tris_sorted_cap = 0;   // N x 48 B, sorted-leaf order, v1.w = triangle id
   float4* d_leafbox_sorted = nullptr; size_t leafbox_cap = 0;           // N x 32 B: leaf boxes (min, max) in sorted-leaf order
   uint32_t pairs_items = 0;
+  uint32_t max_run = 0;           // longest collapsed equal-key run (read back after construct; selects the traversal variant)
   bool built = false;
   // --- primary contacts / frame scratch ---
   clrt_contact* d_contacts = nullptr; size_t contacts_cap = 0;
