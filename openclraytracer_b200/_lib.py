@@ -6,7 +6,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libclrt_cuda.so")
+LIB_PATH = os.environ.get("CLRT_LIB_PATH") or os.path.join(_HERE, "libclrt_cuda.so")   # CLRT_LIB_PATH: kernel-tuning builds
 
 c_void_pp = C.POINTER(C.c_void_p)
 

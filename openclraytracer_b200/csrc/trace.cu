@@ -123,77 +123,144 @@ __device__ __forceinline__ Hit traverse_ref(const TraceNode* __restrict__ tnodes
   return h;
 }
 
-// ---- FAST policy: warp-synchronous loop, every lane of the warp must call (active == false: no ray) --------------------
-// ANYHIT: returns at the first triangle with 0 < t < tmax - an occlusion query; "some hit below tmax exists" equals "the
-// closest hit is below tmax", which is what the shading's shadow test asks.
-// COOP: the structure holds equal-key runs of COOP_MIN or more leaves -> warp-synchronous loop with a cooperative phase;
-// otherwise every lane runs its own loop (no per-step votes) and the few short runs are tested inline.
+// ---- FAST policy ---------------------------------------------------------------------------------------------------------
+// Per-lane traversal state.  ANYHIT: an occlusion query - ends at the first triangle with 0 < t < tmax; "some hit below
+// tmax exists" equals "the closest hit is below tmax", which is what the shading's shadow test asks.
+struct Lane {
+  Vec3 o, d, inv;
+  Hit h;
+  uint32_t cur;
+  int sp;
+  uint32_t visits;                // statistics mode only: inner-node visits of the current ray (-> Contact.pad[1])
+};   // the traversal stack lives in its own local array so that these scalars stay in registers
+
+template <bool STATS, bool ANYHIT>
+__device__ __forceinline__ void lane_begin(Lane& L, const clrt_triangle* __restrict__ tris, uint32_t n, Vec3 o, Vec3 d, float tmax, Stats& st) {
+  L.o = o; L.d = d; L.inv = v3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+  L.h.t = tmax; L.h.tri = SENTINEL; L.h.cull = ANYHIT ? tmax * CULL_SLACK : RT_FLT_MAX;
+  L.sp = 0;                                    // an empty stack pops SENTINEL (lane_step)
+  L.cur = n >= 2 ? n : SENTINEL;
+  if (STATS) { st.rays++; L.visits = 0; }
+  if (n == 1) { test_triangle<false>(tris, 0, o, d, L.h); if (STATS) st.tris++; }     // the reference reads past its node buffer here
+}
+
+// One inner-node visit.  Leaf children are intersected at once; equal-key runs shorter than COOP_MIN (or all runs when
+// !COOP) inline, longer ones are handed to the warp through (rs, rc).  Near child first, far child on the stack, children
+// beyond best_t * (1 + 1e-5) culled.
 template <bool STATS, bool ANYHIT, bool COOP>
-__device__ __forceinline__ Hit traverse_fast(const TraceNode* __restrict__ tnodes, const clrt_triangle* __restrict__ tris,
-                                             const float4* __restrict__ leafbox, uint32_t n, bool active, Vec3 o, Vec3 d, Stats& st,
-                                             float tmax = RT_FLT_MAX) {
-  const unsigned FULL = 0xffffffffu;
-  Hit h; h.t = tmax; h.tri = SENTINEL; h.cull = ANYHIT ? tmax * CULL_SLACK : RT_FLT_MAX;
-  if (STATS && active) st.rays++;
-  const Vec3 inv = v3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
-  uint32_t stack[FAST_STACK];
-  int sp = 0;
-  stack[sp++] = SENTINEL;
-  uint32_t cur = (active && n >= 2) ? n : SENTINEL;
-  if (active && n == 1) { test_triangle<false>(tris, 0, o, d, h); if (STATS) st.tris++; }
-  while (COOP ? __any_sync(FULL, cur != SENTINEL) : (cur != SENTINEL)) {
-    uint32_t rs0 = 0, rc0 = 0, rs1 = 0, rc1 = 0;               // runs waiting for the cooperative phase
-    if (cur != SENTINEL) {
-      if (STATS) st.inner++;
-      const float4* p = reinterpret_cast<const float4*>(tnodes + (cur - n));
-      const float4 q0 = __ldg(p), q1 = __ldg(p + 1), q2 = __ldg(p + 2);
-      const uint4 q3 = __ldg(reinterpret_cast<const uint4*>(p + 3));
-      const float tA = aabb_intersect(q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, o, inv);
-      const float tB = aabb_intersect(q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, o, inv);
-      bool aValid = (tA > 0.0f || point_inside(q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, o)) && !(tA > h.cull);
-      bool bValid = (tB > 0.0f || point_inside(q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, o)) && !(tB > h.cull);
-      const uint32_t cA = q3.x, cB = q3.y, cntA = q3.w & 0xFFFFu, cntB = q3.w >> 16;
-      if (aValid && cA < n) { test_triangle<true>(tris, cA, o, d, h); if (STATS) st.tris++; aValid = false; }
-      else if (aValid && cntA) {
-        if (COOP && cntA >= COOP_MIN) { rs0 = q3.z; rc0 = cntA; }
-        else for (uint32_t k = 0; k < cntA; k++) test_run_element<STATS>(tris, leafbox, q3.z + k, o, d, inv, h, st);
-        aValid = false;
-      }
-      if (bValid && !(tB > h.cull) && cB < n) { test_triangle<true>(tris, cB, o, d, h); if (STATS) st.tris++; bValid = false; }
-      else if (bValid && cntB) {
-        if (COOP && cntB >= COOP_MIN) { if (rc0) { rs1 = cB - n; rc1 = cntB; } else { rs0 = cB - n; rc0 = cntB; } }
-        else if (!(tB > h.cull)) for (uint32_t k = 0; k < cntB; k++) test_run_element<STATS>(tris, leafbox, cB - n + k, o, d, inv, h, st);
-        bValid = false;
-      }
-      aValid = aValid && !(tA > h.cull);
-      bValid = bValid && !(tB > h.cull);
-      if (aValid && bValid) {
-        const bool bNear = tB < tA;
-        cur = bNear ? cB : cA;
-        if (sp < FAST_STACK) stack[sp++] = bNear ? cA : cB;
-      }
-      else if (aValid) cur = cA;
-      else if (bValid) cur = cB;
-      else cur = stack[--sp];
-    }
-    // cooperative phase: the warp works off the pending runs, one owner lane at a time
-    if (COOP) {
-      unsigned pend = __ballot_sync(FULL, rc0 != 0);
-      while (pend) {
-        const int leader = __ffs(pend) - 1;
-        coop_run<STATS>(tris, leafbox, leader, rs0, rc0, o, d, inv, h, st);
-        if ((int)(threadIdx.x & 31) == leader) { rs0 = rs1; rc0 = rc1; rc1 = 0; }
-        pend = __ballot_sync(FULL, rc0 != 0);
-      }
-    }
-    if (ANYHIT && h.tri != SENTINEL) cur = SENTINEL;
+__device__ __forceinline__ void lane_step(Lane& L, const TraceNode* __restrict__ tnodes, const clrt_triangle* __restrict__ tris,
+                                          const float4* __restrict__ leafbox, uint32_t n, Stats& st, uint32_t* __restrict__ stack,
+                                          uint32_t& rs0, uint32_t& rc0, uint32_t& rs1, uint32_t& rc1) {
+  if (STATS) { st.inner++; L.visits++; }
+  const Vec3 o = L.o, d = L.d, inv = L.inv;
+  const float4* p = reinterpret_cast<const float4*>(tnodes + (L.cur - n));
+  const float4 q0 = __ldg(p), q1 = __ldg(p + 1), q2 = __ldg(p + 2);
+  const uint4 q3 = __ldg(reinterpret_cast<const uint4*>(p + 3));
+  const float tA = aabb_intersect(q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, o, inv);
+  const float tB = aabb_intersect(q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, o, inv);
+  bool aValid = (tA > 0.0f || point_inside(q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, o)) && !(tA > L.h.cull);
+  bool bValid = (tB > 0.0f || point_inside(q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, o)) && !(tB > L.h.cull);
+  const uint32_t cA = q3.x, cB = q3.y, cntA = q3.w & 0xFFFFu, cntB = q3.w >> 16;
+  if (aValid && cA < n) { test_triangle<true>(tris, cA, o, d, L.h); if (STATS) st.tris++; aValid = false; }
+  else if (aValid && cntA) {
+    if (COOP && cntA >= COOP_MIN) { rs0 = q3.z; rc0 = cntA; }
+    else for (uint32_t k = 0; k < cntA; k++) test_run_element<STATS>(tris, leafbox, q3.z + k, o, d, inv, L.h, st);
+    aValid = false;
   }
-  return h;
+  if (bValid && !(tB > L.h.cull) && cB < n) { test_triangle<true>(tris, cB, o, d, L.h); if (STATS) st.tris++; bValid = false; }
+  else if (bValid && cntB) {
+    if (COOP && cntB >= COOP_MIN) { if (rc0) { rs1 = cB - n; rc1 = cntB; } else { rs0 = cB - n; rc0 = cntB; } }
+    else if (!(tB > L.h.cull)) for (uint32_t k = 0; k < cntB; k++) test_run_element<STATS>(tris, leafbox, cB - n + k, o, d, inv, L.h, st);
+    bValid = false;
+  }
+  aValid = aValid && !(tA > L.h.cull);
+  bValid = bValid && !(tB > L.h.cull);
+  if (aValid && bValid) {
+    const bool bNear = tB < tA;
+    L.cur = bNear ? cB : cA;
+    if (L.sp < FAST_STACK) stack[L.sp++] = bNear ? cA : cB;
+  }
+  else if (aValid) L.cur = cA;
+  else if (bValid) L.cur = cB;
+  else L.cur = L.sp > 0 ? stack[--L.sp] : SENTINEL;
+  if (ANYHIT && !COOP && L.h.tri != SENTINEL) L.cur = SENTINEL;
+}
+
+// Persistent-warp driver with lane refill.  A "unit" is a pixel slot / ray / contact; units come from one global atomic
+// counter in warp-private batches of BATCH consecutive indices (work stealing between all warps of the GPU).  A lane
+// whose unit is complete goes idle; when REFILL_MIN lanes are idle the warp hands them the next units of its batch, so
+// lanes do not wait for the slowest ray of a packet (rays of one warp differ several-fold in node visits).  Between
+// refill checks every lane runs WINDOW traversal steps on its own; with COOP the steps are warp-synchronous and each is
+// followed by the cooperative phase for long equal-key runs.
+//   Job::start(unit, L)  -> true: a ray is ready in L;  false: the unit completed without tracing (output written)
+//   Job::finish(L)       -> true: the unit continues with another ray (L re-initialised); false: unit complete
+#ifndef CLRT_WINDOW
+#define CLRT_WINDOW 8
+#endif
+#ifndef CLRT_REFILL_MIN
+#define CLRT_REFILL_MIN 12
+#endif
+#ifndef CLRT_BATCH
+#define CLRT_BATCH 64
+#endif
+constexpr int WINDOW = CLRT_WINDOW;
+constexpr int REFILL_MIN = CLRT_REFILL_MIN;
+constexpr uint32_t BATCH = CLRT_BATCH;
+
+template <class Job, bool STATS, bool ANYHIT, bool COOP>
+__device__ __forceinline__ void run_jobs(Job& job, const TraceNode* __restrict__ tnodes, const clrt_triangle* __restrict__ tris,
+                                         const float4* __restrict__ leafbox, uint32_t n, uint32_t total, uint32_t* __restrict__ counter, Stats& st) {
+  const unsigned FULL = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  const unsigned lt_mask = (1u << lane) - 1u;
+  Lane L; L.cur = SENTINEL; L.sp = 0;
+  uint32_t stack[FAST_STACK];
+  bool busy = false, exhausted = false;
+  uint32_t pool_next = 0, pool_end = 0;                         // warp-uniform
+  while (true) {
+    // window boundary, all lanes converged: rays that ended during the window are completed together (Job::finish may aim
+    // the unit's next ray), then idle lanes are refilled together once enough of them wait.
+    if (busy && L.cur == SENTINEL) busy = job.finish(L);
+    unsigned idle = __ballot_sync(FULL, !busy);
+    if (__popc(idle) >= REFILL_MIN) {
+      while (idle) {
+        if (pool_next >= pool_end) {
+          if (exhausted) break;
+          uint32_t b = 0;
+          if (lane == 0) b = atomicAdd(counter, BATCH);
+          b = __shfl_sync(FULL, b, 0);
+          if (b >= total) { exhausted = true; break; }
+          pool_next = b; pool_end = min(b + BATCH, total);
+        }
+        const uint32_t avail = pool_end - pool_next;
+        const uint32_t rank = __popc(idle & lt_mask);
+        if (!busy && rank < avail) busy = job.start(pool_next + rank, L);
+        pool_next += min(avail, (uint32_t)__popc(idle));
+        idle = __ballot_sync(FULL, !busy);
+      }
+      if (idle == FULL) break;                                  // nothing left anywhere
+    }
+#pragma unroll 1
+    for (int k = 0; k < WINDOW; k++) {
+      uint32_t rs0 = 0, rc0 = 0, rs1 = 0, rc1 = 0;
+      if (busy && L.cur != SENTINEL) lane_step<STATS, ANYHIT, COOP>(L, tnodes, tris, leafbox, n, st, stack, rs0, rc0, rs1, rc1);
+      if (COOP) {
+        unsigned pend = __ballot_sync(FULL, rc0 != 0);
+        while (pend) {
+          const int leader = __ffs(pend) - 1;
+          coop_run<STATS>(tris, leafbox, leader, rs0, rc0, L.o, L.d, L.inv, L.h, st);
+          if (lane == leader) { rs0 = rs1; rc0 = rc1; rc1 = 0; }
+          pend = __ballot_sync(FULL, rc0 != 0);
+        }
+        if (ANYHIT && busy && L.h.tri != SENTINEL) L.cur = SENTINEL;
+      }
+    }
+  }
 }
 
 __device__ __forceinline__ void write_contact(clrt_contact* __restrict__ out, uint32_t slot, uint32_t pixelIndex, const Hit& h,
-                                              const clrt_triangle* __restrict__ tris) {
-  uint4 head = make_uint4(pixelIndex, 0u, SENTINEL, 0u);
+                                              const clrt_triangle* __restrict__ tris, uint32_t pad1 = 0u) {
+  uint4 head = make_uint4(pixelIndex, 0u, SENTINEL, pad1);
   float4 nd = make_float4(0.0f, 0.0f, 0.0f, 0.0f);                 // miss: contactDist = 0 (BVH.h:402-406)
   if (h.tri != SENTINEL) {
     const float4* p = reinterpret_cast<const float4*>(tris + h.tri);
@@ -222,9 +289,102 @@ __device__ __forceinline__ void flush_stats(const Stats& st, unsigned long long*
   }
 }
 
-// Primary rays.  Work unit: 8x4-pixel packet; 8 packets form a 32x8 tile; local tile lt of this rank is global
+// ---- units -----------------------------------------------------------------------------------------------------------------
+// Primary rays: unit u = slot of the (padded) stripe: local tile lt = u / 256, inside the 32x8 tile eight 8x4 sub-blocks of
+// 32 consecutive units (so the lanes of a warp start on a compact pixel block); local tile lt of this rank is global
 // tile rank + lt*nranks.  raster != 0: contact goes to out[pixelIndex] (the reference's output[c.pixelIndex] = c);
 // raster == 0: stripe order, slot = lt*256 + y*32 + x, out-of-image slots get pixelIndex = UINT_MAX.
+struct PixelRef { uint32_t pixel, slot; bool inside; };
+__device__ __forceinline__ PixelRef pixel_of_unit(const clrt_camera& cam, const TileGrid& g, uint32_t u, uint32_t rank, uint32_t nranks, int raster) {
+  const uint32_t lt = u >> 8, sub = (u >> 5) & 7u, l = u & 31u;
+  const uint32_t gt = rank + lt * nranks;
+  const uint32_t tx = (gt % g.tilesX) * CLRT_TILE_W + (sub & 3u) * 8u + (l & 7u);
+  const uint32_t ty = (gt / g.tilesX) * CLRT_TILE_H + (sub >> 2) * 4u + (l >> 3);
+  PixelRef r;
+  r.inside = tx < cam.resX && ty < cam.resY;
+  r.pixel = ty * cam.resX + tx;
+  r.slot = raster ? r.pixel : lt * CLRT_TILE_PIXELS + ((sub >> 2) * 4u + (l >> 3)) * CLRT_TILE_W + (sub & 3u) * 8u + (l & 7u);
+  return r;
+}
+
+template <bool STATS>
+struct PrimaryJob {
+  const clrt_camera& cam; TileGrid g; uint32_t rank, nranks; int raster;
+  const clrt_triangle* __restrict__ tris; uint32_t n; clrt_contact* __restrict__ out; Stats& st;
+  uint32_t pixel, slot;
+  __device__ __forceinline__ bool start(uint32_t u, Lane& L) {
+    const PixelRef r = pixel_of_unit(cam, g, u, rank, nranks, raster);
+    if (!r.inside) {
+      if (!raster) { Hit h; h.t = RT_FLT_MAX; h.tri = SENTINEL; write_contact(out, r.slot, SENTINEL, h, tris); }
+      return false;
+    }
+    pixel = r.pixel; slot = r.slot;
+    Vec3 o, d; generate_ray(cam, pixel, o, d);
+    lane_begin<STATS, false>(L, tris, n, o, d, RT_FLT_MAX, st);
+    return true;
+  }
+  __device__ __forceinline__ bool finish(Lane& L) { write_contact(out, slot, pixel, L.h, tris, STATS ? L.visits : 0u); return false; }
+};
+
+// Generic rays (generateContacts2): contact i for ray i, pixelIndex = i.  A ray with a zero direction cannot hit
+// anything in the reference either (det == 0 for every triangle); it is answered without traversal.
+template <bool STATS>
+struct RaysJob {
+  const clrt_ray* __restrict__ rays; const clrt_triangle* __restrict__ tris; uint32_t n; clrt_contact* __restrict__ out; Stats& st;
+  uint32_t index;
+  __device__ __forceinline__ bool start(uint32_t i, Lane& L) {
+    const float4* p = reinterpret_cast<const float4*>(rays + i);
+    const float4 ro = __ldcs(p + 1), rd = __ldcs(p + 2);
+    if (rd.x == 0.0f && rd.y == 0.0f && rd.z == 0.0f) { Hit h; h.t = RT_FLT_MAX; h.tri = SENTINEL; write_contact(out, i, i, h, tris); return false; }
+    index = i;
+    lane_begin<STATS, false>(L, tris, n, v3(ro.x, ro.y, ro.z), v3(rd.x, rd.y, rd.z), RT_FLT_MAX, st);
+    return true;
+  }
+  __device__ __forceinline__ bool finish(Lane& L) { write_contact(out, index, index, L.h, tris); return false; }
+};
+
+// Shadow pass + shading fused (ours; the reference shades on the host and has no shadow rays): unit = primary contact;
+// for every light an occlusion query (ANYHIT) along the same shadow ray the stand-alone path builds (shade_math.cuh),
+// then Blinn-Phong -> RGBA8.  Same pixels as shadow_rays_kernel + trace_rays_kernel + shade_kernel, without the 48-byte
+// rays and 32-byte shadow contacts ever touching HBM.  Needs L+1 <= 32 lights.
+template <bool STATS>
+struct ShadowJob {
+  const clrt_camera& cam; const clrt_contact* __restrict__ contacts;
+  const clrt_light* __restrict__ lights; uint32_t n_lights; const clrt_material* __restrict__ materials; uint32_t n_materials;
+  const clrt_triangle* __restrict__ tris; uint32_t n; uint32_t* __restrict__ rgba8; Stats& st; uint32_t& live_rays;
+  uint4 head; float4 nd; Vec3 o, P; uint32_t index, l, occl;
+  __device__ __forceinline__ void shade_and_store() {
+    uint32_t packed;
+    const uint32_t oc = occl;
+    shade_contact(cam, head, nd, lights, n_lights, materials, n_materials, [oc](uint32_t k, float) { return ((oc >> k) & 1u) != 0u; }, packed);
+    __stcs(rgba8 + index, packed);
+  }
+  __device__ __forceinline__ void aim(Lane& L) {
+    float energy; const Vec3 lp = light_position(lights, n_lights, l, o, energy);
+    const float limit = vlength(vsub(lp, P)) - SHADOW_EPS_REL * nd.w;
+    Vec3 org, dir; shadow_ray(cam, head.x, nd.w, lights, n_lights, l, org, dir);
+    lane_begin<STATS, true>(L, tris, n, org, dir, limit, st);
+  }
+  __device__ __forceinline__ bool start(uint32_t i, Lane& L) {
+    index = i; occl = 0; l = 0;
+    head = __ldcs(reinterpret_cast<const uint4*>(contacts + i));
+    nd = __ldcs(reinterpret_cast<const float4*>(contacts + i) + 1);
+    if (!(nd.w > 0.0f && head.x != SENTINEL)) { __stcs(rgba8 + i, 0u); return false; }
+    Vec3 d; generate_ray(cam, head.x, o, d);
+    P = vadd(o, vscale(d, nd.w));
+    live_rays += n_lights + 1;
+    aim(L);
+    return true;
+  }
+  __device__ __forceinline__ bool finish(Lane& L) {
+    occl |= (L.h.tri != SENTINEL ? 1u : 0u) << l;
+    if (++l <= n_lights) { aim(L); return true; }
+    shade_and_store();
+    return false;
+  }
+};
+
+// ---- kernels ---------------------------------------------------------------------------------------------------------------
 template <int MODE, bool STATS>      // MODE 0: REFERENCE_ORDER, 1: FAST, 2: FAST with cooperative runs
 __global__ void __launch_bounds__(TRACE_THREADS)
 trace_primary_kernel(const clrt_camera cam, const TraceNode* __restrict__ tnodes,
@@ -233,66 +393,61 @@ trace_primary_kernel(const clrt_camera cam, const TraceNode* __restrict__ tnodes
                      unsigned long long* __restrict__ stats) {
   Stats st; st.rays = st.inner = st.tris = st.lboxes = 0;
   const TileGrid g = make_tile_grid(cam.resX, cam.resY);
-  const uint32_t packets = stripe_tile_count(g.tiles, rank, nranks) * 8u;
-  const int lane = threadIdx.x & 31;
-  while (true) {
-    uint32_t pk = 0;
-    if (lane == 0) pk = atomicAdd(counter, 1u);
-    pk = __shfl_sync(0xffffffffu, pk, 0);
-    if (pk >= packets) break;
-    const uint32_t lt = pk >> 3, sub = pk & 7u;
-    const uint32_t gt = rank + lt * nranks;
-    const uint32_t tx = (gt % g.tilesX) * CLRT_TILE_W + (sub & 3u) * 8u + (lane & 7);
-    const uint32_t ty = (gt / g.tilesX) * CLRT_TILE_H + (sub >> 2) * 4u + (lane >> 3);
-    const uint32_t inTile = ((sub >> 2) * 4u + (lane >> 3)) * CLRT_TILE_W + (sub & 3u) * 8u + (lane & 7);
-    const bool inside = tx < cam.resX && ty < cam.resY;
-    const uint32_t pixel = ty * cam.resX + tx;
-    Vec3 o = v3(0.f, 0.f, 0.f), d = v3(0.f, 0.f, 1.f);
-    if (inside) generate_ray(cam, pixel, o, d);
-    Hit h; h.t = RT_FLT_MAX; h.tri = SENTINEL; h.cull = RT_FLT_MAX;
-    if (MODE == 0) { if (inside) h = traverse_ref<STATS>(tnodes, tris, n, o, d, st); }
-    else h = traverse_fast<STATS, false, MODE == 2>(tnodes, tris, leafbox, n, inside, o, d, st);
-    if (inside) {
-      write_contact(out, raster ? pixel : lt * CLRT_TILE_PIXELS + inTile, pixel, h, tris);
-    } else if (!raster) {
-      Hit h; h.t = RT_FLT_MAX; h.tri = SENTINEL; h.cull = RT_FLT_MAX;
-      write_contact(out, lt * CLRT_TILE_PIXELS + inTile, SENTINEL, h, tris);
+  const uint32_t total = stripe_tile_count(g.tiles, rank, nranks) * CLRT_TILE_PIXELS;
+  if (MODE == 0) {
+    const int lane = threadIdx.x & 31;
+    while (true) {                                               // 32-unit packets, one ray per thread, the reference's order
+      uint32_t pk = 0;
+      if (lane == 0) pk = atomicAdd(counter, 32u);
+      pk = __shfl_sync(0xffffffffu, pk, 0);
+      if (pk >= total) break;
+      const PixelRef r = pixel_of_unit(cam, g, pk + lane, rank, nranks, raster);
+      if (r.inside) {
+        Vec3 o, d; generate_ray(cam, r.pixel, o, d);
+        const Hit h = traverse_ref<STATS>(tnodes, tris, n, o, d, st);
+        write_contact(out, r.slot, r.pixel, h, tris);
+      } else if (!raster) {
+        Hit h; h.t = RT_FLT_MAX; h.tri = SENTINEL;
+        write_contact(out, r.slot, SENTINEL, h, tris);
+      }
     }
+  } else {
+    PrimaryJob<STATS> job{cam, g, rank, nranks, raster, tris, n, out, st, 0u, 0u};
+    run_jobs<PrimaryJob<STATS>, STATS, false, MODE == 2>(job, tnodes, tris, leafbox, n, total, counter, st);
   }
   if (STATS) flush_stats(st, stats);
 }
 
-// Generic rays (generateContacts2): contact i for ray i, pixelIndex = i.  A ray with a zero direction cannot hit
-// anything in the reference either (det == 0 for every triangle); it is skipped without traversal.
 template <int MODE, bool STATS>
 __global__ void __launch_bounds__(TRACE_THREADS)
 trace_rays_kernel(const clrt_ray* __restrict__ rays, uint32_t count, const TraceNode* __restrict__ tnodes,
                   const clrt_triangle* __restrict__ tris, const float4* __restrict__ leafbox, uint32_t n, clrt_contact* __restrict__ out,
                   uint32_t* __restrict__ counter, unsigned long long* __restrict__ stats) {
   Stats st; st.rays = st.inner = st.tris = st.lboxes = 0;
-  const int lane = threadIdx.x & 31;
-  const uint32_t packets = (count + 31u) / 32u;
-  while (true) {
-    uint32_t pk = 0;
-    if (lane == 0) pk = atomicAdd(counter, 1u);
-    pk = __shfl_sync(0xffffffffu, pk, 0);
-    if (pk >= packets) break;
-    const uint32_t i = pk * 32u + lane;
-    float4 ro = make_float4(0.f, 0.f, 0.f, 0.f), rd = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (i < count) { const float4* p = reinterpret_cast<const float4*>(rays + i); ro = __ldcs(p + 1); rd = __ldcs(p + 2); }
-    const bool live = i < count && !(rd.x == 0.0f && rd.y == 0.0f && rd.z == 0.0f);
-    Hit h; h.t = RT_FLT_MAX; h.tri = SENTINEL; h.cull = RT_FLT_MAX;
-    if (MODE == 0) { if (live) h = traverse_ref<STATS>(tnodes, tris, n, v3(ro.x, ro.y, ro.z), v3(rd.x, rd.y, rd.z), st); }
-    else h = traverse_fast<STATS, false, MODE == 2>(tnodes, tris, leafbox, n, live, v3(ro.x, ro.y, ro.z), v3(rd.x, rd.y, rd.z), st);
-    if (i < count) write_contact(out, i, i, h, tris);
+  if (MODE == 0) {
+    const int lane = threadIdx.x & 31;
+    while (true) {
+      uint32_t pk = 0;
+      if (lane == 0) pk = atomicAdd(counter, 32u);
+      pk = __shfl_sync(0xffffffffu, pk, 0);
+      if (pk >= count) break;
+      const uint32_t i = pk + lane;
+      if (i < count) {
+        const float4* p = reinterpret_cast<const float4*>(rays + i);
+        const float4 ro = __ldcs(p + 1), rd = __ldcs(p + 2);
+        Hit h; h.t = RT_FLT_MAX; h.tri = SENTINEL; h.cull = RT_FLT_MAX;
+        if (!(rd.x == 0.0f && rd.y == 0.0f && rd.z == 0.0f))
+          h = traverse_ref<STATS>(tnodes, tris, n, v3(ro.x, ro.y, ro.z), v3(rd.x, rd.y, rd.z), st);
+        write_contact(out, i, i, h, tris);
+      }
+    }
+  } else {
+    RaysJob<STATS> job{rays, tris, n, out, st, 0u};
+    run_jobs<RaysJob<STATS>, STATS, false, MODE == 2>(job, tnodes, tris, leafbox, n, count, counter, st);
   }
   if (STATS) flush_stats(st, stats);
 }
 
-// Shadow pass + shading fused (ours; the reference shades on the host and has no shadow rays): one thread per primary
-// contact; for every light an occlusion query (ANYHIT) along the same shadow ray the stand-alone path builds
-// (shade_math.cuh), then Blinn-Phong -> RGBA8.  Same pixels as shadow_rays_kernel + trace_rays_kernel + shade_kernel,
-// without the 48-byte rays and 32-byte shadow contacts ever touching HBM.  Needs L+1 <= 32 lights.
 template <bool STATS, bool COOP>
 __global__ void __launch_bounds__(TRACE_THREADS)
 shadow_shade_kernel(const clrt_camera cam, const clrt_contact* __restrict__ contacts, uint32_t count,
@@ -301,46 +456,13 @@ shadow_shade_kernel(const clrt_camera cam, const clrt_contact* __restrict__ cont
                     uint32_t* __restrict__ rgba8, uint32_t* __restrict__ counter, unsigned long long* __restrict__ ray_counter,
                     unsigned long long* __restrict__ stats) {
   Stats st; st.rays = st.inner = st.tris = st.lboxes = 0;
-  const int lane = threadIdx.x & 31;
-  const uint32_t packets = (count + 31u) / 32u, L1 = n_lights + 1;
   uint32_t live_rays = 0;
-  while (true) {
-    uint32_t pk = 0;
-    if (lane == 0) pk = atomicAdd(counter, 1u);
-    pk = __shfl_sync(0xffffffffu, pk, 0);
-    if (pk >= packets) break;
-    const uint32_t i = pk * 32u + lane;
-    uint4 head = make_uint4(SENTINEL, 0u, SENTINEL, 0u);
-    float4 nd = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (i < count) {
-      head = __ldcs(reinterpret_cast<const uint4*>(contacts + i));
-      nd = __ldcs(reinterpret_cast<const float4*>(contacts + i) + 1);
-    }
-    const bool live = nd.w > 0.0f && head.x != SENTINEL;
-    uint32_t occl = 0;
-    Vec3 o = v3(0.f, 0.f, 0.f), P = v3(0.f, 0.f, 0.f);
-    if (live) { Vec3 d; generate_ray(cam, head.x, o, d); P = vadd(o, vscale(d, nd.w)); live_rays += L1; }
-    for (uint32_t l = 0; l < L1; l++) {                       // warp-uniform: every lane takes part in the traversal loop
-      Vec3 org = v3(0.f, 0.f, 0.f), dir = v3(0.f, 0.f, 1.f);
-      float limit = 0.0f;
-      if (live) {
-        float energy; const Vec3 lp = light_position(lights, n_lights, l, o, energy);
-        limit = vlength(vsub(lp, P)) - SHADOW_EPS_REL * nd.w;
-        shadow_ray(cam, head.x, nd.w, lights, n_lights, l, org, dir);
-      }
-      const Hit h = traverse_fast<STATS, true, COOP>(tnodes, tris, leafbox, n, live, org, dir, st, limit);
-      occl |= (h.tri != SENTINEL ? 1u : 0u) << l;
-    }
-    if (i < count) {
-      uint32_t packed;
-      shade_contact(cam, head, nd, lights, n_lights, materials, n_materials, [&](uint32_t l, float) { return ((occl >> l) & 1u) != 0u; }, packed);
-      __stcs(rgba8 + i, packed);
-    }
-  }
+  ShadowJob<STATS> job{cam, contacts, lights, n_lights, materials, n_materials, tris, n, rgba8, st, live_rays};
+  run_jobs<ShadowJob<STATS>, STATS, true, COOP>(job, tnodes, tris, leafbox, n, count, counter, st);
   if (ray_counter) {
 #pragma unroll
     for (int dd = 16; dd > 0; dd >>= 1) live_rays += __shfl_xor_sync(0xffffffffu, live_rays, dd);
-    if (lane == 0 && live_rays) atomicAdd(ray_counter, (unsigned long long)live_rays);
+    if ((threadIdx.x & 31) == 0 && live_rays) atomicAdd(ray_counter, (unsigned long long)live_rays);
   }
   if (STATS) flush_stats(st, stats);
 }
