@@ -113,12 +113,24 @@ void* clrt_accel_primary_contacts_dptr(clrt_accel* accel);     /* getPrimaryCont
 #define CLRT_TRACE_FAST            0
 #define CLRT_TRACE_REFERENCE_ORDER 1
 int clrt_accel_set_trace_mode(clrt_accel* accel, int mode);
+/* Trace tree (ours; openclraytracer_b200/csrc/trace_tree.cu).  The reference-layout BVH is always built bit-exactly; when it
+ * is a poor thing to traverse — equal-key chains (BVH.h:153-154,212-233) of 6+ leaves, or a scene box reaching below zero so
+ * that a Morton axis collapses (BVH.h:112-114 divides without subtracting min) — construct() also builds a plain LBVH over
+ * the same triangles from a min-subtracted Morton code, and CLRT_TRACE_FAST walks that one.  Same closest hits; exact ties
+ * go to the reference's winner (smallest position in the reference's sorted order).  policy: 0 auto (default), 1 always,
+ * 2 never.  Takes effect at the next construct(). */
+#define CLRT_TRACE_TREE_AUTO   0
+#define CLRT_TRACE_TREE_ALWAYS 1
+#define CLRT_TRACE_TREE_NEVER  2
+int clrt_accel_set_trace_tree(clrt_accel* accel, int policy);
+int clrt_accel_has_trace_tree(clrt_accel* accel, int* out);
 /* Stage timings of the last construct() in ms (CUDA events on the context's stream). */
 #define CLRT_STAGE_MORTON 0
 #define CLRT_STAGE_SORT   1
 #define CLRT_STAGE_EMIT   2
 #define CLRT_STAGE_REFIT  3
-#define CLRT_STAGE_TOTAL  4
+#define CLRT_STAGE_TOTAL  4   /* everything construct() launched, the trace tree included */
+#define CLRT_STAGE_TRACE_TREE 5 /* the separate traversal hierarchy (0 when none was built) */
 /* Two-Level Grid stages (TwoLevelGridManager.cpp:207-469): count+scan, top pairs (scatter+sort+ranges), leaf cells,
  * leaf-pair count+scan, leaf pairs (exact scatter+sort+ranges). */
 #define CLRT_STAGE_TLG_COUNT_TOP  8

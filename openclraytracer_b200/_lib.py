@@ -47,6 +47,8 @@ SIGNATURES = {
     "clrt_trace_rays": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32]),
     "clrt_accel_primary_contacts_dptr": (C.c_void_p, [C.c_void_p]),
     "clrt_accel_set_trace_mode": (C.c_int, [C.c_void_p, C.c_int]),
+    "clrt_accel_set_trace_tree": (C.c_int, [C.c_void_p, C.c_int]),
+    "clrt_accel_has_trace_tree": (C.c_int, [C.c_void_p, C.POINTER(C.c_int)]),
     "clrt_accel_stage_ms": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_float)]),
     "clrt_accel_enable_stage_timing": (C.c_int, [C.c_void_p, C.c_int]),
     "clrt_accel_set_fused_shadows": (C.c_int, [C.c_void_p, C.c_int]),

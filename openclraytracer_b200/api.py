@@ -20,7 +20,8 @@ from ._lib import ClrtError, check
 
 SORT_RADIX, SORT_BITONIC_COMPAT = 0, 1
 TRACE_FAST, TRACE_REFERENCE_ORDER = 0, 1
-STAGE_MORTON, STAGE_SORT, STAGE_EMIT, STAGE_REFIT, STAGE_TOTAL = 0, 1, 2, 3, 4
+STAGE_MORTON, STAGE_SORT, STAGE_EMIT, STAGE_REFIT, STAGE_TOTAL, STAGE_TRACE_TREE = 0, 1, 2, 3, 4, 5
+TRACE_TREE_AUTO, TRACE_TREE_ALWAYS, TRACE_TREE_NEVER = 0, 1, 2
 
 
 def _ptr(a):
@@ -294,6 +295,15 @@ class AccelerationStructureManager:
 
     def set_trace_mode(self, mode):
         check(self._lib.clrt_accel_set_trace_mode(self.handle, mode))
+
+    def set_trace_tree(self, policy):                   # 0 auto, 1 always, 2 never; effective at the next construct()
+        check(self._lib.clrt_accel_set_trace_tree(self.handle, policy))
+
+    def has_trace_tree(self):
+        import ctypes
+        v = ctypes.c_int(0)
+        check(self._lib.clrt_accel_has_trace_tree(self.handle, ctypes.byref(v)))
+        return bool(v.value)
 
     def enable_stage_timing(self, on=True):
         check(self._lib.clrt_accel_enable_stage_timing(self.handle, int(on)))

@@ -43,6 +43,8 @@ extern "C" int clrt_accel_destroy(clrt_accel* a) {
   if (a->d_pairs) cudaFree(a->d_pairs);
   if (a->d_counters) cudaFree(a->d_counters);
   if (a->d_tnodes) cudaFree(a->d_tnodes);
+  if (a->d_refpos) cudaFree(a->d_refpos);
+  trace_tree_destroy(a);
   if (a->d_tris_sorted) cudaFree(a->d_tris_sorted);
   if (a->d_leafbox_sorted) cudaFree(a->d_leafbox_sorted);
   if (a->d_contacts) cudaFree(a->d_contacts);

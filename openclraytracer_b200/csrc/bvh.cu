@@ -134,7 +134,7 @@ __device__ __forceinline__ int2 determine_range(const uint2* __restrict__ list, 
 __global__ void __launch_bounds__(256)
 karras_emit_kernel(const clrt_uint2* __restrict__ pairs_, uint32_t n, clrt_bvh_node* __restrict__ nodes,
                    const clrt_triangle* __restrict__ tris, clrt_triangle* __restrict__ tris_sorted, float4* __restrict__ leafbox_sorted,
-                   TraceNode* __restrict__ tnodes, uint32_t* __restrict__ max_run) {
+                   TraceNode* __restrict__ tnodes, uint32_t* __restrict__ max_run, uint32_t* __restrict__ refpos) {
   const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= n) return;
   const uint2* list = reinterpret_cast<const uint2*>(pairs_);
@@ -143,6 +143,8 @@ karras_emit_kernel(const clrt_uint2* __restrict__ pairs_, uint32_t n, clrt_bvh_n
     const float4* src = reinterpret_cast<const float4*>(tris + leaf);
     float4 a = __ldg(src), b = __ldg(src + 1), c = __ldg(src + 2);
     b.w = __uint_as_float(leaf);
+    c.w = __uint_as_float(idx);                 // position in the reference's sorted order: the tie-break key of the traversal
+    refpos[leaf] = idx;
     float4* dst = reinterpret_cast<float4*>(tris_sorted + idx);
     dst[0] = a; dst[1] = b; dst[2] = c;
     const float4* lb = reinterpret_cast<const float4*>(nodes + leaf) + 1;      // leaf box written by morton_leaves_kernel
@@ -215,14 +217,16 @@ int bvh_init_frame(clrt_accel* a) {
   const uint32_t n = a->scene->n_tris;
   a->n = n;
   a->built = false;
+  a->tt_built = false;
   a->pairs_items = pow2ceil_u32(n ? n : 1);                  // the reference pads to 2^k for its bitonic sort (BVHManager.cpp:129-131)
   const size_t nodes_bytes = (size_t)(n ? 2 * (size_t)n - 1 : 1) * sizeof(clrt_bvh_node);
   if (nodes_bytes > a->nodes_cap || (size_t)a->pairs_items * 8 > a->pairs_cap || (size_t)n * 4 > a->counters_cap ||
-      (size_t)n * sizeof(TraceNode) > a->tnodes_cap || (size_t)n * sizeof(clrt_triangle) > a->tris_sorted_cap || (size_t)n * 32 > a->leafbox_cap)
+      (size_t)n * 4 > a->refpos_cap || (size_t)n * sizeof(TraceNode) > a->tnodes_cap || (size_t)n * sizeof(clrt_triangle) > a->tris_sorted_cap || (size_t)n * 32 > a->leafbox_cap)
     CLRT_CUDA(cudaStreamSynchronize(ctx->stream));
   CLRT_TRY(clrt_grow((void**)&a->d_nodes, &a->nodes_cap, nodes_bytes));
   CLRT_TRY(clrt_grow((void**)&a->d_pairs, &a->pairs_cap, (size_t)a->pairs_items * 8));
   CLRT_TRY(clrt_grow((void**)&a->d_counters, &a->counters_cap, (size_t)(n ? n : 1) * 4));
+  CLRT_TRY(clrt_grow((void**)&a->d_refpos, &a->refpos_cap, (size_t)(n ? n : 1) * 4));
   CLRT_TRY(clrt_grow((void**)&a->d_tnodes, &a->tnodes_cap, (size_t)(n ? n : 1) * sizeof(TraceNode)));
   CLRT_TRY(clrt_grow((void**)&a->d_tris_sorted, &a->tris_sorted_cap, (size_t)(n ? n : 1) * sizeof(clrt_triangle)));
   CLRT_TRY(clrt_grow((void**)&a->d_leafbox_sorted, &a->leafbox_cap, (size_t)(n ? n : 1) * 32));
@@ -252,7 +256,7 @@ int bvh_construct(clrt_accel* a) {
   if (tm) CLRT_CUDA(cudaEventRecord(a->ev[2], s));
   CLRT_CUDA(cudaMemsetAsync(a->d_tile_counter + 12, 0, 4, s));
   if (n) {
-    karras_emit_kernel<<<(n + 255) / 256, 256, 0, s>>>(a->d_pairs, n, a->d_nodes, a->scene->d_tris, a->d_tris_sorted, a->d_leafbox_sorted, a->d_tnodes, a->d_tile_counter + 12);
+    karras_emit_kernel<<<(n + 255) / 256, 256, 0, s>>>(a->d_pairs, n, a->d_nodes, a->scene->d_tris, a->d_tris_sorted, a->d_leafbox_sorted, a->d_tnodes, a->d_tile_counter + 12, a->d_refpos);
     CLRT_CHECK_LAUNCH();
   }
   if (tm) CLRT_CUDA(cudaEventRecord(a->ev[3], s));
@@ -274,6 +278,7 @@ int bvh_construct(clrt_accel* a) {
     CLRT_CUDA(cudaStreamSynchronize(s));
     a->max_run = *(uint32_t*)pin;
   }
+  CLRT_TRY(trace_tree_build(a));
   a->built = true;
   return 0;
 }

@@ -90,9 +90,18 @@ struct clrt_accel {
   TraceNode* d_tnodes = nullptr;  size_t tnodes_cap = 0;      // (N-1) x 64 B
   clrt_triangle* d_tris_sorted = nullptr; size_t tris_sorted_cap = 0;   // N x 48 B, sorted-leaf order, v1.w = triangle id
   float4* d_leafbox_sorted = nullptr; size_t leafbox_cap = 0;           // N x 32 B: leaf boxes (min, max) in sorted-leaf order
+  uint32_t* d_refpos = nullptr; size_t refpos_cap = 0;                  // N x 4 B: triangle -> position in the reference's sorted order
   uint32_t pairs_items = 0;
-  uint32_t max_run = 0;           // longest collapsed equal-key run (read back after construct; selects the traversal variant)
+  uint32_t max_run = 0;           // longest collapsed equal-key run (read back after construct; decides whether a trace tree is built)
   bool built = false;
+  // --- separate trace tree (trace_tree.cu): built by construct() when the reference tree is a poor traversal structure ---
+  int tt_policy = 0;              // 0 auto, 1 always, 2 never
+  bool tt_built = false;
+  TraceNode* d_tt_nodes = nullptr; size_t tt_nodes_cap = 0;             // (N-1) x 64 B
+  clrt_triangle* d_tt_tris = nullptr; size_t tt_tris_cap = 0;           // N x 48 B in trace-tree order; v1.w = triangle id, v2.w = reference sorted position
+  float4* d_tt_leafbox = nullptr; size_t tt_leafbox_cap = 0;            // unused by the trace tree's kernels (no runs); kept for a uniform kernel signature
+  clrt_uint2* d_tt_pairs = nullptr; size_t tt_pairs_cap = 0;            // N x 8 B (fine Morton code, triangle)
+  uint32_t* d_tt_parent = nullptr; size_t tt_parent_cap = 0;            // (2N) x 4 B: parent link | side bit
   // --- primary contacts / frame scratch ---
   clrt_contact* d_contacts = nullptr; size_t contacts_cap = 0;
   void* d_frame_scratch = nullptr; size_t frame_scratch_cap = 0;
@@ -107,6 +116,8 @@ struct clrt_accel {
 int clrt_grow(void** p, size_t* cap, size_t bytes);               // cudaFree+cudaMalloc when bytes > *cap
 int bvh_init_frame(clrt_accel* a);
 int bvh_construct(clrt_accel* a);
+int trace_tree_build(clrt_accel* a);                              // trace_tree.cu
+void trace_tree_destroy(clrt_accel* a);
 // nranks == 0: whole frame with raster-ordered output; otherwise stripe `rank` of `nranks` in stripe order
 int bvh_trace_primary(clrt_accel* a, const clrt_camera& cam, clrt_contact* out, uint32_t rank, uint32_t nranks);
 int bvh_trace_rays(clrt_accel* a, const clrt_ray* rays, clrt_contact* out, uint32_t n);

@@ -31,7 +31,7 @@ constexpr uint32_t SENTINEL = 0xFFFFFFFFu;
 // leaves in ascending sorted position and accepts `0 < t < best` (BVH.h:392), so among exact ties its winner is the
 // smallest position: ORDERED == false relies on visiting order (REFERENCE_ORDER policy), ORDERED == true applies the
 // same rule explicitly so that a reordered traversal returns the same triangle.
-struct Hit { float t; uint32_t tri; float cull; };
+struct Hit { float t; uint32_t tri; float cull; uint32_t ref; };
 constexpr float CULL_SLACK = 1.00001f;   // boxes are culled against best_t * (1 + 1e-5): slab-t vs triangle-t rounding never hides a tie
 
 template <bool ORDERED>
@@ -39,7 +39,10 @@ __device__ __forceinline__ void test_triangle(const clrt_triangle* __restrict__ 
   const float4* p = reinterpret_cast<const float4*>(tris + id);
   const float4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
   const float t = triangle_intersect(v3(a.x, a.y, a.z), v3(b.x, b.y, b.z), v3(c.x, c.y, c.z), o, d);
-  if (t > 0.0f && (t < h.t || (ORDERED && t == h.t && h.tri != SENTINEL && id < h.tri))) { h.t = t; h.tri = id; h.cull = t * CULL_SLACK; }
+  // c.w = the leaf's position in the REFERENCE's sorted order (== id when the traversal tree is the reference tree)
+  if (t > 0.0f && (t < h.t || (ORDERED && t == h.t && h.tri != SENTINEL && __float_as_uint(c.w) < h.ref))) {
+    h.t = t; h.tri = id; h.cull = t * CULL_SLACK; h.ref = __float_as_uint(c.w);
+  }
 }
 
 struct Stats { uint32_t rays, inner, tris, lboxes; };
@@ -50,7 +53,6 @@ struct Stats { uint32_t rays, inner, tris, lboxes; };
 // box and every enclosing suffix box are valid; suffix boxes contain the leaf boxes and the slab test is monotone under
 // box inclusion (also in floating point), hence "leaf box valid" alone selects the same leaves.  Boxes and triangles of
 // a run are contiguous in memory (sorted order) and independent of each other - no pointer chasing.
-constexpr uint32_t COOP_MIN = 6;       // runs at least this long are processed by the whole warp
 
 template <bool STATS>
 __device__ __forceinline__ void test_run_element(const clrt_triangle* __restrict__ tris, const float4* __restrict__ leafbox,
@@ -60,31 +62,6 @@ __device__ __forceinline__ void test_run_element(const clrt_triangle* __restrict
   const float tb = aabb_intersect(lo.x, lo.y, lo.z, hi.x, hi.y, hi.z, o, inv);
   const bool valid = tb > 0.0f || point_inside(lo.x, lo.y, lo.z, hi.x, hi.y, hi.z, o);
   if (valid && !(tb > h.cull)) { test_triangle<true>(tris, p, o, d, h); if (STATS) st.tris++; }
-}
-
-// Warp-cooperative run: every lane of the warp calls this; lane `leader` owns the ray and the run.  Lanes split the run's
-// elements, test them against the LEADER's ray with the same arithmetic a single thread would use, and the best
-// candidate is reduced with the reference's tie rule (equal t -> smaller sorted position).  Returns the merged hit in
-// the leader's `h` (other lanes' `h` are untouched).
-template <bool STATS>
-__device__ __forceinline__ void coop_run(const clrt_triangle* __restrict__ tris, const float4* __restrict__ leafbox, int leader,
-                                         uint32_t start, uint32_t count, Vec3 o, Vec3 d, Vec3 inv, Hit& h, Stats& st) {
-  const int lane = threadIdx.x & 31;
-  const unsigned FULL = 0xffffffffu;
-  start = __shfl_sync(FULL, start, leader); count = __shfl_sync(FULL, count, leader);
-  Vec3 lo_, ld_, li_;
-  lo_.x = __shfl_sync(FULL, o.x, leader); lo_.y = __shfl_sync(FULL, o.y, leader); lo_.z = __shfl_sync(FULL, o.z, leader);
-  ld_.x = __shfl_sync(FULL, d.x, leader); ld_.y = __shfl_sync(FULL, d.y, leader); ld_.z = __shfl_sync(FULL, d.z, leader);
-  li_.x = __shfl_sync(FULL, inv.x, leader); li_.y = __shfl_sync(FULL, inv.y, leader); li_.z = __shfl_sync(FULL, inv.z, leader);
-  Hit b;
-  b.t = __shfl_sync(FULL, h.t, leader); b.tri = __shfl_sync(FULL, h.tri, leader); b.cull = __shfl_sync(FULL, h.cull, leader);
-  for (uint32_t p = start + lane; p < start + count; p += 32) test_run_element<STATS>(tris, leafbox, p, lo_, ld_, li_, b, st);
-#pragma unroll
-  for (int s = 16; s > 0; s >>= 1) {
-    const float ot = __shfl_xor_sync(FULL, b.t, s); const uint32_t op = __shfl_xor_sync(FULL, b.tri, s);
-    if (ot < b.t || (ot == b.t && op < b.tri)) { b.t = ot; b.tri = op; }
-  }
-  if (lane == leader) { h.t = b.t; h.tri = b.tri; h.cull = b.t == RT_FLT_MAX ? RT_FLT_MAX : b.t * CULL_SLACK; }
 }
 
 // ---- REFERENCE_ORDER policy: the reference's visiting order, one ray per thread ---------------------------------------
@@ -144,13 +121,12 @@ __device__ __forceinline__ void lane_begin(Lane& L, const clrt_triangle* __restr
   if (n == 1) { test_triangle<false>(tris, 0, o, d, L.h); if (STATS) st.tris++; }     // the reference reads past its node buffer here
 }
 
-// One inner-node visit.  Leaf children are intersected at once; equal-key runs shorter than COOP_MIN (or all runs when
-// !COOP) inline, longer ones are handed to the warp through (rs, rc).  Near child first, far child on the stack, children
-// beyond best_t * (1 + 1e-5) culled.
-template <bool STATS, bool ANYHIT, bool COOP>
+// One inner-node visit.  Leaf children are intersected at once; short equal-key runs of the reference tree inline (a
+// structure with long runs or collapsed axes is traversed through the separate trace tree of trace_tree.cu, which has
+// none).  Near child first, far child on the stack, children beyond best_t * (1 + 1e-5) culled.
+template <bool STATS, bool ANYHIT>
 __device__ __forceinline__ void lane_step(Lane& L, const TraceNode* __restrict__ tnodes, const clrt_triangle* __restrict__ tris,
-                                          const float4* __restrict__ leafbox, uint32_t n, Stats& st, uint32_t* __restrict__ stack,
-                                          uint32_t& rs0, uint32_t& rc0, uint32_t& rs1, uint32_t& rc1) {
+                                          const float4* __restrict__ leafbox, uint32_t n, Stats& st, uint32_t* __restrict__ stack) {
   if (STATS) { st.inner++; L.visits++; }
   const Vec3 o = L.o, d = L.d, inv = L.inv;
   const float4* p = reinterpret_cast<const float4*>(tnodes + (L.cur - n));
@@ -163,14 +139,12 @@ __device__ __forceinline__ void lane_step(Lane& L, const TraceNode* __restrict__
   const uint32_t cA = q3.x, cB = q3.y, cntA = q3.w & 0xFFFFu, cntB = q3.w >> 16;
   if (aValid && cA < n) { test_triangle<true>(tris, cA, o, d, L.h); if (STATS) st.tris++; aValid = false; }
   else if (aValid && cntA) {
-    if (COOP && cntA >= COOP_MIN) { rs0 = q3.z; rc0 = cntA; }
-    else for (uint32_t k = 0; k < cntA; k++) test_run_element<STATS>(tris, leafbox, q3.z + k, o, d, inv, L.h, st);
+    for (uint32_t k = 0; k < cntA; k++) test_run_element<STATS>(tris, leafbox, q3.z + k, o, d, inv, L.h, st);
     aValid = false;
   }
   if (bValid && !(tB > L.h.cull) && cB < n) { test_triangle<true>(tris, cB, o, d, L.h); if (STATS) st.tris++; bValid = false; }
   else if (bValid && cntB) {
-    if (COOP && cntB >= COOP_MIN) { if (rc0) { rs1 = cB - n; rc1 = cntB; } else { rs0 = cB - n; rc0 = cntB; } }
-    else if (!(tB > L.h.cull)) for (uint32_t k = 0; k < cntB; k++) test_run_element<STATS>(tris, leafbox, cB - n + k, o, d, inv, L.h, st);
+    if (!(tB > L.h.cull)) for (uint32_t k = 0; k < cntB; k++) test_run_element<STATS>(tris, leafbox, cB - n + k, o, d, inv, L.h, st);
     bValid = false;
   }
   aValid = aValid && !(tA > L.h.cull);
@@ -183,15 +157,14 @@ __device__ __forceinline__ void lane_step(Lane& L, const TraceNode* __restrict__
   else if (aValid) L.cur = cA;
   else if (bValid) L.cur = cB;
   else L.cur = L.sp > 0 ? stack[--L.sp] : SENTINEL;
-  if (ANYHIT && !COOP && L.h.tri != SENTINEL) L.cur = SENTINEL;
+  if (ANYHIT && L.h.tri != SENTINEL) L.cur = SENTINEL;
 }
 
 // Persistent-warp driver with lane refill.  A "unit" is a pixel slot / ray / contact; units come from one global atomic
 // counter in warp-private batches of BATCH consecutive indices (work stealing between all warps of the GPU).  A lane
 // whose unit is complete goes idle; when REFILL_MIN lanes are idle the warp hands them the next units of its batch, so
 // lanes do not wait for the slowest ray of a packet (rays of one warp differ several-fold in node visits).  Between
-// refill checks every lane runs WINDOW traversal steps on its own; with COOP the steps are warp-synchronous and each is
-// followed by the cooperative phase for long equal-key runs.
+// refill checks every lane runs WINDOW traversal steps on its own.
 //   Job::start(unit, L)  -> true: a ray is ready in L;  false: the unit completed without tracing (output written)
 //   Job::finish(L)       -> true: the unit continues with another ray (L re-initialised); false: unit complete
 #ifndef CLRT_WINDOW
@@ -207,7 +180,7 @@ constexpr int WINDOW = CLRT_WINDOW;
 constexpr int REFILL_MIN = CLRT_REFILL_MIN;
 constexpr uint32_t BATCH = CLRT_BATCH;
 
-template <class Job, bool STATS, bool ANYHIT, bool COOP>
+template <class Job, bool STATS, bool ANYHIT>
 __device__ __forceinline__ void run_jobs(Job& job, const TraceNode* __restrict__ tnodes, const clrt_triangle* __restrict__ tris,
                                          const float4* __restrict__ leafbox, uint32_t n, uint32_t total, uint32_t* __restrict__ counter, Stats& st) {
   const unsigned FULL = 0xffffffffu;
@@ -241,20 +214,8 @@ __device__ __forceinline__ void run_jobs(Job& job, const TraceNode* __restrict__
       if (idle == FULL) break;                                  // nothing left anywhere
     }
 #pragma unroll 1
-    for (int k = 0; k < WINDOW; k++) {
-      uint32_t rs0 = 0, rc0 = 0, rs1 = 0, rc1 = 0;
-      if (busy && L.cur != SENTINEL) lane_step<STATS, ANYHIT, COOP>(L, tnodes, tris, leafbox, n, st, stack, rs0, rc0, rs1, rc1);
-      if (COOP) {
-        unsigned pend = __ballot_sync(FULL, rc0 != 0);
-        while (pend) {
-          const int leader = __ffs(pend) - 1;
-          coop_run<STATS>(tris, leafbox, leader, rs0, rc0, L.o, L.d, L.inv, L.h, st);
-          if (lane == leader) { rs0 = rs1; rc0 = rc1; rc1 = 0; }
-          pend = __ballot_sync(FULL, rc0 != 0);
-        }
-        if (ANYHIT && busy && L.h.tri != SENTINEL) L.cur = SENTINEL;
-      }
-    }
+    for (int k = 0; k < WINDOW; k++)
+      if (busy && L.cur != SENTINEL) lane_step<STATS, ANYHIT>(L, tnodes, tris, leafbox, n, st, stack);
   }
 }
 
@@ -385,7 +346,7 @@ struct ShadowJob {
 };
 
 // ---- kernels ---------------------------------------------------------------------------------------------------------------
-template <int MODE, bool STATS>      // MODE 0: REFERENCE_ORDER, 1: FAST, 2: FAST with cooperative runs
+template <int MODE, bool STATS>      // MODE 0: REFERENCE_ORDER, 1: FAST
 __global__ void __launch_bounds__(TRACE_THREADS)
 trace_primary_kernel(const clrt_camera cam, const TraceNode* __restrict__ tnodes,
                      const clrt_triangle* __restrict__ tris, const float4* __restrict__ leafbox, uint32_t n, clrt_contact* __restrict__ out,
@@ -413,7 +374,7 @@ trace_primary_kernel(const clrt_camera cam, const TraceNode* __restrict__ tnodes
     }
   } else {
     PrimaryJob<STATS> job{cam, g, rank, nranks, raster, tris, n, out, st, 0u, 0u};
-    run_jobs<PrimaryJob<STATS>, STATS, false, MODE == 2>(job, tnodes, tris, leafbox, n, total, counter, st);
+    run_jobs<PrimaryJob<STATS>, STATS, false>(job, tnodes, tris, leafbox, n, total, counter, st);
   }
   if (STATS) flush_stats(st, stats);
 }
@@ -443,12 +404,12 @@ trace_rays_kernel(const clrt_ray* __restrict__ rays, uint32_t count, const Trace
     }
   } else {
     RaysJob<STATS> job{rays, tris, n, out, st, 0u};
-    run_jobs<RaysJob<STATS>, STATS, false, MODE == 2>(job, tnodes, tris, leafbox, n, count, counter, st);
+    run_jobs<RaysJob<STATS>, STATS, false>(job, tnodes, tris, leafbox, n, count, counter, st);
   }
   if (STATS) flush_stats(st, stats);
 }
 
-template <bool STATS, bool COOP>
+template <bool STATS>
 __global__ void __launch_bounds__(TRACE_THREADS)
 shadow_shade_kernel(const clrt_camera cam, const clrt_contact* __restrict__ contacts, uint32_t count,
                     const clrt_light* __restrict__ lights, uint32_t n_lights, const clrt_material* __restrict__ materials, uint32_t n_materials,
@@ -458,7 +419,7 @@ shadow_shade_kernel(const clrt_camera cam, const clrt_contact* __restrict__ cont
   Stats st; st.rays = st.inner = st.tris = st.lboxes = 0;
   uint32_t live_rays = 0;
   ShadowJob<STATS> job{cam, contacts, lights, n_lights, materials, n_materials, tris, n, rgba8, st, live_rays};
-  run_jobs<ShadowJob<STATS>, STATS, true, COOP>(job, tnodes, tris, leafbox, n, count, counter, st);
+  run_jobs<ShadowJob<STATS>, STATS, true>(job, tnodes, tris, leafbox, n, count, counter, st);
   if (ray_counter) {
 #pragma unroll
     for (int dd = 16; dd > 0; dd >>= 1) live_rays += __shfl_xor_sync(0xffffffffu, live_rays, dd);
@@ -478,12 +439,21 @@ int persistent_grid(clrt_ctx* ctx, K kernel, int threads, unsigned* grid) {
 
 } // namespace
 
+// The structure a launch traverses: REFERENCE_ORDER always walks the reference topology; FAST walks the separate trace tree
+// (trace_tree.cu) when construct() built one, else the reference tree.
+struct TraceView { const TraceNode* tnodes; const clrt_triangle* tris; const float4* leafbox; };
+static TraceView trace_view(const clrt_accel* a, bool fast) {
+  if (fast && a->tt_built) return TraceView{a->d_tt_nodes, a->d_tt_tris, a->d_tt_leafbox};
+  return TraceView{a->d_tnodes, a->d_tris_sorted, a->d_leafbox_sorted};
+}
+
 template <int M, bool S>
 static int launch_primary(clrt_accel* a, const clrt_camera& cam, clrt_contact* out, uint32_t rank, uint32_t nranks, int raster, uint32_t packets) {
   unsigned grid = 0;
   CLRT_TRY(persistent_grid(a->ctx, trace_primary_kernel<M, S>, TRACE_THREADS, &grid));
   grid = min(grid, (packets + 3) / 4);
-  trace_primary_kernel<M, S><<<grid, TRACE_THREADS, 0, a->ctx->stream>>>(cam, a->d_tnodes, a->d_tris_sorted, a->d_leafbox_sorted, a->n, out, rank, nranks, raster,
+  const TraceView v = trace_view(a, M != 0);
+  trace_primary_kernel<M, S><<<grid, TRACE_THREADS, 0, a->ctx->stream>>>(cam, v.tnodes, v.tris, v.leafbox, a->n, out, rank, nranks, raster,
                                                                         a->d_tile_counter, (unsigned long long*)(a->d_tile_counter + 4));
   CLRT_CHECK_LAUNCH();
   return 0;
@@ -493,16 +463,13 @@ static int launch_rays(clrt_accel* a, const clrt_ray* rays, clrt_contact* out, u
   unsigned grid = 0;
   CLRT_TRY(persistent_grid(a->ctx, trace_rays_kernel<M, S>, TRACE_THREADS, &grid));
   grid = min(grid, (packets + 3) / 4);
-  trace_rays_kernel<M, S><<<grid, TRACE_THREADS, 0, a->ctx->stream>>>(rays, count, a->d_tnodes, a->d_tris_sorted, a->d_leafbox_sorted, a->n, out,
+  const TraceView v = trace_view(a, M != 0);
+  trace_rays_kernel<M, S><<<grid, TRACE_THREADS, 0, a->ctx->stream>>>(rays, count, v.tnodes, v.tris, v.leafbox, a->n, out,
                                                                      a->d_tile_counter, (unsigned long long*)(a->d_tile_counter + 4));
   CLRT_CHECK_LAUNCH();
   return 0;
 }
-// 0: REFERENCE_ORDER, 1: FAST, 2: FAST + cooperative runs (the structure holds runs of COOP_MIN or more equal keys)
-static int trace_mode_index(const clrt_accel* a) {
-  if (a->trace_mode == CLRT_TRACE_REFERENCE_ORDER) return 0;
-  return a->max_run >= COOP_MIN ? 2 : 1;
-}
+static int trace_mode_index(const clrt_accel* a) { return a->trace_mode == CLRT_TRACE_REFERENCE_ORDER ? 0 : 1; }
 
 int bvh_trace_primary(clrt_accel* a, const clrt_camera& cam, clrt_contact* out, uint32_t rank, uint32_t nranks) {
   const uint32_t resX = cam.resX, resY = cam.resY;
@@ -516,11 +483,9 @@ int bvh_trace_primary(clrt_accel* a, const clrt_camera& cam, clrt_contact* out, 
   CLRT_CUDA(cudaMemsetAsync(a->d_tile_counter, 0, 4, ctx->stream));
   const int m = trace_mode_index(a);
   if (a->stats) return m == 0 ? launch_primary<0, true>(a, cam, out, rank, nranks, raster, packets)
-                     : m == 1 ? launch_primary<1, true>(a, cam, out, rank, nranks, raster, packets)
-                              : launch_primary<2, true>(a, cam, out, rank, nranks, raster, packets);
+                              : launch_primary<1, true>(a, cam, out, rank, nranks, raster, packets);
   return m == 0 ? launch_primary<0, false>(a, cam, out, rank, nranks, raster, packets)
-       : m == 1 ? launch_primary<1, false>(a, cam, out, rank, nranks, raster, packets)
-                : launch_primary<2, false>(a, cam, out, rank, nranks, raster, packets);
+                : launch_primary<1, false>(a, cam, out, rank, nranks, raster, packets);
 }
 
 int bvh_trace_rays(clrt_accel* a, const clrt_ray* rays, clrt_contact* out, uint32_t count) {
@@ -530,21 +495,20 @@ int bvh_trace_rays(clrt_accel* a, const clrt_ray* rays, clrt_contact* out, uint3
   const uint32_t packets = (count + 31u) / 32u;
   CLRT_CUDA(cudaMemsetAsync(a->d_tile_counter, 0, 4, ctx->stream));
   const int m = trace_mode_index(a);
-  if (a->stats) return m == 0 ? launch_rays<0, true>(a, rays, out, count, packets) : m == 1 ? launch_rays<1, true>(a, rays, out, count, packets)
-                                                                                            : launch_rays<2, true>(a, rays, out, count, packets);
-  return m == 0 ? launch_rays<0, false>(a, rays, out, count, packets) : m == 1 ? launch_rays<1, false>(a, rays, out, count, packets)
-                                                                               : launch_rays<2, false>(a, rays, out, count, packets);
+  if (a->stats) return m == 0 ? launch_rays<0, true>(a, rays, out, count, packets) : launch_rays<1, true>(a, rays, out, count, packets);
+  return m == 0 ? launch_rays<0, false>(a, rays, out, count, packets) : launch_rays<1, false>(a, rays, out, count, packets);
 }
 
-template <bool S, bool C>
+template <bool S>
 static int launch_shadow_shade(clrt_accel* a, const clrt_camera& cam, const clrt_contact* contacts, uint32_t count, uint32_t* rgba8,
                                unsigned long long* d_ray_counter, uint32_t packets) {
   const clrt_scene* sc = a->scene;
   unsigned grid = 0;
-  CLRT_TRY(persistent_grid(a->ctx, shadow_shade_kernel<S, C>, TRACE_THREADS, &grid));
+  CLRT_TRY(persistent_grid(a->ctx, shadow_shade_kernel<S>, TRACE_THREADS, &grid));
   grid = min(grid, (packets + 3) / 4);
-  shadow_shade_kernel<S, C><<<grid, TRACE_THREADS, 0, a->ctx->stream>>>(cam, contacts, count, sc->d_lights, sc->n_lights, sc->d_materials, sc->n_materials,
-      a->d_tnodes, a->d_tris_sorted, a->d_leafbox_sorted, a->n, rgba8, a->d_tile_counter, d_ray_counter, (unsigned long long*)(a->d_tile_counter + 4));
+  const TraceView v = trace_view(a, true);
+  shadow_shade_kernel<S><<<grid, TRACE_THREADS, 0, a->ctx->stream>>>(cam, contacts, count, sc->d_lights, sc->n_lights, sc->d_materials, sc->n_materials,
+      v.tnodes, v.tris, v.leafbox, a->n, rgba8, a->d_tile_counter, d_ray_counter, (unsigned long long*)(a->d_tile_counter + 4));
   CLRT_CHECK_LAUNCH();
   return 0;
 }
@@ -558,9 +522,6 @@ int bvh_shadow_shade(clrt_accel* a, const clrt_camera& cam, const clrt_contact* 
   if (a->scene->n_lights + 1 > 32) CLRT_FAIL("fused shadow pass supports at most 31 scene lights");
   const uint32_t packets = (count + 31u) / 32u;
   CLRT_CUDA(cudaMemsetAsync(a->d_tile_counter, 0, 4, ctx->stream));
-  const bool coop = a->max_run >= COOP_MIN;
-  if (a->stats) return coop ? launch_shadow_shade<true, true>(a, cam, contacts, count, rgba8, d_ray_counter, packets)
-                            : launch_shadow_shade<true, false>(a, cam, contacts, count, rgba8, d_ray_counter, packets);
-  return coop ? launch_shadow_shade<false, true>(a, cam, contacts, count, rgba8, d_ray_counter, packets)
-              : launch_shadow_shade<false, false>(a, cam, contacts, count, rgba8, d_ray_counter, packets);
+  return a->stats ? launch_shadow_shade<true>(a, cam, contacts, count, rgba8, d_ray_counter, packets)
+                  : launch_shadow_shade<false>(a, cam, contacts, count, rgba8, d_ray_counter, packets);
 }

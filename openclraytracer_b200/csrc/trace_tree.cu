@@ -1,0 +1,197 @@
+// trace_tree.cu — the separate traversal hierarchy ("trace tree"; ours, the reference has none).
+//
+// Why: the reference's Morton code is c/(max-min) WITHOUT subtracting min (BVH.h:112-114), so every
+// axis on which the scene box reaches below zero collapses to cell 0 for all negative centroids, and equal codes become
+// right-leaning chains (BVH.h:153-154,212-233, Q8).  On ClumsyDragon 20 % of the triangles sit in 174 runs of 32..211
+// equal keys whose boxes are slabs through the model: a ray that enters one tests every member.  The reference-layout
+// tree (bvh.cu) stays bit-exact — it is what construct() is specified to produce — but it is a poor thing to traverse.
+//
+// What: when the reference tree has long runs or collapsed axes, construct() also builds a plain LBVH over the SAME
+// triangles from a proper 30-bit Morton code ((c-min)/(max-min), 10 bits per axis) with the usual index tie-break for
+// equal codes (Karras 2012, section 4), so there are no chains.  The closest hit does not depend on the hierarchy; exact
+// ties are resolved by the triangle's position in the REFERENCE's sorted order (kept in v2.w), i.e. the reference's
+// winner (trace.cu).  Traversal kernels take it through the same TraceNode / clrt_triangle layouts.
+//
+// Kernels: tt_morton_kernel (48 B in, 8 B out per triangle) -> onesweep sort (sort.cu) -> tt_emit_kernel (Karras
+// ranges + gather of the triangles in tree order, ~110 B per triangle) -> tt_refit_kernel (bottom-up with arrival
+// counters; a child's box is stored INSIDE its parent's TraceNode, so no separate box array exists: 64 B per node).
+#include "common.cuh"
+#include "rtmath.cuh"
+
+namespace {
+
+__device__ __forceinline__ uint32_t tt_expand_bits(uint32_t v) {
+  v = (v * 0x00010001u) & 0xFF0000FFu;
+  v = (v * 0x00000101u) & 0x0F00F00Fu;
+  v = (v * 0x00000011u) & 0xC30C30C3u;
+  v = (v * 0x00000005u) & 0x49249249u;
+  return v;
+}
+__device__ __forceinline__ uint32_t tt_quantise(float c, float lo, float inv_len) {
+  const float q = (c - lo) * inv_len * 1024.0f;
+  return (uint32_t)fminf(fmaxf(q, 0.0f), 1023.0f);
+}
+
+__global__ void __launch_bounds__(256)
+tt_morton_kernel(const clrt_triangle* __restrict__ tris, uint32_t n, clrt_aabb bb, uint2* __restrict__ pairs) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float4* t = reinterpret_cast<const float4*>(tris + i);
+  const float4 a = __ldg(t), b = __ldg(t + 1), c = __ldg(t + 2);
+  const float lx = bb.bounds[1].x - bb.bounds[0].x, ly = bb.bounds[1].y - bb.bounds[0].y, lz = bb.bounds[1].z - bb.bounds[0].z;
+  const uint32_t qx = tt_quantise((a.x + b.x + c.x) * (1.0f / 3.0f), bb.bounds[0].x, lx > 0.0f ? 1.0f / lx : 0.0f);
+  const uint32_t qy = tt_quantise((a.y + b.y + c.y) * (1.0f / 3.0f), bb.bounds[0].y, ly > 0.0f ? 1.0f / ly : 0.0f);
+  const uint32_t qz = tt_quantise((a.z + b.z + c.z) * (1.0f / 3.0f), bb.bounds[0].z, lz > 0.0f ? 1.0f / lz : 0.0f);
+  pairs[i] = make_uint2(tt_expand_bits(qx) * 4 + tt_expand_bits(qy) * 2 + tt_expand_bits(qz), i);
+}
+
+// delta(i, j): length of the common prefix of the (code, position) keys; -1 outside the array (Karras 2012).
+__device__ __forceinline__ int tt_delta(const uint2* __restrict__ list, int n, uint32_t ki, int i, int j) {
+  if (j < 0 || j >= n) return -1;
+  const uint32_t kj = __ldg(&list[j].x);
+  return ki != kj ? __clz(ki ^ kj) : 32 + __clz((uint32_t)i ^ (uint32_t)j);
+}
+
+// One thread per sorted position p: gathers triangle + leaf box into tree order; threads p < n-1 also emit inner node p.
+// parent[] holds, for inner node i at [i] and leaf p at [n + p], (parent inner index << 1) | side (0 = child A, 1 = child B);
+// the root's entry is 0xFFFFFFFF.
+__global__ void __launch_bounds__(256)
+tt_emit_kernel(const uint2* __restrict__ list, uint32_t n_, const clrt_triangle* __restrict__ tris, const clrt_bvh_node* __restrict__ ref_nodes,
+               const uint32_t* __restrict__ refpos, clrt_triangle* __restrict__ tris_out, float4* __restrict__ leafbox_out,
+               TraceNode* __restrict__ tnodes, uint32_t* __restrict__ parent) {
+  const int n = (int)n_;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  {
+    const uint32_t leaf = __ldg(&list[i].y);
+    const float4* src = reinterpret_cast<const float4*>(tris + leaf);
+    float4 a = __ldg(src), b = __ldg(src + 1), c = __ldg(src + 2);
+    b.w = __uint_as_float(leaf);
+    c.w = __uint_as_float(__ldg(refpos + leaf));
+    float4* dst = reinterpret_cast<float4*>(tris_out + i);
+    dst[0] = a; dst[1] = b; dst[2] = c;
+    const float4* lb = reinterpret_cast<const float4*>(ref_nodes + leaf) + 1;      // leaf box of morton_leaves_kernel (reference arithmetic)
+    leafbox_out[2 * (size_t)i] = __ldg(lb); leafbox_out[2 * (size_t)i + 1] = __ldg(lb + 1);
+  }
+  if (i + 1 >= n) return;
+  const uint32_t ki = __ldg(&list[i].x);
+  const int d = tt_delta(list, n, ki, i, i + 1) - tt_delta(list, n, ki, i, i - 1) >= 0 ? 1 : -1;
+  const int dmin = tt_delta(list, n, ki, i, i - d);
+  int lmax = 2;
+  while (tt_delta(list, n, ki, i, i + lmax * d) > dmin) lmax <<= 1;
+  int l = 0;
+  for (int t = lmax >> 1; t >= 1; t >>= 1)
+    if (tt_delta(list, n, ki, i, i + (l + t) * d) > dmin) l += t;
+  const int j = i + l * d;
+  const int dnode = tt_delta(list, n, ki, i, j);
+  int s = 0;
+  for (int t = (l + 1) >> 1; ; t = (t + 1) >> 1) {
+    if (tt_delta(list, n, ki, i, i + (s + t) * d) > dnode) s += t;
+    if (t <= 1) break;
+  }
+  const int gamma = i + s * d + min(d, 0);
+  const int first = min(i, j), last = max(i, j);
+  const bool aLeaf = first == gamma, bLeaf = last == gamma + 1;
+  const uint32_t cA = aLeaf ? (uint32_t)gamma : (uint32_t)gamma + n_;
+  const uint32_t cB = bLeaf ? (uint32_t)gamma + 1u : (uint32_t)gamma + 1u + n_;
+  reinterpret_cast<uint4*>(tnodes + i)[3] = make_uint4(cA, cB, 0u, 0u);        // no runs in this tree
+  parent[aLeaf ? n_ + (uint32_t)gamma : (uint32_t)gamma] = ((uint32_t)i << 1);
+  parent[bLeaf ? n_ + (uint32_t)gamma + 1u : (uint32_t)gamma + 1u] = ((uint32_t)i << 1) | 1u;
+  if (i == 0) parent[0] = 0xFFFFFFFFu;
+}
+
+// One thread per leaf: writes its box into its parent's TraceNode slot, then climbs; the second thread to arrive at a node
+// reads the sibling box from the same TraceNode (written before the first arrival's atomic), merges and goes on.
+__device__ __forceinline__ void tt_store_child_box(TraceNode* node, uint32_t side, float4 lo, float4 hi) {
+  float* f = reinterpret_cast<float*>(node);
+  if (side == 0) { __stcg(f + 0, lo.x); __stcg(f + 1, lo.y); __stcg(f + 2, lo.z); __stcg(f + 3, hi.x); __stcg(f + 4, hi.y); __stcg(f + 5, hi.z); }
+  else           { __stcg(f + 6, lo.x); __stcg(f + 7, lo.y); __stcg(f + 8, lo.z); __stcg(f + 9, hi.x); __stcg(f + 10, hi.y); __stcg(f + 11, hi.z); }
+}
+__global__ void __launch_bounds__(256)
+tt_refit_kernel(const float4* __restrict__ leafbox, const uint32_t* __restrict__ parent, uint32_t* __restrict__ counters, uint32_t n,
+                TraceNode* __restrict__ tnodes) {
+  const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= n) return;
+  float4 lo = __ldg(leafbox + 2 * (size_t)p), hi = __ldg(leafbox + 2 * (size_t)p + 1);
+  uint32_t link = __ldg(parent + n + p);
+  while (link != 0xFFFFFFFFu) {
+    const uint32_t node = link >> 1, side = link & 1u;
+    tt_store_child_box(tnodes + node, side, lo, hi);
+    __threadfence();
+    if (atomicAdd(counters + node, 1u) == 0) return;          // the sibling subtree is not done yet
+    __threadfence();
+    const float* f = reinterpret_cast<const float*>(tnodes + node) + (side ? 0 : 6);     // the sibling's box
+    const float sx0 = __ldcg(f), sy0 = __ldcg(f + 1), sz0 = __ldcg(f + 2), sx1 = __ldcg(f + 3), sy1 = __ldcg(f + 4), sz1 = __ldcg(f + 5);
+    lo.x = fminf(lo.x, sx0); lo.y = fminf(lo.y, sy0); lo.z = fminf(lo.z, sz0);
+    hi.x = fmaxf(hi.x, sx1); hi.y = fmaxf(hi.y, sy1); hi.z = fmaxf(hi.z, sz1);
+    link = __ldg(parent + node);
+  }
+}
+
+} // namespace
+
+void trace_tree_destroy(clrt_accel* a) {
+  if (a->d_tt_nodes) cudaFree(a->d_tt_nodes);
+  if (a->d_tt_tris) cudaFree(a->d_tt_tris);
+  if (a->d_tt_leafbox) cudaFree(a->d_tt_leafbox);
+  if (a->d_tt_pairs) cudaFree(a->d_tt_pairs);
+  if (a->d_tt_parent) cudaFree(a->d_tt_parent);
+  a->d_tt_nodes = nullptr; a->d_tt_tris = nullptr; a->d_tt_leafbox = nullptr; a->d_tt_pairs = nullptr; a->d_tt_parent = nullptr;
+}
+
+// Called at the end of bvh_construct (a->max_run is known).  Auto policy: build when the reference tree holds an equal-key
+// run of TT_RUN_MIN or more, or when the scene box reaches more than one Morton cell below zero on some axis (collapsed axis, Q6).
+constexpr uint32_t TT_RUN_MIN = 6;
+int trace_tree_build(clrt_accel* a) {
+  clrt_ctx* ctx = a->ctx;
+  const uint32_t n = a->n;
+  a->tt_built = false;
+  a->stage_ms[CLRT_STAGE_TRACE_TREE] = 0.0f;
+  const clrt_aabb bb = a->scene->header.modelsBoundingBox;
+  // an axis collapses when more than one Morton cell (1/1024 of the extent) of the scene box lies below zero
+  auto below = [](float lo, float hi) { return lo < 0.0f && -lo * 1024.0f > (hi - lo); };
+  const bool collapsed = below(bb.bounds[0].x, bb.bounds[1].x) || below(bb.bounds[0].y, bb.bounds[1].y) || below(bb.bounds[0].z, bb.bounds[1].z);
+  const bool want = a->tt_policy == 1 || (a->tt_policy == 0 && (a->max_run >= TT_RUN_MIN || collapsed));
+  if (!want || n < 2) return 0;
+  cudaStream_t s = ctx->stream;
+  if ((size_t)n * sizeof(TraceNode) > a->tt_nodes_cap || (size_t)n * sizeof(clrt_triangle) > a->tt_tris_cap || (size_t)n * 32 > a->tt_leafbox_cap ||
+      (size_t)n * 8 > a->tt_pairs_cap || (size_t)n * 8 > a->tt_parent_cap)
+    CLRT_CUDA(cudaStreamSynchronize(s));
+  CLRT_TRY(clrt_grow((void**)&a->d_tt_nodes, &a->tt_nodes_cap, (size_t)n * sizeof(TraceNode)));
+  CLRT_TRY(clrt_grow((void**)&a->d_tt_tris, &a->tt_tris_cap, (size_t)n * sizeof(clrt_triangle)));
+  CLRT_TRY(clrt_grow((void**)&a->d_tt_leafbox, &a->tt_leafbox_cap, (size_t)n * 32));
+  CLRT_TRY(clrt_grow((void**)&a->d_tt_pairs, &a->tt_pairs_cap, (size_t)n * 8));
+  CLRT_TRY(clrt_grow((void**)&a->d_tt_parent, &a->tt_parent_cap, (size_t)n * 8));
+  const bool tm = a->timing;
+  if (tm) CLRT_CUDA(cudaEventRecord(a->ev[5], s));
+  const unsigned grid = (n + 255) / 256;
+  tt_morton_kernel<<<grid, 256, 0, s>>>(a->scene->d_tris, n, bb, reinterpret_cast<uint2*>(a->d_tt_pairs));
+  CLRT_CHECK_LAUNCH();
+  CLRT_TRY(sort_pairs_radix(ctx, a->d_tt_pairs, n, 30));
+  CLRT_CUDA(cudaMemsetAsync(a->d_counters, 0, (size_t)n * 4, s));              // the reference refit is done with them
+  tt_emit_kernel<<<grid, 256, 0, s>>>(reinterpret_cast<const uint2*>(a->d_tt_pairs), n, a->scene->d_tris, a->d_nodes, a->d_refpos,
+                                      a->d_tt_tris, a->d_tt_leafbox, a->d_tt_nodes, a->d_tt_parent);
+  CLRT_CHECK_LAUNCH();
+  tt_refit_kernel<<<grid, 256, 0, s>>>(a->d_tt_leafbox, a->d_tt_parent, a->d_counters, n, a->d_tt_nodes);
+  CLRT_CHECK_LAUNCH();
+  if (tm) {
+    CLRT_CUDA(cudaEventRecord(a->ev[6], s));
+    CLRT_CUDA(cudaEventSynchronize(a->ev[6]));
+    CLRT_CUDA(cudaEventElapsedTime(&a->stage_ms[CLRT_STAGE_TRACE_TREE], a->ev[5], a->ev[6]));
+    a->stage_ms[CLRT_STAGE_TOTAL] += a->stage_ms[CLRT_STAGE_TRACE_TREE];
+  }
+  a->tt_built = true;
+  return 0;
+}
+
+extern "C" int clrt_accel_set_trace_tree(clrt_accel* a, int policy) {
+  if (!a) CLRT_FAIL("clrt_accel_set_trace_tree: NULL accel");
+  if (policy < 0 || policy > 2) CLRT_FAIL("clrt_accel_set_trace_tree: policy %d (0 auto, 1 always, 2 never)", policy);
+  a->tt_policy = policy;
+  return 0;
+}
+extern "C" int clrt_accel_has_trace_tree(clrt_accel* a, int* out) {
+  if (!a || !out) CLRT_FAIL("clrt_accel_has_trace_tree: NULL argument");
+  *out = a->tt_built ? 1 : 0;
+  return 0;
+}

@@ -295,3 +295,31 @@ def test_fused_shadow_pass_equals_three_kernel_pipeline(ctx, name):
     for x in (u8a, u8b, srays, scont):
         x.free()
     bvh.free(); scene.free()
+
+
+@pytest.mark.parametrize("name", ["cube", "gardenlight", "clumsydragon", "soup"])
+def test_trace_tree_returns_the_reference_tree_hits(ctx, O, name):
+    """The separate trace tree (trace_tree.cu) is another hierarchy over the same triangles: FAST contacts through it equal
+    FAST contacts through the reference tree — ids included (ties go to the reference's winner) — and both meet the oracle."""
+    buf = scenes.soup_scene(30_000, seed=7, tris_per_mesh=4096) if name == "soup" else scenes.load_bundled(name)
+    scene = api.Scene(buf); scene.loadToGPU(ctx)
+    bvh = api.BVHManager(ctx, scene); bvh.initialize()
+    b = O.bvh_build(buf)
+    cam = api.demo_camera(buf, 400, 300)
+    want = O.bvh_trace_primary(cam, b)
+    got = {}
+    for policy in (api.TRACE_TREE_NEVER, api.TRACE_TREE_ALWAYS, api.TRACE_TREE_AUTO):
+        bvh.set_trace_tree(policy)
+        bvh.initializeFrame(); bvh.construct()
+        if policy != api.TRACE_TREE_AUTO:
+            assert bvh.has_trace_tree() == (policy == api.TRACE_TREE_ALWAYS and scene.triangle_count() >= 2)
+        assert np.array_equal(bvh.export_pairs(), b["pairs"])            # the reference-layout build is untouched
+        bvh.set_trace_mode(api.TRACE_FAST)
+        bvh.generateContacts(cam)
+        got[policy] = bvh.download_primary_contacts()
+        compare_fast(got[policy], want, b["tris"])
+    a, c = got[api.TRACE_TREE_NEVER], got[api.TRACE_TREE_ALWAYS]
+    assert np.array_equal(a["pad"][:, 0], c["pad"][:, 0]) and np.array_equal(a["nd"], c["nd"])
+    if name == "clumsydragon":
+        assert bvh.has_trace_tree()          # auto: long equal-key runs + a scene box below zero
+    bvh.free(); scene.free()
