@@ -186,6 +186,10 @@ int clrt_render_stripe(clrt_accel* accel, const clrt_camera* h_camera, int shado
  * forces the three-call pipeline (clrt_generate_shadow_rays -> clrt_trace_rays -> clrt_shade); pixels are identical. */
 int clrt_accel_set_fused_shadows(clrt_accel* accel, int on);
 int clrt_frame_untile(clrt_ctx* ctx, const void* dptr_stripes, uint32_t resX, uint32_t resY, uint32_t nranks, void* dptr_raster_rgba8);
+/* The same on a caller-chosen cudaStream_t (the frame pipeline runs gather + untile + read-back of frame k on a second
+ * stream while frame k+1 is traced on the context's stream). */
+int clrt_frame_untile_on(clrt_ctx* ctx, void* stream, const void* dptr_stripes, uint32_t resX, uint32_t resY, uint32_t nranks,
+                         void* dptr_raster_rgba8);
 /* Whole frame with HOST output: upload camera, trace, (shadow,) shade, download RGBA8 raster — the e2e path. */
 int clrt_render_frame_host(clrt_accel* accel, const clrt_camera* h_camera, int shadows, void* h_rgba8, uint64_t* out_rays);
 

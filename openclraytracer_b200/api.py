@@ -442,6 +442,11 @@ def frame_untile(context, dptr_stripes, resX, resY, nranks, dptr_raster):
     check(_lib.load().clrt_frame_untile(context.handle, C.c_void_p(dptr_stripes), resX, resY, nranks, C.c_void_p(dptr_raster)))
 
 
+def frame_untile_on(context, stream, dptr_stripes, resX, resY, nranks, dptr_raster):
+    check(_lib.load().clrt_frame_untile_on(context.handle, C.c_void_p(stream), C.c_void_p(dptr_stripes), resX, resY, nranks,
+                                           C.c_void_p(dptr_raster)))
+
+
 def frame_stripe_pixels(resX, resY, rank, nranks):
     px, tiles = C.c_uint32(), C.c_uint32()
     check(_lib.load().clrt_frame_stripe_pixels(resX, resY, rank, nranks, C.byref(px), C.byref(tiles)))

@@ -70,6 +70,15 @@ struct __align__(16) TraceNode {
   uint32_t childA, childB, runStartA, runCounts;  // child id < N : leaf (= SORTED POSITION of the leaf), else N + inner node index
 };
 
+// 128-byte 4-wide traversal node (FAST policy): the 2-level collapse of a binary TraceNode tree, written by widen_kernel
+// (trace_tree.cu).  Wide node i stands for binary inner node i; only the nodes reachable from the root through wide links
+// are ever visited.  child < N: leaf (position in the tree-ordered triangle array); >= N: N + inner index; 0xFFFFFFFF: empty.
+struct __align__(16) WideNode {
+  float lox[4], loy[4], loz[4], hix[4], hiy[4], hiz[4];
+  uint32_t child[4];
+  uint32_t pad[4];
+};
+
 enum AccelKind { ACCEL_BVH = 0, ACCEL_TLG = 1 };
 
 struct clrt_accel {
@@ -95,6 +104,7 @@ struct clrt_accel {
   uint32_t max_run = 0;           // longest collapsed equal-key run (read back after construct; decides whether a trace tree is built)
   bool built = false;
   // --- separate trace tree (trace_tree.cu): built by construct() when the reference tree is a poor traversal structure ---
+  WideNode* d_wnodes = nullptr; size_t wnodes_cap = 0;                  // (N-1) x 128 B: what CLRT_TRACE_FAST walks
   int tt_policy = 0;              // 0 auto, 1 always, 2 never
   bool tt_built = false;
   TraceNode* d_tt_nodes = nullptr; size_t tt_nodes_cap = 0;             // (N-1) x 64 B
@@ -116,7 +126,7 @@ struct clrt_accel {
 int clrt_grow(void** p, size_t* cap, size_t bytes);               // cudaFree+cudaMalloc when bytes > *cap
 int bvh_init_frame(clrt_accel* a);
 int bvh_construct(clrt_accel* a);
-int trace_tree_build(clrt_accel* a);                              // trace_tree.cu
+int trace_tree_build(clrt_accel* a);                              // trace_tree.cu (ends with the widen pass)
 void trace_tree_destroy(clrt_accel* a);
 // nranks == 0: whole frame with raster-ordered output; otherwise stripe `rank` of `nranks` in stripe order
 int bvh_trace_primary(clrt_accel* a, const clrt_camera& cam, clrt_contact* out, uint32_t rank, uint32_t nranks);

@@ -129,12 +129,17 @@ extern "C" int clrt_shade(clrt_ctx* ctx, const clrt_scene* scene, const clrt_cam
                       (uint32_t*)dptr_rgba8, (float4*)dptr_rgba_f32);
 }
 
-extern "C" int clrt_frame_untile(clrt_ctx* ctx, const void* dptr_stripes, uint32_t resX, uint32_t resY, uint32_t nranks, void* dptr_raster_rgba8) {
+extern "C" int clrt_frame_untile_on(clrt_ctx* ctx, void* stream, const void* dptr_stripes, uint32_t resX, uint32_t resY, uint32_t nranks,
+                                    void* dptr_raster_rgba8) {
   if (!ctx || !dptr_stripes || !dptr_raster_rgba8 || !nranks) CLRT_FAIL("clrt_frame_untile: bad argument");
   CLRT_CUDA(cudaSetDevice(ctx->device));
   const TileGrid g = make_tile_grid(resX, resY);
   if (!g.tiles) return 0;
-  untile_kernel<<<g.tiles, 256, 0, ctx->stream>>>((const uint32_t*)dptr_stripes, resX, resY, nranks, (uint32_t*)dptr_raster_rgba8);
+  untile_kernel<<<g.tiles, 256, 0, (cudaStream_t)stream>>>((const uint32_t*)dptr_stripes, resX, resY, nranks, (uint32_t*)dptr_raster_rgba8);
   CLRT_CHECK_LAUNCH();
   return 0;
+}
+extern "C" int clrt_frame_untile(clrt_ctx* ctx, const void* dptr_stripes, uint32_t resX, uint32_t resY, uint32_t nranks, void* dptr_raster_rgba8) {
+  if (!ctx) CLRT_FAIL("clrt_frame_untile: bad argument");
+  return clrt_frame_untile_on(ctx, ctx->stream, dptr_stripes, resX, resY, nranks, dptr_raster_rgba8);
 }

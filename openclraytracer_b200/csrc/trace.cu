@@ -6,15 +6,15 @@
 //  * persistent warps: the grid is sized to the resident capacity of the 148 SMs; every warp pulls 8x4-pixel packets
 //    (primary) or 32-ray packets (generic) from one atomic counter -> dynamic work stealing inside the GPU, and the
 //    unit the image-space multi-GPU stripes are made of (32x8-pixel tiles = 8 packets, tile t owned by rank t % nranks).
-//  * 64-byte TraceNode per inner node (both child boxes + child ids, four 16-byte loads) instead of the reference's
-//    48-byte node + two 32-byte child-box fetches from the children's records; 48-byte 16-byte-aligned triangles
-//    instead of the per-fetch header walk of the packed scene.
-//  * FAST policy: leaf children are intersected as soon as their box is accepted (so duplicate-key chains never
-//    touch the stack), the nearer inner child is entered first and a child whose entry t exceeds the current best
-//    is culled.  The stack only ever holds inner nodes with strictly growing key prefixes -> at most 32 entries
-//    (the "short stack"), kept in local memory that stays L1 resident.
-//  * REFERENCE_ORDER policy: child A before child B, no culling, leaves go through the stack — the reference's
-//    exact visiting order, hence bit-identical contacts including the winners of exact ties.  Parity vehicle.
+//  * 48-byte 16-byte-aligned triangles in tree order instead of the per-fetch header walk of the packed scene.
+//  * FAST policy: 128-byte 4-wide nodes (WideNode: four child boxes SoA + four child ids, eight 16-byte loads) — the
+//    2-level collapse of the binary tree, so a ray's dependent load chain is half as long; leaf children are intersected
+//    as soon as their box is accepted, inner children are entered nearest first, the others wait on a stack of
+//    (entry distance, node) pairs in local memory and are culled against the current best when popped.
+//  * The tree FAST walks is the reference tree, or the separate trace tree (trace_tree.cu) when the reference tree has
+//    long equal-key chains or collapsed Morton axes.  Exact ties go to the reference's winner in both.
+//  * REFERENCE_ORDER policy: the binary reference topology through 64-byte TraceNodes (both child boxes + child ids in
+//    one record), child A before child B, no culling, leaves go through the stack — the reference's exact visiting order, hence bit-identical contacts including the winners of exact ties.  Parity vehicle.
 //  Box validity is the reference's in both policies: `t > 0 || origin inside` with the compare-select slab test.
 #include "common.cuh"
 #include "rtmath.cuh"
@@ -23,7 +23,7 @@
 namespace {
 
 constexpr int TRACE_THREADS = 128;
-constexpr int FAST_STACK = 40;
+constexpr int FAST_STACK = 72;     // (entry distance, node) pairs; a visit pushes at most three
 constexpr int REF_STACK = 96;
 constexpr uint32_t SENTINEL = 0xFFFFFFFFu;
 
@@ -46,23 +46,6 @@ __device__ __forceinline__ void test_triangle(const clrt_triangle* __restrict__ 
 }
 
 struct Stats { uint32_t rays, inner, tris, lboxes; };
-
-// ---- equal-key runs ----------------------------------------------------------------------------------------------------
-// An equal-key run [start, start+count) is entered as ONE multi-triangle leaf.  The reference walks the chain node by node:
-// at chain node i it tests the box of leaf i and the box of the remaining suffix, so leaf j is intersected iff its own
-// box and every enclosing suffix box are valid; suffix boxes contain the leaf boxes and the slab test is monotone under
-// box inclusion (also in floating point), hence "leaf box valid" alone selects the same leaves.  Boxes and triangles of
-// a run are contiguous in memory (sorted order) and independent of each other - no pointer chasing.
-
-template <bool STATS>
-__device__ __forceinline__ void test_run_element(const clrt_triangle* __restrict__ tris, const float4* __restrict__ leafbox,
-                                                 uint32_t p, Vec3 o, Vec3 d, Vec3 inv, Hit& h, Stats& st) {
-  const float4 lo = __ldg(leafbox + 2 * (size_t)p), hi = __ldg(leafbox + 2 * (size_t)p + 1);
-  if (STATS) st.lboxes++;
-  const float tb = aabb_intersect(lo.x, lo.y, lo.z, hi.x, hi.y, hi.z, o, inv);
-  const bool valid = tb > 0.0f || point_inside(lo.x, lo.y, lo.z, hi.x, hi.y, hi.z, o);
-  if (valid && !(tb > h.cull)) { test_triangle<true>(tris, p, o, d, h); if (STATS) st.tris++; }
-}
 
 // ---- REFERENCE_ORDER policy: the reference's visiting order, one ray per thread ---------------------------------------
 template <bool STATS>
@@ -115,49 +98,63 @@ template <bool STATS, bool ANYHIT>
 __device__ __forceinline__ void lane_begin(Lane& L, const clrt_triangle* __restrict__ tris, uint32_t n, Vec3 o, Vec3 d, float tmax, Stats& st) {
   L.o = o; L.d = d; L.inv = v3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
   L.h.t = tmax; L.h.tri = SENTINEL; L.h.cull = ANYHIT ? tmax * CULL_SLACK : RT_FLT_MAX;
-  L.sp = 0;                                    // an empty stack pops SENTINEL (lane_step)
+  L.sp = 0;
   L.cur = n >= 2 ? n : SENTINEL;
   if (STATS) { st.rays++; L.visits = 0; }
   if (n == 1) { test_triangle<false>(tris, 0, o, d, L.h); if (STATS) st.tris++; }     // the reference reads past its node buffer here
 }
 
-// One inner-node visit.  Leaf children are intersected at once; short equal-key runs of the reference tree inline (a
-// structure with long runs or collapsed axes is traversed through the separate trace tree of trace_tree.cu, which has
-// none).  Near child first, far child on the stack, children beyond best_t * (1 + 1e-5) culled.
+// One visit of a 4-wide node (WideNode, common.cuh: the 2-level collapse of the binary trace structure written by
+// widen_kernel, trace_tree.cu): ONE dependent 128-byte fetch decides four boxes, which halves the length of the dependent
+// load chain a ray walks — the chain, not bandwidth, is what bounds this kernel.  Leaf children are intersected at once;
+// valid inner children are sorted by entry distance, the nearest is entered, the others go to the stack WITH their entry
+// distance so that a pop can cull them against the hit found meanwhile.  Box validity is the reference's
+// (`t > 0 || origin inside`, AABB.h:126-142,178-184); children beyond best_t * (1 + 1e-5) are culled.
+#define T_INVALID __int_as_float(0x7f800000)      /* +inf marks an empty / rejected slot */
+
+__device__ __forceinline__ float child_entry(float x0, float y0, float z0, float x1, float y1, float z1, uint32_t child,
+                                             Vec3 o, Vec3 inv, float cull) {
+  const float tb = aabb_intersect(x0, y0, z0, x1, y1, z1, o, inv);
+  const bool valid = child != SENTINEL && (tb > 0.0f || point_inside(x0, y0, z0, x1, y1, z1, o)) && !(tb > cull);
+  return valid ? tb : T_INVALID;
+}
+__device__ __forceinline__ void cswap(float& ta, uint32_t& ca, float& tb, uint32_t& cb) {
+  if (tb < ta) { const float t = ta; ta = tb; tb = t; const uint32_t c = ca; ca = cb; cb = c; }
+}
+
 template <bool STATS, bool ANYHIT>
-__device__ __forceinline__ void lane_step(Lane& L, const TraceNode* __restrict__ tnodes, const clrt_triangle* __restrict__ tris,
-                                          const float4* __restrict__ leafbox, uint32_t n, Stats& st, uint32_t* __restrict__ stack) {
+__device__ __forceinline__ void lane_step(Lane& L, const WideNode* __restrict__ wnodes, const clrt_triangle* __restrict__ tris,
+                                          uint32_t n, Stats& st, uint2* __restrict__ stack) {
   if (STATS) { st.inner++; L.visits++; }
   const Vec3 o = L.o, d = L.d, inv = L.inv;
-  const float4* p = reinterpret_cast<const float4*>(tnodes + (L.cur - n));
-  const float4 q0 = __ldg(p), q1 = __ldg(p + 1), q2 = __ldg(p + 2);
-  const uint4 q3 = __ldg(reinterpret_cast<const uint4*>(p + 3));
-  const float tA = aabb_intersect(q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, o, inv);
-  const float tB = aabb_intersect(q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, o, inv);
-  bool aValid = (tA > 0.0f || point_inside(q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, o)) && !(tA > L.h.cull);
-  bool bValid = (tB > 0.0f || point_inside(q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, o)) && !(tB > L.h.cull);
-  const uint32_t cA = q3.x, cB = q3.y, cntA = q3.w & 0xFFFFu, cntB = q3.w >> 16;
-  if (aValid && cA < n) { test_triangle<true>(tris, cA, o, d, L.h); if (STATS) st.tris++; aValid = false; }
-  else if (aValid && cntA) {
-    for (uint32_t k = 0; k < cntA; k++) test_run_element<STATS>(tris, leafbox, q3.z + k, o, d, inv, L.h, st);
-    aValid = false;
+  const float4* p = reinterpret_cast<const float4*>(wnodes + (L.cur - n));
+  const float4 lx = __ldg(p), ly = __ldg(p + 1), lz = __ldg(p + 2), hx = __ldg(p + 3), hy = __ldg(p + 4), hz = __ldg(p + 5);
+  const uint4 ch = __ldg(reinterpret_cast<const uint4*>(p + 6));
+  uint32_t c0 = ch.x, c1 = ch.y, c2 = ch.z, c3 = ch.w;
+  float t0 = child_entry(lx.x, ly.x, lz.x, hx.x, hy.x, hz.x, c0, o, inv, L.h.cull);
+  float t1 = child_entry(lx.y, ly.y, lz.y, hx.y, hy.y, hz.y, c1, o, inv, L.h.cull);
+  float t2 = child_entry(lx.z, ly.z, lz.z, hx.z, hy.z, hz.z, c2, o, inv, L.h.cull);
+  float t3 = child_entry(lx.w, ly.w, lz.w, hx.w, hy.w, hz.w, c3, o, inv, L.h.cull);
+  // leaves first: a hit shrinks the cull distance before the inner children are ordered
+  if (c0 < n && t0 != T_INVALID) { if (!(t0 > L.h.cull)) { test_triangle<true>(tris, c0, o, d, L.h); if (STATS) st.tris++; } t0 = T_INVALID; }
+  if (c1 < n && t1 != T_INVALID) { if (!(t1 > L.h.cull)) { test_triangle<true>(tris, c1, o, d, L.h); if (STATS) st.tris++; } t1 = T_INVALID; }
+  if (c2 < n && t2 != T_INVALID) { if (!(t2 > L.h.cull)) { test_triangle<true>(tris, c2, o, d, L.h); if (STATS) st.tris++; } t2 = T_INVALID; }
+  if (c3 < n && t3 != T_INVALID) { if (!(t3 > L.h.cull)) { test_triangle<true>(tris, c3, o, d, L.h); if (STATS) st.tris++; } t3 = T_INVALID; }
+  if (ANYHIT && L.h.tri != SENTINEL) { L.cur = SENTINEL; return; }
+  if (t0 > L.h.cull) t0 = T_INVALID;
+  if (t1 > L.h.cull) t1 = T_INVALID;
+  if (t2 > L.h.cull) t2 = T_INVALID;
+  if (t3 > L.h.cull) t3 = T_INVALID;
+  cswap(t0, c0, t1, c1); cswap(t2, c2, t3, c3); cswap(t0, c0, t2, c2); cswap(t1, c1, t3, c3); cswap(t1, c1, t2, c2);   // ascending entry distance
+  if (t3 != T_INVALID && L.sp < FAST_STACK) stack[L.sp++] = make_uint2(__float_as_uint(t3), c3);
+  if (t2 != T_INVALID && L.sp < FAST_STACK) stack[L.sp++] = make_uint2(__float_as_uint(t2), c2);
+  if (t1 != T_INVALID && L.sp < FAST_STACK) stack[L.sp++] = make_uint2(__float_as_uint(t1), c1);
+  if (t0 != T_INVALID) { L.cur = c0; return; }
+  L.cur = SENTINEL;
+  while (L.sp > 0) {
+    const uint2 e = stack[--L.sp];
+    if (!(__uint_as_float(e.x) > L.h.cull)) { L.cur = e.y; break; }
   }
-  if (bValid && !(tB > L.h.cull) && cB < n) { test_triangle<true>(tris, cB, o, d, L.h); if (STATS) st.tris++; bValid = false; }
-  else if (bValid && cntB) {
-    if (!(tB > L.h.cull)) for (uint32_t k = 0; k < cntB; k++) test_run_element<STATS>(tris, leafbox, cB - n + k, o, d, inv, L.h, st);
-    bValid = false;
-  }
-  aValid = aValid && !(tA > L.h.cull);
-  bValid = bValid && !(tB > L.h.cull);
-  if (aValid && bValid) {
-    const bool bNear = tB < tA;
-    L.cur = bNear ? cB : cA;
-    if (L.sp < FAST_STACK) stack[L.sp++] = bNear ? cA : cB;
-  }
-  else if (aValid) L.cur = cA;
-  else if (bValid) L.cur = cB;
-  else L.cur = L.sp > 0 ? stack[--L.sp] : SENTINEL;
-  if (ANYHIT && L.h.tri != SENTINEL) L.cur = SENTINEL;
 }
 
 // Persistent-warp driver with lane refill.  A "unit" is a pixel slot / ray / contact; units come from one global atomic
@@ -181,13 +178,13 @@ constexpr int REFILL_MIN = CLRT_REFILL_MIN;
 constexpr uint32_t BATCH = CLRT_BATCH;
 
 template <class Job, bool STATS, bool ANYHIT>
-__device__ __forceinline__ void run_jobs(Job& job, const TraceNode* __restrict__ tnodes, const clrt_triangle* __restrict__ tris,
-                                         const float4* __restrict__ leafbox, uint32_t n, uint32_t total, uint32_t* __restrict__ counter, Stats& st) {
+__device__ __forceinline__ void run_jobs(Job& job, const WideNode* __restrict__ wnodes, const clrt_triangle* __restrict__ tris,
+                                         uint32_t n, uint32_t total, uint32_t* __restrict__ counter, Stats& st) {
   const unsigned FULL = 0xffffffffu;
   const int lane = threadIdx.x & 31;
   const unsigned lt_mask = (1u << lane) - 1u;
   Lane L; L.cur = SENTINEL; L.sp = 0;
-  uint32_t stack[FAST_STACK];
+  uint2 stack[FAST_STACK];
   bool busy = false, exhausted = false;
   uint32_t pool_next = 0, pool_end = 0;                         // warp-uniform
   while (true) {
@@ -215,7 +212,7 @@ __device__ __forceinline__ void run_jobs(Job& job, const TraceNode* __restrict__
     }
 #pragma unroll 1
     for (int k = 0; k < WINDOW; k++)
-      if (busy && L.cur != SENTINEL) lane_step<STATS, ANYHIT>(L, tnodes, tris, leafbox, n, st, stack);
+      if (busy && L.cur != SENTINEL) lane_step<STATS, ANYHIT>(L, wnodes, tris, n, st, stack);
   }
 }
 
@@ -348,8 +345,8 @@ struct ShadowJob {
 // ---- kernels ---------------------------------------------------------------------------------------------------------------
 template <int MODE, bool STATS>      // MODE 0: REFERENCE_ORDER, 1: FAST
 __global__ void __launch_bounds__(TRACE_THREADS)
-trace_primary_kernel(const clrt_camera cam, const TraceNode* __restrict__ tnodes,
-                     const clrt_triangle* __restrict__ tris, const float4* __restrict__ leafbox, uint32_t n, clrt_contact* __restrict__ out,
+trace_primary_kernel(const clrt_camera cam, const TraceNode* __restrict__ tnodes, const WideNode* __restrict__ wnodes,
+                     const clrt_triangle* __restrict__ tris, uint32_t n, clrt_contact* __restrict__ out,
                      uint32_t rank, uint32_t nranks, int raster, uint32_t* __restrict__ counter,
                      unsigned long long* __restrict__ stats) {
   Stats st; st.rays = st.inner = st.tris = st.lboxes = 0;
@@ -374,15 +371,15 @@ trace_primary_kernel(const clrt_camera cam, const TraceNode* __restrict__ tnodes
     }
   } else {
     PrimaryJob<STATS> job{cam, g, rank, nranks, raster, tris, n, out, st, 0u, 0u};
-    run_jobs<PrimaryJob<STATS>, STATS, false>(job, tnodes, tris, leafbox, n, total, counter, st);
+    run_jobs<PrimaryJob<STATS>, STATS, false>(job, wnodes, tris, n, total, counter, st);
   }
   if (STATS) flush_stats(st, stats);
 }
 
 template <int MODE, bool STATS>
 __global__ void __launch_bounds__(TRACE_THREADS)
-trace_rays_kernel(const clrt_ray* __restrict__ rays, uint32_t count, const TraceNode* __restrict__ tnodes,
-                  const clrt_triangle* __restrict__ tris, const float4* __restrict__ leafbox, uint32_t n, clrt_contact* __restrict__ out,
+trace_rays_kernel(const clrt_ray* __restrict__ rays, uint32_t count, const TraceNode* __restrict__ tnodes, const WideNode* __restrict__ wnodes,
+                  const clrt_triangle* __restrict__ tris, uint32_t n, clrt_contact* __restrict__ out,
                   uint32_t* __restrict__ counter, unsigned long long* __restrict__ stats) {
   Stats st; st.rays = st.inner = st.tris = st.lboxes = 0;
   if (MODE == 0) {
@@ -404,7 +401,7 @@ trace_rays_kernel(const clrt_ray* __restrict__ rays, uint32_t count, const Trace
     }
   } else {
     RaysJob<STATS> job{rays, tris, n, out, st, 0u};
-    run_jobs<RaysJob<STATS>, STATS, false>(job, tnodes, tris, leafbox, n, count, counter, st);
+    run_jobs<RaysJob<STATS>, STATS, false>(job, wnodes, tris, n, count, counter, st);
   }
   if (STATS) flush_stats(st, stats);
 }
@@ -413,13 +410,13 @@ template <bool STATS>
 __global__ void __launch_bounds__(TRACE_THREADS)
 shadow_shade_kernel(const clrt_camera cam, const clrt_contact* __restrict__ contacts, uint32_t count,
                     const clrt_light* __restrict__ lights, uint32_t n_lights, const clrt_material* __restrict__ materials, uint32_t n_materials,
-                    const TraceNode* __restrict__ tnodes, const clrt_triangle* __restrict__ tris, const float4* __restrict__ leafbox, uint32_t n,
+                    const WideNode* __restrict__ wnodes, const clrt_triangle* __restrict__ tris, uint32_t n,
                     uint32_t* __restrict__ rgba8, uint32_t* __restrict__ counter, unsigned long long* __restrict__ ray_counter,
                     unsigned long long* __restrict__ stats) {
   Stats st; st.rays = st.inner = st.tris = st.lboxes = 0;
   uint32_t live_rays = 0;
   ShadowJob<STATS> job{cam, contacts, lights, n_lights, materials, n_materials, tris, n, rgba8, st, live_rays};
-  run_jobs<ShadowJob<STATS>, STATS, true>(job, tnodes, tris, leafbox, n, count, counter, st);
+  run_jobs<ShadowJob<STATS>, STATS, true>(job, wnodes, tris, n, count, counter, st);
   if (ray_counter) {
 #pragma unroll
     for (int dd = 16; dd > 0; dd >>= 1) live_rays += __shfl_xor_sync(0xffffffffu, live_rays, dd);
@@ -441,10 +438,10 @@ int persistent_grid(clrt_ctx* ctx, K kernel, int threads, unsigned* grid) {
 
 // The structure a launch traverses: REFERENCE_ORDER always walks the reference topology; FAST walks the separate trace tree
 // (trace_tree.cu) when construct() built one, else the reference tree.
-struct TraceView { const TraceNode* tnodes; const clrt_triangle* tris; const float4* leafbox; };
+struct TraceView { const TraceNode* tnodes; const WideNode* wnodes; const clrt_triangle* tris; };
 static TraceView trace_view(const clrt_accel* a, bool fast) {
-  if (fast && a->tt_built) return TraceView{a->d_tt_nodes, a->d_tt_tris, a->d_tt_leafbox};
-  return TraceView{a->d_tnodes, a->d_tris_sorted, a->d_leafbox_sorted};
+  if (fast && a->tt_built) return TraceView{a->d_tt_nodes, a->d_wnodes, a->d_tt_tris};
+  return TraceView{a->d_tnodes, a->d_wnodes, a->d_tris_sorted};
 }
 
 template <int M, bool S>
@@ -453,7 +450,7 @@ static int launch_primary(clrt_accel* a, const clrt_camera& cam, clrt_contact* o
   CLRT_TRY(persistent_grid(a->ctx, trace_primary_kernel<M, S>, TRACE_THREADS, &grid));
   grid = min(grid, (packets + 3) / 4);
   const TraceView v = trace_view(a, M != 0);
-  trace_primary_kernel<M, S><<<grid, TRACE_THREADS, 0, a->ctx->stream>>>(cam, v.tnodes, v.tris, v.leafbox, a->n, out, rank, nranks, raster,
+  trace_primary_kernel<M, S><<<grid, TRACE_THREADS, 0, a->ctx->stream>>>(cam, v.tnodes, v.wnodes, v.tris, a->n, out, rank, nranks, raster,
                                                                         a->d_tile_counter, (unsigned long long*)(a->d_tile_counter + 4));
   CLRT_CHECK_LAUNCH();
   return 0;
@@ -464,7 +461,7 @@ static int launch_rays(clrt_accel* a, const clrt_ray* rays, clrt_contact* out, u
   CLRT_TRY(persistent_grid(a->ctx, trace_rays_kernel<M, S>, TRACE_THREADS, &grid));
   grid = min(grid, (packets + 3) / 4);
   const TraceView v = trace_view(a, M != 0);
-  trace_rays_kernel<M, S><<<grid, TRACE_THREADS, 0, a->ctx->stream>>>(rays, count, v.tnodes, v.tris, v.leafbox, a->n, out,
+  trace_rays_kernel<M, S><<<grid, TRACE_THREADS, 0, a->ctx->stream>>>(rays, count, v.tnodes, v.wnodes, v.tris, a->n, out,
                                                                      a->d_tile_counter, (unsigned long long*)(a->d_tile_counter + 4));
   CLRT_CHECK_LAUNCH();
   return 0;
@@ -508,7 +505,7 @@ static int launch_shadow_shade(clrt_accel* a, const clrt_camera& cam, const clrt
   grid = min(grid, (packets + 3) / 4);
   const TraceView v = trace_view(a, true);
   shadow_shade_kernel<S><<<grid, TRACE_THREADS, 0, a->ctx->stream>>>(cam, contacts, count, sc->d_lights, sc->n_lights, sc->d_materials, sc->n_materials,
-      v.tnodes, v.tris, v.leafbox, a->n, rgba8, a->d_tile_counter, d_ray_counter, (unsigned long long*)(a->d_tile_counter + 4));
+      v.wnodes, v.tris, a->n, rgba8, a->d_tile_counter, d_ray_counter, (unsigned long long*)(a->d_tile_counter + 4));
   CLRT_CHECK_LAUNCH();
   return 0;
 }

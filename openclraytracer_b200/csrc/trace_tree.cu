@@ -128,6 +128,40 @@ tt_refit_kernel(const float4* __restrict__ leafbox, const uint32_t* __restrict__
   }
 }
 
+// 2-level collapse: wide node i = the grandchildren of binary node i (a leaf child stays as it is).  One thread per binary
+// inner node, 3 x 64 B in, 128 B out; no ordering between nodes is needed because EVERY binary node gets a wide node —
+// the ones not reachable through wide links are never visited.
+__device__ __forceinline__ void wn_put(WideNode& w, int& k, uint32_t child, float x0, float y0, float z0, float x1, float y1, float z1) {
+  w.lox[k] = x0; w.loy[k] = y0; w.loz[k] = z0; w.hix[k] = x1; w.hiy[k] = y1; w.hiz[k] = z1; w.child[k] = child; k++;
+}
+__device__ __forceinline__ void wn_expand(WideNode& w, int& k, const TraceNode* __restrict__ tnodes, uint32_t n, uint32_t child,
+                                          float x0, float y0, float z0, float x1, float y1, float z1) {
+  if (child < n) { wn_put(w, k, child, x0, y0, z0, x1, y1, z1); return; }
+  const float4* p = reinterpret_cast<const float4*>(tnodes + (child - n));
+  const float4 q0 = __ldg(p), q1 = __ldg(p + 1), q2 = __ldg(p + 2);
+  const uint4 q3 = __ldg(reinterpret_cast<const uint4*>(p + 3));
+  wn_put(w, k, q3.x, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y);
+  wn_put(w, k, q3.y, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w);
+}
+__global__ void __launch_bounds__(128)
+widen_kernel(const TraceNode* __restrict__ tnodes, uint32_t n, WideNode* __restrict__ wnodes) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i + 1 >= n) return;
+  const float4* p = reinterpret_cast<const float4*>(tnodes + i);
+  const float4 q0 = __ldg(p), q1 = __ldg(p + 1), q2 = __ldg(p + 2);
+  const uint4 q3 = __ldg(reinterpret_cast<const uint4*>(p + 3));
+  WideNode w;
+  int k = 0;
+  wn_expand(w, k, tnodes, n, q3.x, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y);
+  wn_expand(w, k, tnodes, n, q3.y, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w);
+  for (; k < 4; ) wn_put(w, k, 0xFFFFFFFFu, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f);
+  w.pad[0] = w.pad[1] = w.pad[2] = w.pad[3] = 0u;
+  float4* o = reinterpret_cast<float4*>(wnodes + i);
+  const float4* src = reinterpret_cast<const float4*>(&w);
+#pragma unroll
+  for (int j = 0; j < 8; j++) o[j] = src[j];
+}
+
 } // namespace
 
 void trace_tree_destroy(clrt_accel* a) {
@@ -136,12 +170,15 @@ void trace_tree_destroy(clrt_accel* a) {
   if (a->d_tt_leafbox) cudaFree(a->d_tt_leafbox);
   if (a->d_tt_pairs) cudaFree(a->d_tt_pairs);
   if (a->d_tt_parent) cudaFree(a->d_tt_parent);
+  if (a->d_wnodes) cudaFree(a->d_wnodes);
+  a->d_wnodes = nullptr;
   a->d_tt_nodes = nullptr; a->d_tt_tris = nullptr; a->d_tt_leafbox = nullptr; a->d_tt_pairs = nullptr; a->d_tt_parent = nullptr;
 }
 
 // Called at the end of bvh_construct (a->max_run is known).  Auto policy: build when the reference tree holds an equal-key
 // run of TT_RUN_MIN or more, or when the scene box reaches more than one Morton cell below zero on some axis (collapsed axis, Q6).
 constexpr uint32_t TT_RUN_MIN = 6;
+static int trace_tree_separate(clrt_accel* a);
 int trace_tree_build(clrt_accel* a) {
   clrt_ctx* ctx = a->ctx;
   const uint32_t n = a->n;
@@ -152,7 +189,29 @@ int trace_tree_build(clrt_accel* a) {
   auto below = [](float lo, float hi) { return lo < 0.0f && -lo * 1024.0f > (hi - lo); };
   const bool collapsed = below(bb.bounds[0].x, bb.bounds[1].x) || below(bb.bounds[0].y, bb.bounds[1].y) || below(bb.bounds[0].z, bb.bounds[1].z);
   const bool want = a->tt_policy == 1 || (a->tt_policy == 0 && (a->max_run >= TT_RUN_MIN || collapsed));
-  if (!want || n < 2) return 0;
+  if (n < 2) return 0;
+  cudaStream_t s = ctx->stream;
+  const bool tm = a->timing;
+  if ((size_t)n * sizeof(WideNode) > a->wnodes_cap) CLRT_CUDA(cudaStreamSynchronize(s));
+  CLRT_TRY(clrt_grow((void**)&a->d_wnodes, &a->wnodes_cap, (size_t)n * sizeof(WideNode)));
+  if (tm) CLRT_CUDA(cudaEventRecord(a->ev[5], s));
+  if (want) CLRT_TRY(trace_tree_separate(a));
+  widen_kernel<<<(n + 127) / 128, 128, 0, s>>>(want ? a->d_tt_nodes : a->d_tnodes, n, a->d_wnodes);
+  CLRT_CHECK_LAUNCH();
+  if (tm) {
+    CLRT_CUDA(cudaEventRecord(a->ev[6], s));
+    CLRT_CUDA(cudaEventSynchronize(a->ev[6]));
+    CLRT_CUDA(cudaEventElapsedTime(&a->stage_ms[CLRT_STAGE_TRACE_TREE], a->ev[5], a->ev[6]));
+    a->stage_ms[CLRT_STAGE_TOTAL] += a->stage_ms[CLRT_STAGE_TRACE_TREE];
+  }
+  a->tt_built = want;
+  return 0;
+}
+
+static int trace_tree_separate(clrt_accel* a) {
+  clrt_ctx* ctx = a->ctx;
+  const uint32_t n = a->n;
+  const clrt_aabb bb = a->scene->header.modelsBoundingBox;
   cudaStream_t s = ctx->stream;
   if ((size_t)n * sizeof(TraceNode) > a->tt_nodes_cap || (size_t)n * sizeof(clrt_triangle) > a->tt_tris_cap || (size_t)n * 32 > a->tt_leafbox_cap ||
       (size_t)n * 8 > a->tt_pairs_cap || (size_t)n * 8 > a->tt_parent_cap)
@@ -162,8 +221,6 @@ int trace_tree_build(clrt_accel* a) {
   CLRT_TRY(clrt_grow((void**)&a->d_tt_leafbox, &a->tt_leafbox_cap, (size_t)n * 32));
   CLRT_TRY(clrt_grow((void**)&a->d_tt_pairs, &a->tt_pairs_cap, (size_t)n * 8));
   CLRT_TRY(clrt_grow((void**)&a->d_tt_parent, &a->tt_parent_cap, (size_t)n * 8));
-  const bool tm = a->timing;
-  if (tm) CLRT_CUDA(cudaEventRecord(a->ev[5], s));
   const unsigned grid = (n + 255) / 256;
   tt_morton_kernel<<<grid, 256, 0, s>>>(a->scene->d_tris, n, bb, reinterpret_cast<uint2*>(a->d_tt_pairs));
   CLRT_CHECK_LAUNCH();
@@ -174,13 +231,6 @@ int trace_tree_build(clrt_accel* a) {
   CLRT_CHECK_LAUNCH();
   tt_refit_kernel<<<grid, 256, 0, s>>>(a->d_tt_leafbox, a->d_tt_parent, a->d_counters, n, a->d_tt_nodes);
   CLRT_CHECK_LAUNCH();
-  if (tm) {
-    CLRT_CUDA(cudaEventRecord(a->ev[6], s));
-    CLRT_CUDA(cudaEventSynchronize(a->ev[6]));
-    CLRT_CUDA(cudaEventElapsedTime(&a->stage_ms[CLRT_STAGE_TRACE_TREE], a->ev[5], a->ev[6]));
-    a->stage_ms[CLRT_STAGE_TOTAL] += a->stage_ms[CLRT_STAGE_TRACE_TREE];
-  }
-  a->tt_built = true;
   return 0;
 }
 

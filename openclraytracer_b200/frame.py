@@ -6,7 +6,8 @@ once (redundant rebuild: a 1M-triangle LBVH build costs less than broadcasting i
 renders its stripe — 32x8-pixel tiles, tile t owned by rank t % world, persistent warps inside the GPU pull packets
 from an atomic counter — into a device buffer in stripe order; ONE collective (all-gather of equal, padded RGBA8
 stripes, 8.3 MB per 1080p frame) follows, and an untile kernel restores raster order.  No other exchange exists on
-the path.
+the path.  Two frames are in flight: the collective, the untile and the read-back of frame k run on a second stream
+while the stripe of frame k+1 is traced.
 
 PyTorch is plumbing here: device memory, the stream shared with NCCL, and the collective.
 """
@@ -91,34 +92,72 @@ class FrameRenderer:
         self.accel.initialize()
         self.cap = stripe_capacity(resX, resY, world)
         torch.cuda.synchronize()
-        self.stripe = torch.zeros(self.cap, dtype=torch.int32, device=self.device)
-        self.gathered = torch.zeros(self.cap * world, dtype=torch.int32, device=self.device) if world > 1 else self.stripe
-        self.raster = torch.zeros(resY * resX, dtype=torch.int32, device=self.device)
-        self.host_raster = torch.zeros(resY * resX, dtype=torch.int32).pin_memory()
+        # Two frames in flight: the stripe trace of frame k+1 (context stream) overlaps the gather + untile (+ read-back)
+        # of frame k on a second stream.  Buffers are double; events order reuse.
+        self.DEPTH = 2
+        self.comm = torch.cuda.Stream(self.device)
+        self.stripes = [torch.zeros(self.cap, dtype=torch.int32, device=self.device) for _ in range(self.DEPTH)]
+        self.gathereds = [torch.zeros(self.cap * world, dtype=torch.int32, device=self.device) if world > 1 else self.stripes[i]
+                          for i in range(self.DEPTH)]
+        self.rasters = [torch.zeros(resY * resX, dtype=torch.int32, device=self.device) for _ in range(self.DEPTH)]
+        self.host_rasters = [torch.zeros(resY * resX, dtype=torch.int32).pin_memory() for _ in range(self.DEPTH)]
+        self.ev_traced = [torch.cuda.Event() for _ in range(self.DEPTH)]
+        self.ev_free = [torch.cuda.Event() for _ in range(self.DEPTH)]
+        self.ev_host = [torch.cuda.Event() for _ in range(self.DEPTH)]
+        self.frame_no = 0
+        self.stripe, self.gathered, self.raster, self.host_raster = self.stripes[0], self.gathereds[0], self.rasters[0], self.host_rasters[0]
 
     def build(self):
         self.accel.initializeFrame()
         self.accel.construct()
 
-    def render_device(self, camera, shadows=True, want_rays=False):
-        """One frame, result left on the device in raster order (on every rank).  Returns rays traced by this rank
-        if want_rays (that costs a host sync)."""
-        with self.torch.cuda.stream(self.stream):
-            rays = self.accel.render_stripe(camera, shadows, self.rank, self.world, self.stripe.data_ptr(), want_rays)
+    def _submit(self, camera, shadows, want_rays, to_host):
+        torch = self.torch
+        k = self.frame_no % self.DEPTH
+        self.frame_no += 1
+        if to_host:
+            self.ev_host[k].synchronize()             # the host buffer of slot k may still be the target of frame k-DEPTH's copy
+        with torch.cuda.stream(self.stream):
+            self.stream.wait_event(self.ev_free[k])   # slot k's stripe buffer is free once frame k-DEPTH was gathered
+            rays = self.accel.render_stripe(camera, shadows, self.rank, self.world, self.stripes[k].data_ptr(), want_rays)
+            self.ev_traced[k].record(self.stream)
+        with torch.cuda.stream(self.comm):
+            self.comm.wait_event(self.ev_traced[k])
             if self.world > 1:
                 import torch.distributed as dist
-                dist.all_gather_into_tensor(self.gathered, self.stripe, group=self.group)
-            api.frame_untile(self.ctx, self.gathered.data_ptr(), self.resX, self.resY, self.world, self.raster.data_ptr())
+                dist.all_gather_into_tensor(self.gathereds[k], self.stripes[k], group=self.group)
+            api.frame_untile_on(self.ctx, self.comm.cuda_stream, self.gathereds[k].data_ptr(), self.resX, self.resY, self.world,
+                                self.rasters[k].data_ptr())
+            if to_host and self.rank == 0:
+                self.host_rasters[k].copy_(self.rasters[k], non_blocking=True)
+            self.ev_free[k].record(self.comm)
+            if to_host:
+                self.ev_host[k].record(self.comm)
+        self.stripe, self.gathered, self.raster, self.host_raster = self.stripes[k], self.gathereds[k], self.rasters[k], self.host_rasters[k]
         return rays
 
-    def render_host(self, camera, shadows=True):
-        """e2e: host camera in, RGBA8 raster in pinned host memory out (rank 0 reads the frame back)."""
-        self.render_device(camera, shadows)
-        with self.torch.cuda.stream(self.stream):
-            if self.rank == 0:
-                self.host_raster.copy_(self.raster, non_blocking=True)
-        self.stream.synchronize()
+    def render_device(self, camera, shadows=True, want_rays=False):
+        """Submits one frame; its raster-ordered result (every rank holds the whole frame) is in `self.raster` once the
+        second stream has passed — `finish()` joins.  Returns the rays traced by this rank if want_rays (a host sync)."""
+        return self._submit(camera, shadows, want_rays, False)
+
+    def render_host_async(self, camera, shadows=True):
+        """e2e, pipelined: host camera in, RGBA8 raster into pinned host memory (rank 0); returns the host buffer the
+        frame will land in — valid after `finish()` or once two more frames were submitted."""
+        self._submit(camera, shadows, False, True)
         return self.host_raster
+
+    def render_host(self, camera, shadows=True):
+        """e2e, synchronous: returns when the frame is in pinned host memory (rank 0 reads the frame back)."""
+        out = self.render_host_async(camera, shadows)
+        self.finish()
+        return out
+
+    def finish(self):
+        """Joins the second stream into the context's stream and waits for both."""
+        self.stream.wait_stream(self.comm)
+        self.comm.synchronize()
+        self.stream.synchronize()
 
     def close(self):
         self.accel.free(); self.scene.free(); self.ctx.close()

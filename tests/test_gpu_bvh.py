@@ -323,3 +323,27 @@ def test_trace_tree_returns_the_reference_tree_hits(ctx, O, name):
     if name == "clumsydragon":
         assert bvh.has_trace_tree()          # auto: long equal-key runs + a scene box below zero
     bvh.free(); scene.free()
+
+
+def test_frame_renderer_pipeline_equals_synchronous_frames(ctx):
+    """FrameRenderer keeps two frames in flight (second stream for untile + read-back); every frame must equal the one the
+    synchronous C-ABI frame call returns for the same camera."""
+    from openclraytracer_b200 import frame
+    buf = scenes.load_bundled("tenryuu")
+    r = frame.FrameRenderer(buf, 320, 200, "BVH", 0, 1, 0)
+    r.build()
+    cams = [frame.orbit_camera(buf, 320, 200, s) for s in range(5)]
+    want = [r.accel.render_frame_host(c, True)[0].copy() for c in cams]
+    outs = []
+    for c in cams[:2]:
+        outs.append(r.render_host_async(c, True))
+    r.finish()
+    got01 = [o.numpy().reshape(200, 320).copy() for o in outs]
+    for k in range(2):
+        assert np.array_equal(got01[k].view(np.uint8).reshape(200, 320, 4), want[k])
+    for k in range(2, 5):
+        got = r.render_host(cams[k], True).numpy().reshape(200, 320).view(np.uint8).reshape(200, 320, 4)
+        assert np.array_equal(got, want[k])
+        r.render_device(cams[k], True); r.finish()
+        assert np.array_equal(r.raster.cpu().numpy().view(np.uint8).reshape(200, 320, 4), want[k])
+    r.close()
