@@ -243,7 +243,7 @@ def main():
     for i in range(8):
         r.build()
         build_ms.append(r.accel.stage_ms(api.STAGE_TOTAL))
-        stages.append([r.accel.stage_ms(s) for s in range(4)])
+        stages.append([r.accel.stage_ms(s) for s in (0, 1, 2, 3, api.STAGE_TRACE_TREE)])
     r.accel.enable_stage_timing(False)
     r.build()
     build_med = float(np.median(build_ms[2:]))
@@ -319,7 +319,9 @@ def main():
             "gpu_launches": args.steps * 3,   # trace_primary_kernel, shadow_shade_kernel, untile_kernel per step
             "pipeline": "2 frames in flight: gather + untile (+ read-back) of frame k overlap the trace of frame k+1",
             "build_ms": build_med, "build_ms_per_Mtri": build_med / (n_tris / 1e6),
-            "build_stage_ms": {"morton": float(stage_med[0]), "sort": float(stage_med[1]), "emit": float(stage_med[2]), "refit": float(stage_med[3])},
+            "build_stage_ms": {"morton": float(stage_med[0]), "sort": float(stage_med[1]), "emit": float(stage_med[2]), "refit": float(stage_med[3]),
+                               "trace_structure": float(stage_med[4])},
+            "trace_structure": "separate trace tree + 4-wide collapse" if r.accel.has_trace_tree() else "4-wide collapse of the reference tree",
             "clocks": clocks,
         }
         # roofline of the dominant kernel (the longer of the two traversal kernels of the frame)

@@ -114,7 +114,7 @@ void* clrt_accel_primary_contacts_dptr(clrt_accel* accel);     /* getPrimaryCont
 #define CLRT_TRACE_REFERENCE_ORDER 1
 int clrt_accel_set_trace_mode(clrt_accel* accel, int mode);
 /* Trace tree (ours; openclraytracer_b200/csrc/trace_tree.cu).  The reference-layout BVH is always built bit-exactly; when it
- * is a poor thing to traverse — equal-key chains (BVH.h:153-154,212-233) of 6+ leaves, or a scene box reaching below zero so
+ * is a poor thing to traverse — equal-key chains (BVH.h:153-154,212-233) of 6+ leaves, or a scene box with more than 1/16 of an axis below zero so
  * that a Morton axis collapses (BVH.h:112-114 divides without subtracting min) — construct() also builds a plain LBVH over
  * the same triangles from a min-subtracted Morton code, and CLRT_TRACE_FAST walks that one.  Same closest hits; exact ties
  * go to the reference's winner (smallest position in the reference's sorted order).  policy: 0 auto (default), 1 always,

@@ -109,14 +109,21 @@ __device__ __forceinline__ void lane_begin(Lane& L, const clrt_triangle* __restr
 // load chain a ray walks — the chain, not bandwidth, is what bounds this kernel.  Leaf children are intersected at once;
 // valid inner children are sorted by entry distance, the nearest is entered, the others go to the stack WITH their entry
 // distance so that a pop can cull them against the hit found meanwhile.  Box validity is the reference's
-// (`t > 0 || origin inside`, AABB.h:126-142,178-184); children beyond best_t * (1 + 1e-5) are culled.
+// (child_entry below); children beyond best_t * (1 + 1e-5) are culled.
 #define T_INVALID __int_as_float(0x7f800000)      /* +inf marks an empty / rejected slot */
 
-__device__ __forceinline__ float child_entry(float x0, float y0, float z0, float x1, float y1, float z1, uint32_t child,
-                                             Vec3 o, Vec3 inv, float cull) {
-  const float tb = aabb_intersect(x0, y0, z0, x1, y1, z1, o, inv);
-  const bool valid = child != SENTINEL && (tb > 0.0f || point_inside(x0, y0, z0, x1, y1, z1, o)) && !(tb > cull);
-  return valid ? tb : T_INVALID;
+// Entry distance of one child box, or T_INVALID.  Same six products (bound - origin) * (1/d) as the reference's AABBIntersect
+// (AABB.h:126-142), so tn / tf are the reference's tmin / tmax bit for bit; the per-axis near/far pick is a min/max instead of
+// the sign select, the three pairwise overlap flags are `tn <= tf`, and the reference's validity `t > 0 || origin inside`
+// (AABB.h:178-184) is `tf >= 0` (origin inside <=> every axis has near <= 0 <= far).  22 instructions instead of ~50.
+// Empty slots hold NaN boxes (widen_kernel): every comparison fails.
+__device__ __forceinline__ float child_entry(float x0, float y0, float z0, float x1, float y1, float z1, Vec3 o, Vec3 inv, float cull) {
+  const float ax = (x0 - o.x) * inv.x, bx = (x1 - o.x) * inv.x;
+  const float ay = (y0 - o.y) * inv.y, by = (y1 - o.y) * inv.y;
+  const float az = (z0 - o.z) * inv.z, bz = (z1 - o.z) * inv.z;
+  const float tn = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fminf(az, bz));
+  const float tf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fmaxf(az, bz));
+  return (tn <= fminf(tf, cull) && tf >= 0.0f) ? tn : T_INVALID;
 }
 __device__ __forceinline__ void cswap(float& ta, uint32_t& ca, float& tb, uint32_t& cb) {
   if (tb < ta) { const float t = ta; ta = tb; tb = t; const uint32_t c = ca; ca = cb; cb = c; }
@@ -131,10 +138,10 @@ __device__ __forceinline__ void lane_step(Lane& L, const WideNode* __restrict__ 
   const float4 lx = __ldg(p), ly = __ldg(p + 1), lz = __ldg(p + 2), hx = __ldg(p + 3), hy = __ldg(p + 4), hz = __ldg(p + 5);
   const uint4 ch = __ldg(reinterpret_cast<const uint4*>(p + 6));
   uint32_t c0 = ch.x, c1 = ch.y, c2 = ch.z, c3 = ch.w;
-  float t0 = child_entry(lx.x, ly.x, lz.x, hx.x, hy.x, hz.x, c0, o, inv, L.h.cull);
-  float t1 = child_entry(lx.y, ly.y, lz.y, hx.y, hy.y, hz.y, c1, o, inv, L.h.cull);
-  float t2 = child_entry(lx.z, ly.z, lz.z, hx.z, hy.z, hz.z, c2, o, inv, L.h.cull);
-  float t3 = child_entry(lx.w, ly.w, lz.w, hx.w, hy.w, hz.w, c3, o, inv, L.h.cull);
+  float t0 = child_entry(lx.x, ly.x, lz.x, hx.x, hy.x, hz.x, o, inv, L.h.cull);
+  float t1 = child_entry(lx.y, ly.y, lz.y, hx.y, hy.y, hz.y, o, inv, L.h.cull);
+  float t2 = child_entry(lx.z, ly.z, lz.z, hx.z, hy.z, hz.z, o, inv, L.h.cull);
+  float t3 = child_entry(lx.w, ly.w, lz.w, hx.w, hy.w, hz.w, o, inv, L.h.cull);
   // leaves first: a hit shrinks the cull distance before the inner children are ordered
   if (c0 < n && t0 != T_INVALID) { if (!(t0 > L.h.cull)) { test_triangle<true>(tris, c0, o, d, L.h); if (STATS) st.tris++; } t0 = T_INVALID; }
   if (c1 < n && t1 != T_INVALID) { if (!(t1 > L.h.cull)) { test_triangle<true>(tris, c1, o, d, L.h); if (STATS) st.tris++; } t1 = T_INVALID; }

@@ -154,7 +154,8 @@ widen_kernel(const TraceNode* __restrict__ tnodes, uint32_t n, WideNode* __restr
   int k = 0;
   wn_expand(w, k, tnodes, n, q3.x, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y);
   wn_expand(w, k, tnodes, n, q3.y, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w);
-  for (; k < 4; ) wn_put(w, k, 0xFFFFFFFFu, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f);
+  const float qnan = __int_as_float(0x7fc00000);          // empty slot: a NaN box fails every comparison of the slab test
+  for (; k < 4; ) wn_put(w, k, 0xFFFFFFFFu, qnan, qnan, qnan, qnan, qnan, qnan);
   w.pad[0] = w.pad[1] = w.pad[2] = w.pad[3] = 0u;
   float4* o = reinterpret_cast<float4*>(wnodes + i);
   const float4* src = reinterpret_cast<const float4*>(&w);
@@ -176,7 +177,7 @@ void trace_tree_destroy(clrt_accel* a) {
 }
 
 // Called at the end of bvh_construct (a->max_run is known).  Auto policy: build when the reference tree holds an equal-key
-// run of TT_RUN_MIN or more, or when the scene box reaches more than one Morton cell below zero on some axis (collapsed axis, Q6).
+// run of TT_RUN_MIN or more, or when more than 1/16 of the scene box lies below zero on some axis (collapsed axis, Q6).
 constexpr uint32_t TT_RUN_MIN = 6;
 static int trace_tree_separate(clrt_accel* a);
 int trace_tree_build(clrt_accel* a) {
@@ -185,8 +186,8 @@ int trace_tree_build(clrt_accel* a) {
   a->tt_built = false;
   a->stage_ms[CLRT_STAGE_TRACE_TREE] = 0.0f;
   const clrt_aabb bb = a->scene->header.modelsBoundingBox;
-  // an axis collapses when more than one Morton cell (1/1024 of the extent) of the scene box lies below zero
-  auto below = [](float lo, float hi) { return lo < 0.0f && -lo * 1024.0f > (hi - lo); };
+  // an axis counts as collapsed when more than 1/16 of the scene box's extent lies below zero (all of it maps to cell 0)
+  auto below = [](float lo, float hi) { return lo < 0.0f && -lo * 16.0f > (hi - lo); };
   const bool collapsed = below(bb.bounds[0].x, bb.bounds[1].x) || below(bb.bounds[0].y, bb.bounds[1].y) || below(bb.bounds[0].z, bb.bounds[1].z);
   const bool want = a->tt_policy == 1 || (a->tt_policy == 0 && (a->max_run >= TT_RUN_MIN || collapsed));
   if (n < 2) return 0;

@@ -8,5 +8,6 @@ for f in ["b_cd","b_soup"]:
         d=json.loads(open("gpurun_out/%s.json"%f).read())
         print(f, "Mrays/s %.0f ms/step %.3f e2e %.0f build %.3f"%(d["value"], d["ms_per_step"], d["e2e"]["value"], d["build_ms"]), d["build_stage_ms"])
         for k,v in d["trace_kernels"].items(): print("   ",k, {a:round(b,3) for a,b in v.items()})
+        print("   ", d.get("trace_structure"))
     except Exception as e: print(f, "ERR", e, open("gpurun_out/%s.json"%f).read()[-800:])
 PY
