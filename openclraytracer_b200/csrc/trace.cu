@@ -142,11 +142,29 @@ __device__ __forceinline__ void lane_step(Lane& L, const WideNode* __restrict__ 
   float t1 = child_entry(lx.y, ly.y, lz.y, hx.y, hy.y, hz.y, o, inv, L.h.cull);
   float t2 = child_entry(lx.z, ly.z, lz.z, hx.z, hy.z, hz.z, o, inv, L.h.cull);
   float t3 = child_entry(lx.w, ly.w, lz.w, hx.w, hy.w, hz.w, o, inv, L.h.cull);
-  // leaves first: a hit shrinks the cull distance before the inner children are ordered
-  if (c0 < n && t0 != T_INVALID) { if (!(t0 > L.h.cull)) { test_triangle<true>(tris, c0, o, d, L.h); if (STATS) st.tris++; } t0 = T_INVALID; }
-  if (c1 < n && t1 != T_INVALID) { if (!(t1 > L.h.cull)) { test_triangle<true>(tris, c1, o, d, L.h); if (STATS) st.tris++; } t1 = T_INVALID; }
-  if (c2 < n && t2 != T_INVALID) { if (!(t2 > L.h.cull)) { test_triangle<true>(tris, c2, o, d, L.h); if (STATS) st.tris++; } t2 = T_INVALID; }
-  if (c3 < n && t3 != T_INVALID) { if (!(t3 > L.h.cull)) { test_triangle<true>(tris, c3, o, d, L.h); if (STATS) st.tris++; } t3 = T_INVALID; }
+  // leaves first: a hit shrinks the cull distance before the inner children are ordered.  Closest-hit rays run ONE copy of
+  // the triangle test in a loop over the accepted leaf slots, so the lanes that have a leaf in ANY slot run it together (four
+  // inlined copies, one per slot, each ran with the few lanes whose leaf sat in that slot); occlusion queries measured faster
+  // with the per-slot form.
+  if (!ANYHIT) {
+    uint32_t leaves = (c0 < n && t0 != T_INVALID ? 1u : 0u) | (c1 < n && t1 != T_INVALID ? 2u : 0u) |
+                      (c2 < n && t2 != T_INVALID ? 4u : 0u) | (c3 < n && t3 != T_INVALID ? 8u : 0u);
+    if (leaves & 1u) t0 = T_INVALID;
+    if (leaves & 2u) t1 = T_INVALID;
+    if (leaves & 4u) t2 = T_INVALID;
+    if (leaves & 8u) t3 = T_INVALID;
+    while (leaves) {
+      const uint32_t id = (leaves & 1u) ? c0 : (leaves & 2u) ? c1 : (leaves & 4u) ? c2 : c3;
+      leaves &= leaves - 1u;
+      test_triangle<true>(tris, id, o, d, L.h);
+      if (STATS) st.tris++;
+    }
+  } else {
+    if (c0 < n && t0 != T_INVALID) { test_triangle<true>(tris, c0, o, d, L.h); if (STATS) st.tris++; t0 = T_INVALID; }
+    if (c1 < n && t1 != T_INVALID) { test_triangle<true>(tris, c1, o, d, L.h); if (STATS) st.tris++; t1 = T_INVALID; }
+    if (c2 < n && t2 != T_INVALID) { test_triangle<true>(tris, c2, o, d, L.h); if (STATS) st.tris++; t2 = T_INVALID; }
+    if (c3 < n && t3 != T_INVALID) { test_triangle<true>(tris, c3, o, d, L.h); if (STATS) st.tris++; t3 = T_INVALID; }
+  }
   if (ANYHIT && L.h.tri != SENTINEL) { L.cur = SENTINEL; return; }
   if (t0 > L.h.cull) t0 = T_INVALID;
   if (t1 > L.h.cull) t1 = T_INVALID;
@@ -178,7 +196,7 @@ __device__ __forceinline__ void lane_step(Lane& L, const WideNode* __restrict__ 
 #define CLRT_REFILL_MIN 12
 #endif
 #ifndef CLRT_BATCH
-#define CLRT_BATCH 64
+#define CLRT_BATCH 32
 #endif
 constexpr int WINDOW = CLRT_WINDOW;
 constexpr int REFILL_MIN = CLRT_REFILL_MIN;
