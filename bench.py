@@ -273,7 +273,7 @@ def main():
     ev0.record(stream)
     for s in range(args.warmup, args.warmup + args.steps):
         r.render_device(cams[s], True)
-    stream.wait_stream(r.comm)                     # join the gather/untile stream: every frame is complete at ev1
+    r.join()                                       # device-side join of the trace / gather streams: every frame is complete at ev1
     ev1.record(stream)
     barrier()
     dev_ms = ev0.elapsed_time(ev1)
@@ -285,7 +285,7 @@ def main():
     t_e2e0.record(stream)
     for s in range(args.warmup, args.warmup + args.steps):
         r.render_host_async(cams[s], True)         # two frames in flight; every frame's raster lands in pinned host memory
-    stream.wait_stream(r.comm)
+    r.join()
     t_e2e1.record(stream)
     barrier()
     e2e_ms = t_e2e0.elapsed_time(t_e2e1)
@@ -317,7 +317,7 @@ def main():
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 64, "d2h_bytes_per_step": RES[0] * RES[1] * 4,
                     "ms_per_step": e2e_ms / args.steps},
             "gpu_launches": args.steps * 3,   # trace_primary_kernel, shadow_shade_kernel, untile_kernel per step
-            "pipeline": "2 frames in flight: gather + untile (+ read-back) of frame k overlap the trace of frame k+1",
+            "pipeline": "3 frames in flight: frames traced on alternating streams (frame slots), gather + untile (+ read-back) on one more",
             "build_ms": build_med, "build_ms_per_Mtri": build_med / (n_tris / 1e6),
             "build_stage_ms": {"morton": float(stage_med[0]), "sort": float(stage_med[1]), "emit": float(stage_med[2]), "refit": float(stage_med[3]),
                                "trace_structure": float(stage_med[4])},

@@ -182,6 +182,12 @@ int clrt_shadow_shade(clrt_accel* accel, const clrt_camera* h_camera, const void
 int clrt_frame_stripe_pixels(uint32_t resX, uint32_t resY, uint32_t rank, uint32_t nranks, uint32_t* out_pixels, uint32_t* out_tiles);
 int clrt_render_stripe(clrt_accel* accel, const clrt_camera* h_camera, int shadows, uint32_t rank, uint32_t nranks,
                        void* dptr_rgba8, uint64_t* out_rays);
+/* The same on a caller-chosen cudaStream_t with frame slot `slot` (0..3): the slot's private work counter and scratch, so that
+ * frames submitted on different streams overlap on the device — the tail of one frame's persistent kernels (a few long rays)
+ * runs next to the head of the next frame's.  BVH with the fused shadow pass (or shadows == 0) only.  The caller orders reuse of
+ * a slot and of dptr_rgba8 (stream order / events). */
+int clrt_render_stripe_on(clrt_accel* accel, void* stream, int slot, const clrt_camera* h_camera, int shadows, uint32_t rank,
+                          uint32_t nranks, void* dptr_rgba8, uint64_t* out_rays);
 /* The frame entry points fuse the shadow pass with the shading on a BVH (occlusion queries inside one kernel).  on == 0
  * forces the three-call pipeline (clrt_generate_shadow_rays -> clrt_trace_rays -> clrt_shade); pixels are identical. */
 int clrt_accel_set_fused_shadows(clrt_accel* accel, int on);

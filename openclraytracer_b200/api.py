@@ -336,6 +336,13 @@ class AccelerationStructureManager:
                                            C.byref(rays) if want_rays else None))
         return rays.value
 
+    def render_stripe_on(self, stream, slot, camera, shadows, rank, nranks, dptr_rgba8, want_rays=False):
+        cam = np.ascontiguousarray(camera, dtype=L.CAMERA)
+        rays = C.c_uint64()
+        check(self._lib.clrt_render_stripe_on(self.handle, C.c_void_p(stream), slot, _ptr(cam), int(shadows), rank, nranks,
+                                              C.c_void_p(dptr_rgba8), C.byref(rays) if want_rays else None))
+        return rays.value
+
     def render_frame_host(self, camera, shadows, out_rgba8=None, want_rays=False):
         cam = np.ascontiguousarray(camera, dtype=L.CAMERA)
         if out_rgba8 is None:

@@ -20,6 +20,8 @@ static int accel_create(clrt_ctx* ctx, const clrt_scene* scene, AccelKind kind, 
   for (int i = 0; i <= CLRT_STAGE_COUNT; i++) CLRT_CUDA(cudaEventCreate(&a->ev[i]));
   CLRT_CUDA(cudaMalloc(&a->d_tile_counter, 64));
   CLRT_CUDA(cudaMemsetAsync(a->d_tile_counter, 0, 64, ctx->stream));
+  CLRT_CUDA(cudaMalloc(&a->d_slot_counters, 64 * clrt_accel::FRAME_SLOTS));
+  CLRT_CUDA(cudaMemsetAsync(a->d_slot_counters, 0, 64 * clrt_accel::FRAME_SLOTS, ctx->stream));
   *out = a;
   return 0;
 }
@@ -51,6 +53,8 @@ extern "C" int clrt_accel_destroy(clrt_accel* a) {
   if (a->d_frame_scratch) cudaFree(a->d_frame_scratch);
   if (a->d_fb) cudaFree(a->d_fb);
   if (a->d_tile_counter) cudaFree(a->d_tile_counter);
+  if (a->d_slot_counters) cudaFree(a->d_slot_counters);
+  for (int i = 0; i < clrt_accel::FRAME_SLOTS; i++) if (a->d_slot_scratch[i]) cudaFree(a->d_slot_scratch[i]);
   for (int i = 0; i <= CLRT_STAGE_COUNT; i++) if (a->ev[i]) cudaEventDestroy(a->ev[i]);
   delete a;
   return 0;
@@ -147,12 +151,25 @@ extern "C" int clrt_frame_stripe_pixels(uint32_t resX, uint32_t resY, uint32_t r
 }
 
 // scratch layout of one stripe: contacts[slots] | shadow rays[slots*(L+1)] | shadow contacts[slots*(L+1)] | ray counter
-extern "C" int clrt_render_stripe(clrt_accel* a, const clrt_camera* h_camera, int shadows, uint32_t rank, uint32_t nranks,
-                                  void* dptr_rgba8, uint64_t* out_rays) {
+// slot < 0: the context's stream, the accel's own scratch and counter.  slot >= 0: the caller's stream with the slot's private
+// scratch and counter, so that frames submitted on different streams overlap on the device (the tail of one frame's persistent
+// kernels — a few long rays — runs next to the head of the next frame's).
+static int render_stripe_impl(clrt_accel* a, const clrt_camera* h_camera, int shadows, uint32_t rank, uint32_t nranks,
+                              void* dptr_rgba8, uint64_t* out_rays, cudaStream_t stream, int slot) {
   if (!a || !h_camera || !dptr_rgba8) CLRT_FAIL("clrt_render_stripe: NULL argument");
   if (!nranks || rank >= nranks) CLRT_FAIL("clrt_render_stripe: rank %u of %u", rank, nranks);
   clrt_ctx* ctx = a->ctx;
   CLRT_CUDA(cudaSetDevice(ctx->device));
+  if (slot >= clrt_accel::FRAME_SLOTS) CLRT_FAIL("clrt_render_stripe_on: slot %d of %d", slot, clrt_accel::FRAME_SLOTS);
+  if (slot >= 0 && a->kind != ACCEL_BVH) CLRT_FAIL("clrt_render_stripe_on: frame slots exist for the BVH only");
+  if (slot < 0) stream = ctx->stream;
+  void** scratch_p = slot < 0 ? &a->d_frame_scratch : &a->d_slot_scratch[slot];
+  size_t* scratch_cap = slot < 0 ? &a->frame_scratch_cap : &a->slot_scratch_cap[slot];
+  struct LaunchEnv {                              // lends the slot's stream + counter to the trace launches of this call
+    clrt_accel* a;
+    LaunchEnv(clrt_accel* a_, cudaStream_t s, uint32_t* c) : a(a_) { a->launch_stream = s; a->launch_counter = c; }
+    ~LaunchEnv() { a->launch_stream = nullptr; a->launch_counter = nullptr; }
+  } env(a, slot < 0 ? nullptr : stream, slot < 0 ? nullptr : a->d_slot_counters + 16 * slot);
   const clrt_camera cam = *h_camera;
   const TileGrid g = make_tile_grid(cam.resX, cam.resY);
   const uint32_t tiles = stripe_tile_count(g.tiles, rank, nranks);
@@ -165,11 +182,11 @@ extern "C" int clrt_render_stripe(clrt_accel* a, const clrt_camera* h_camera, in
   const size_t srays_bytes = (shadows && !fused) ? (size_t)slots * L1 * sizeof(clrt_ray) : 0;
   const size_t scont_bytes = (shadows && !fused) ? (size_t)slots * L1 * sizeof(clrt_contact) : 0;
   const size_t total = contacts_bytes + srays_bytes + scont_bytes + 64;
-  if (total > a->frame_scratch_cap) {
-    CLRT_CUDA(cudaStreamSynchronize(ctx->stream));
-    CLRT_TRY(clrt_grow(&a->d_frame_scratch, &a->frame_scratch_cap, total));
+  if (total > *scratch_cap) {
+    CLRT_CUDA(cudaStreamSynchronize(stream));
+    CLRT_TRY(clrt_grow(scratch_p, scratch_cap, total));
   }
-  uint8_t* base = (uint8_t*)a->d_frame_scratch;
+  uint8_t* base = (uint8_t*)*scratch_p;
   clrt_contact* contacts = (clrt_contact*)base;
   clrt_ray* srays = (clrt_ray*)(base + contacts_bytes);
   clrt_contact* scont = (clrt_contact*)(base + contacts_bytes + srays_bytes);
@@ -177,13 +194,14 @@ extern "C" int clrt_render_stripe(clrt_accel* a, const clrt_camera* h_camera, in
   if (slots) {
     CLRT_TRY(accel_trace_primary(a, cam, contacts, rank, nranks));
     if (fused) {
-      CLRT_CUDA(cudaMemsetAsync(counter, 0, 8, ctx->stream));
+      CLRT_CUDA(cudaMemsetAsync(counter, 0, 8, stream));
       CLRT_TRY(bvh_shadow_shade(a, cam, contacts, slots, (uint32_t*)dptr_rgba8, out_rays ? counter : nullptr));
     } else if (shadows) {
       CLRT_CUDA(cudaMemsetAsync(counter, 0, 8, ctx->stream));
       CLRT_TRY(shade_launch_shadow_rays(ctx, a->scene, cam, contacts, slots, srays, out_rays ? counter : nullptr));
       CLRT_TRY(a->kind == ACCEL_BVH ? bvh_trace_rays(a, srays, scont, slots * L1) : tlg_trace_rays(a, srays, scont, slots * L1));
     }
+    if (!fused && slot >= 0) CLRT_FAIL("clrt_render_stripe_on: frame slots need the fused shadow pass");
     if (!fused) CLRT_TRY(shade_launch(ctx, a->scene, cam, contacts, slots, shadows ? scont : nullptr, (uint32_t*)dptr_rgba8, nullptr));
   }
   if (out_rays) {
@@ -197,11 +215,21 @@ extern "C" int clrt_render_stripe(clrt_accel* a, const clrt_camera* h_camera, in
       primary += (uint64_t)w * h;
     }
     unsigned long long srays_count = 0;
-    if (shadows && slots) CLRT_CUDA(cudaMemcpyAsync(&srays_count, counter, 8, cudaMemcpyDeviceToHost, ctx->stream));
-    CLRT_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (shadows && slots) CLRT_CUDA(cudaMemcpyAsync(&srays_count, counter, 8, cudaMemcpyDeviceToHost, stream));
+    CLRT_CUDA(cudaStreamSynchronize(stream));
     *out_rays = primary + srays_count;
   }
   return 0;
+}
+
+extern "C" int clrt_render_stripe(clrt_accel* a, const clrt_camera* h_camera, int shadows, uint32_t rank, uint32_t nranks,
+                                  void* dptr_rgba8, uint64_t* out_rays) {
+  return render_stripe_impl(a, h_camera, shadows, rank, nranks, dptr_rgba8, out_rays, nullptr, -1);
+}
+extern "C" int clrt_render_stripe_on(clrt_accel* a, void* stream, int slot, const clrt_camera* h_camera, int shadows, uint32_t rank,
+                                     uint32_t nranks, void* dptr_rgba8, uint64_t* out_rays) {
+  if (slot < 0) CLRT_FAIL("clrt_render_stripe_on: slot %d", slot);
+  return render_stripe_impl(a, h_camera, shadows, rank, nranks, dptr_rgba8, out_rays, (cudaStream_t)stream, slot);
 }
 
 extern "C" int clrt_render_frame_host(clrt_accel* a, const clrt_camera* h_camera, int shadows, void* h_rgba8, uint64_t* out_rays) {

@@ -463,6 +463,11 @@ int persistent_grid(clrt_ctx* ctx, K kernel, int threads, unsigned* grid) {
 
 // The structure a launch traverses: REFERENCE_ORDER always walks the reference topology; FAST walks the separate trace tree
 // (trace_tree.cu) when construct() built one, else the reference tree.
+// Where a launch goes: the context's stream and the accel's work counter, unless a frame slot lent its own (accel.cu:
+// frames in flight on several streams, each with a private counter and scratch).
+static inline cudaStream_t trace_stream(const clrt_accel* a) { return a->launch_stream ? a->launch_stream : a->ctx->stream; }
+static inline uint32_t* trace_counter(const clrt_accel* a) { return a->launch_counter ? a->launch_counter : a->d_tile_counter; }
+
 struct TraceView { const TraceNode* tnodes; const WideNode* wnodes; const clrt_triangle* tris; };
 static TraceView trace_view(const clrt_accel* a, bool fast) {
   if (fast && a->tt_built) return TraceView{a->d_tt_nodes, a->d_wnodes, a->d_tt_tris};
@@ -475,8 +480,8 @@ static int launch_primary(clrt_accel* a, const clrt_camera& cam, clrt_contact* o
   CLRT_TRY(persistent_grid(a->ctx, trace_primary_kernel<M, S>, TRACE_THREADS, &grid));
   grid = min(grid, (packets + 3) / 4);
   const TraceView v = trace_view(a, M != 0);
-  trace_primary_kernel<M, S><<<grid, TRACE_THREADS, 0, a->ctx->stream>>>(cam, v.tnodes, v.wnodes, v.tris, a->n, out, rank, nranks, raster,
-                                                                        a->d_tile_counter, (unsigned long long*)(a->d_tile_counter + 4));
+  trace_primary_kernel<M, S><<<grid, TRACE_THREADS, 0, trace_stream(a)>>>(cam, v.tnodes, v.wnodes, v.tris, a->n, out, rank, nranks, raster,
+                                                                        trace_counter(a), (unsigned long long*)(a->d_tile_counter + 4));
   CLRT_CHECK_LAUNCH();
   return 0;
 }
@@ -486,8 +491,8 @@ static int launch_rays(clrt_accel* a, const clrt_ray* rays, clrt_contact* out, u
   CLRT_TRY(persistent_grid(a->ctx, trace_rays_kernel<M, S>, TRACE_THREADS, &grid));
   grid = min(grid, (packets + 3) / 4);
   const TraceView v = trace_view(a, M != 0);
-  trace_rays_kernel<M, S><<<grid, TRACE_THREADS, 0, a->ctx->stream>>>(rays, count, v.tnodes, v.wnodes, v.tris, a->n, out,
-                                                                     a->d_tile_counter, (unsigned long long*)(a->d_tile_counter + 4));
+  trace_rays_kernel<M, S><<<grid, TRACE_THREADS, 0, trace_stream(a)>>>(rays, count, v.tnodes, v.wnodes, v.tris, a->n, out,
+                                                                     trace_counter(a), (unsigned long long*)(a->d_tile_counter + 4));
   CLRT_CHECK_LAUNCH();
   return 0;
 }
@@ -495,14 +500,13 @@ static int trace_mode_index(const clrt_accel* a) { return a->trace_mode == CLRT_
 
 int bvh_trace_primary(clrt_accel* a, const clrt_camera& cam, clrt_contact* out, uint32_t rank, uint32_t nranks) {
   const uint32_t resX = cam.resX, resY = cam.resY;
-  clrt_ctx* ctx = a->ctx;
   if (!a->built) CLRT_FAIL("generateContacts: the BVH was not constructed");
   const bool raster = (nranks == 0);                 // nranks == 0: whole frame, raster-ordered output
   if (raster) { rank = 0; nranks = 1; }
   const TileGrid g = make_tile_grid(resX, resY);
   const uint32_t packets = stripe_tile_count(g.tiles, rank, nranks) * 8u;
   if (!packets) return 0;
-  CLRT_CUDA(cudaMemsetAsync(a->d_tile_counter, 0, 4, ctx->stream));
+  CLRT_CUDA(cudaMemsetAsync(trace_counter(a), 0, 4, trace_stream(a)));
   const int m = trace_mode_index(a);
   if (a->stats) return m == 0 ? launch_primary<0, true>(a, cam, out, rank, nranks, raster, packets)
                               : launch_primary<1, true>(a, cam, out, rank, nranks, raster, packets);
@@ -511,11 +515,10 @@ int bvh_trace_primary(clrt_accel* a, const clrt_camera& cam, clrt_contact* out, 
 }
 
 int bvh_trace_rays(clrt_accel* a, const clrt_ray* rays, clrt_contact* out, uint32_t count) {
-  clrt_ctx* ctx = a->ctx;
   if (!a->built) CLRT_FAIL("generateContacts: the BVH was not constructed");
   if (!count) return 0;
   const uint32_t packets = (count + 31u) / 32u;
-  CLRT_CUDA(cudaMemsetAsync(a->d_tile_counter, 0, 4, ctx->stream));
+  CLRT_CUDA(cudaMemsetAsync(trace_counter(a), 0, 4, trace_stream(a)));
   const int m = trace_mode_index(a);
   if (a->stats) return m == 0 ? launch_rays<0, true>(a, rays, out, count, packets) : launch_rays<1, true>(a, rays, out, count, packets);
   return m == 0 ? launch_rays<0, false>(a, rays, out, count, packets) : launch_rays<1, false>(a, rays, out, count, packets);
@@ -529,8 +532,8 @@ static int launch_shadow_shade(clrt_accel* a, const clrt_camera& cam, const clrt
   CLRT_TRY(persistent_grid(a->ctx, shadow_shade_kernel<S>, TRACE_THREADS, &grid));
   grid = min(grid, (packets + 3) / 4);
   const TraceView v = trace_view(a, true);
-  shadow_shade_kernel<S><<<grid, TRACE_THREADS, 0, a->ctx->stream>>>(cam, contacts, count, sc->d_lights, sc->n_lights, sc->d_materials, sc->n_materials,
-      v.wnodes, v.tris, a->n, rgba8, a->d_tile_counter, d_ray_counter, (unsigned long long*)(a->d_tile_counter + 4));
+  shadow_shade_kernel<S><<<grid, TRACE_THREADS, 0, trace_stream(a)>>>(cam, contacts, count, sc->d_lights, sc->n_lights, sc->d_materials, sc->n_materials,
+      v.wnodes, v.tris, a->n, rgba8, trace_counter(a), d_ray_counter, (unsigned long long*)(a->d_tile_counter + 4));
   CLRT_CHECK_LAUNCH();
   return 0;
 }
@@ -538,12 +541,11 @@ static int launch_shadow_shade(clrt_accel* a, const clrt_camera& cam, const clrt
 // Fused shadow + shade over `count` contacts (BVH only).  d_ray_counter (may be NULL) accumulates the live shadow rays.
 int bvh_shadow_shade(clrt_accel* a, const clrt_camera& cam, const clrt_contact* contacts, uint32_t count, uint32_t* rgba8,
                      unsigned long long* d_ray_counter) {
-  clrt_ctx* ctx = a->ctx;
   if (!a->built) CLRT_FAIL("shadow pass: the BVH was not constructed");
   if (!count) return 0;
   if (a->scene->n_lights + 1 > 32) CLRT_FAIL("fused shadow pass supports at most 31 scene lights");
   const uint32_t packets = (count + 31u) / 32u;
-  CLRT_CUDA(cudaMemsetAsync(a->d_tile_counter, 0, 4, ctx->stream));
+  CLRT_CUDA(cudaMemsetAsync(trace_counter(a), 0, 4, trace_stream(a)));
   return a->stats ? launch_shadow_shade<true>(a, cam, contacts, count, rgba8, d_ray_counter, packets)
                   : launch_shadow_shade<false>(a, cam, contacts, count, rgba8, d_ray_counter, packets);
 }

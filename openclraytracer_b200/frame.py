@@ -6,8 +6,8 @@ once (redundant rebuild: a 1M-triangle LBVH build costs less than broadcasting i
 renders its stripe — 32x8-pixel tiles, tile t owned by rank t % world, persistent warps inside the GPU pull packets
 from an atomic counter — into a device buffer in stripe order; ONE collective (all-gather of equal, padded RGBA8
 stripes, 8.3 MB per 1080p frame) follows, and an untile kernel restores raster order.  No other exchange exists on
-the path.  Two frames are in flight: the collective, the untile and the read-back of frame k run on a second stream
-while the stripe of frame k+1 is traced.
+the path.  Three frames are in flight: frames are traced on alternating streams (frame slots of the C ABI) so that the
+latency-bound tail of one frame overlaps the next, and the collective, the untile and the read-back run on one more stream.
 
 PyTorch is plumbing here: device memory, the stream shared with NCCL, and the collective.
 """
@@ -92,10 +92,13 @@ class FrameRenderer:
         self.accel.initialize()
         self.cap = stripe_capacity(resX, resY, world)
         torch.cuda.synchronize()
-        # Two frames in flight: the stripe trace of frame k+1 (context stream) overlaps the gather + untile (+ read-back)
-        # of frame k on a second stream.  Buffers are double; events order reuse.
-        self.DEPTH = 2
+        # DEPTH frames in flight.  Frame k is traced on trace stream k % DEPTH with frame slot k % DEPTH of the C ABI (private
+        # work counter + scratch), so the tail of one frame's persistent kernels — a few long rays on a mostly idle GPU —
+        # overlaps the head of the next frame's; gather + untile (+ read-back) run on one more stream (`comm`), in frame
+        # order on every rank (the collective's order must agree across ranks).  Buffers are per slot; events order reuse.
+        self.DEPTH = 3 if accel.upper() == "BVH" else 1
         self.comm = torch.cuda.Stream(self.device)
+        self.trace_streams = [self.stream] + [torch.cuda.Stream(self.device) for _ in range(self.DEPTH - 1)]
         self.stripes = [torch.zeros(self.cap, dtype=torch.int32, device=self.device) for _ in range(self.DEPTH)]
         self.gathereds = [torch.zeros(self.cap * world, dtype=torch.int32, device=self.device) if world > 1 else self.stripes[i]
                           for i in range(self.DEPTH)]
@@ -108,8 +111,10 @@ class FrameRenderer:
         self.stripe, self.gathered, self.raster, self.host_raster = self.stripes[0], self.gathereds[0], self.rasters[0], self.host_rasters[0]
 
     def build(self):
+        self.join()
         self.accel.initializeFrame()
         self.accel.construct()
+        self.stream.synchronize()
 
     def _submit(self, camera, shadows, want_rays, to_host):
         torch = self.torch
@@ -117,10 +122,14 @@ class FrameRenderer:
         self.frame_no += 1
         if to_host:
             self.ev_host[k].synchronize()             # the host buffer of slot k may still be the target of frame k-DEPTH's copy
-        with torch.cuda.stream(self.stream):
-            self.stream.wait_event(self.ev_free[k])   # slot k's stripe buffer is free once frame k-DEPTH was gathered
-            rays = self.accel.render_stripe(camera, shadows, self.rank, self.world, self.stripes[k].data_ptr(), want_rays)
-            self.ev_traced[k].record(self.stream)
+        ts = self.trace_streams[k]
+        with torch.cuda.stream(ts):
+            ts.wait_event(self.ev_free[k])            # slot k's stripe buffer is free once frame k-DEPTH was gathered
+            if self.DEPTH > 1:
+                rays = self.accel.render_stripe_on(ts.cuda_stream, k, camera, shadows, self.rank, self.world, self.stripes[k].data_ptr(), want_rays)
+            else:
+                rays = self.accel.render_stripe(camera, shadows, self.rank, self.world, self.stripes[k].data_ptr(), want_rays)
+            self.ev_traced[k].record(ts)
         with torch.cuda.stream(self.comm):
             self.comm.wait_event(self.ev_traced[k])
             if self.world > 1:
@@ -153,10 +162,15 @@ class FrameRenderer:
         self.finish()
         return out
 
-    def finish(self):
-        """Joins the second stream into the context's stream and waits for both."""
+    def join(self):
+        """Makes the context's stream wait for every frame submitted so far (device-side join, no host wait)."""
+        for ts in self.trace_streams[1:]:
+            self.stream.wait_stream(ts)
         self.stream.wait_stream(self.comm)
-        self.comm.synchronize()
+
+    def finish(self):
+        """Joins all streams into the context's stream and waits for it."""
+        self.join()
         self.stream.synchronize()
 
     def close(self):
