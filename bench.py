@@ -329,7 +329,8 @@ def main():
         kd = kt[dom]
         achieved = kd["bytes"] / (kd["ms"] * 1e-3) / 1e9
         line["roofline"] = {"bound": "hbm", "kernel": "trace_primary_kernel" if dom == "primary" else "shadow_shade_kernel",
-                            "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": None,
+                            "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
+                            "traffic": ncu_traffic(args.workload, "trace_primary_kernel" if dom == "primary" else "shadow_shade_kernel"),
                             "peak_source": peak_src, "ms_per_launch": kd["ms"], "rays": kd["rays"],
                             "mrays_per_s_kernel_only": kd["rays"] / kd["ms"] / 1e3,
                             "note": "traversal is latency/divergence bound and served by L1/L2 (DESIGN.md section 4): the fraction explains, "
@@ -348,6 +349,16 @@ def main():
     r.close()
     if world > 1:
         dist.destroy_process_group()
+
+
+def ncu_traffic(workload, kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one launch of `kernel` from the committed `ncu --set full` capture of this
+    workload (profiles/r01_traffic.json, written by profiles/summarize.py); None when no capture is committed."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "r01_traffic.json")))
+        return t.get(f"{workload}_{kernel}")
+    except Exception:
+        return None
 
 
 def kernel_rooflines(r, hbm_peak, n_tris, stage_med):

@@ -182,7 +182,7 @@ int clrt_shadow_shade(clrt_accel* accel, const clrt_camera* h_camera, const void
 int clrt_frame_stripe_pixels(uint32_t resX, uint32_t resY, uint32_t rank, uint32_t nranks, uint32_t* out_pixels, uint32_t* out_tiles);
 int clrt_render_stripe(clrt_accel* accel, const clrt_camera* h_camera, int shadows, uint32_t rank, uint32_t nranks,
                        void* dptr_rgba8, uint64_t* out_rays);
-/* The same on a caller-chosen cudaStream_t with frame slot `slot` (0..3): the slot's private work counter and scratch, so that
+/* The same on a caller-chosen cudaStream_t with frame slot `slot` (0..7): the slot's private work counter and scratch, so that
  * frames submitted on different streams overlap on the device — the tail of one frame's persistent kernels (a few long rays)
  * runs next to the head of the next frame's.  BVH with the fused shadow pass (or shadows == 0) only.  The caller orders reuse of
  * a slot and of dptr_rgba8 (stream order / events). */

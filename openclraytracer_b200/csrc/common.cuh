@@ -118,8 +118,8 @@ struct clrt_accel {
   void* d_fb = nullptr; size_t fb_cap = 0;
   uint32_t* d_tile_counter = nullptr;
   // frame slots: frames in flight on caller-chosen streams (clrt_render_stripe_on), each with its own work counter + scratch
-  static constexpr int FRAME_SLOTS = 4;
-  void* d_slot_scratch[FRAME_SLOTS] = {nullptr, nullptr, nullptr, nullptr}; size_t slot_scratch_cap[FRAME_SLOTS] = {0, 0, 0, 0};
+  static constexpr int FRAME_SLOTS = 8;
+  void* d_slot_scratch[FRAME_SLOTS] = {nullptr}; size_t slot_scratch_cap[FRAME_SLOTS] = {0};
   uint32_t* d_slot_counters = nullptr;            // FRAME_SLOTS x 64 B
   cudaStream_t launch_stream = nullptr;           // set only while a slot's launches are being enqueued
   uint32_t* launch_counter = nullptr;

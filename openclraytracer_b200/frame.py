@@ -11,6 +11,8 @@ latency-bound tail of one frame overlaps the next, and the collective, the until
 
 PyTorch is plumbing here: device memory, the stream shared with NCCL, and the collective.
 """
+import os
+
 import numpy as np
 
 from . import api, layouts as L
@@ -96,7 +98,7 @@ class FrameRenderer:
         # work counter + scratch), so the tail of one frame's persistent kernels — a few long rays on a mostly idle GPU —
         # overlaps the head of the next frame's; gather + untile (+ read-back) run on one more stream (`comm`), in frame
         # order on every rank (the collective's order must agree across ranks).  Buffers are per slot; events order reuse.
-        self.DEPTH = 3 if accel.upper() == "BVH" else 1
+        self.DEPTH = max(1, min(8, int(os.environ.get("CLRT_FRAME_DEPTH", "4")))) if accel.upper() == "BVH" else 1
         self.comm = torch.cuda.Stream(self.device)
         self.trace_streams = [self.stream] + [torch.cuda.Stream(self.device) for _ in range(self.DEPTH - 1)]
         self.stripes = [torch.zeros(self.cap, dtype=torch.int32, device=self.device) for _ in range(self.DEPTH)]

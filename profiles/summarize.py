@@ -36,13 +36,14 @@ def raw(path):
 
 def main():
     lines = [f"# ncu --set full summaries ({TAG})", "",
-             "Command: `python bench.py --steps 2 --warmup 3 --no-cpu-baseline` (profiles/capture.sh), `--clock-control none`.",
+             "Commands: `python bench.py --steps 2 --warmup 3 --no-cpu-baseline --workload <w>` and `python profiles/sort_probe.py 24` (profiles/capture.sh), `--clock-control none`; section names carry the workload.",
              "Numbers under a profiler are cold-cache and serialised; they explain, the bench line measures.", ""]
     for path in sorted(glob.glob(os.path.join(ROOT, "gpurun_out", f"full_*_{TAG}.ncu-rep"))):
         hdr, units, rows = raw(path)
         idx = {h: i for i, h in enumerate(hdr)}
         name = rows[0][idx["Kernel Name"]].split("(")[0].replace("void ", "").replace("<unnamed>::", "")
-        lines.append(f"## {name}  ({len(rows)} launches captured)")
+        tag = os.path.basename(path)[len("full_"):].split("_")[0]
+        lines.append(f"## [{tag}] {name}  ({len(rows)} launches captured)")
         lines.append("")
         lines.append("| metric | " + " | ".join(f"launch {k}" for k in range(len(rows))) + " | unit |")
         lines.append("|---|" + "---|" * (len(rows) + 1))
@@ -58,9 +59,9 @@ def main():
                      ", ".join(f"{h[len('smsp__average_warps_issue_stalled_'):-len('_per_issue_active.ratio')]}={v[0]:.2f}" for h, v in stalls[:5]))
         lines.append("")
     open(os.path.join(ROOT, "profiles", f"{TAG}_kernels.md"), "w").write("\n".join(lines) + "\n")
-    # launch list -> per-kernel totals
-    lp = os.path.join(ROOT, "gpurun_out", f"launches_{TAG}.csv")
-    if os.path.exists(lp):
+    # launch lists (one per workload) -> per-kernel totals
+    for lp in sorted(glob.glob(os.path.join(ROOT, "gpurun_out", f"launches_*_{TAG}.csv"))):
+        wl = os.path.basename(lp)[len("launches_"):-len(f"_{TAG}.csv")]
         text = open(lp).read()
         start = text.index('"ID"')
         rows = list(csv.DictReader(io.StringIO(text[start:])))
@@ -70,18 +71,30 @@ def main():
                 continue
             k = r["Kernel Name"].split("(")[0]
             v = float(r["Metric Value"].replace(",", ""))
-            if r["Metric Unit"] in ("us", "usecond"):
-                v *= 1.0
-            elif r["Metric Unit"] in ("ns", "nsecond"):
+            if r["Metric Unit"] in ("ns", "nsecond"):
                 v /= 1e3
             elif r["Metric Unit"] in ("ms", "msecond"):
                 v *= 1e3
             tot[k][0] += 1; tot[k][1] += v
         total = sum(v[1] for v in tot.values())
-        with open(os.path.join(ROOT, "profiles", f"{TAG}_launches.csv"), "w") as f:
+        with open(os.path.join(ROOT, "profiles", f"{TAG}_launches_{wl}.csv"), "w") as f:
             f.write("kernel,launches,total_us,share_pct,avg_us\n")
             for k, (c, t) in sorted(tot.items(), key=lambda kv: -kv[1][1]):
                 f.write(f"\"{k}\",{c},{t:.1f},{100 * t / total:.2f},{t / c:.2f}\n")
+        import shutil
+        shutil.copy(lp, os.path.join(ROOT, "profiles", f"{TAG}_launch_list_raw_{wl}.csv"))
+    # DRAM traffic per launch of the captured kernels -> profiles/<tag>_traffic.json (bench.py's roofline.traffic)
+    import json
+    traffic = {}
+    for path in sorted(glob.glob(os.path.join(ROOT, "gpurun_out", f"full_*_{TAG}.ncu-rep"))):
+        hdr, units, rows = raw(path)
+        idx = {h: i for i, h in enumerate(hdr)}
+        def val(m, r):
+            v = float(r[idx[m]].replace(",", "")); u = units[idx[m]]
+            return v * {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(u, 1)
+        name = os.path.basename(path)[len("full_"):-len(f"_{TAG}.ncu-rep")]
+        traffic[name] = val("dram__bytes_read.sum", rows[0]) + val("dram__bytes_write.sum", rows[0])
+    json.dump(traffic, open(os.path.join(ROOT, "profiles", f"{TAG}_traffic.json"), "w"), indent=1, sort_keys=True)
     print(open(os.path.join(ROOT, "profiles", f"{TAG}_kernels.md")).read()[:200])
 
 
