@@ -317,7 +317,7 @@ def main():
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 64, "d2h_bytes_per_step": RES[0] * RES[1] * 4,
                     "ms_per_step": e2e_ms / args.steps},
             "gpu_launches": args.steps * 3,   # trace_primary_kernel, shadow_shade_kernel, untile_kernel per step
-            "pipeline": "3 frames in flight: frames traced on alternating streams (frame slots), gather + untile (+ read-back) on one more",
+            "pipeline": f"{r.DEPTH} frames in flight: frames traced on alternating streams (frame slots), gather + untile (+ read-back) on one more",
             "build_ms": build_med, "build_ms_per_Mtri": build_med / (n_tris / 1e6),
             "build_stage_ms": {"morton": float(stage_med[0]), "sort": float(stage_med[1]), "emit": float(stage_med[2]), "refit": float(stage_med[3]),
                                "trace_structure": float(stage_med[4])},

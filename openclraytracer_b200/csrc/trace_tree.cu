@@ -131,17 +131,24 @@ tt_refit_kernel(const float4* __restrict__ leafbox, const uint32_t* __restrict__
 // 2-level collapse: wide node i = the grandchildren of binary node i (a leaf child stays as it is).  One thread per binary
 // inner node, 3 x 64 B in, 128 B out; no ordering between nodes is needed because EVERY binary node gets a wide node —
 // the ones not reachable through wide links are never visited.
-__device__ __forceinline__ void wn_put(WideNode& w, int& k, uint32_t child, float x0, float y0, float z0, float x1, float y1, float z1) {
-  w.lox[k] = x0; w.loy[k] = y0; w.loz[k] = z0; w.hix[k] = x1; w.hiy[k] = y1; w.hiz[k] = z1; w.child[k] = child; k++;
-}
-__device__ __forceinline__ void wn_expand(WideNode& w, int& k, const TraceNode* __restrict__ tnodes, uint32_t n, uint32_t child,
-                                          float x0, float y0, float z0, float x1, float y1, float z1) {
-  if (child < n) { wn_put(w, k, child, x0, y0, z0, x1, y1, z1); return; }
+// Slots 0,1 come from child A, slots 2,3 from child B (a leaf child fills one slot, the other stays empty): static slot
+// indices keep the node in registers (a running slot index put it in local memory: lg_throttle = 174 in the first capture).
+struct Slot2 { float4 lo0, hi0, lo1, hi1; uint32_t c0, c1; };     // .xyz used
+__device__ __forceinline__ Slot2 wn_expand(const TraceNode* __restrict__ tnodes, uint32_t n, uint32_t child,
+                                           float x0, float y0, float z0, float x1, float y1, float z1) {
+  const float qnan = __int_as_float(0x7fc00000);          // empty slot: a NaN box fails every comparison of the slab test
+  Slot2 s;
+  if (child < n) {
+    s.lo0 = make_float4(x0, y0, z0, 0.0f); s.hi0 = make_float4(x1, y1, z1, 0.0f); s.c0 = child;
+    s.lo1 = make_float4(qnan, qnan, qnan, 0.0f); s.hi1 = s.lo1; s.c1 = 0xFFFFFFFFu;
+    return s;
+  }
   const float4* p = reinterpret_cast<const float4*>(tnodes + (child - n));
   const float4 q0 = __ldg(p), q1 = __ldg(p + 1), q2 = __ldg(p + 2);
   const uint4 q3 = __ldg(reinterpret_cast<const uint4*>(p + 3));
-  wn_put(w, k, q3.x, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y);
-  wn_put(w, k, q3.y, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w);
+  s.lo0 = make_float4(q0.x, q0.y, q0.z, 0.0f); s.hi0 = make_float4(q0.w, q1.x, q1.y, 0.0f); s.c0 = q3.x;
+  s.lo1 = make_float4(q1.z, q1.w, q2.x, 0.0f); s.hi1 = make_float4(q2.y, q2.z, q2.w, 0.0f); s.c1 = q3.y;
+  return s;
 }
 __global__ void __launch_bounds__(128)
 widen_kernel(const TraceNode* __restrict__ tnodes, uint32_t n, WideNode* __restrict__ wnodes) {
@@ -150,17 +157,17 @@ widen_kernel(const TraceNode* __restrict__ tnodes, uint32_t n, WideNode* __restr
   const float4* p = reinterpret_cast<const float4*>(tnodes + i);
   const float4 q0 = __ldg(p), q1 = __ldg(p + 1), q2 = __ldg(p + 2);
   const uint4 q3 = __ldg(reinterpret_cast<const uint4*>(p + 3));
-  WideNode w;
-  int k = 0;
-  wn_expand(w, k, tnodes, n, q3.x, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y);
-  wn_expand(w, k, tnodes, n, q3.y, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w);
-  const float qnan = __int_as_float(0x7fc00000);          // empty slot: a NaN box fails every comparison of the slab test
-  for (; k < 4; ) wn_put(w, k, 0xFFFFFFFFu, qnan, qnan, qnan, qnan, qnan, qnan);
-  w.pad[0] = w.pad[1] = w.pad[2] = w.pad[3] = 0u;
+  const Slot2 a = wn_expand(tnodes, n, q3.x, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y);
+  const Slot2 b = wn_expand(tnodes, n, q3.y, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w);
   float4* o = reinterpret_cast<float4*>(wnodes + i);
-  const float4* src = reinterpret_cast<const float4*>(&w);
-#pragma unroll
-  for (int j = 0; j < 8; j++) o[j] = src[j];
+  o[0] = make_float4(a.lo0.x, a.lo1.x, b.lo0.x, b.lo1.x);
+  o[1] = make_float4(a.lo0.y, a.lo1.y, b.lo0.y, b.lo1.y);
+  o[2] = make_float4(a.lo0.z, a.lo1.z, b.lo0.z, b.lo1.z);
+  o[3] = make_float4(a.hi0.x, a.hi1.x, b.hi0.x, b.hi1.x);
+  o[4] = make_float4(a.hi0.y, a.hi1.y, b.hi0.y, b.hi1.y);
+  o[5] = make_float4(a.hi0.z, a.hi1.z, b.hi0.z, b.hi1.z);
+  reinterpret_cast<uint4*>(o)[6] = make_uint4(a.c0, a.c1, b.c0, b.c1);
+  reinterpret_cast<uint4*>(o)[7] = make_uint4(0u, 0u, 0u, 0u);
 }
 
 } // namespace
