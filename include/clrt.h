@@ -163,6 +163,12 @@ int clrt_generate_primary_rays(clrt_ctx* ctx, const clrt_camera* h_camera, void*
  * pass produce a degenerate ray with idx = UINT_MAX that the trace kernels skip.  dptr_rays: n*(L+1)*48 B. */
 int clrt_generate_shadow_rays(clrt_ctx* ctx, const clrt_scene* scene, const clrt_camera* h_camera,
                               const void* dptr_contacts, uint32_t n, void* dptr_rays, uint32_t* out_rays_per_contact);
+/* One cosine-weighted diffuse bounce ray per contact (incoherent secondary rays: BASELINE.json configs[3]; the reference's
+ * TODO, KNOWN_ISSUES_AND_TODO.txt:27-33): ray i leaves the hit point of contact i (pushed 1e-4 * t along the normal turned
+ * against the incoming ray) in a direction drawn from splitmix64(seed * 0x9E3779B97F4A7C15 + pixelIndex); misses give the
+ * degenerate ray (idx = UINT_MAX, zero direction).  Trace them with clrt_trace_rays.  dptr_rays: n * 48 B. */
+int clrt_generate_bounce_rays(clrt_ctx* ctx, const clrt_camera* h_camera, const void* dptr_contacts, uint32_t n, uint64_t seed,
+                              void* dptr_rays);
 /* Blinn-Phong of every contact -> RGBA8 (and/or float4) at the contact's slot.  dptr_shadow_contacts (may be
  * NULL) are the contacts of the shadow rays above: a light whose shadow ray hit before reaching it adds nothing. */
 int clrt_shade(clrt_ctx* ctx, const clrt_scene* scene, const clrt_camera* h_camera, const void* dptr_contacts,

@@ -437,6 +437,11 @@ def generate_shadow_rays(context, scene, camera, dptr_contacts, n, dptr_rays):
     return per.value
 
 
+def generate_bounce_rays(context, camera, dptr_contacts, n, seed, dptr_rays):
+    cam = np.ascontiguousarray(camera, dtype=L.CAMERA)
+    check(_lib.load().clrt_generate_bounce_rays(context.handle, _ptr(cam), C.c_void_p(dptr_contacts), n, C.c_uint64(seed), C.c_void_p(dptr_rays)))
+
+
 def shade(context, scene, camera, dptr_contacts, n, dptr_shadow=None, dptr_rgba8=None, dptr_rgba_f32=None):
     cam = np.ascontiguousarray(camera, dtype=L.CAMERA)
     check(_lib.load().clrt_shade(context.handle, scene.handle, _ptr(cam), C.c_void_p(dptr_contacts), n,

@@ -46,6 +46,46 @@ shadow_rays_kernel(clrt_camera cam, const clrt_contact* __restrict__ contacts, u
   if ((threadIdx.x & 31) == 0 && m && ray_counter) atomicAdd(ray_counter, (unsigned long long)__popc(m));
 }
 
+// Incoherent secondary rays (BASELINE.json configs[3]; the reference's TODO list names them,
+// KNOWN_ISSUES_AND_TODO.txt:27-33): one cosine-weighted diffuse bounce per primary hit.  The two uniforms come from
+// splitmix64(seed * 0x9E3779B97F4A7C15 + pixelIndex) (high / low 24 bits), the direction is Malley's: a uniform disk point
+// lifted to the hemisphere around the geometric normal turned against the incoming ray; the origin is pushed 1e-4 * t along
+// that normal (the shadow rays' offset).  Misses give the zero-direction ray the trace kernels answer without traversal.
+__device__ __forceinline__ uint64_t splitmix64_dev(uint64_t x) {
+  x += 0x9E3779B97F4A7C15ull;
+  x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+  x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+  return x ^ (x >> 31);
+}
+__global__ void __launch_bounds__(256)
+bounce_rays_kernel(clrt_camera cam, const clrt_contact* __restrict__ contacts, uint32_t n, uint64_t seed, clrt_ray* __restrict__ rays) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint4 head = __ldg(reinterpret_cast<const uint4*>(contacts + i));
+  const float4 nd = __ldg(reinterpret_cast<const float4*>(contacts + i) + 1);
+  uint4 h = make_uint4(0xFFFFFFFFu, 0u, 0u, 0u);
+  float4 ro = make_float4(0.f, 0.f, 0.f, 0.f), rd = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (nd.w > 0.0f && head.x != 0xFFFFFFFFu) {
+    Vec3 o, d; generate_ray(cam, head.x, o, d);
+    Vec3 nrm = v3(nd.x, nd.y, nd.z);
+    if (vdot(nrm, d) > 0.0f) nrm = vscale(nrm, -1.0f);                        // face the incoming ray (two-sided triangles)
+    const Vec3 P = vadd(o, vscale(d, nd.w));
+    const uint64_t u = splitmix64_dev(seed * 0x9E3779B97F4A7C15ull + (uint64_t)head.x);
+    const float u1 = (float)(uint32_t)(u >> 40) * (1.0f / 16777216.0f), u2 = (float)(uint32_t)(u & 0xFFFFFFu) * (1.0f / 16777216.0f);
+    const float r = sqrtf(u1), phi = 6.283185307179586f * u2;
+    float sn, cs; sincosf(phi, &sn, &cs);
+    const float dx = r * cs, dy = r * sn, dz = sqrtf(fmaxf(0.0f, 1.0f - u1));
+    // orthonormal basis around the normal: the axis least aligned with it, crossed twice
+    const Vec3 ax = fabsf(nrm.x) < 0.5f ? v3(1.0f, 0.0f, 0.0f) : v3(0.0f, 1.0f, 0.0f);
+    const Vec3 t1 = vnormalize(vcross(ax, nrm)), t2 = vcross(nrm, t1);
+    const Vec3 dir = vnormalize(vadd(vadd(vscale(t1, dx), vscale(t2, dy)), vscale(nrm, dz)));
+    const Vec3 org = vadd(P, vscale(nrm, SHADOW_EPS_REL * nd.w));
+    h.x = head.x; ro = make_float4(org.x, org.y, org.z, 0.f); rd = make_float4(dir.x, dir.y, dir.z, 0.f);
+  }
+  uint4* p = reinterpret_cast<uint4*>(rays + i);
+  p[0] = h; reinterpret_cast<float4*>(p)[1] = ro; reinterpret_cast<float4*>(p)[2] = rd;
+}
+
 // One thread per contact.
 __global__ void __launch_bounds__(256)
 shade_kernel(clrt_camera cam, const clrt_contact* __restrict__ contacts, uint32_t n, const clrt_light* __restrict__ lights,
@@ -118,6 +158,16 @@ extern "C" int clrt_generate_shadow_rays(clrt_ctx* ctx, const clrt_scene* scene,
   CLRT_CUDA(cudaSetDevice(ctx->device));
   if (out_rays_per_contact) *out_rays_per_contact = scene->n_lights + 1;
   return shade_launch_shadow_rays(ctx, scene, *h_camera, (const clrt_contact*)dptr_contacts, n, (clrt_ray*)dptr_rays, nullptr);
+}
+
+extern "C" int clrt_generate_bounce_rays(clrt_ctx* ctx, const clrt_camera* h_camera, const void* dptr_contacts, uint32_t n, uint64_t seed,
+                                         void* dptr_rays) {
+  if (!ctx || !h_camera || (n && (!dptr_contacts || !dptr_rays))) CLRT_FAIL("clrt_generate_bounce_rays: NULL argument");
+  CLRT_CUDA(cudaSetDevice(ctx->device));
+  if (!n) return 0;
+  bounce_rays_kernel<<<(n + 255) / 256, 256, 0, ctx->stream>>>(*h_camera, (const clrt_contact*)dptr_contacts, n, seed, (clrt_ray*)dptr_rays);
+  CLRT_CHECK_LAUNCH();
+  return 0;
 }
 
 extern "C" int clrt_shade(clrt_ctx* ctx, const clrt_scene* scene, const clrt_camera* h_camera, const void* dptr_contacts,
