@@ -143,10 +143,13 @@ __device__ __forceinline__ void lane_step(Lane& L, const WideNode* __restrict__ 
   float t1 = child_entry(lx.y, ly.y, lz.y, hx.y, hy.y, hz.y, o, inv, L.h.cull);
   float t2 = child_entry(lx.z, ly.z, lz.z, hx.z, hy.z, hz.z, o, inv, L.h.cull);
   float t3 = child_entry(lx.w, ly.w, lz.w, hx.w, hy.w, hz.w, o, inv, L.h.cull);
-  // Accepted leaf children are POSTPONED: their ids go to a four-entry queue in registers and the triangle tests of the whole
-  // warp run together at the end of the window (flush_leaves).  Tested on the spot, the Moeller-Trumbore code ran with 2.7 of
-  // 32 lanes (ncu source view: 17 % of all issue slots for 2 tests per ray), because only ~9 % of the lane-steps find a leaf.
-  // The price is a cull distance that is up to a window late.  A fifth leaf within one window is tested at once.
+  // Leaves.  Closest-hit rays test them on the spot, in ONE looped copy of the triangle test (a hit shrinks the cull distance
+  // before the inner children are ordered).  Occlusion queries POSTPONE them: the ids go to a four-entry queue in registers and
+  // the triangle tests of the whole warp run together at the end of the window (flush_leaves).  Tested on the spot, the
+  // Moeller-Trumbore code ran with 2.7 of 32 lanes (ncu source view: 17 % of the issue slots), because only ~9 % of the
+  // lane-steps find a leaf; an occlusion query has a fixed cull distance, so waiting costs nothing but a few extra visits
+  // (shadow pass -10 %); for closest-hit rays the late cull distance ate the gain (measured).  A fifth leaf in a window is
+  // tested at once.
   {
     uint32_t leaves = (c0 < n && t0 != T_INVALID ? 1u : 0u) | (c1 < n && t1 != T_INVALID ? 2u : 0u) |
                       (c2 < n && t2 != T_INVALID ? 4u : 0u) | (c3 < n && t3 != T_INVALID ? 8u : 0u);
@@ -157,7 +160,7 @@ __device__ __forceinline__ void lane_step(Lane& L, const WideNode* __restrict__ 
     while (leaves) {
       const uint32_t id = (leaves & 1u) ? c0 : (leaves & 2u) ? c1 : (leaves & 4u) ? c2 : c3;
       leaves &= leaves - 1u;
-      if (L.qn < 4u) { L.q3 = L.q2; L.q2 = L.q1; L.q1 = L.q0; L.q0 = id; L.qn++; }
+      if (ANYHIT && L.qn < 4u) { L.q3 = L.q2; L.q2 = L.q1; L.q1 = L.q0; L.q0 = id; L.qn++; }
       else { test_triangle<true>(tris, id, o, d, L.h); if (STATS) st.tris++; }
     }
   }
@@ -248,7 +251,7 @@ __device__ __forceinline__ void run_jobs(Job& job, const WideNode* __restrict__ 
 #pragma unroll 1
     for (int k = 0; k < WINDOW; k++)
       if (busy && L.cur != SENTINEL) lane_step<STATS, ANYHIT>(L, wnodes, tris, n, st, stack);
-    flush_leaves<STATS, ANYHIT>(L, tris, st);
+    if (ANYHIT) flush_leaves<STATS, ANYHIT>(L, tris, st);
   }
 }
 
