@@ -84,7 +84,7 @@ radix_scan_hist_kernel(uint32_t* __restrict__ hist, int passes) {
 
 // ---- one onesweep pass ---------------------------------------------------------------------------------
 template <int IPT, bool FULL>
-__global__ void __launch_bounds__(SORT_THREADS, 3)
+__global__ void __launch_bounds__(SORT_THREADS, 4)
 onesweep_pass_kernel(const uint2* __restrict__ in, uint2* __restrict__ out, uint32_t n, int shift,
                      const uint32_t* __restrict__ digit_base,   // [BINS] exclusive global offsets of this pass
                      uint32_t* __restrict__ status,             // [tiles][BINS] look-back descriptors (zeroed)
