@@ -48,7 +48,6 @@ extern "C" int clrt_accel_destroy(clrt_accel* a) {
   if (a->d_refpos) cudaFree(a->d_refpos);
   trace_tree_destroy(a);
   if (a->d_tris_sorted) cudaFree(a->d_tris_sorted);
-  if (a->d_leafbox_sorted) cudaFree(a->d_leafbox_sorted);
   if (a->d_contacts) cudaFree(a->d_contacts);
   if (a->d_frame_scratch) cudaFree(a->d_frame_scratch);
   if (a->d_fb) cudaFree(a->d_fb);

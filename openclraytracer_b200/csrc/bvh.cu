@@ -135,7 +135,7 @@ __device__ __forceinline__ int2 determine_range(const uint2* __restrict__ list, 
 // which is the tie-break the FAST traversal uses to pick the reference's winner on exact ties.
 __global__ void __launch_bounds__(256)
 karras_emit_kernel(const clrt_uint2* __restrict__ pairs_, uint32_t n, clrt_bvh_node* __restrict__ nodes,
-                   const clrt_triangle* __restrict__ tris, clrt_triangle* __restrict__ tris_sorted, float4* __restrict__ leafbox_sorted,
+                   const clrt_triangle* __restrict__ tris, clrt_triangle* __restrict__ tris_sorted,
                    TraceNode* __restrict__ tnodes, uint32_t* __restrict__ max_run, uint32_t* __restrict__ refpos) {
   const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= n) return;
@@ -149,8 +149,6 @@ karras_emit_kernel(const clrt_uint2* __restrict__ pairs_, uint32_t n, clrt_bvh_n
     refpos[leaf] = idx;
     float4* dst = reinterpret_cast<float4*>(tris_sorted + idx);
     dst[0] = a; dst[1] = b; dst[2] = c;
-    const float4* lb = reinterpret_cast<const float4*>(nodes + leaf) + 1;      // leaf box written by morton_leaves_kernel
-    leafbox_sorted[2 * (size_t)idx] = lb[0]; leafbox_sorted[2 * (size_t)idx + 1] = lb[1];
   }
   if (idx + 1 >= n) return;
   const int2 range = determine_range(list, (int)idx, n);
@@ -213,7 +211,7 @@ __device__ __forceinline__ Box6 box_clamped(const Box6& b) {                  //
 }
 
 __global__ void __launch_bounds__(256)
-chain_suffix_kernel(const uint2* __restrict__ list, uint32_t n, const float4* __restrict__ leafbox_sorted,
+chain_suffix_kernel(const uint2* __restrict__ list, uint32_t n,
                     clrt_bvh_node* __restrict__ nodes, TraceNode* __restrict__ tnodes) {
   const unsigned FULL = 0xffffffffu;
   const int lane = threadIdx.x & 31;
@@ -246,7 +244,8 @@ chain_suffix_kernel(const uint2* __restrict__ list, uint32_t n, const float4* __
       const bool valid = p >= (int64_t)s + 1;
       Box6 v; v.lx = v.ly = v.lz = v.hx = v.hy = v.hz = 0.0f;
       if (valid) {
-        const float4 lo = __ldg(leafbox_sorted + 2 * (size_t)p), hb = __ldg(leafbox_sorted + 2 * (size_t)p + 1);
+        const float4* lb = reinterpret_cast<const float4*>(nodes + __ldg(&list[p].y)) + 1;        // leaf box of morton_leaves_kernel
+        const float4 lo = __ldcg(lb), hb = __ldcg(lb + 1);
         v.lx = lo.x; v.ly = lo.y; v.lz = lo.z; v.hx = hb.x; v.hy = hb.y; v.hz = hb.z;
       }
       const Box6 leaf = v;
@@ -286,7 +285,7 @@ refit_atomic_kernel(clrt_bvh_node* __restrict__ nodes, uint32_t* __restrict__ co
                     const uint2* __restrict__ list, const uint32_t* __restrict__ refpos) {
   const uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x;
   if (gid >= n) return;
-  uint32_t current;
+  uint32_t current, me = gid;
   {
     const uint32_t pos = __ldg(refpos + gid);
     const uint32_t c = __ldg(&list[pos].x);
@@ -294,19 +293,24 @@ refit_atomic_kernel(clrt_bvh_node* __restrict__ nodes, uint32_t* __restrict__ co
     const bool prev2Eq = prevEq && pos > 1 && __ldg(&list[pos - 2].x) == c;
     const bool nextEq = pos + 1 < n && __ldg(&list[pos + 1].x) == c;
     if (prev2Eq) return;                                                     // s+2..e: inside a pre-computed chain
-    current = (prevEq && nextEq) ? __ldcg(&nodes[n + pos].data[0])           // s+1 of a run of 3+: the chain's parent
-                                 : __ldcg(&nodes[gid].data[0]);
+    if (prevEq && nextEq) me = n + pos;                                      // s+1 of a run of 3+: stands in for chain node s+1
+    current = __ldcg(&nodes[me].data[0]);
   }
+  // The thread carries the box of the subtree it comes from (`me`) in registers; per level it needs ONE dependent load (the
+  // sibling's box) after the arrival atomic — the parent's header (children, grandparent) is static and is fetched while the
+  // fence and the atomic are in flight.
+  float4 mlo = ldcg4(reinterpret_cast<const float4*>(nodes + me) + 1), mhi = ldcg4(reinterpret_cast<const float4*>(nodes + me) + 2);
   while (current != 0xFFFFFFFFu) {
-    __threadfence();                                         // make this thread's box (written below) visible first
-    const uint32_t arrived = atomicAdd(counters + (current - n), 1u);
+    const uint4 d = __ldcg(reinterpret_cast<const uint4*>(nodes + current));   // {parent, childA, childB, -}: written by the emit stage
+    // release: this thread's box (written below / by the leaf stage) is visible before the count; acquire: the sibling's box,
+    // written before ITS increment, is visible after ours (Q3: the reference has neither and races)
+    uint32_t arrived;
+    asm volatile("atom.add.acq_rel.gpu.global.u32 %0, [%1], 1;" : "=r"(arrived) : "l"(counters + (current - n)) : "memory");
     if (arrived == 0) return;                                // first arrival: the sibling subtree is not done yet
-    __threadfence();
-    const uint4 d = __ldcg(reinterpret_cast<const uint4*>(nodes + current));
-    const uint32_t cA = d.y, cB = d.z;
-    const float4* pa = reinterpret_cast<const float4*>(nodes + cA) + 1;
-    const float4* pb = reinterpret_cast<const float4*>(nodes + cB) + 1;
-    const float4 a0 = ldcg4(pa), a1 = ldcg4(pa + 1), b0 = ldcg4(pb), b1 = ldcg4(pb + 1);
+    const bool fromA = d.y == me;
+    const float4* ps = reinterpret_cast<const float4*>(nodes + (fromA ? d.z : d.y)) + 1;
+    const float4 s0 = ldcg4(ps), s1 = ldcg4(ps + 1);
+    const float4 a0 = fromA ? mlo : s0, a1 = fromA ? mhi : s1, b0 = fromA ? s0 : mlo, b1 = fromA ? s1 : mhi;
     // merge3(childA, childB, self) (AABB.h:107-113) with self = (FLT_MAX,FLT_MAX,FLT_MAX,INNER=0.0f),(FLT_MIN,FLT_MIN,FLT_MIN,0.0f)
     float4 lo, hi;
     lo.x = rmin(rmin(a0.x, b0.x), RT_FLT_MAX); lo.y = rmin(rmin(a0.y, b0.y), RT_FLT_MAX); lo.z = rmin(rmin(a0.z, b0.z), RT_FLT_MAX);
@@ -319,6 +323,7 @@ refit_atomic_kernel(clrt_bvh_node* __restrict__ nodes, uint32_t* __restrict__ co
     __stcg(tn,     make_float4(a0.x, a0.y, a0.z, a1.x));
     __stcg(tn + 1, make_float4(a1.y, a1.z, b0.x, b0.y));
     __stcg(tn + 2, make_float4(b0.z, b1.x, b1.y, b1.z));
+    mlo = lo; mhi = hi; me = current;
     current = d.x;
   }
 }
@@ -335,7 +340,7 @@ int bvh_init_frame(clrt_accel* a) {
   a->pairs_items = pow2ceil_u32(n ? n : 1);                  // the reference pads to 2^k for its bitonic sort (BVHManager.cpp:129-131)
   const size_t nodes_bytes = (size_t)(n ? 2 * (size_t)n - 1 : 1) * sizeof(clrt_bvh_node);
   if (nodes_bytes > a->nodes_cap || (size_t)a->pairs_items * 8 > a->pairs_cap || (size_t)n * 4 > a->counters_cap ||
-      (size_t)n * 4 > a->refpos_cap || (size_t)n * sizeof(TraceNode) > a->tnodes_cap || (size_t)n * sizeof(clrt_triangle) > a->tris_sorted_cap || (size_t)n * 32 > a->leafbox_cap)
+      (size_t)n * 4 > a->refpos_cap || (size_t)n * sizeof(TraceNode) > a->tnodes_cap || (size_t)n * sizeof(clrt_triangle) > a->tris_sorted_cap)
     CLRT_CUDA(cudaStreamSynchronize(ctx->stream));
   CLRT_TRY(clrt_grow((void**)&a->d_nodes, &a->nodes_cap, nodes_bytes));
   CLRT_TRY(clrt_grow((void**)&a->d_pairs, &a->pairs_cap, (size_t)a->pairs_items * 8));
@@ -343,7 +348,6 @@ int bvh_init_frame(clrt_accel* a) {
   CLRT_TRY(clrt_grow((void**)&a->d_refpos, &a->refpos_cap, (size_t)(n ? n : 1) * 4));
   CLRT_TRY(clrt_grow((void**)&a->d_tnodes, &a->tnodes_cap, (size_t)(n ? n : 1) * sizeof(TraceNode)));
   CLRT_TRY(clrt_grow((void**)&a->d_tris_sorted, &a->tris_sorted_cap, (size_t)(n ? n : 1) * sizeof(clrt_triangle)));
-  CLRT_TRY(clrt_grow((void**)&a->d_leafbox_sorted, &a->leafbox_cap, (size_t)(n ? n : 1) * 32));
   // fills of initializeFrame (BVHManager.cpp:138-147): pairs = (UINT_MAX,UINT_MAX), counters = 0
   CLRT_CUDA(cudaMemsetAsync(a->d_pairs, 0xFF, (size_t)a->pairs_items * 8, ctx->stream));
   CLRT_CUDA(cudaMemsetAsync(a->d_counters, 0, (size_t)(n ? n : 1) * 4, ctx->stream));
@@ -370,12 +374,12 @@ int bvh_construct(clrt_accel* a) {
   if (tm) CLRT_CUDA(cudaEventRecord(a->ev[2], s));
   CLRT_CUDA(cudaMemsetAsync(a->d_tile_counter + 12, 0, 4, s));
   if (n) {
-    karras_emit_kernel<<<(n + 255) / 256, 256, 0, s>>>(a->d_pairs, n, a->d_nodes, a->scene->d_tris, a->d_tris_sorted, a->d_leafbox_sorted, a->d_tnodes, a->d_tile_counter + 12, a->d_refpos);
+    karras_emit_kernel<<<(n + 255) / 256, 256, 0, s>>>(a->d_pairs, n, a->d_nodes, a->scene->d_tris, a->d_tris_sorted, a->d_tnodes, a->d_tile_counter + 12, a->d_refpos);
     CLRT_CHECK_LAUNCH();
   }
   if (tm) CLRT_CUDA(cudaEventRecord(a->ev[3], s));
   if (n > 1) {
-    chain_suffix_kernel<<<(n + 255) / 256, 256, 0, s>>>(reinterpret_cast<const uint2*>(a->d_pairs), n, a->d_leafbox_sorted, a->d_nodes, a->d_tnodes);
+    chain_suffix_kernel<<<(n + 255) / 256, 256, 0, s>>>(reinterpret_cast<const uint2*>(a->d_pairs), n, a->d_nodes, a->d_tnodes);
     CLRT_CHECK_LAUNCH();
     refit_atomic_kernel<<<(n + 255) / 256, 256, 0, s>>>(a->d_nodes, a->d_counters, n, a->d_tnodes, reinterpret_cast<const uint2*>(a->d_pairs), a->d_refpos);
     CLRT_CHECK_LAUNCH();

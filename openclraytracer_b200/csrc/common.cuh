@@ -98,7 +98,6 @@ struct clrt_accel {
   uint32_t* d_counters = nullptr; size_t counters_cap = 0;    // N x 4 B
   TraceNode* d_tnodes = nullptr;  size_t tnodes_cap = 0;      // (N-1) x 64 B
   clrt_triangle* d_tris_sorted = nullptr; size_t tris_sorted_cap = 0;   // N x 48 B, sorted-leaf order, v1.w = triangle id
-  float4* d_leafbox_sorted = nullptr; size_t leafbox_cap = 0;           // N x 32 B: leaf boxes (min, max) in sorted-leaf order
   uint32_t* d_refpos = nullptr; size_t refpos_cap = 0;                  // N x 4 B: triangle -> position in the reference's sorted order
   uint32_t pairs_items = 0;
   uint32_t max_run = 0;           // longest collapsed equal-key run (read back after construct; decides whether a trace tree is built)

@@ -117,9 +117,9 @@ tt_refit_kernel(const float4* __restrict__ leafbox, const uint32_t* __restrict__
   while (link != 0xFFFFFFFFu) {
     const uint32_t node = link >> 1, side = link & 1u;
     tt_store_child_box(tnodes + node, side, lo, hi);
-    __threadfence();
-    if (atomicAdd(counters + node, 1u) == 0) return;          // the sibling subtree is not done yet
-    __threadfence();
+    uint32_t arrived;                                         // release our box / acquire the sibling's (one acq_rel atomic, no fences)
+    asm volatile("atom.add.acq_rel.gpu.global.u32 %0, [%1], 1;" : "=r"(arrived) : "l"(counters + node) : "memory");
+    if (arrived == 0) return;                                 // the sibling subtree is not done yet
     const float* f = reinterpret_cast<const float*>(tnodes + node) + (side ? 0 : 6);     // the sibling's box
     const float sx0 = __ldcg(f), sy0 = __ldcg(f + 1), sz0 = __ldcg(f + 2), sx1 = __ldcg(f + 3), sy1 = __ldcg(f + 4), sz1 = __ldcg(f + 5);
     lo.x = fminf(lo.x, sx0); lo.y = fminf(lo.y, sy0); lo.z = fminf(lo.z, sz0);
