@@ -2,17 +2,17 @@
 """bench.py — the headline benchmark of BASELINE.json on N B200s of one box.
 
 metric   : Mrays/s (primary + shadow rays, 1920x1080), whole job.  Also reported: BVH build ms per M triangles.
-workload : BASELINE.json configs[1] — the largest bundled TestModels mesh present (ClumsyDragon, 50 032 triangles;
-           Skull / swfighter are missing blobs), LBVH build once, then per step ONE 1080p frame: primary rays, one
-           shadow ray per hit per light (scene light + the reference's camera light), Blinn-Phong shading.
-           `--workload soup1m` selects configs[2] (1M-triangle random soup) instead.
+workload : default `soup1m` = BASELINE.json configs[2], the configuration the metric is quoted on at 1/2/4/8 B200 (synthetic
+           1M-triangle random soup, 46 sub-meshes); `--workload clumsydragon` = configs[1], the largest bundled TestModels mesh
+           present (50 032 triangles; Skull / swfighter are missing blobs).  LBVH build once, then per step ONE 1080p frame:
+           primary rays, one shadow ray per hit per light (scene light + the reference's camera light), Blinn-Phong shading.
 step     : one frame of the moving demo camera.  N > 1: the frame is sharded in image space (tile stripes), the
            RGBA8 stripes are all-gathered — total work fixed => "scaling": "strong".
 value    : rays traced by all ranks / device time (CUDA events on the launching stream, max over ranks), with the
            camera and the built structure already resident.
-e2e      : the same through FrameRenderer.render_host (what a user calls): host camera in, pinned-host RGBA8 raster out.
-roofline : the dominant kernel of the step (BVH traversal): algorithmic bytes = node + triangle + contact bytes its
-           rays touch (counted by the same traversal policy on the CPU oracle for a sample of rays),
+e2e      : the same through FrameRenderer.render_host_async (what a user calls; frames in flight): host camera in, pinned-host RGBA8 raster out.
+roofline : the dominant kernel of the step (BVH traversal): algorithmic bytes = wide-node + triangle + contact bytes its
+           rays touch (counted by the kernel's statistics mode),
            against the measured HBM copy peak — traversal is latency/divergence bound, so this fraction explains
            rather than bounds; the HBM-bound build kernels are reported per kernel under "kernels".
 cpu_baseline / --impl reference : the reference's own CPU code for the path (oracle/_ref/libclrt_ref.so = its headers
@@ -211,7 +211,8 @@ def main():
     ap.add_argument("--steps", type=int, default=30)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="clumsydragon", choices=["clumsydragon", "soup1m"])
+    ap.add_argument("--workload", default="soup1m", choices=["clumsydragon", "soup1m"],
+                    help="soup1m = BASELINE.json configs[2] (the config the metric is quoted on at 1/2/4/8 GPUs; default), clumsydragon = configs[1]")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-kernels", action="store_true", help="skip the per-kernel build/sort/scan roofline section")
     args = ap.parse_args()

@@ -16,6 +16,7 @@
 //  * REFERENCE_ORDER policy: the binary reference topology through 64-byte TraceNodes (both child boxes + child ids in
 //    one record), child A before child B, no culling, leaves go through the stack — the reference's exact visiting order, hence bit-identical contacts including the winners of exact ties.  Parity vehicle.
 //  Box validity is the reference's in both policies: `t > 0 || origin inside` with the compare-select slab test.
+#include <stdlib.h>
 #include "common.cuh"
 #include "rtmath.cuh"
 #include "shade_math.cuh"
@@ -464,12 +465,25 @@ shadow_shade_kernel(const clrt_camera cam, const clrt_contact* __restrict__ cont
   if (STATS) flush_stats(st, stats);
 }
 
+// Grid of a persistent launch.  Resident capacity (148 SMs x occupancy; queried once per kernel) caps it.  A synchronous call
+// wants the shortest kernel: one 32-unit packet per warp is enough to start every warp.  A launch in a FRAME SLOT (several frames
+// in flight on their own streams) wants throughput: warps that hold an SM slot must have work for their whole life, so the grid
+// is sized for `rays_per_lane` units per lane and the other frames' kernels take the rest of the machine — with one unit per
+// lane a 1/8 stripe held every slot of the GPU while most lanes had already run out of work.
 template <typename K>
-int persistent_grid(clrt_ctx* ctx, K kernel, int threads, unsigned* grid) {
-  int per_sm = 0;
-  CLRT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, 0));
-  if (per_sm < 1) per_sm = 1;
-  *grid = (unsigned)(ctx->sm_count * per_sm);
+int persistent_grid(clrt_accel* a, K kernel, int threads, uint32_t packets, unsigned* grid) {
+  static int per_sm = 0;                       // one instance per kernel template instantiation
+  if (per_sm == 0) {
+    CLRT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, 0));
+    if (per_sm < 1) per_sm = 1;
+  }
+  static int rays_per_lane = 0;
+  if (rays_per_lane == 0) { const char* e = getenv("CLRT_RAYS_PER_LANE"); rays_per_lane = e ? atoi(e) : 4; if (rays_per_lane < 1) rays_per_lane = 1; }
+  const unsigned resident = (unsigned)(a->ctx->sm_count * per_sm);
+  const unsigned warps_per_cta = (unsigned)threads / 32u;
+  const unsigned want = a->launch_stream ? (packets + warps_per_cta * rays_per_lane - 1) / (warps_per_cta * rays_per_lane)
+                                         : (packets + warps_per_cta - 1) / warps_per_cta;
+  *grid = min(resident, max(1u, want));
   return 0;
 }
 
@@ -491,8 +505,7 @@ static TraceView trace_view(const clrt_accel* a, bool fast) {
 template <int M, bool S>
 static int launch_primary(clrt_accel* a, const clrt_camera& cam, clrt_contact* out, uint32_t rank, uint32_t nranks, int raster, uint32_t packets) {
   unsigned grid = 0;
-  CLRT_TRY(persistent_grid(a->ctx, trace_primary_kernel<M, S>, TRACE_THREADS, &grid));
-  grid = min(grid, (packets + 3) / 4);
+  CLRT_TRY(persistent_grid(a, trace_primary_kernel<M, S>, TRACE_THREADS, packets, &grid));
   const TraceView v = trace_view(a, M != 0);
   trace_primary_kernel<M, S><<<grid, TRACE_THREADS, 0, trace_stream(a)>>>(cam, v.tnodes, v.wnodes, v.tris, a->n, out, rank, nranks, raster,
                                                                         trace_counter(a), (unsigned long long*)(a->d_tile_counter + 4));
@@ -502,8 +515,7 @@ static int launch_primary(clrt_accel* a, const clrt_camera& cam, clrt_contact* o
 template <int M, bool S>
 static int launch_rays(clrt_accel* a, const clrt_ray* rays, clrt_contact* out, uint32_t count, uint32_t packets) {
   unsigned grid = 0;
-  CLRT_TRY(persistent_grid(a->ctx, trace_rays_kernel<M, S>, TRACE_THREADS, &grid));
-  grid = min(grid, (packets + 3) / 4);
+  CLRT_TRY(persistent_grid(a, trace_rays_kernel<M, S>, TRACE_THREADS, packets, &grid));
   const TraceView v = trace_view(a, M != 0);
   trace_rays_kernel<M, S><<<grid, TRACE_THREADS, 0, trace_stream(a)>>>(rays, count, v.tnodes, v.wnodes, v.tris, a->n, out,
                                                                      trace_counter(a), (unsigned long long*)(a->d_tile_counter + 4));
@@ -543,8 +555,7 @@ static int launch_shadow_shade(clrt_accel* a, const clrt_camera& cam, const clrt
                                unsigned long long* d_ray_counter, uint32_t packets) {
   const clrt_scene* sc = a->scene;
   unsigned grid = 0;
-  CLRT_TRY(persistent_grid(a->ctx, shadow_shade_kernel<S>, TRACE_THREADS, &grid));
-  grid = min(grid, (packets + 3) / 4);
+  CLRT_TRY(persistent_grid(a, shadow_shade_kernel<S>, TRACE_THREADS, packets, &grid));
   const TraceView v = trace_view(a, true);
   shadow_shade_kernel<S><<<grid, TRACE_THREADS, 0, trace_stream(a)>>>(cam, contacts, count, sc->d_lights, sc->n_lights, sc->d_materials, sc->n_materials,
       v.wnodes, v.tris, a->n, rgba8, trace_counter(a), d_ray_counter, (unsigned long long*)(a->d_tile_counter + 4));

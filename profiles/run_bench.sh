@@ -1,5 +1,5 @@
 timeout 700 python -m pytest tests -m gpu -q -x 2>&1 | tail -6
-timeout 300 python bench.py --steps 20 --warmup 5 --no-cpu-baseline --no-kernels 2>&1 | tail -1 > gpurun_out/b_cd.json
+timeout 300 python bench.py --steps 20 --warmup 5 --no-cpu-baseline --no-kernels --workload clumsydragon 2>&1 | tail -1 > gpurun_out/b_cd.json
 timeout 300 python bench.py --steps 20 --warmup 5 --no-cpu-baseline --no-kernels --workload soup1m 2>&1 | tail -1 > gpurun_out/b_soup.json
 python - <<PY
 import json
