@@ -312,13 +312,15 @@ def main():
             "dtype": "f32", "data": DATA[args.workload],
             "config": {"workload": workload_desc, "resolution": "1920x1080", "accel": "LBVH", "triangles": n_tris,
                        "rays_per_step": total_rays // args.steps, "shadow": "1 per hit per light (scene light + camera light)",
-                       "parallelism": f"image-space tile stripes x{world}, redundant build, all-gather of RGBA8 stripes",
+                       "parallelism": f"image-space tile stripes x{world}, redundant build, " + EXCHANGE_DESC[r.exchange],
                        "l2": "per-step working set (contacts + shadow rays + shadow contacts, >400 MB at 1080p) exceeds the 126 MB L2; "
                              "the camera moves every step; the BVH stays L2 resident as in steady-state rendering"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 64, "d2h_bytes_per_step": RES[0] * RES[1] * 4,
                     "ms_per_step": e2e_ms / args.steps},
-            "gpu_launches": args.steps * 3,   # trace_primary_kernel, shadow_shade_kernel, untile_kernel per step
-            "pipeline": f"{r.DEPTH} frames in flight: frames traced on alternating streams (frame slots), gather + untile (+ read-back) on one more",
+            # trace_primary_kernel, shadow_shade_kernel + untile_kernel (nccl) | push, 2 signal, 2 wait (push) | 2 signal, 2 wait (fused)
+            "gpu_launches": args.steps * {"nccl": 3, "push": 7, "fused": 6}[r.exchange],
+            "pipeline": f"{r.DEPTH} frames in flight: frames traced on alternating streams (frame slots)" +
+                        (", gather + untile (+ read-back) on one more" if r.exchange == "nccl" else ", exchange + read-back on the frame's own stream"),
             "build_ms": build_med, "build_ms_per_Mtri": build_med / (n_tris / 1e6),
             "build_stage_ms": {"morton": float(stage_med[0]), "sort": float(stage_med[1]), "emit": float(stage_med[2]), "refit": float(stage_med[3]),
                                "trace_structure": float(stage_med[4])},
@@ -350,6 +352,11 @@ def main():
     r.close()
     if world > 1:
         dist.destroy_process_group()
+
+
+EXCHANGE_DESC = {"nccl": "all-gather of RGBA8 stripes",
+                 "push": "stripes pushed into every GPU's framebuffer over peer memory (no collective)",
+                 "fused": "pixels stored by the shading kernel into every GPU's framebuffer over peer memory (no collective)"}
 
 
 def ncu_traffic(workload, kernel):

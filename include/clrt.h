@@ -202,6 +202,33 @@ int clrt_frame_untile(clrt_ctx* ctx, const void* dptr_stripes, uint32_t resX, ui
  * stream while frame k+1 is traced on the context's stream). */
 int clrt_frame_untile_on(clrt_ctx* ctx, void* stream, const void* dptr_stripes, uint32_t resX, uint32_t resY, uint32_t nranks,
                          void* dptr_raster_rgba8);
+
+/* ---- frame exchange over peer memory (one process per GPU of one box; new, the reference is single-device:
+ * OpenCLRayTracerDemo.cpp:271-326).  Every process allocates its raster framebuffers and a block of flag words with
+ * clrt_peer_alloc, exports them (64-byte cudaIpc handle, carried to the peers by any host channel) and opens its peers'.
+ * A frame then needs no collective: each GPU stores the pixels of its own tiles into EVERY GPU's framebuffer over NVLink —
+ * from the shading kernel (clrt_render_stripe_peers) or by one pass over its stripe buffer (clrt_frame_push) — raises a word on
+ * every peer (clrt_peer_signal) and waits for the others' words (clrt_peer_wait).  All calls are asynchronous on `stream`. */
+#define CLRT_PEER_HANDLE_BYTES 64
+int clrt_peer_alloc(clrt_ctx* ctx, uint64_t bytes, void** out_dptr);            /* zeroed, exportable device memory */
+int clrt_peer_free(clrt_ctx* ctx, void* dptr);
+int clrt_peer_export(clrt_ctx* ctx, void* dptr, uint8_t* out_handle64);
+int clrt_peer_open(clrt_ctx* ctx, const uint8_t* handle64, void** out_dptr);    /* another process's allocation */
+int clrt_peer_close(clrt_ctx* ctx, void* dptr);
+/* clrt_render_stripe_on with shadows, the pixels going to peer_rasters[0..nranks) (raster order, resX*resY RGBA8 each;
+ * peer_rasters[rank] is this GPU's own) instead of a stripe buffer. */
+int clrt_render_stripe_peers(clrt_accel* accel, void* stream, int slot, const clrt_camera* h_camera, uint32_t rank, uint32_t nranks,
+                             void* const* peer_rasters, uint64_t* out_rays);
+/* This GPU's stripe buffer (as written by clrt_render_stripe[_on]) -> raster position in every peer's framebuffer. */
+int clrt_frame_push(clrt_ctx* ctx, void* stream, const void* dptr_stripe, uint32_t resX, uint32_t resY, uint32_t rank,
+                    uint32_t nranks, void* const* peer_rasters);
+/* peer_words[p][word] = value for p in 0..npeers, ordered behind everything enqueued on `stream` before (release, system scope). */
+int clrt_peer_signal(clrt_ctx* ctx, void* stream, void* const* peer_words, uint32_t npeers, uint32_t word, uint32_t value);
+/* Blocks `stream` (not the host) until words[first_word .. first_word+n) are all >= value (acquire, system scope).  After
+ * timeout_ms (0: 10 s) the waiting kernel traps: the next synchronisation reports a CUDA error instead of hanging. */
+int clrt_peer_wait(clrt_ctx* ctx, void* stream, const void* dptr_words, uint32_t first_word, uint32_t n, uint32_t value,
+                   uint32_t timeout_ms);
+
 /* Whole frame with HOST output: upload camera, trace, (shadow,) shade, download RGBA8 raster — the e2e path. */
 int clrt_render_frame_host(clrt_accel* accel, const clrt_camera* h_camera, int shadows, void* h_rgba8, uint64_t* out_rays);
 

@@ -343,6 +343,14 @@ class AccelerationStructureManager:
                                               C.c_void_p(dptr_rgba8), C.byref(rays) if want_rays else None))
         return rays.value
 
+    def render_stripe_peers(self, stream, slot, camera, rank, nranks, peer_rasters, want_rays=False):
+        """peer_rasters: ctypes array of nranks device pointers (peer_pointer_array)."""
+        cam = np.ascontiguousarray(camera, dtype=L.CAMERA)
+        rays = C.c_uint64()
+        check(self._lib.clrt_render_stripe_peers(self.handle, C.c_void_p(stream), slot, _ptr(cam), rank, nranks, peer_rasters,
+                                                 C.byref(rays) if want_rays else None))
+        return rays.value
+
     def render_frame_host(self, camera, shadows, out_rgba8=None, want_rays=False):
         cam = np.ascontiguousarray(camera, dtype=L.CAMERA)
         if out_rgba8 is None:
@@ -457,6 +465,53 @@ def frame_untile(context, dptr_stripes, resX, resY, nranks, dptr_raster):
 def frame_untile_on(context, stream, dptr_stripes, resX, resY, nranks, dptr_raster):
     check(_lib.load().clrt_frame_untile_on(context.handle, C.c_void_p(stream), C.c_void_p(dptr_stripes), resX, resY, nranks,
                                            C.c_void_p(dptr_raster)))
+
+
+# ---- frame exchange over peer memory (include/clrt.h, csrc/peer.cu) -----------------------------------------------------------
+PEER_HANDLE_BYTES = 64
+
+
+def peer_pointer_array(ptrs):
+    return (C.c_void_p * len(ptrs))(*[C.c_void_p(int(p)) for p in ptrs])
+
+
+def peer_alloc(context, nbytes):
+    p = C.c_void_p()
+    check(_lib.load().clrt_peer_alloc(context.handle, nbytes, C.byref(p)))
+    return p.value
+
+
+def peer_free(context, dptr):
+    check(_lib.load().clrt_peer_free(context.handle, C.c_void_p(dptr)))
+
+
+def peer_export(context, dptr):
+    buf = C.create_string_buffer(PEER_HANDLE_BYTES)
+    check(_lib.load().clrt_peer_export(context.handle, C.c_void_p(dptr), buf))
+    return buf.raw
+
+
+def peer_open(context, handle):
+    assert len(handle) == PEER_HANDLE_BYTES
+    p = C.c_void_p()
+    check(_lib.load().clrt_peer_open(context.handle, handle, C.byref(p)))
+    return p.value
+
+
+def peer_close(context, dptr):
+    check(_lib.load().clrt_peer_close(context.handle, C.c_void_p(dptr)))
+
+
+def frame_push(context, stream, dptr_stripe, resX, resY, rank, nranks, peer_rasters):
+    check(_lib.load().clrt_frame_push(context.handle, C.c_void_p(stream), C.c_void_p(dptr_stripe), resX, resY, rank, nranks, peer_rasters))
+
+
+def peer_signal(context, stream, peer_words, npeers, word, value):
+    check(_lib.load().clrt_peer_signal(context.handle, C.c_void_p(stream), peer_words, npeers, word, value))
+
+
+def peer_wait(context, stream, dptr_words, first_word, n, value, timeout_ms=0):
+    check(_lib.load().clrt_peer_wait(context.handle, C.c_void_p(stream), C.c_void_p(dptr_words), first_word, n, value, timeout_ms))
 
 
 def frame_stripe_pixels(resX, resY, rank, nranks):

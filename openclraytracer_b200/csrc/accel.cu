@@ -6,7 +6,7 @@
 int shade_launch_shadow_rays(clrt_ctx* ctx, const clrt_scene* scene, const clrt_camera& cam, const clrt_contact* contacts,
                              uint32_t n, clrt_ray* rays, unsigned long long* d_counter);
 int shade_launch(clrt_ctx* ctx, const clrt_scene* scene, const clrt_camera& cam, const clrt_contact* contacts, uint32_t n,
-                 const clrt_contact* shadow, uint32_t* rgba8, float4* rgba_f32);
+                 const clrt_contact* shadow, uint32_t* rgba8, float4* rgba_f32, cudaStream_t stream);
 
 int bvh_shadow_shade(clrt_accel* a, const clrt_camera& cam, const clrt_contact* contacts, uint32_t count, uint32_t* rgba8,
                      unsigned long long* d_ray_counter);
@@ -200,8 +200,8 @@ static int render_stripe_impl(clrt_accel* a, const clrt_camera* h_camera, int sh
       CLRT_TRY(shade_launch_shadow_rays(ctx, a->scene, cam, contacts, slots, srays, out_rays ? counter : nullptr));
       CLRT_TRY(a->kind == ACCEL_BVH ? bvh_trace_rays(a, srays, scont, slots * L1) : tlg_trace_rays(a, srays, scont, slots * L1));
     }
-    if (!fused && slot >= 0) CLRT_FAIL("clrt_render_stripe_on: frame slots need the fused shadow pass");
-    if (!fused) CLRT_TRY(shade_launch(ctx, a->scene, cam, contacts, slots, shadows ? scont : nullptr, (uint32_t*)dptr_rgba8, nullptr));
+    if (!fused && shadows && slot >= 0) CLRT_FAIL("clrt_render_stripe_on: frame slots need the fused shadow pass");
+    if (!fused) CLRT_TRY(shade_launch(ctx, a->scene, cam, contacts, slots, shadows ? scont : nullptr, (uint32_t*)dptr_rgba8, nullptr, stream));
   }
   if (out_rays) {
     // primary rays = pixels of this stripe that lie inside the image; shadow rays = live rays counted on the device
@@ -229,6 +229,23 @@ extern "C" int clrt_render_stripe_on(clrt_accel* a, void* stream, int slot, cons
                                      uint32_t nranks, void* dptr_rgba8, uint64_t* out_rays) {
   if (slot < 0) CLRT_FAIL("clrt_render_stripe_on: slot %d", slot);
   return render_stripe_impl(a, h_camera, shadows, rank, nranks, dptr_rgba8, out_rays, (cudaStream_t)stream, slot);
+}
+
+// The fused exchange: the shading kernel stores each pixel of this GPU's tiles into the raster-ordered framebuffer of every GPU of
+// the box (peer.cu); no stripe buffer, no gather, no untile.
+extern "C" int clrt_render_stripe_peers(clrt_accel* a, void* stream, int slot, const clrt_camera* h_camera, uint32_t rank, uint32_t nranks,
+                                        void* const* peer_rasters, uint64_t* out_rays) {
+  if (!a || !peer_rasters || !nranks || nranks > 8 || rank >= nranks) CLRT_FAIL("clrt_render_stripe_peers: bad argument");
+  if (slot < 0) CLRT_FAIL("clrt_render_stripe_peers: slot %d", slot);
+  if (a->kind != ACCEL_BVH || a->scene->n_lights + 1 > 32 || a->unfused_shadows)
+    CLRT_FAIL("clrt_render_stripe_peers: needs the BVH with the fused shadow pass");
+  struct Targets {
+    clrt_accel* a;
+    Targets(clrt_accel* a_, void* const* p, uint32_t n) : a(a_) { a->launch_targets.n = n; for (uint32_t i = 0; i < 8; i++) a->launch_targets.p[i] = i < n ? (uint32_t*)p[i] : nullptr; }
+    ~Targets() { a->launch_targets.n = 0; }
+  } targets(a, peer_rasters, nranks);
+  for (uint32_t i = 0; i < nranks; i++) if (!peer_rasters[i]) CLRT_FAIL("clrt_render_stripe_peers: peer %u is NULL", i);
+  return render_stripe_impl(a, h_camera, 1, rank, nranks, peer_rasters[rank], out_rays, (cudaStream_t)stream, slot);
 }
 
 extern "C" int clrt_render_frame_host(clrt_accel* a, const clrt_camera* h_camera, int shadows, void* h_rgba8, uint64_t* out_rays) {

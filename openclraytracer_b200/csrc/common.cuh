@@ -79,6 +79,10 @@ struct __align__(16) WideNode {
   uint32_t pad[4];
 };
 
+// Peer framebuffers of the image-space exchange (accel.cu: clrt_render_stripe_p2p): up to 8 raster-ordered RGBA8 buffers, one per
+// GPU of the box (the local one included), that the shading kernel writes its pixels into directly over NVLink.
+struct PeerTargets { uint32_t* p[8]; uint32_t n; };
+
 enum AccelKind { ACCEL_BVH = 0, ACCEL_TLG = 1 };
 
 struct clrt_accel {
@@ -121,6 +125,7 @@ struct clrt_accel {
   void* d_slot_scratch[FRAME_SLOTS] = {nullptr}; size_t slot_scratch_cap[FRAME_SLOTS] = {0};
   uint32_t* d_slot_counters = nullptr;            // FRAME_SLOTS x 64 B
   cudaStream_t launch_stream = nullptr;           // set only while a slot's launches are being enqueued
+  PeerTargets launch_targets = {{nullptr}, 0};     // ditto: peer framebuffers of a p2p frame (n == 0: write the local stripe buffer)
   uint32_t* launch_counter = nullptr;
   // --- TLG --- (tlg.cu)
   struct TlgState* tlg = nullptr;

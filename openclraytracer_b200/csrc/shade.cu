@@ -144,9 +144,9 @@ int shade_launch_shadow_rays(clrt_ctx* ctx, const clrt_scene* scene, const clrt_
 }
 
 int shade_launch(clrt_ctx* ctx, const clrt_scene* scene, const clrt_camera& cam, const clrt_contact* contacts, uint32_t n,
-                 const clrt_contact* shadow, uint32_t* rgba8, float4* rgba_f32) {
+                 const clrt_contact* shadow, uint32_t* rgba8, float4* rgba_f32, cudaStream_t stream) {
   if (!n) return 0;
-  shade_kernel<<<(n + 255) / 256, 256, 0, ctx->stream>>>(cam, contacts, n, scene->d_lights, scene->n_lights, scene->d_materials,
+  shade_kernel<<<(n + 255) / 256, 256, 0, stream ? stream : ctx->stream>>>(cam, contacts, n, scene->d_lights, scene->n_lights, scene->d_materials,
                                                         scene->n_materials, shadow, rgba8, rgba_f32);
   CLRT_CHECK_LAUNCH();
   return 0;
@@ -176,7 +176,7 @@ extern "C" int clrt_shade(clrt_ctx* ctx, const clrt_scene* scene, const clrt_cam
   if (!dptr_rgba8 && !dptr_rgba_f32) CLRT_FAIL("clrt_shade: no output buffer");
   CLRT_CUDA(cudaSetDevice(ctx->device));
   return shade_launch(ctx, scene, *h_camera, (const clrt_contact*)dptr_contacts, n, (const clrt_contact*)dptr_shadow_contacts,
-                      (uint32_t*)dptr_rgba8, (float4*)dptr_rgba_f32);
+                      (uint32_t*)dptr_rgba8, (float4*)dptr_rgba_f32, nullptr);
 }
 
 extern "C" int clrt_frame_untile_on(clrt_ctx* ctx, void* stream, const void* dptr_stripes, uint32_t resX, uint32_t resY, uint32_t nranks,

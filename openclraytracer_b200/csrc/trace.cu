@@ -349,13 +349,22 @@ template <bool STATS>
 struct ShadowJob {
   const clrt_camera& cam; const clrt_contact* __restrict__ contacts;
   const clrt_light* __restrict__ lights; uint32_t n_lights; const clrt_material* __restrict__ materials; uint32_t n_materials;
-  const clrt_triangle* __restrict__ tris; uint32_t n; uint32_t* __restrict__ rgba8; Stats& st; uint32_t& live_rays;
+  const clrt_triangle* __restrict__ tris; uint32_t n; uint32_t* __restrict__ rgba8; const PeerTargets& peers; Stats& st; uint32_t& live_rays;
   uint4 head; float4 nd; Vec3 o, P; uint32_t index, l, occl;
+  // peers.n == 0: the local stripe buffer at the contact's slot.  Otherwise the fused exchange: the pixel goes straight into the
+  // raster-ordered framebuffer of EVERY GPU of the box (peer memory over NVLink; the local one is among them) — no all-gather,
+  // no untile pass.  Slots outside the image (pixel == SENTINEL) have no raster position.
+  __device__ __forceinline__ void store_pixel(uint32_t slot, uint32_t pixel, uint32_t packed) {
+    if (peers.n == 0) { __stcs(rgba8 + slot, packed); return; }
+    if (pixel == SENTINEL) return;
+#pragma unroll
+    for (uint32_t t = 0; t < 8; t++) if (t < peers.n) peers.p[t][pixel] = packed;
+  }
   __device__ __forceinline__ void shade_and_store() {
     uint32_t packed;
     const uint32_t oc = occl;
     shade_contact(cam, head, nd, lights, n_lights, materials, n_materials, [oc](uint32_t k, float) { return ((oc >> k) & 1u) != 0u; }, packed);
-    __stcs(rgba8 + index, packed);
+    store_pixel(index, head.x, packed);
   }
   __device__ __forceinline__ void aim(Lane& L) {
     float energy; const Vec3 lp = light_position(lights, n_lights, l, o, energy);
@@ -367,7 +376,7 @@ struct ShadowJob {
     index = i; occl = 0; l = 0;
     head = __ldcs(reinterpret_cast<const uint4*>(contacts + i));
     nd = __ldcs(reinterpret_cast<const float4*>(contacts + i) + 1);
-    if (!(nd.w > 0.0f && head.x != SENTINEL)) { __stcs(rgba8 + i, 0u); return false; }
+    if (!(nd.w > 0.0f && head.x != SENTINEL)) { store_pixel(i, head.x, 0u); return false; }
     Vec3 d; generate_ray(cam, head.x, o, d);
     P = vadd(o, vscale(d, nd.w));
     live_rays += n_lights + 1;
@@ -451,11 +460,11 @@ __global__ void __launch_bounds__(TRACE_THREADS)
 shadow_shade_kernel(const clrt_camera cam, const clrt_contact* __restrict__ contacts, uint32_t count,
                     const clrt_light* __restrict__ lights, uint32_t n_lights, const clrt_material* __restrict__ materials, uint32_t n_materials,
                     const WideNode* __restrict__ wnodes, const clrt_triangle* __restrict__ tris, uint32_t n,
-                    uint32_t* __restrict__ rgba8, uint32_t* __restrict__ counter, unsigned long long* __restrict__ ray_counter,
+                    uint32_t* __restrict__ rgba8, const PeerTargets peers, uint32_t* __restrict__ counter, unsigned long long* __restrict__ ray_counter,
                     unsigned long long* __restrict__ stats) {
   Stats st; st.rays = st.inner = st.tris = st.lboxes = 0;
   uint32_t live_rays = 0;
-  ShadowJob<STATS> job{cam, contacts, lights, n_lights, materials, n_materials, tris, n, rgba8, st, live_rays};
+  ShadowJob<STATS> job{cam, contacts, lights, n_lights, materials, n_materials, tris, n, rgba8, peers, st, live_rays};
   run_jobs<ShadowJob<STATS>, STATS, true>(job, wnodes, tris, n, count, counter, st);
   if (ray_counter) {
 #pragma unroll
@@ -558,7 +567,7 @@ static int launch_shadow_shade(clrt_accel* a, const clrt_camera& cam, const clrt
   CLRT_TRY(persistent_grid(a, shadow_shade_kernel<S>, TRACE_THREADS, packets, &grid));
   const TraceView v = trace_view(a, true);
   shadow_shade_kernel<S><<<grid, TRACE_THREADS, 0, trace_stream(a)>>>(cam, contacts, count, sc->d_lights, sc->n_lights, sc->d_materials, sc->n_materials,
-      v.wnodes, v.tris, a->n, rgba8, trace_counter(a), d_ray_counter, (unsigned long long*)(a->d_tile_counter + 4));
+      v.wnodes, v.tris, a->n, rgba8, a->launch_targets, trace_counter(a), d_ray_counter, (unsigned long long*)(a->d_tile_counter + 4));
   CLRT_CHECK_LAUNCH();
   return 0;
 }

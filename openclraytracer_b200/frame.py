@@ -9,9 +9,16 @@ stripes, 8.3 MB per 1080p frame) follows, and an untile kernel restores raster o
 the path.  Three frames are in flight: frames are traced on alternating streams (frame slots of the C ABI) so that the
 latency-bound tail of one frame overlaps the next, and the collective, the untile and the read-back run on one more stream.
 
+CLRT_EXCHANGE selects the exchange (BVH): "nccl" (the above; the default on one GPU), "fused" (the default at world > 1;
+measured 8 GPUs, Soup-1M: 0.40 ms/frame against 0.49 with NCCL) or "push" — both over peer memory
+(csrc/peer.cu): every rank exports its raster framebuffers + a block of flag words (cudaIpc), and a frame's pixels are stored
+straight into EVERY GPU's framebuffer over NVLink, by one pass over the stripe buffer ("push") or by the shading kernel itself
+("fused"); a "ready" word per (frame slot, rank) replaces the collective, an "ack" word orders the reuse of a slot's framebuffer.
+
 PyTorch is plumbing here: device memory, the stream shared with NCCL, and the collective.
 """
 import os
+import sys
 
 import numpy as np
 
@@ -110,6 +117,12 @@ class FrameRenderer:
         self.ev_free = [torch.cuda.Event() for _ in range(self.DEPTH)]
         self.ev_host = [torch.cuda.Event() for _ in range(self.DEPTH)]
         self.frame_no = 0
+        self.exchange = os.environ.get("CLRT_EXCHANGE", "fused" if world > 1 else "nccl").lower() if accel.upper() == "BVH" else "nccl"
+        if self.exchange not in ("nccl", "push", "fused"):
+            raise ValueError("CLRT_EXCHANGE=%r (nccl, push or fused)" % self.exchange)
+        self._peer_block = None
+        if self.exchange != "nccl":
+            self._setup_peers()
         self.stripe, self.gathered, self.raster, self.host_raster = self.stripes[0], self.gathereds[0], self.rasters[0], self.host_rasters[0]
 
     def build(self):
@@ -118,7 +131,94 @@ class FrameRenderer:
         self.accel.construct()
         self.stream.synchronize()
 
+    # ---- exchange over peer memory ------------------------------------------------------------------------------------------
+    READY, ACK = 0, 64                                    # word offsets inside a rank's flag block: [kind + slot*8 + writer rank]
+
+    def _setup_peers(self):
+        """One exportable block per rank: DEPTH raster framebuffers + 1 KiB of flag words.  Handles travel by all_gather_object.
+        Every rank must end up in the same mode: if any rank cannot export or open (no peer access between two GPUs), all of
+        them fall back to the NCCL exchange, and say so."""
+        import torch.distributed as dist
+        torch = self.torch
+        raster_bytes = (self.resX * self.resY * 4 + 255) & ~255
+
+        def everyone(ok):
+            if self.world == 1:
+                return ok
+            oks = [None] * self.world
+            dist.all_gather_object(oks, bool(ok), group=self.group)
+            return all(oks)
+
+        handle, why = None, ""
+        try:
+            self._peer_block = api.peer_alloc(self.ctx, self.DEPTH * raster_bytes + 1024)
+            handle = api.peer_export(self.ctx, self._peer_block)
+        except api.ClrtError as e:
+            why = str(e)
+        handles = [handle]
+        if self.world > 1:
+            handles = [None] * self.world
+            dist.all_gather_object(handles, handle, group=self.group)
+        self._peer_bases = [None] * self.world
+        if all(h is not None for h in handles):
+            try:
+                for r in range(self.world):
+                    self._peer_bases[r] = self._peer_block if r == self.rank else api.peer_open(self.ctx, handles[r])
+            except api.ClrtError as e:
+                why = str(e)
+        if not everyone(all(b is not None for b in self._peer_bases)):
+            for r, b in enumerate(self._peer_bases):
+                if b is not None and r != self.rank:
+                    api.peer_close(self.ctx, b)
+            if self._peer_block is not None:
+                api.peer_free(self.ctx, self._peer_block)
+            self._peer_block = None
+            print("[clrt] rank %d: peer-memory exchange unavailable (%s); using the NCCL exchange" % (self.rank, why or "a peer failed"),
+                  file=sys.stderr, flush=True)
+            self.exchange = "nccl"
+            return
+        self._peer_rasters = [api.peer_pointer_array([b + k * raster_bytes for b in self._peer_bases]) for k in range(self.DEPTH)]
+        self._peer_flags = api.peer_pointer_array([b + self.DEPTH * raster_bytes for b in self._peer_bases])
+        self._own_flags = self._peer_block + self.DEPTH * raster_bytes
+
+        class _Raw:                                       # torch view of our own allocation (for the read-back and the tests)
+            def __init__(self, ptr, n):
+                self.__cuda_array_interface__ = {"shape": (n,), "typestr": "<i4", "data": (ptr, False), "version": 2}
+        self.rasters = [torch.as_tensor(_Raw(self._peer_block + k * raster_bytes, self.resX * self.resY), device=self.device)
+                        for k in range(self.DEPTH)]
+        if self.world > 1:
+            dist.barrier(group=self.group)                # nobody writes before everybody has opened
+
+    def _submit_peers(self, camera, shadows, want_rays, to_host):
+        torch = self.torch
+        k = self.frame_no % self.DEPTH
+        seq = self.frame_no // self.DEPTH + 1             # per-slot sequence number carried by the flag words
+        self.frame_no += 1
+        if to_host:
+            self.ev_host[k].synchronize()
+        ts = self.trace_streams[k]
+        s = ts.cuda_stream
+        with torch.cuda.stream(ts):
+            if seq > 1:                                   # every GPU has consumed the previous frame of slot k from its framebuffer
+                api.peer_wait(self.ctx, s, self._own_flags, self.ACK + k * 8, self.world, seq - 1)
+            if self.exchange == "fused" and shadows:
+                rays = self.accel.render_stripe_peers(s, k, camera, self.rank, self.world, self._peer_rasters[k], want_rays)
+            else:
+                rays = self.accel.render_stripe_on(s, k, camera, shadows, self.rank, self.world, self.stripes[k].data_ptr(), want_rays)
+                api.frame_push(self.ctx, s, self.stripes[k].data_ptr(), self.resX, self.resY, self.rank, self.world, self._peer_rasters[k])
+            api.peer_signal(self.ctx, s, self._peer_flags, self.world, self.READY + k * 8 + self.rank, seq)
+            api.peer_wait(self.ctx, s, self._own_flags, self.READY + k * 8, self.world, seq)
+            if to_host and self.rank == 0:
+                self.host_rasters[k].copy_(self.rasters[k], non_blocking=True)
+            api.peer_signal(self.ctx, s, self._peer_flags, self.world, self.ACK + k * 8 + self.rank, seq)
+            if to_host:
+                self.ev_host[k].record(ts)
+        self.stripe, self.raster, self.host_raster = self.stripes[k], self.rasters[k], self.host_rasters[k]
+        return rays
+
     def _submit(self, camera, shadows, want_rays, to_host):
+        if self.exchange != "nccl":
+            return self._submit_peers(camera, shadows, want_rays, to_host)
         torch = self.torch
         k = self.frame_no % self.DEPTH
         self.frame_no += 1
@@ -149,7 +249,8 @@ class FrameRenderer:
 
     def render_device(self, camera, shadows=True, want_rays=False):
         """Submits one frame; its raster-ordered result (every rank holds the whole frame) is in `self.raster` once the
-        second stream has passed — `finish()` joins.  Returns the rays traced by this rank if want_rays (a host sync)."""
+        second stream has passed — `finish()` joins — and stays there until frame k+DEPTH is submitted (by any rank, with the
+        peer-memory exchanges).  Returns the rays traced by this rank if want_rays (a host sync)."""
         return self._submit(camera, shadows, want_rays, False)
 
     def render_host_async(self, camera, shadows=True):
@@ -176,6 +277,17 @@ class FrameRenderer:
         self.stream.synchronize()
 
     def close(self):
+        if self._peer_block is not None:
+            import torch.distributed as dist
+            self.finish()
+            if self.world > 1:
+                dist.barrier(group=self.group)            # no peer still writes into (or reads flags from) our block
+            for r, b in enumerate(self._peer_bases):
+                if r != self.rank:
+                    api.peer_close(self.ctx, b)
+            self.rasters = []
+            api.peer_free(self.ctx, self._peer_block)
+            self._peer_block = None
         self.accel.free(); self.scene.free(); self.ctx.close()
 
 

@@ -347,3 +347,30 @@ def test_frame_renderer_pipeline_equals_synchronous_frames(ctx):
         r.render_device(cams[k], True); r.finish()
         assert np.array_equal(r.raster.cpu().numpy().view(np.uint8).reshape(200, 320, 4), want[k])
     r.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("exchange", ["push", "fused"])
+def test_frame_renderer_peer_memory_exchange_equals_synchronous_frames(ctx, exchange, monkeypatch):
+    """The exchanges over peer memory (csrc/peer.cu; here with one GPU, i.e. the GPU is its own only peer): pixels stored in
+    raster order by the push pass / by the shading kernel, ready + ack words per frame slot.  More frames than slots, so that
+    every slot is reused; each frame must equal the synchronous C-ABI frame.  One frame is 321x203 (ragged tiles)."""
+    from openclraytracer_b200 import frame
+    monkeypatch.setenv("CLRT_EXCHANGE", exchange)
+    buf = scenes.load_bundled("tenryuu")
+    for res in ((320, 200), (321, 203)):
+        r = frame.FrameRenderer(buf, res[0], res[1], "BVH", 0, 1, 0)
+        assert r.exchange == exchange
+        r.build()
+        cams = [frame.orbit_camera(buf, res[0], res[1], s) for s in range(2 * r.DEPTH + 1)]
+        want = [r.accel.render_frame_host(c, True)[0].copy() for c in cams]
+        for k, c in enumerate(cams):
+            r.render_device(c, True); r.finish()
+            assert np.array_equal(r.raster.cpu().numpy().view(np.uint8).reshape(res[1], res[0], 4), want[k]), (res, k)
+        outs = [r.render_host_async(c, True) for c in cams[:r.DEPTH]]
+        r.finish()
+        for k, o in enumerate(outs):
+            assert np.array_equal(o.numpy().view(np.uint8).reshape(res[1], res[0], 4), want[k]), (res, k)
+        got = r.render_host(cams[-1], False).numpy().view(np.uint8).reshape(res[1], res[0], 4)      # no shadows: the push pass in both modes
+        assert np.array_equal(got, r.accel.render_frame_host(cams[-1], False)[0])
+        r.close()
