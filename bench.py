@@ -317,8 +317,8 @@ def main():
                              "the camera moves every step; the BVH stays L2 resident as in steady-state rendering"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 64, "d2h_bytes_per_step": RES[0] * RES[1] * 4,
                     "ms_per_step": e2e_ms / args.steps},
-            # trace_primary_kernel, shadow_shade_kernel + untile_kernel (nccl) | push, 2 signal, 2 wait (push) | 2 signal, 2 wait (fused)
-            "gpu_launches": args.steps * {"nccl": 3, "push": 7, "fused": 6}[r.exchange],
+            # trace_primary_kernel, shadow_shade_kernel + untile_kernel (nccl) | push, 2 signal, 2 wait (push) | ack wait, exchange (fused)
+            "gpu_launches": args.steps * {"nccl": 3, "push": 7, "fused": 4}[r.exchange],
             "pipeline": f"{r.DEPTH} frames in flight: frames traced on alternating streams (frame slots)" +
                         (", gather + untile (+ read-back) on one more" if r.exchange == "nccl" else ", exchange + read-back on the frame's own stream"),
             "build_ms": build_med, "build_ms_per_Mtri": build_med / (n_tris / 1e6),

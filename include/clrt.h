@@ -219,13 +219,20 @@ int clrt_peer_close(clrt_ctx* ctx, void* dptr);
  * peer_rasters[rank] is this GPU's own) instead of a stripe buffer. */
 int clrt_render_stripe_peers(clrt_accel* accel, void* stream, int slot, const clrt_camera* h_camera, uint32_t rank, uint32_t nranks,
                              void* const* peer_rasters, uint64_t* out_rays);
+/* One call per frame and GPU: the whole protocol around clrt_render_stripe_peers.  peer_words[p] = 128 flag words of GPU p
+ * (zeroed; ready at [slot*8 + writer], ack at [64 + slot*8 + writer]); seq = 1, 2, ... counts the frames of this slot.  Enqueued
+ * on `stream`: wait until every GPU acked frame seq-1 of the slot (its framebuffer may be overwritten) -> trace + shade, pixels
+ * to every framebuffer -> ready to all, wait for all -> h_rgba8 ? (copy this GPU's framebuffer to pinned host memory -> ack) : ack.
+ * Every GPU of the box must submit the same frames in the same order. */
+int clrt_render_frame_peers(clrt_accel* accel, void* stream, int slot, const clrt_camera* h_camera, uint32_t rank, uint32_t nranks,
+                            void* const* peer_rasters, void* const* peer_words, uint32_t seq, void* h_rgba8, uint64_t* out_rays);
 /* This GPU's stripe buffer (as written by clrt_render_stripe[_on]) -> raster position in every peer's framebuffer. */
 int clrt_frame_push(clrt_ctx* ctx, void* stream, const void* dptr_stripe, uint32_t resX, uint32_t resY, uint32_t rank,
                     uint32_t nranks, void* const* peer_rasters);
 /* peer_words[p][word] = value for p in 0..npeers, ordered behind everything enqueued on `stream` before (release, system scope). */
 int clrt_peer_signal(clrt_ctx* ctx, void* stream, void* const* peer_words, uint32_t npeers, uint32_t word, uint32_t value);
 /* Blocks `stream` (not the host) until words[first_word .. first_word+n) are all >= value (acquire, system scope).  After
- * timeout_ms (0: 10 s) the waiting kernel traps: the next synchronisation reports a CUDA error instead of hanging. */
+ * timeout_ms (0: 30 s) the waiting kernel traps: the next synchronisation reports a CUDA error instead of hanging. */
 int clrt_peer_wait(clrt_ctx* ctx, void* stream, const void* dptr_words, uint32_t first_word, uint32_t n, uint32_t value,
                    uint32_t timeout_ms);
 

@@ -351,6 +351,14 @@ class AccelerationStructureManager:
                                                  C.byref(rays) if want_rays else None))
         return rays.value
 
+    def render_frame_peers(self, stream, slot, camera, rank, nranks, peer_rasters, peer_words, seq, h_rgba8=None, want_rays=False):
+        """The whole per-frame protocol of the fused peer-memory exchange in one call (include/clrt.h)."""
+        cam = np.ascontiguousarray(camera, dtype=L.CAMERA)
+        rays = C.c_uint64()
+        check(self._lib.clrt_render_frame_peers(self.handle, C.c_void_p(stream), slot, _ptr(cam), rank, nranks, peer_rasters, peer_words, seq,
+                                                C.c_void_p(h_rgba8) if h_rgba8 else None, C.byref(rays) if want_rays else None))
+        return rays.value
+
     def render_frame_host(self, camera, shadows, out_rgba8=None, want_rays=False):
         cam = np.ascontiguousarray(camera, dtype=L.CAMERA)
         if out_rgba8 is None:

@@ -234,6 +234,8 @@ extern "C" int clrt_render_stripe_on(clrt_accel* a, void* stream, int slot, cons
 // The fused exchange: the shading kernel stores each pixel of this GPU's tiles into the raster-ordered framebuffer of every GPU of
 // the box (peer.cu); no stripe buffer, no gather, no untile.
 extern "C" int clrt_render_stripe_peers(clrt_accel* a, void* stream, int slot, const clrt_camera* h_camera, uint32_t rank, uint32_t nranks,
+                                        void* const* peer_rasters, uint64_t* out_rays);
+extern "C" int clrt_render_stripe_peers(clrt_accel* a, void* stream, int slot, const clrt_camera* h_camera, uint32_t rank, uint32_t nranks,
                                         void* const* peer_rasters, uint64_t* out_rays) {
   if (!a || !peer_rasters || !nranks || nranks > 8 || rank >= nranks) CLRT_FAIL("clrt_render_stripe_peers: bad argument");
   if (slot < 0) CLRT_FAIL("clrt_render_stripe_peers: slot %d", slot);
@@ -246,6 +248,36 @@ extern "C" int clrt_render_stripe_peers(clrt_accel* a, void* stream, int slot, c
   } targets(a, peer_rasters, nranks);
   for (uint32_t i = 0; i < nranks; i++) if (!peer_rasters[i]) CLRT_FAIL("clrt_render_stripe_peers: peer %u is NULL", i);
   return render_stripe_impl(a, h_camera, 1, rank, nranks, peer_rasters[rank], out_rays, (cudaStream_t)stream, slot);
+}
+
+int peer_launch_wait(cudaStream_t stream, const uint32_t* words, uint32_t n, uint32_t value);
+int peer_launch_exchange(cudaStream_t stream, const PeerTargets& flags, const uint32_t* own, uint32_t ready_base, uint32_t ack_base,
+                         uint32_t rank, uint32_t seq);
+int peer_launch_signal(cudaStream_t stream, const PeerTargets& flags, uint32_t word, uint32_t value);
+
+// One call per frame and GPU.  Flag words of a GPU (peer_words[p], 128 words): ready at [slot*8 + writer], ack at [64 + slot*8 +
+// writer]; seq = 1, 2, ... per slot.  Enqueues on `stream`: wait until every GPU acked seq-1 of this slot (its framebuffer is
+// free) -> trace + shade with the pixels going to every framebuffer -> ready to all, wait for all -> (copy to host ->) ack to all.
+extern "C" int clrt_render_frame_peers(clrt_accel* a, void* stream_, int slot, const clrt_camera* h_camera, uint32_t rank, uint32_t nranks,
+                                       void* const* peer_rasters, void* const* peer_words, uint32_t seq, void* h_rgba8, uint64_t* out_rays) {
+  if (!a || !h_camera || !peer_rasters || !peer_words || !nranks || nranks > 8 || rank >= nranks || !seq)
+    CLRT_FAIL("clrt_render_frame_peers: bad argument");
+  if (slot < 0 || slot >= clrt_accel::FRAME_SLOTS) CLRT_FAIL("clrt_render_frame_peers: slot %d of %d", slot, clrt_accel::FRAME_SLOTS);
+  cudaStream_t stream = (cudaStream_t)stream_;
+  PeerTargets flags; flags.n = nranks;
+  for (uint32_t i = 0; i < 8; i++) flags.p[i] = i < nranks ? (uint32_t*)peer_words[i] : nullptr;
+  for (uint32_t i = 0; i < nranks; i++) if (!flags.p[i]) CLRT_FAIL("clrt_render_frame_peers: peer %u is NULL", i);
+  CLRT_CUDA(cudaSetDevice(a->ctx->device));
+  const uint32_t* own = flags.p[rank];
+  const uint32_t ready = (uint32_t)slot * 8u, ack = 64u + (uint32_t)slot * 8u;
+  if (seq > 1) CLRT_TRY(peer_launch_wait(stream, own + ack, nranks, seq - 1));
+  CLRT_TRY(clrt_render_stripe_peers(a, stream_, slot, h_camera, rank, nranks, peer_rasters, out_rays));
+  CLRT_TRY(peer_launch_exchange(stream, flags, own, ready, h_rgba8 ? ~0u : ack, rank, seq));
+  if (h_rgba8) {
+    CLRT_CUDA(cudaMemcpyAsync(h_rgba8, peer_rasters[rank], (size_t)h_camera->resX * h_camera->resY * 4, cudaMemcpyDeviceToHost, stream));
+    CLRT_TRY(peer_launch_signal(stream, flags, ack + rank, seq));
+  }
+  return 0;
 }
 
 extern "C" int clrt_render_frame_host(clrt_accel* a, const clrt_camera* h_camera, int shadows, void* h_rgba8, uint64_t* out_rays) {

@@ -49,6 +49,23 @@ __global__ void wait_kernel(const uint32_t* __restrict__ words, uint32_t n, uint
   }
 }
 
+// ready[rank] = seq on every peer, wait for everybody's ready word here, then (ack_base != ~0u) ack[rank] = seq on every peer.
+__global__ void exchange_kernel(const PeerTargets flags, const uint32_t* __restrict__ own, uint32_t ready_base, uint32_t ack_base,
+                                uint32_t rank, uint32_t seq, unsigned long long timeout_ns) {
+  const uint32_t t = threadIdx.x;
+  __threadfence_system();
+  if (t < flags.n) {
+    st_release_sys(flags.p[t] + ready_base + rank, seq);
+    const unsigned long long t0 = global_ns();
+    while ((int32_t)(ld_acquire_sys(own + ready_base + t) - seq) < 0) {
+      __nanosleep(100);
+      if (global_ns() - t0 > timeout_ns) __trap();
+    }
+  }
+  __syncthreads();
+  if (ack_base != ~0u && t < flags.n) st_release_sys(flags.p[t] + ack_base + rank, seq);
+}
+
 int fill_targets(PeerTargets& t, void* const* ptrs, uint32_t n, const char* what) {
   if (!ptrs || !n || n > 8) CLRT_FAIL("%s: %u peers (1..8)", what, n);
   t.n = n;
@@ -58,6 +75,24 @@ int fill_targets(PeerTargets& t, void* const* ptrs, uint32_t n, const char* what
 }
 
 } // namespace
+
+// internal (accel.cu: clrt_render_frame_peers)
+int peer_launch_wait(cudaStream_t stream, const uint32_t* words, uint32_t n, uint32_t value) {
+  wait_kernel<<<1, 32, 0, stream>>>(words, n, value, 30000000000ull);
+  CLRT_CHECK_LAUNCH();
+  return 0;
+}
+int peer_launch_exchange(cudaStream_t stream, const PeerTargets& flags, const uint32_t* own, uint32_t ready_base, uint32_t ack_base,
+                         uint32_t rank, uint32_t seq) {
+  exchange_kernel<<<1, 32, 0, stream>>>(flags, own, ready_base, ack_base, rank, seq, 30000000000ull);
+  CLRT_CHECK_LAUNCH();
+  return 0;
+}
+int peer_launch_signal(cudaStream_t stream, const PeerTargets& flags, uint32_t word, uint32_t value) {
+  signal_kernel<<<1, 32, 0, stream>>>(flags, word, value);
+  CLRT_CHECK_LAUNCH();
+  return 0;
+}
 
 extern "C" int clrt_peer_alloc(clrt_ctx* ctx, uint64_t bytes, void** out_dptr) {
   if (!ctx || !out_dptr || !bytes) CLRT_FAIL("clrt_peer_alloc: bad argument");
@@ -125,7 +160,7 @@ extern "C" int clrt_peer_wait(clrt_ctx* ctx, void* stream, const void* dptr_word
   if (!ctx || !dptr_words || !n || n > 32) CLRT_FAIL("clrt_peer_wait: bad argument");
   CLRT_CUDA(cudaSetDevice(ctx->device));
   wait_kernel<<<1, 32, 0, (cudaStream_t)stream>>>((const uint32_t*)dptr_words + first_word, n, value,
-                                                  (unsigned long long)(timeout_ms ? timeout_ms : 10000u) * 1000000ull);
+                                                  (unsigned long long)(timeout_ms ? timeout_ms : 30000u) * 1000000ull);
   CLRT_CHECK_LAUNCH();
   return 0;
 }

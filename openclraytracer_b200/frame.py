@@ -198,14 +198,18 @@ class FrameRenderer:
             self.ev_host[k].synchronize()
         ts = self.trace_streams[k]
         s = ts.cuda_stream
+        if self.exchange == "fused" and shadows:          # the whole protocol below in one C call
+            host = self.host_rasters[k].data_ptr() if (to_host and self.rank == 0) else None
+            rays = self.accel.render_frame_peers(s, k, camera, self.rank, self.world, self._peer_rasters[k], self._peer_flags, seq, host, want_rays)
+            if to_host:
+                self.ev_host[k].record(ts)
+            self.stripe, self.raster, self.host_raster = self.stripes[k], self.rasters[k], self.host_rasters[k]
+            return rays
         with torch.cuda.stream(ts):
             if seq > 1:                                   # every GPU has consumed the previous frame of slot k from its framebuffer
                 api.peer_wait(self.ctx, s, self._own_flags, self.ACK + k * 8, self.world, seq - 1)
-            if self.exchange == "fused" and shadows:
-                rays = self.accel.render_stripe_peers(s, k, camera, self.rank, self.world, self._peer_rasters[k], want_rays)
-            else:
-                rays = self.accel.render_stripe_on(s, k, camera, shadows, self.rank, self.world, self.stripes[k].data_ptr(), want_rays)
-                api.frame_push(self.ctx, s, self.stripes[k].data_ptr(), self.resX, self.resY, self.rank, self.world, self._peer_rasters[k])
+            rays = self.accel.render_stripe_on(s, k, camera, shadows, self.rank, self.world, self.stripes[k].data_ptr(), want_rays)
+            api.frame_push(self.ctx, s, self.stripes[k].data_ptr(), self.resX, self.resY, self.rank, self.world, self._peer_rasters[k])
             api.peer_signal(self.ctx, s, self._peer_flags, self.world, self.READY + k * 8 + self.rank, seq)
             api.peer_wait(self.ctx, s, self._own_flags, self.READY + k * 8, self.world, seq)
             if to_host and self.rank == 0:
