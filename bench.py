@@ -199,10 +199,8 @@ def time_trace_kernels(r, cam, repeats=5):
         ms_p, ms_s = timed(prim), timed(shad)
     bytes_p = sp[1] * 128 + sp[2] * 48 + n * 32            # 128-B wide node per visit, 48-B triangle per test, 32-B contact out
     bytes_s = ss[1] * 128 + ss[2] * 48 + n * 36
-    return {"primary": {"ms": ms_p, "rays": sp[0], "bytes": bytes_p, "inner_per_ray": sp[1] / max(sp[0], 1), "tris_per_ray": sp[2] / max(sp[0], 1),
-                        "leafboxes_per_ray": sp[3] / max(sp[0], 1)},
-            "shadow": {"ms": ms_s, "rays": ss[0], "bytes": bytes_s, "inner_per_ray": ss[1] / max(ss[0], 1), "tris_per_ray": ss[2] / max(ss[0], 1),
-                       "leafboxes_per_ray": ss[3] / max(ss[0], 1)}}
+    return {"primary": {"ms": ms_p, "rays": sp[0], "bytes": bytes_p, "inner_per_ray": sp[1] / max(sp[0], 1), "tris_per_ray": sp[2] / max(sp[0], 1)},
+            "shadow": {"ms": ms_s, "rays": ss[0], "bytes": bytes_s, "inner_per_ray": ss[1] / max(ss[0], 1), "tris_per_ray": ss[2] / max(ss[0], 1)}}
 
 
 def main():
@@ -340,7 +338,6 @@ def main():
                                     "it does not bound; HBM-bound kernels are under 'kernels'"}
         line["trace_kernels"] = {k: {"ms": v["ms"], "rays": v["rays"], "mrays_per_s": v["rays"] / v["ms"] / 1e3,
                                      "inner_visits_per_ray": v["inner_per_ray"], "tri_tests_per_ray": v["tris_per_ray"],
-                                     "run_leafbox_tests_per_ray": v["leafboxes_per_ray"],
                                      "algorithmic_GBs": v["bytes"] / (v["ms"] * 1e-3) / 1e9} for k, v in kt.items()}
         if not args.no_kernels:
             line["kernels"] = kernel_rooflines(r, hbm_peak, n_tris, stage_med)

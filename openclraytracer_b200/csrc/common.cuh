@@ -112,7 +112,7 @@ struct clrt_accel {
   bool tt_built = false;
   TraceNode* d_tt_nodes = nullptr; size_t tt_nodes_cap = 0;             // (N-1) x 64 B
   clrt_triangle* d_tt_tris = nullptr; size_t tt_tris_cap = 0;           // N x 48 B in trace-tree order; v1.w = triangle id, v2.w = reference sorted position
-  float4* d_tt_leafbox = nullptr; size_t tt_leafbox_cap = 0;            // unused by the trace tree's kernels (no runs); kept for a uniform kernel signature
+  float4* d_tt_leafbox = nullptr; size_t tt_leafbox_cap = 0;            // leaf boxes in trace-tree order (tt_emit_kernel -> tt_refit_kernel)
   clrt_uint2* d_tt_pairs = nullptr; size_t tt_pairs_cap = 0;            // N x 8 B (fine Morton code, triangle)
   uint32_t* d_tt_parent = nullptr; size_t tt_parent_cap = 0;            // (2N) x 4 B: parent link | side bit
   // --- primary contacts / frame scratch ---
