@@ -169,6 +169,16 @@ int clrt_generate_shadow_rays(clrt_ctx* ctx, const clrt_scene* scene, const clrt
  * degenerate ray (idx = UINT_MAX, zero direction).  Trace them with clrt_trace_rays.  dptr_rays: n * 48 B. */
 int clrt_generate_bounce_rays(clrt_ctx* ctx, const clrt_camera* h_camera, const void* dptr_contacts, uint32_t n, uint64_t seed,
                               void* dptr_rays);
+/* Secondary rays of either kind from the contacts of ANY pass — the depth loop of the reference's TODO 2.2
+ * (KNOWN_ISSUES_AND_TODO.txt: "generating rays from viewing rays-scene contacts, and execute ray tracing kernel in loop as many
+ * times as specified by ray tracing depth"): rays_0 = contacts of clrt_trace_primary (dptr_in_rays == NULL, incoming ray from
+ * h_camera), rays_k+1 = contacts of clrt_trace_rays(rays_k) with dptr_in_rays = rays_k (contact i belongs to ray i; h_camera may
+ * be NULL; dptr_rays may alias dptr_in_rays).  The new ray keeps the pixel in idx; a miss or a dead incoming ray gives the
+ * degenerate ray.  CLRT_RAYS_REFLECT: direction d - 2 (d.n) n about the normal turned against d (seed unused). */
+#define CLRT_RAYS_DIFFUSE 0
+#define CLRT_RAYS_REFLECT 1
+int clrt_generate_secondary_rays(clrt_ctx* ctx, int kind, const clrt_camera* h_camera, const void* dptr_in_rays,
+                                 const void* dptr_contacts, uint32_t n, uint64_t seed, void* dptr_rays);
 /* Blinn-Phong of every contact -> RGBA8 (and/or float4) at the contact's slot.  dptr_shadow_contacts (may be
  * NULL) are the contacts of the shadow rays above: a light whose shadow ray hit before reaching it adds nothing. */
 int clrt_shade(clrt_ctx* ctx, const clrt_scene* scene, const clrt_camera* h_camera, const void* dptr_contacts,
@@ -236,7 +246,10 @@ int clrt_peer_signal(clrt_ctx* ctx, void* stream, void* const* peer_words, uint3
 int clrt_peer_wait(clrt_ctx* ctx, void* stream, const void* dptr_words, uint32_t first_word, uint32_t n, uint32_t value,
                    uint32_t timeout_ms);
 
-/* Whole frame with HOST output: upload camera, trace, (shadow,) shade, download RGBA8 raster — the e2e path. */
+/* Whole frame with HOST output: upload camera, trace, (shadow,) shade, download RGBA8 raster — the e2e path.
+ * Camera.supersampilngFactor = s in 2..8 (R/Include/CLData/CLStructs.h:49; the reference sets 1 and never reads it — its TODO
+ * 2.4) renders s*s rays per pixel: the frame of the camera (s*resX, s*resY, s*FOVDistance), box-filtered per channel with
+ * rounding to resX x resY (alpha = coverage).  out_rays counts the sample rays.  0 and 1 mean one ray per pixel. */
 int clrt_render_frame_host(clrt_accel* accel, const clrt_camera* h_camera, int shadows, void* h_rgba8, uint64_t* out_rays);
 
 #ifdef __cplusplus

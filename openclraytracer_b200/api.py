@@ -458,6 +458,18 @@ def generate_bounce_rays(context, camera, dptr_contacts, n, seed, dptr_rays):
     check(_lib.load().clrt_generate_bounce_rays(context.handle, _ptr(cam), C.c_void_p(dptr_contacts), n, C.c_uint64(seed), C.c_void_p(dptr_rays)))
 
 
+RAYS_DIFFUSE, RAYS_REFLECT = 0, 1
+
+
+def generate_secondary_rays(context, kind, camera, dptr_in_rays, dptr_contacts, n, seed, dptr_rays):
+    """camera: the primary pass's camera (contacts of generateContacts(camera)) or None with dptr_in_rays (contacts of
+    generateContacts(rays, contacts, n) over those rays) — include/clrt.h."""
+    cam = np.ascontiguousarray(camera, dtype=L.CAMERA) if camera is not None else None
+    check(_lib.load().clrt_generate_secondary_rays(context.handle, kind, _ptr(cam) if cam is not None else None,
+                                                   C.c_void_p(dptr_in_rays) if dptr_in_rays else None, C.c_void_p(dptr_contacts), n,
+                                                   C.c_uint64(seed), C.c_void_p(dptr_rays)))
+
+
 def shade(context, scene, camera, dptr_contacts, n, dptr_shadow=None, dptr_rgba8=None, dptr_rgba_f32=None):
     cam = np.ascontiguousarray(camera, dtype=L.CAMERA)
     check(_lib.load().clrt_shade(context.handle, scene.handle, _ptr(cam), C.c_void_p(dptr_contacts), n,

@@ -2,6 +2,7 @@
 // (R/Include/Algorithms/AccelerationStructureManager.h:52-78; BVHManager.cpp / TwoLevelGridManager.cpp) and the
 // per-frame flow of the Demo's RTFrame() (R/src/Demos/OpenCLRayTracerDemo/OpenCLRayTracerDemo.cpp:271-326).
 #include "common.cuh"
+#include <vector>
 
 int shade_launch_shadow_rays(clrt_ctx* ctx, const clrt_scene* scene, const clrt_camera& cam, const clrt_contact* contacts,
                              uint32_t n, clrt_ray* rays, unsigned long long* d_counter);
@@ -280,27 +281,51 @@ extern "C" int clrt_render_frame_peers(clrt_accel* a, void* stream_, int slot, c
   return 0;
 }
 
+int shade_launch_downsample(clrt_ctx* ctx, const uint32_t* hi, uint32_t resX, uint32_t resY, uint32_t s, uint32_t* lo);
+
+// Camera.supersampilngFactor (CLStructs.h:49; set to 1 and never read by the reference — its TODO 2.4) = s: the frame of the camera
+// (s*resX, s*resY, s*FOVDistance) — s*s rays per pixel on a regular grid, same field of view — box-filtered to resX x resY.
 extern "C" int clrt_render_frame_host(clrt_accel* a, const clrt_camera* h_camera, int shadows, void* h_rgba8, uint64_t* out_rays) {
   if (!a || !h_camera || !h_rgba8) CLRT_FAIL("clrt_render_frame_host: NULL argument");
   clrt_ctx* ctx = a->ctx;
   CLRT_CUDA(cudaSetDevice(ctx->device));
-  const TileGrid g = make_tile_grid(h_camera->resX, h_camera->resY);
-  const size_t stripe_bytes = (size_t)g.tiles * CLRT_TILE_PIXELS * 4, raster_bytes = (size_t)h_camera->resX * h_camera->resY * 4;
-  // framebuffers owned by the accel: [stripe | raster]
+  const uint32_t ss = h_camera->supersampilngFactor > 1 ? h_camera->supersampilngFactor : 1;
+  if (ss > 8) CLRT_FAIL("clrt_render_frame_host: supersampilngFactor %u (1..8)", ss);
+  clrt_camera cam = *h_camera;
+  cam.resX *= ss; cam.resY *= ss; cam.FOVDistance *= (float)ss; cam.supersampilngFactor = 1;
+  if ((uint64_t)cam.resX * cam.resY > 0x7FFFFFFFull) CLRT_FAIL("clrt_render_frame_host: %u x %u samples", cam.resX, cam.resY);
+  const TileGrid g = make_tile_grid(cam.resX, cam.resY);
+  const size_t stripe_bytes = (size_t)g.tiles * CLRT_TILE_PIXELS * 4, raster_bytes = (size_t)cam.resX * cam.resY * 4;
+  const size_t out_bytes = (size_t)h_camera->resX * h_camera->resY * 4;
+  // framebuffers owned by the accel: [stripe | raster]; the filtered frame reuses the stripe area (free once untiled)
   if (stripe_bytes + raster_bytes + 256 > a->fb_cap) {
     CLRT_CUDA(cudaStreamSynchronize(ctx->stream));
     CLRT_TRY(clrt_grow(&a->d_fb, &a->fb_cap, stripe_bytes + raster_bytes + 256));
   }
   uint8_t* stripe = (uint8_t*)a->d_fb; uint8_t* raster = stripe + ((stripe_bytes + 255) & ~(size_t)255);
-  CLRT_TRY(clrt_render_stripe(a, h_camera, shadows, 0, 1, stripe, nullptr));
-  CLRT_TRY(clrt_frame_untile(ctx, stripe, h_camera->resX, h_camera->resY, 1, raster));
-  CLRT_CUDA(cudaMemcpyAsync(h_rgba8, raster, raster_bytes, cudaMemcpyDeviceToHost, ctx->stream));
+  CLRT_TRY(clrt_render_stripe(a, &cam, shadows, 0, 1, stripe, nullptr));
+  CLRT_TRY(clrt_frame_untile(ctx, stripe, cam.resX, cam.resY, 1, raster));
+  const uint8_t* result = raster;
+  if (ss > 1) {
+    CLRT_TRY(shade_launch_downsample(ctx, (const uint32_t*)raster, h_camera->resX, h_camera->resY, ss, (uint32_t*)stripe));
+    result = stripe;
+  }
+  CLRT_CUDA(cudaMemcpyAsync(h_rgba8, result, out_bytes, cudaMemcpyDeviceToHost, ctx->stream));
   CLRT_CUDA(cudaStreamSynchronize(ctx->stream));
   if (out_rays) {
-    // recount without re-rendering: primary = all pixels; shadow = (L+1) per hit pixel, counted from the alpha channel
-    uint64_t hits = 0; const uint8_t* px = (const uint8_t*)h_rgba8;
-    for (size_t i = 0; i < raster_bytes / 4; i++) hits += px[4 * i + 3] != 0;
-    *out_rays = (uint64_t)h_camera->resX * h_camera->resY + (shadows ? hits * (a->scene->n_lights + 1) : 0);
+    // counted without re-rendering: primary = all samples; shadow = (L+1) per hit sample.  Without supersampling the hits are the
+    // pixels with alpha != 0 of the frame just read back; with it, of the sample raster (a second read-back, only when asked).
+    uint64_t hits = 0;
+    if (ss == 1) {
+      const uint8_t* px = (const uint8_t*)h_rgba8;
+      for (size_t i = 0; i < raster_bytes / 4; i++) hits += px[4 * i + 3] != 0;
+    } else if (shadows) {
+      std::vector<uint8_t> hi(raster_bytes);
+      CLRT_CUDA(cudaMemcpyAsync(hi.data(), raster, raster_bytes, cudaMemcpyDeviceToHost, ctx->stream));
+      CLRT_CUDA(cudaStreamSynchronize(ctx->stream));
+      for (size_t i = 0; i < raster_bytes / 4; i++) hits += hi[4 * i + 3] != 0;
+    }
+    *out_rays = (uint64_t)cam.resX * cam.resY + (shadows ? hits * (a->scene->n_lights + 1) : 0);
   }
   return 0;
 }

@@ -57,32 +57,52 @@ __device__ __forceinline__ uint64_t splitmix64_dev(uint64_t x) {
   x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
   return x ^ (x >> 31);
 }
+// Secondary rays (the reference's TODO 2.2, KNOWN_ISSUES_AND_TODO.txt: "generating rays from viewing rays-scene contacts, and execute
+// ray tracing kernel in loop as many times as specified by ray tracing depth").  Contact i is either a primary contact (incoming
+// ray = generateRay(camera, pixelIndex)) or the contact of in_rays[i] from the generic-ray entry point; the new ray carries the pixel
+// along in idx.  KIND 0: cosine-weighted diffuse direction about the normal; KIND 1: mirror direction d - 2 (d.n) n.
+template <int KIND, bool FROM_RAYS>
 __global__ void __launch_bounds__(256)
-bounce_rays_kernel(clrt_camera cam, const clrt_contact* __restrict__ contacts, uint32_t n, uint64_t seed, clrt_ray* __restrict__ rays) {
+secondary_rays_kernel(clrt_camera cam, const clrt_ray* in_rays, const clrt_contact* __restrict__ contacts, uint32_t n, uint64_t seed,
+                      clrt_ray* out_rays) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const uint4 head = __ldg(reinterpret_cast<const uint4*>(contacts + i));
   const float4 nd = __ldg(reinterpret_cast<const float4*>(contacts + i) + 1);
   uint4 h = make_uint4(0xFFFFFFFFu, 0u, 0u, 0u);
   float4 ro = make_float4(0.f, 0.f, 0.f, 0.f), rd = make_float4(0.f, 0.f, 0.f, 0.f);
-  if (nd.w > 0.0f && head.x != 0xFFFFFFFFu) {
-    Vec3 o, d; generate_ray(cam, head.x, o, d);
-    Vec3 nrm = v3(nd.x, nd.y, nd.z);
-    if (vdot(nrm, d) > 0.0f) nrm = vscale(nrm, -1.0f);                        // face the incoming ray (two-sided triangles)
-    const Vec3 P = vadd(o, vscale(d, nd.w));
-    const uint64_t u = splitmix64_dev(seed * 0x9E3779B97F4A7C15ull + (uint64_t)head.x);
-    const float u1 = (float)(uint32_t)(u >> 40) * (1.0f / 16777216.0f), u2 = (float)(uint32_t)(u & 0xFFFFFFu) * (1.0f / 16777216.0f);
-    const float r = sqrtf(u1), phi = 6.283185307179586f * u2;
-    float sn, cs; sincosf(phi, &sn, &cs);
-    const float dx = r * cs, dy = r * sn, dz = sqrtf(fmaxf(0.0f, 1.0f - u1));
-    // orthonormal basis around the normal: the axis least aligned with it, crossed twice
-    const Vec3 ax = fabsf(nrm.x) < 0.5f ? v3(1.0f, 0.0f, 0.0f) : v3(0.0f, 1.0f, 0.0f);
-    const Vec3 t1 = vnormalize(vcross(ax, nrm)), t2 = vcross(nrm, t1);
-    const Vec3 dir = vnormalize(vadd(vadd(vscale(t1, dx), vscale(t2, dy)), vscale(nrm, dz)));
-    const Vec3 org = vadd(P, vscale(nrm, SHADOW_EPS_REL * nd.w));
-    h.x = head.x; ro = make_float4(org.x, org.y, org.z, 0.f); rd = make_float4(dir.x, dir.y, dir.z, 0.f);
+  Vec3 o = v3(0.f, 0.f, 0.f), d = v3(0.f, 0.f, 0.f);
+  uint32_t pixel = 0xFFFFFFFFu;
+  if (FROM_RAYS) {                                          // in_rays may alias out_rays: ray i is read before it is written, by this thread only
+    const uint4 rh = *reinterpret_cast<const uint4*>(in_rays + i);
+    const float4 io = reinterpret_cast<const float4*>(in_rays + i)[1], id = reinterpret_cast<const float4*>(in_rays + i)[2];
+    pixel = rh.x; o = v3(io.x, io.y, io.z); d = v3(id.x, id.y, id.z);
+  } else if (head.x != 0xFFFFFFFFu) {
+    pixel = head.x; generate_ray(cam, pixel, o, d);
   }
-  uint4* p = reinterpret_cast<uint4*>(rays + i);
+  if (nd.w > 0.0f && pixel != 0xFFFFFFFFu) {
+    Vec3 nrm = v3(nd.x, nd.y, nd.z);
+    const float dn = vdot(nrm, d);
+    if (dn > 0.0f) nrm = vscale(nrm, -1.0f);                                   // face the incoming ray (two-sided triangles)
+    const Vec3 P = vadd(o, vscale(d, nd.w));
+    Vec3 dir;
+    if (KIND == 1) {
+      dir = vnormalize(vsub(d, vscale(nrm, 2.0f * vdot(nrm, d))));
+    } else {
+      const uint64_t u = splitmix64_dev(seed * 0x9E3779B97F4A7C15ull + (uint64_t)pixel);
+      const float u1 = (float)(uint32_t)(u >> 40) * (1.0f / 16777216.0f), u2 = (float)(uint32_t)(u & 0xFFFFFFu) * (1.0f / 16777216.0f);
+      const float r = sqrtf(u1), phi = 6.283185307179586f * u2;
+      float sn, cs; sincosf(phi, &sn, &cs);
+      const float dx = r * cs, dy = r * sn, dz = sqrtf(fmaxf(0.0f, 1.0f - u1));
+      // orthonormal basis around the normal: the axis least aligned with it, crossed twice
+      const Vec3 ax = fabsf(nrm.x) < 0.5f ? v3(1.0f, 0.0f, 0.0f) : v3(0.0f, 1.0f, 0.0f);
+      const Vec3 t1 = vnormalize(vcross(ax, nrm)), t2 = vcross(nrm, t1);
+      dir = vnormalize(vadd(vadd(vscale(t1, dx), vscale(t2, dy)), vscale(nrm, dz)));
+    }
+    const Vec3 org = vadd(P, vscale(nrm, SHADOW_EPS_REL * nd.w));
+    h.x = pixel; ro = make_float4(org.x, org.y, org.z, 0.f); rd = make_float4(dir.x, dir.y, dir.z, 0.f);
+  }
+  uint4* p = reinterpret_cast<uint4*>(out_rays + i);
   p[0] = h; reinterpret_cast<float4*>(p)[1] = ro; reinterpret_cast<float4*>(p)[2] = rd;
 }
 
@@ -120,7 +140,31 @@ untile_kernel(const uint32_t* __restrict__ stripes, uint32_t resX, uint32_t resY
   if (x < resX && y < resY) raster[y * resX + x] = __ldcs(stripes + (size_t)(stripe_first_tile + lt) * CLRT_TILE_PIXELS + t);
 }
 
+// s x s box filter over an (resX*s) x (resY*s) RGBA8 raster -> resX x resY; per channel (sum + s*s/2) / (s*s)
+__global__ void __launch_bounds__(256)
+downsample_kernel(const uint32_t* __restrict__ hi, uint32_t resX, uint32_t resY, uint32_t s, uint32_t* __restrict__ lo) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= resX * resY) return;
+  const uint32_t x = i % resX, y = i / resX;
+  uint32_t r = 0, g = 0, b = 0, a = 0;
+  for (uint32_t j = 0; j < s; j++)
+    for (uint32_t k = 0; k < s; k++) {
+      const uint32_t v = __ldcs(hi + (size_t)(y * s + j) * (resX * s) + (x * s + k));
+      r += v & 255u; g += (v >> 8) & 255u; b += (v >> 16) & 255u; a += v >> 24;
+    }
+  const uint32_t q = s * s, h = q / 2;
+  lo[i] = ((r + h) / q) | (((g + h) / q) << 8) | (((b + h) / q) << 16) | (((a + h) / q) << 24);
+}
+
 } // namespace
+
+int shade_launch_downsample(clrt_ctx* ctx, const uint32_t* hi, uint32_t resX, uint32_t resY, uint32_t s, uint32_t* lo) {
+  const uint32_t n = resX * resY;
+  if (!n) return 0;
+  downsample_kernel<<<(n + 255) / 256, 256, 0, ctx->stream>>>(hi, resX, resY, s, lo);
+  CLRT_CHECK_LAUNCH();
+  return 0;
+}
 
 extern "C" int clrt_generate_primary_rays(clrt_ctx* ctx, const clrt_camera* h_camera, void* dptr_rays) {
   if (!ctx || !h_camera || !dptr_rays) CLRT_FAIL("clrt_generate_primary_rays: NULL argument");
@@ -160,14 +204,30 @@ extern "C" int clrt_generate_shadow_rays(clrt_ctx* ctx, const clrt_scene* scene,
   return shade_launch_shadow_rays(ctx, scene, *h_camera, (const clrt_contact*)dptr_contacts, n, (clrt_ray*)dptr_rays, nullptr);
 }
 
-extern "C" int clrt_generate_bounce_rays(clrt_ctx* ctx, const clrt_camera* h_camera, const void* dptr_contacts, uint32_t n, uint64_t seed,
-                                         void* dptr_rays) {
-  if (!ctx || !h_camera || (n && (!dptr_contacts || !dptr_rays))) CLRT_FAIL("clrt_generate_bounce_rays: NULL argument");
+extern "C" int clrt_generate_secondary_rays(clrt_ctx* ctx, int kind, const clrt_camera* h_camera, const void* dptr_in_rays,
+                                            const void* dptr_contacts, uint32_t n, uint64_t seed, void* dptr_rays) {
+  if (!ctx || (!h_camera && !dptr_in_rays) || (n && (!dptr_contacts || !dptr_rays))) CLRT_FAIL("clrt_generate_secondary_rays: NULL argument");
+  if (kind != CLRT_RAYS_DIFFUSE && kind != CLRT_RAYS_REFLECT) CLRT_FAIL("clrt_generate_secondary_rays: kind %d", kind);
   CLRT_CUDA(cudaSetDevice(ctx->device));
   if (!n) return 0;
-  bounce_rays_kernel<<<(n + 255) / 256, 256, 0, ctx->stream>>>(*h_camera, (const clrt_contact*)dptr_contacts, n, seed, (clrt_ray*)dptr_rays);
+  clrt_camera cam; memset(&cam, 0, sizeof cam);
+  if (h_camera) cam = *h_camera;
+  const clrt_ray* in = (const clrt_ray*)dptr_in_rays; const clrt_contact* c = (const clrt_contact*)dptr_contacts; clrt_ray* out = (clrt_ray*)dptr_rays;
+  const unsigned grid = (n + 255) / 256;
+  if (kind == CLRT_RAYS_DIFFUSE) {
+    if (in) secondary_rays_kernel<0, true><<<grid, 256, 0, ctx->stream>>>(cam, in, c, n, seed, out);
+    else    secondary_rays_kernel<0, false><<<grid, 256, 0, ctx->stream>>>(cam, in, c, n, seed, out);
+  } else {
+    if (in) secondary_rays_kernel<1, true><<<grid, 256, 0, ctx->stream>>>(cam, in, c, n, seed, out);
+    else    secondary_rays_kernel<1, false><<<grid, 256, 0, ctx->stream>>>(cam, in, c, n, seed, out);
+  }
   CLRT_CHECK_LAUNCH();
   return 0;
+}
+extern "C" int clrt_generate_bounce_rays(clrt_ctx* ctx, const clrt_camera* h_camera, const void* dptr_contacts, uint32_t n, uint64_t seed,
+                                         void* dptr_rays) {
+  if (!h_camera) CLRT_FAIL("clrt_generate_bounce_rays: NULL argument");
+  return clrt_generate_secondary_rays(ctx, CLRT_RAYS_DIFFUSE, h_camera, nullptr, dptr_contacts, n, seed, dptr_rays);
 }
 
 extern "C" int clrt_shade(clrt_ctx* ctx, const clrt_scene* scene, const clrt_camera* h_camera, const void* dptr_contacts,

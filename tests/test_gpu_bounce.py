@@ -137,3 +137,80 @@ def test_spheres_10m_incoherent_bounce_at_4k(ctx):
     for x in (rays, contacts, rs, cs):
         x.free()
     bvh.free(); scene.free()
+
+
+def reflect_reference(o, d, contacts):
+    """numpy (float64) restatement of secondary_rays_kernel<REFLECT>: rays (o, d) with their contacts -> mirrored rays."""
+    t = contacts["nd"][:, 3].astype(np.float64)[:, None]
+    n = contacts["nd"][:, :3].astype(np.float64).copy()
+    o = o.astype(np.float64); d = d.astype(np.float64)
+    n[(n * d).sum(axis=1) > 0] *= -1
+    P = o + d * t
+    r = d - n * (2.0 * (n * d).sum(axis=1))[:, None]
+    r /= np.linalg.norm(r, axis=1, keepdims=True) + 1e-300
+    return P + n * (1e-4 * t), r, n
+
+
+@pytest.mark.parametrize("name", ["tenryuu", "soup"])
+def test_reflection_depth_loop(ctx, O, name):
+    """The depth loop of the reference's TODO 2.2: rays_1 from the primary contacts, rays_k+1 from the contacts of rays_k (the pixel
+    travels in idx), three levels deep.  Every level: generator vs numpy, its contacts vs the oracle on the same rays, dead rays stay
+    dead, and writing the new rays over the old ones (aliasing) gives the same bytes."""
+    buf = scenes.soup_scene(20_000, seed=5, tris_per_mesh=4096) if name == "soup" else scenes.load_bundled(name)
+    scene, bvh = build_gpu(ctx, buf)
+    b = O.bvh_build(buf)
+    W, H = 160, 90
+    cam = api.demo_camera(buf, W, H)
+    n = W * H
+    bvh.set_trace_mode(api.TRACE_REFERENCE_ORDER)
+    bvh.generateContacts(cam)
+    prev_c = bvh.download_primary_contacts()
+    prays = api.Buffer(ctx, n * 48)
+    api.generate_primary_rays(ctx, cam, prays.getCLMem())
+    prev_r = prays.copyToHost(L.RAY, n)
+    pixel = prev_c["pixelIndex"].copy()
+    bufs = [api.Buffer(ctx, n * 48) for _ in range(2)]
+    contacts = api.Buffer(ctx, n * 32)
+    alive_counts = []
+    for level in range(1, 4):
+        out = bufs[level & 1]
+        if level == 1:
+            api.generate_secondary_rays(ctx, api.RAYS_REFLECT, cam, None, bvh.getPrimaryContacts(), n, 0, out.getCLMem())
+        else:
+            api.generate_secondary_rays(ctx, api.RAYS_REFLECT, None, bufs[(level - 1) & 1].getCLMem(), contacts.getCLMem(), n, 0, out.getCLMem())
+        r = out.copyToHost(L.RAY, n)
+        alive = (prev_c["nd"][:, 3] > 0) & (prev_r["idx"] != 0xFFFFFFFF)
+        alive_counts.append(int(alive.sum()))
+        org, dirs, nrm = reflect_reference(prev_r["origin"][:, :3], prev_r["direction"][:, :3], prev_c)
+        assert (r["idx"][~alive] == 0xFFFFFFFF).all() and (r["direction"][~alive] == 0).all()
+        assert np.array_equal(r["idx"][alive], pixel[alive])
+        if alive.any():
+            scale = max(np.abs(org[alive]).max(), 1.0)
+            assert np.abs(r["direction"][alive, :3] - dirs[alive]).max() < 2e-5
+            assert np.abs(r["origin"][alive, :3] - org[alive]).max() < 2e-5 * scale
+            din = prev_r["direction"][alive, :3].astype(np.float64)
+            # mirror law: the normal component flips, the tangential one stays
+            assert np.abs((r["direction"][alive, :3] * nrm[alive]).sum(axis=1) + (din * nrm[alive]).sum(axis=1)).max() < 2e-5
+        if level > 1:                                   # aliasing: new rays written over the rays they were made from
+            tmp = api.Buffer.from_array(ctx, np.ascontiguousarray(prev_r))
+            api.generate_secondary_rays(ctx, api.RAYS_REFLECT, None, tmp.getCLMem(), contacts.getCLMem(), n, 0, tmp.getCLMem())
+            assert tmp.copyToHost(L.RAY, n).tobytes() == r.tobytes()
+            tmp.free()
+        want = O.bvh_trace_rays(r, b)
+        bvh.set_trace_mode(api.TRACE_FAST)
+        bvh.generateContacts(out, contacts, n)
+        compare_fast(contacts.copyToHost(L.CONTACT, n), want, b["tris"])
+        bvh.set_trace_mode(api.TRACE_REFERENCE_ORDER)
+        bvh.generateContacts(out, contacts, n)
+        got = contacts.copyToHost(L.CONTACT, n)
+        h2 = want["nd"][:, 3] > 0
+        assert np.array_equal(got["nd"][:, 3] > 0, h2) and np.array_equal(got["nd"][h2], want["nd"][h2])
+        assert np.array_equal(got["pad"][h2, 0], want["pad"][h2, 0])
+        assert (got["nd"][~alive, 3] == 0).all()
+        prev_c, prev_r = got, r
+    assert alive_counts[0] > 500 and alive_counts[0] >= alive_counts[1] >= alive_counts[2]
+    if name == "soup":
+        assert alive_counts[2] > 50                     # a soup keeps mirrors bouncing
+    for x in (prays, contacts, *bufs):
+        x.free()
+    bvh.free(); scene.free()

@@ -374,3 +374,29 @@ def test_frame_renderer_peer_memory_exchange_equals_synchronous_frames(ctx, exch
         got = r.render_host(cams[-1], False).numpy().view(np.uint8).reshape(res[1], res[0], 4)      # no shadows: the push pass in both modes
         assert np.array_equal(got, r.accel.render_frame_host(cams[-1], False)[0])
         r.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("ss", [2, 3])
+def test_supersampled_frame_is_the_box_filtered_fine_frame(ctx, ss):
+    """Camera.supersampilngFactor (CLStructs.h:49, unused by the reference; its TODO 2.4): s*s rays per pixel = the frame of the
+    camera (s*resX, s*resY, s*FOVDistance) averaged over s x s blocks with rounding; bit-exact against numpy on the fine frame."""
+    buf = scenes.load_bundled("tenryuu")
+    scene, bvh = build_gpu(ctx, buf)
+    W, H = 161, 100
+    cam = api.demo_camera(buf, W, H)
+    fine = api.make_camera(W * ss, H * ss, np.float32(cam["FOVDistance"]) * np.float32(ss), cam["viewTransform"])
+    cam_ss = cam.copy(); cam_ss["supersampilngFactor"] = ss
+    for shadows in (False, True):
+        got, rays = bvh.render_frame_host(cam_ss, shadows, want_rays=True)
+        hi, rays_hi = bvh.render_frame_host(fine, shadows, want_rays=True)
+        want = ((hi.reshape(H, ss, W, ss, 4).astype(np.uint32).sum(axis=(1, 3)) + ss * ss // 2) // (ss * ss)).astype(np.uint8)
+        assert got.shape == (H, W, 4) and np.array_equal(got, want)
+        assert rays == rays_hi and rays >= W * H * ss * ss
+        assert 0 < (got[..., 3] % 255 != 0).sum() < W * H // 4          # partial coverage exists, and only along silhouettes
+    cam0 = cam.copy(); cam0["supersampilngFactor"] = 0
+    assert np.array_equal(bvh.render_frame_host(cam0, True)[0], bvh.render_frame_host(cam, True)[0])
+    cam9 = cam.copy(); cam9["supersampilngFactor"] = 9
+    with pytest.raises(api.ClrtError):
+        bvh.render_frame_host(cam9, True)
+    bvh.free(); scene.free()
