@@ -163,6 +163,7 @@ static int render_stripe_impl(clrt_accel* a, const clrt_camera* h_camera, int sh
   if (slot >= clrt_accel::FRAME_SLOTS) CLRT_FAIL("clrt_render_stripe_on: slot %d of %d", slot, clrt_accel::FRAME_SLOTS);
   if (slot >= 0 && a->kind != ACCEL_BVH) CLRT_FAIL("clrt_render_stripe_on: frame slots exist for the BVH only");
   if (slot < 0) stream = ctx->stream;
+  if (slot + 1 > a->slots_seen) a->slots_seen = slot + 1;
   void** scratch_p = slot < 0 ? &a->d_frame_scratch : &a->d_slot_scratch[slot];
   size_t* scratch_cap = slot < 0 ? &a->frame_scratch_cap : &a->slot_scratch_cap[slot];
   struct LaunchEnv {                              // lends the slot's stream + counter to the trace launches of this call

@@ -124,6 +124,7 @@ struct clrt_accel {
   static constexpr int FRAME_SLOTS = 8;
   void* d_slot_scratch[FRAME_SLOTS] = {nullptr}; size_t slot_scratch_cap[FRAME_SLOTS] = {0};
   uint32_t* d_slot_counters = nullptr;            // FRAME_SLOTS x 64 B
+  int slots_seen = 0;                             // highest frame slot used so far + 1 = the caller's frames in flight (grid sizing)
   cudaStream_t launch_stream = nullptr;           // set only while a slot's launches are being enqueued
   PeerTargets launch_targets = {{nullptr}, 0};     // ditto: peer framebuffers of a p2p frame (n == 0: write the local stripe buffer)
   uint32_t* launch_counter = nullptr;

@@ -474,11 +474,13 @@ shadow_shade_kernel(const clrt_camera cam, const clrt_contact* __restrict__ cont
   if (STATS) flush_stats(st, stats);
 }
 
-// Grid of a persistent launch.  Resident capacity (148 SMs x occupancy; queried once per kernel) caps it.  A synchronous call
-// wants the shortest kernel: one 32-unit packet per warp is enough to start every warp.  A launch in a FRAME SLOT (several frames
-// in flight on their own streams) wants throughput: warps that hold an SM slot must have work for their whole life, so the grid
-// is sized for `rays_per_lane` units per lane and the other frames' kernels take the rest of the machine — with one unit per
-// lane a 1/8 stripe held every slot of the GPU while most lanes had already run out of work.
+// Grid of a persistent launch.  Resident capacity (SMs x occupancy, queried once per kernel) is the upper bound.  A launch alone on
+// the GPU wants the shortest kernel: one 32-unit packet per warp is enough to start every warp.  A launch in a FRAME SLOT (D
+// frames in flight on their own streams) wants throughput, and a warp is efficient only while it lives long: after its last packet
+// its lanes drain one by one.  Measured on 1/8 stripes of Soup-1M (profiles/overlap_probe.py): 4 units per lane 81 % of the
+// full-frame rate, 16 units per lane with 8 slots 94 %, but 24+ units per lane leave too few warps to fill the machine (86 %, 75 %).
+// So: `rays_per_lane` (16) units per lane, but never fewer warps than capacity / D (D kernels run side by side; D = the number of
+// frame slots the caller has used so far).
 template <typename K>
 int persistent_grid(clrt_accel* a, K kernel, int threads, uint32_t packets, unsigned* grid) {
   static int per_sm = 0;                       // one instance per kernel template instantiation
@@ -487,11 +489,16 @@ int persistent_grid(clrt_accel* a, K kernel, int threads, uint32_t packets, unsi
     if (per_sm < 1) per_sm = 1;
   }
   static int rays_per_lane = 0;
-  if (rays_per_lane == 0) { const char* e = getenv("CLRT_RAYS_PER_LANE"); rays_per_lane = e ? atoi(e) : 4; if (rays_per_lane < 1) rays_per_lane = 1; }
+  if (rays_per_lane == 0) { const char* e = getenv("CLRT_RAYS_PER_LANE"); rays_per_lane = e ? atoi(e) : 16; if (rays_per_lane < 1) rays_per_lane = 1; }
   const unsigned resident = (unsigned)(a->ctx->sm_count * per_sm);
   const unsigned warps_per_cta = (unsigned)threads / 32u;
-  const unsigned want = a->launch_stream ? (packets + warps_per_cta * rays_per_lane - 1) / (warps_per_cta * rays_per_lane)
-                                         : (packets + warps_per_cta - 1) / warps_per_cta;
+  const unsigned all = (packets + warps_per_cta - 1) / warps_per_cta;               // one packet per warp
+  unsigned want = all;
+  if (a->launch_stream) {
+    const unsigned slots = (unsigned)max(1, a->slots_seen);
+    const unsigned fill = (resident + slots - 1u) / slots;
+    want = min(all, max((packets + warps_per_cta * rays_per_lane - 1) / (warps_per_cta * rays_per_lane), fill));
+  }
   *grid = min(resident, max(1u, want));
   return 0;
 }

@@ -6,7 +6,7 @@ once (redundant rebuild: a 1M-triangle LBVH build costs less than broadcasting i
 renders its stripe — 32x8-pixel tiles, tile t owned by rank t % world, persistent warps inside the GPU pull packets
 from an atomic counter — into a device buffer in stripe order; ONE collective (all-gather of equal, padded RGBA8
 stripes, 8.3 MB per 1080p frame) follows, and an untile kernel restores raster order.  No other exchange exists on
-the path.  Three frames are in flight: frames are traced on alternating streams (frame slots of the C ABI) so that the
+the path.  Eight frames are in flight: frames are traced on alternating streams (frame slots of the C ABI) so that the
 latency-bound tail of one frame overlaps the next, and the collective, the untile and the read-back run on one more stream.
 
 CLRT_EXCHANGE selects the exchange (BVH): "nccl" (the above; the default on one GPU), "fused" (the default at world > 1;
@@ -105,7 +105,7 @@ class FrameRenderer:
         # work counter + scratch), so the tail of one frame's persistent kernels — a few long rays on a mostly idle GPU —
         # overlaps the head of the next frame's; gather + untile (+ read-back) run on one more stream (`comm`), in frame
         # order on every rank (the collective's order must agree across ranks).  Buffers are per slot; events order reuse.
-        self.DEPTH = max(1, min(8, int(os.environ.get("CLRT_FRAME_DEPTH", "4")))) if accel.upper() == "BVH" else 1
+        self.DEPTH = max(1, min(8, int(os.environ.get("CLRT_FRAME_DEPTH", "8")))) if accel.upper() == "BVH" else 1
         self.comm = torch.cuda.Stream(self.device)
         self.trace_streams = [self.stream] + [torch.cuda.Stream(self.device) for _ in range(self.DEPTH - 1)]
         self.stripes = [torch.zeros(self.cap, dtype=torch.int32, device=self.device) for _ in range(self.DEPTH)]

@@ -5,7 +5,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
 import bench
 from openclraytracer_b200 import frame
-D = int(os.environ.get("CLRT_FRAME_DEPTH", "4"))
+D = int(os.environ.get("CLRT_FRAME_DEPTH", "8"))
 for wl in sys.argv[1:] or ("soup1m",):
     buf, _ = bench.make_scene(wl)
     r = frame.FrameRenderer(buf, 1920, 1080, "BVH", 0, 1, 0)
@@ -27,5 +27,5 @@ for wl in sys.argv[1:] or ("soup1m",):
         e1.record(r.stream); torch.cuda.synchronize()
         ms = e0.elapsed_time(e1) / 40
         if nr == 1: base = ms
-        print(wl, "D", D, "RPL", os.environ.get("CLRT_RAYS_PER_LANE", "8"), "nranks", nr, "ms per stripe %.3f  ideal %.3f  efficiency %.2f" % (ms, base / nr, base / nr / ms), flush=True)
+        print(wl, "D", D, "RPL", os.environ.get("CLRT_RAYS_PER_LANE", "16 (default)"), "nranks", nr, "ms per stripe %.3f  ideal %.3f  efficiency %.2f" % (ms, base / nr, base / nr / ms), flush=True)
     r.close()
