@@ -400,3 +400,36 @@ def test_supersampled_frame_is_the_box_filtered_fine_frame(ctx, ss):
     with pytest.raises(api.ClrtError):
         bvh.render_frame_host(cam9, True)
     bvh.free(); scene.free()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("kind", __import__("edge_scenes").KINDS)
+def test_edge_scenes_build_and_trace_vs_oracle(ctx, O, kind):
+    """tests/edge_scenes.py (zero extent on an axis, all-negative box, identical triangles, zero-area triangles, collapsed axes,
+    clustered keys): triangles, Morton pairs and nodes bit-exact, REFERENCE_ORDER contacts bit-exact, FAST within the north-star
+    tolerances — through whichever trace structure construct() chose, and through both when forced."""
+    import edge_scenes
+    buf = edge_scenes.edge_scene(kind)
+    scene, bvh = build_gpu(ctx, buf)
+    b = O.bvh_build(buf)
+    n = len(b["tris"])
+    assert np.array_equal(scene.export_triangles(), b["tris"])
+    assert np.array_equal(bvh.export_pairs(), b["pairs"])
+    nodes = bvh.export_nodes()
+    assert np.array_equal(masked_nodes(nodes, n), masked_nodes(b["nodes"], n)[: 2 * n - 1])
+    cam = edge_scenes.edge_camera(kind, 96, 64)
+    want = O.bvh_trace_primary(cam, b)
+    hit = want["nd"][:, 3] > 0
+    assert hit.sum() > 10
+    bvh.set_trace_mode(api.TRACE_REFERENCE_ORDER)
+    bvh.generateContacts(cam)
+    got = bvh.download_primary_contacts()
+    assert np.array_equal(got["nd"][:, 3] > 0, hit)
+    assert np.array_equal(got["nd"][hit], want["nd"][hit]) and np.array_equal(got["pad"][hit, 0], want["pad"][hit, 0])
+    bvh.set_trace_mode(api.TRACE_FAST)
+    for policy in (api.TRACE_TREE_AUTO, api.TRACE_TREE_ALWAYS, api.TRACE_TREE_NEVER):
+        bvh.set_trace_tree(policy)
+        bvh.initializeFrame(); bvh.construct()
+        bvh.generateContacts(cam)
+        compare_fast(bvh.download_primary_contacts(), want, b["tris"])
+    bvh.free(); scene.free()

@@ -111,3 +111,26 @@ def test_literal_mode_differs_only_in_last_inner_node(O):
     O.oracle().oracle_bvh_radix_tree(lit.ctypes.data_as(C.c_void_p), pairs.ctypes.data_as(C.c_void_p), C.c_uint32(n), C.c_int(1))
     assert np.array_equal(fixed["data"][n:2 * n - 2, 1:3], lit["data"][n:2 * n - 2, 1:3])
     assert not np.array_equal(fixed["data"][2 * n - 2, 1:3], lit["data"][2 * n - 2, 1:3])
+
+
+@pytest.mark.parametrize("kind", __import__("edge_scenes").KINDS)
+def test_oracle_vs_reference_live_on_edge_scenes(O, kind):
+    """Zero extent on an axis, all-negative boxes, identical triangles, zero-area triangles, collapsed axes, 1e9 dynamic range
+    (tests/edge_scenes.py): whatever the reference's headers produce — inf/NaN normalisation, clamped cells, chains — the
+    restatement produces the same bits: pairs, nodes, contacts."""
+    import edge_scenes
+    if not O.have_ref():
+        pytest.skip("oracle/_ref not built")
+    scene = edge_scenes.edge_scene(kind)
+    b = O.bvh_build(scene)
+    r = O.ref_bvh_build(scene)
+    n = len(b["tris"])
+    assert np.array_equal(b["pairs"], r["pairs"])
+    assert np.array_equal(masked_nodes(b["nodes"], n)[: 2 * n - 1], masked_nodes(r["nodes"], n)[: 2 * n - 1])
+    cam = edge_scenes.edge_camera(kind, 64, 40)
+    a = O.bvh_trace_primary(cam, b)
+    c = O.ref_trace_primary(cam, r["nodes"], n, scene)
+    hit = c["nd"][:, 3] > 0
+    assert hit.sum() > 10, "the camera must see the geometry"
+    assert np.array_equal(a["nd"][:, 3] > 0, hit)
+    assert np.array_equal(a["nd"][hit], c["nd"][hit])
