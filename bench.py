@@ -108,6 +108,10 @@ class CpuReference:
         O.build(("oracle",))
         self.O, self.scene = O, scene_buf
         self.kind = "reference" if O.have_ref() else "port"
+        # all the host cores this process may run on — torchrun exports OMP_NUM_THREADS=1 to its workers, which would time the
+        # reference on one thread at N > 1
+        host_cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+        (O.ref().ref_set_num_threads if self.kind == "reference" else O.oracle().oracle_set_num_threads)(host_cores)
         self.cores = O.ref().ref_num_threads() if self.kind == "reference" else O.oracle().oracle_num_threads()
         t0 = time.perf_counter()
         self.b = O.ref_bvh_build(scene_buf) if self.kind == "reference" else O.bvh_build(scene_buf)

@@ -394,6 +394,15 @@ void ref_tlg_trace_rays(void* h, const uint8_t* rays48, uint32_t rayCount, const
   }
 }
 
+// torchrun exports OMP_NUM_THREADS=1 to its workers; the CPU baseline is specified on all host cores (bench.py sets the count).
+void ref_set_num_threads(int n) {
+#ifdef _OPENMP
+  if (n > 0) omp_set_num_threads(n);
+#else
+  (void)n;
+#endif
+}
+
 int ref_num_threads(void) {
 #ifdef _OPENMP
   return omp_get_max_threads();
