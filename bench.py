@@ -176,8 +176,8 @@ def run_reference(args, workload_desc, scene_buf, n_tris):
 def time_trace_kernels(r, cam, repeats=5):
     """The traversal kernels of one frame, each timed alone with CUDA events on the launching stream:
     trace_primary_kernel (closest hit, camera entry point) and shadow_shade_kernel (occlusion queries + shading).
-    Algorithmic bytes from the kernels' statistics mode: 64 B per inner-node visit + 48 B per triangle test + 32 B per
-    run leaf-box test, + 32 B contact written (primary) / 32 B contact read + 4 B pixel written (shadow)."""
+    Algorithmic bytes from the kernels' statistics mode: 128 B per wide-node visit + 48 B per triangle test, + 32 B contact
+    written (primary) / 32 B contact read + 4 B pixel written (shadow)."""
     import torch
     a = r.accel
     n = r.resX * r.resY
