@@ -76,6 +76,37 @@ def gather_stripes(local_stripe, world, group=None):
     return out
 
 
+# ---- the peer-memory exchange protocol (csrc/peer.cu, clrt_render_frame_peers) in words -----------------------------------------
+PEER_READY, PEER_ACK, PEER_WORDS = 0, 64, 128          # word offsets inside a GPU's flag block: [kind + slot*8 + writer rank]
+
+
+def peer_word(kind, slot, writer):
+    """Index of the flag word that GPU `writer` raises for frame slot `slot` (8 slots x 8 writers per kind)."""
+    assert kind in (PEER_READY, PEER_ACK) and 0 <= slot < 8 and 0 <= writer < 8
+    return kind + slot * 8 + writer
+
+
+def slot_sequence(frame_no, depth):
+    """Frame number -> (slot, sequence number carried by the slot's flag words; 1 for the slot's first frame)."""
+    return frame_no % depth, frame_no // depth + 1
+
+
+def peer_frame_ops(frame_no, depth, rank, world):
+    """The stream-ordered steps one GPU enqueues for one frame, as (op, ...) tuples — what clrt_render_frame_peers launches.
+    tests/test_frame_host.py runs these for all ranks under random interleavings: no deadlock, no framebuffer overwritten
+    before every GPU consumed it, every consumed frame complete."""
+    k, seq = slot_sequence(frame_no, depth)
+    ops = []
+    if seq > 1:
+        ops.append(("wait", [peer_word(PEER_ACK, k, w) for w in range(world)], seq - 1))
+    ops.append(("store_pixels", k, frame_no))                          # into every GPU's framebuffer k
+    ops.append(("signal", peer_word(PEER_READY, k, rank), seq))       # on every GPU
+    ops.append(("wait", [peer_word(PEER_READY, k, w) for w in range(world)], seq))
+    ops.append(("consume", k, frame_no))                               # read-back / display
+    ops.append(("signal", peer_word(PEER_ACK, k, rank), seq))
+    return ops
+
+
 class FrameRenderer:
     """Per-rank renderer: owns the context (on torch's current stream), the device scene and the built structure."""
 
@@ -132,7 +163,6 @@ class FrameRenderer:
         self.stream.synchronize()
 
     # ---- exchange over peer memory ------------------------------------------------------------------------------------------
-    READY, ACK = 0, 64                                    # word offsets inside a rank's flag block: [kind + slot*8 + writer rank]
 
     def _setup_peers(self):
         """One exportable block per rank: DEPTH raster framebuffers + 1 KiB of flag words.  Handles travel by all_gather_object.
@@ -191,8 +221,7 @@ class FrameRenderer:
 
     def _submit_peers(self, camera, shadows, want_rays, to_host):
         torch = self.torch
-        k = self.frame_no % self.DEPTH
-        seq = self.frame_no // self.DEPTH + 1             # per-slot sequence number carried by the flag words
+        k, seq = slot_sequence(self.frame_no, self.DEPTH)
         self.frame_no += 1
         if to_host:
             self.ev_host[k].synchronize()
@@ -207,14 +236,14 @@ class FrameRenderer:
             return rays
         with torch.cuda.stream(ts):
             if seq > 1:                                   # every GPU has consumed the previous frame of slot k from its framebuffer
-                api.peer_wait(self.ctx, s, self._own_flags, self.ACK + k * 8, self.world, seq - 1)
+                api.peer_wait(self.ctx, s, self._own_flags, peer_word(PEER_ACK, k, 0), self.world, seq - 1)
             rays = self.accel.render_stripe_on(s, k, camera, shadows, self.rank, self.world, self.stripes[k].data_ptr(), want_rays)
             api.frame_push(self.ctx, s, self.stripes[k].data_ptr(), self.resX, self.resY, self.rank, self.world, self._peer_rasters[k])
-            api.peer_signal(self.ctx, s, self._peer_flags, self.world, self.READY + k * 8 + self.rank, seq)
-            api.peer_wait(self.ctx, s, self._own_flags, self.READY + k * 8, self.world, seq)
+            api.peer_signal(self.ctx, s, self._peer_flags, self.world, peer_word(PEER_READY, k, self.rank), seq)
+            api.peer_wait(self.ctx, s, self._own_flags, peer_word(PEER_READY, k, 0), self.world, seq)
             if to_host and self.rank == 0:
                 self.host_rasters[k].copy_(self.rasters[k], non_blocking=True)
-            api.peer_signal(self.ctx, s, self._peer_flags, self.world, self.ACK + k * 8 + self.rank, seq)
+            api.peer_signal(self.ctx, s, self._peer_flags, self.world, peer_word(PEER_ACK, k, self.rank), seq)
             if to_host:
                 self.ev_host[k].record(ts)
         self.stripe, self.raster, self.host_raster = self.stripes[k], self.rasters[k], self.host_rasters[k]

@@ -64,3 +64,66 @@ def test_orbit_camera_step0_is_the_demo_camera():
     buf = scenes.load_bundled("cube")
     a, b = frame.orbit_camera(buf, 64, 48, 0), api.demo_camera(buf, 64, 48)
     assert np.allclose(a["viewTransform"], b["viewTransform"], atol=1e-6) and a["FOVDistance"] == b["FOVDistance"]
+
+
+def _simulate_peer_frames(world, depth, frames, seed, skip_ack_wait=False):
+    """Discrete model of the peer-memory exchange: every GPU has `depth` in-order streams, 128 flag words and `depth`
+    framebuffers holding, per writer, the frame number last stored.  A random scheduler picks any stream whose head op can run.
+    Returns None, or a string naming the first violated invariant."""
+    import random
+    rng = random.Random(seed)
+    flags = [[0] * frame.PEER_WORDS for _ in range(world)]
+    fb = [[[-1] * world for _ in range(depth)] for _ in range(world)]          # fb[gpu][slot][writer] = frame
+    consumed = [[-1] * depth for _ in range(world)]                            # last frame consumed from fb[gpu][slot]
+    streams = [[[] for _ in range(depth)] for _ in range(world)]
+    for f in range(frames):
+        for r in range(world):
+            ops = frame.peer_frame_ops(f, depth, r, world)
+            if skip_ack_wait:
+                ops = [o for o in ops if not (o[0] == "wait" and o[1][0] >= frame.PEER_ACK)]
+            streams[r][f % depth].extend(ops)
+    pending = sum(len(q) for s in streams for q in s)
+    while pending:
+        ready = []
+        for r in range(world):
+            for k in range(depth):
+                q = streams[r][k]
+                if q and (q[0][0] != "wait" or all(flags[r][w] >= q[0][2] for w in q[0][1])):
+                    ready.append((r, k))
+        if not ready:
+            return "deadlock with %d ops pending" % pending
+        r, k = rng.choice(ready)
+        op = streams[r][k].pop(0)
+        pending -= 1
+        if op[0] == "store_pixels":
+            _, slot, f = op
+            for g in range(world):
+                if f - depth >= 0 and consumed[g][slot] < f - depth:
+                    return "GPU %d overwrote frame %d in slot %d of GPU %d before it was consumed" % (r, f - depth, slot, g)
+                fb[g][slot][r] = f
+        elif op[0] == "signal":
+            for g in range(world):
+                flags[g][op[1]] = op[2]
+        elif op[0] == "consume":
+            _, slot, f = op
+            if fb[r][slot] != [f] * world:
+                return "GPU %d consumed a torn frame %d: %r" % (r, f, fb[r][slot])
+            consumed[r][slot] = f
+    return None
+
+
+@pytest.mark.parametrize("world,depth", [(2, 1), (2, 4), (3, 2), (4, 8), (8, 8), (8, 3)])
+def test_peer_exchange_protocol_under_random_interleavings(world, depth):
+    """The N > 1 path has no collective to run over gloo: its host-side logic IS the flag protocol (frame.peer_frame_ops = what
+    clrt_render_frame_peers enqueues).  Random schedules of all GPUs' streams: never a deadlock, never a framebuffer overwritten
+    before every GPU consumed it, never a torn frame.  Control: without the ack wait the model must catch an overwrite."""
+    for seed in range(25):
+        assert _simulate_peer_frames(world, depth, 5 * depth + 3, seed) is None
+    caught = [_simulate_peer_frames(world, depth, 5 * depth + 3, seed, skip_ack_wait=True) for seed in range(25)]
+    assert any(c is not None and "overwrote" in c for c in caught)
+
+
+def test_peer_flag_words_do_not_collide():
+    words = {frame.peer_word(kind, slot, w) for kind in (frame.PEER_READY, frame.PEER_ACK) for slot in range(8) for w in range(8)}
+    assert len(words) == 128 and max(words) < frame.PEER_WORDS
+    assert [frame.slot_sequence(f, 3) for f in range(7)] == [(0, 1), (1, 1), (2, 1), (0, 2), (1, 2), (2, 2), (0, 3)]
