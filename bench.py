@@ -111,12 +111,15 @@ class CpuReference:
         # all the host cores this process may run on — torchrun exports OMP_NUM_THREADS=1 to its workers, which would time the
         # reference on one thread at N > 1
         host_cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
-        (O.ref().ref_set_num_threads if self.kind == "reference" else O.oracle().oracle_set_num_threads)(host_cores)
+        self.set_threads(host_cores)
         self.cores = O.ref().ref_num_threads() if self.kind == "reference" else O.oracle().oracle_num_threads()
         t0 = time.perf_counter()
         self.b = O.ref_bvh_build(scene_buf) if self.kind == "reference" else O.bvh_build(scene_buf)
         self.build_ms = (time.perf_counter() - t0) * 1e3
         self.n = self.b["n"]
+
+    def set_threads(self, n):
+        (self.O.ref().ref_set_num_threads if self.kind == "reference" else self.O.oracle().oracle_set_num_threads)(int(n))
 
     def frame(self, cam):
         """-> (rays traced, seconds)"""
@@ -135,7 +138,7 @@ class CpuReference:
         return len(c) + len(srl), (t1 - t0) + (t3 - t2)
 
 
-def cpu_baseline(scene_buf, res, budget_s=12.0):
+def cpu_baseline(scene_buf, res, budget_s=12.0, single_thread_budget_s=4.0):
     from openclraytracer_b200 import frame
     ref = CpuReference(scene_buf)
     rays, secs, frames = 0, 0.0, 0
@@ -143,6 +146,14 @@ def cpu_baseline(scene_buf, res, budget_s=12.0):
         r, s = ref.frame(frame.orbit_camera(scene_buf, res[0], res[1], frames))
         rays += r; secs += s; frames += 1
     sample = f"{frames} frame(s) of {res[0]}x{res[1]} primary+shadow rays ({rays} rays) on the bench camera path"
+    # the same on ONE thread ("timed at 1 thread and at all host cores"), a quarter-size frame, ~4 s
+    ref.set_threads(1)
+    r1, s1, f1, res1 = 0, 0.0, 0, (res[0] // 2, res[1] // 2)
+    while f1 < 1 or (s1 < single_thread_budget_s and f1 < 16):
+        r, s = ref.frame(frame.orbit_camera(scene_buf, res1[0], res1[1], f1))
+        r1 += r; s1 += s; f1 += 1
+    ref.set_threads(ref.cores)
+    ref.single_thread = {"value": r1 / s1 / 1e6, "unit": UNIT, "sample": f"{f1} frame(s) of {res1[0]}x{res1[1]} ({r1} rays)"}
     return rays / secs / 1e6, ref, sample
 
 
@@ -348,6 +359,7 @@ def main():
         if not args.no_cpu_baseline:
             v, ref, sample = cpu_baseline(scene_buf, (960, 540))
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": ref.cores, "kind": ref.kind, "sample": sample,
+                                    "single_thread": ref.single_thread,
                                     "build_ms_per_Mtri": ref.build_ms / (n_tris / 1e6)}
         print(json.dumps(line))
     r.close()
