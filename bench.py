@@ -356,7 +356,7 @@ def main():
                                      "algorithmic_GBs": v["bytes"] / (v["ms"] * 1e-3) / 1e9} for k, v in kt.items()}
         if not args.no_kernels:
             line["kernels"] = kernel_rooflines(r, hbm_peak, n_tris, stage_med)
-        if not args.no_cpu_baseline:
+        if not args.no_cpu_baseline and world == 1:          # the CPU baseline is reported at N = 1 only
             v, ref, sample = cpu_baseline(scene_buf, (960, 540))
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": ref.cores, "kind": ref.kind, "sample": sample,
                                     "single_thread": ref.single_thread,
