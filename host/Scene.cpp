@@ -24,6 +24,9 @@
 #include <clrt_host.h>
 
 #include <cstdio>
+#include <cstring>
+#include <dirent.h>
+#include <strings.h>
 #include <cstdlib>
 #include <fstream>
 #include <map>
@@ -194,6 +197,8 @@ void close_shape(ObjShape& shape, const std::vector<float>& v, const std::vector
   shape = ObjShape();
 }
 
+std::string ci_resolve(const std::string& p);
+
 bool load_obj(const std::string& file, const std::string& mtl_base, std::vector<ObjShape>& shapes, std::vector<ObjMaterial>& materials,
               std::string& err) {
   std::ifstream in(file.c_str());
@@ -228,7 +233,7 @@ bool load_obj(const std::string& file, const std::string& mtl_base, std::vector<
       continue;
     }
     if (0 == strncmp(tok, "mtllib", 6) && is_space(tok[6])) {
-      const std::string path = mtl_base + first_word(tok + 7);
+      const std::string path = ci_resolve(mtl_base + first_word(tok + 7));
       std::ifstream m(path.c_str());
       load_mtl(m, by_name, materials);                  // a missing file still yields the default material
       continue;
@@ -281,22 +286,59 @@ int string_to_floats(const std::string& str, float* result, int size) {       //
 }
 
 bool file_exists(const std::string& p) { std::ifstream f(p.c_str()); return (bool)f; }
+
+// The reference runs on Windows: its scene files and .bat command lines use back-slashes and spell names in whatever case
+// (Bin/ClumsyDragon.bat asks for ..\clumsydragon.txt, the file is ClumsyDragon.txt).  A path that does not exist as written is
+// resolved component by component, ignoring case; if that fails too the path is returned unchanged and the open reports it.
+std::string ci_resolve(const std::string& p) {
+  if (p.empty() || file_exists(p)) return p;
+  std::string cur = p[0] == '/' ? "/" : "";
+  size_t i = p[0] == '/' ? 1 : 0;
+  while (i <= p.size()) {
+    const size_t j = p.find('/', i);
+    const std::string part = p.substr(i, j == std::string::npos ? std::string::npos : j - i);
+    i = j == std::string::npos ? p.size() + 1 : j + 1;
+    if (part.empty()) continue;
+    if (part == "." || part == "..") { cur += part + "/"; continue; }
+    std::string found;
+    if (DIR* d = opendir(cur.empty() ? "." : cur.c_str())) {
+      std::string exact, loose;
+      while (struct dirent* e = readdir(d)) {
+        if (part == e->d_name) exact = e->d_name;
+        else if (loose.empty() && 0 == strcasecmp(part.c_str(), e->d_name)) loose = e->d_name;
+      }
+      closedir(d);
+      found = !exact.empty() ? exact : loose;
+    }
+    if (found.empty()) return p;
+    cur += found + (i <= p.size() ? "/" : "");
+  }
+  return file_exists(cur) ? cur : p;
+}
+std::string host_path(std::string p) {
+  for (size_t i = 0; i < p.size(); i++) if (p[i] == '\\') p[i] = '/';
+  return ci_resolve(p);
+}
 std::string dir_of(const std::string& p) { const size_t s = p.find_last_of('/'); return s == std::string::npos ? std::string("") : p.substr(0, s + 1); }
 std::string resolve_model_path(std::string p, const std::string& scene_file) {
   for (size_t i = 0; i < p.size(); i++) if (p[i] == '\\') p[i] = '/';
   while (!p.empty() && (p[p.size() - 1] == '\r' || p[p.size() - 1] == ' ')) p.erase(p.size() - 1);
-  if (p.empty() || p[0] == '/' || file_exists(p)) return p;
+  if (p.empty() || file_exists(p)) return p;
+  if (p[0] == '/') return ci_resolve(p);
   const std::string base = dir_of(scene_file);
-  if (file_exists(base + p)) return base + p;
-  if (file_exists(base + "Release/" + p)) return base + "Release/" + p;
+  const std::string tries[3] = {base + p, base + "Release/" + p, p};
+  for (int i = 0; i < 3; i++) if (file_exists(tries[i])) return tries[i];
+  for (int i = 0; i < 3; i++) { const std::string r = ci_resolve(tries[i]); if (file_exists(r)) return r; }
   return p;
 }
 
 inline float fmin2(float a, float b) { return a < b ? a : b; }     // the reference's min/max macros (CLPortability.h:147-148)
 inline float fmax2(float a, float b) { return a > b ? a : b; }
 
-Result pack_scene_file(const char* filename, char*& out, uint64_t& out_size, Errata& err) {
+Result pack_scene_file(const char* filename_as_given, char*& out, uint64_t& out_size, Errata& err) {
   std::map<std::string, std::vector<std::string> > raw;
+  const std::string resolved = host_path(filename_as_given ? filename_as_given : "");
+  const char* filename = resolved.c_str();
   {
     std::ifstream f(filename);
     if (!f.is_open()) { CLRT_FILL_ERRATA(err, "File: " << filename << " couldn't be opened!"); return CLRayTracer::Common::Error; }
