@@ -134,3 +134,44 @@ def test_oracle_vs_reference_live_on_edge_scenes(O, kind):
     assert hit.sum() > 10, "the camera must see the geometry"
     assert np.array_equal(a["nd"][:, 3] > 0, hit)
     assert np.array_equal(a["nd"][hit], c["nd"][hit])
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_shading_restatement_vs_reference_live_with_many_lights_and_materials(O, seed):
+    """cpuShadeBlinnPhong (Shading.h:74-166) through the reference's own header vs the restatement, on scenes the bundled models
+    do not have: 0-4 lights (some inside the geometry, one at the camera), 1-5 materials with random coefficients, shininess from
+    0 to 200, zero and >1 colour components (clamping), sub-meshes cycling through the materials.  Bit-exact float4 colours."""
+    if not O.have_ref():
+        pytest.skip("oracle/_ref not built")
+    rng = np.random.default_rng(1000 + seed)
+    n = 400
+    tri = scenes.soup_triangles(n, 50 + seed)
+    nm = int(rng.integers(1, 6))
+    mats = np.zeros(nm, dtype=L.MATERIAL)
+    for m in mats:
+        for key in ("ambient", "diffuse", "specular", "transmittance", "emission"):
+            m[key][:3] = rng.uniform(0.0, 1.6, 3).astype(np.float32) * (rng.random(3) > 0.15)
+        m["shininess"] = np.float32(rng.choice([0.0, 1.0, 8.0, 37.5, 200.0]))
+        m["ior"], m["dissolve"], m["illum"] = 1.0, 1.0, 2.0
+    model = []
+    for i, first in enumerate(range(0, n, 64)):
+        verts = tri[first:first + 64].reshape(-1, 3)
+        model.append((verts, np.arange(len(verts), dtype=np.uint32), i % nm))
+    nl = int(rng.integers(0, 5))
+    lights = np.zeros((nl, 4), dtype=np.float32)
+    for i in range(nl):
+        lights[i, :3] = rng.uniform(-0.5, 1.5, 3)
+        lights[i, 3] = np.float32(rng.choice([0.0, 1.0, 50.0, 1000.0]))
+    scene = scenes.pack_scene(lights, [model], materials=mats)
+    cam = O.demo_camera(scene, 80, 60)
+    if nl:                                                       # a light exactly at the eye
+        lights[0, :3] = cam["viewTransform"][[3, 7, 11]]
+        scene = scenes.pack_scene(lights, [model], materials=mats)
+    b = O.bvh_build(scene)
+    c = O.bvh_trace_primary(cam, b)
+    hit = c["nd"][:, 3] > 0
+    assert hit.sum() > 200 and len(np.unique(c["materialIndex"][hit])) == nm
+    _, f32 = O.shade(cam, scene, c, want_f32=True)
+    ref = O.ref_shade(cam, c, scene)
+    assert np.array_equal(f32[hit].view(np.uint32), ref[hit].view(np.uint32))
+    assert np.isfinite(f32[hit]).all()
