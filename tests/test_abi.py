@@ -56,3 +56,13 @@ def test_layout_sizes_match_header():
         src = os.path.join(d, "t.c")
         open(src, "w").write(f'#include "clrt.h"\n{body}int main(void){{return 0;}}\n')
         subprocess.run(["gcc", "-std=c11", "-I", os.path.join(ROOT, "include"), "-c", src, "-o", os.path.join(d, "t.o")], check=True)
+
+
+def test_every_exported_symbol_is_documented():
+    """INTEGRATION.md / DESIGN.md name every entry point of include/clrt.h (which reference interface it replaces, or that it is new)."""
+    import re
+    text = re.sub(r"/\*.*?\*/", "", open(os.path.join(ROOT, "include", "clrt.h")).read(), flags=re.S)
+    names = sorted(set(re.findall(r"\b(clrt_[a-z0-9_]+)\s*\(", text)))
+    docs = open(os.path.join(ROOT, "INTEGRATION.md")).read() + open(os.path.join(ROOT, "DESIGN.md")).read()
+    assert len(names) > 60
+    assert [n for n in names if n not in docs] == []
