@@ -52,7 +52,7 @@ void* clrt_ctx_stream(clrt_ctx* ctx);                 /* the cudaStream_t       
 #define CLRT_DEV_GLOBAL_MEM_SIZE     3
 int clrt_ctx_device_info(clrt_ctx* ctx, int what, uint64_t* out);
 
-/* ---- buffers: CLBuffer (R/Include/OpenCLUtils/CLBuffer.h:39-112, R/src/OpenCLUtils/CLBuffer.cpp:40-130) -- */
+/* ---- buffers: CLBuffer (R/Include/OpenCLUtils/CLBuffer.h:39-112, R/src/OpenCLUtils/CLBuffer.cpp:42-122) -- */
 int    clrt_buf_alloc(clrt_ctx* ctx, size_t bytes, const void* h_src /* may be NULL */, clrt_buf** out);
 int    clrt_buf_free(clrt_buf* buf);
 int    clrt_buf_resize(clrt_buf* buf, size_t bytes);  /* grow-only; contents discarded on growth (CLBuffer.cpp:70-94) */

@@ -175,7 +175,7 @@ class CLExecutionContext {
   clrt_ctx* _ctx;
 };
 
-class CLBuffer {                                                          // CLBuffer.h:39-112, CLBuffer.cpp:40-130
+class CLBuffer {                                                          // CLBuffer.h:39-112, CLBuffer.cpp:42-122
  public:
   CLBuffer(const CLExecutionContext& context, size_t size, CLBufferFlags::CLBufferAccess access)
       : _context(context), _access(access), _buf(NULL) {

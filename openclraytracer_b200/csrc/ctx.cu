@@ -1,6 +1,6 @@
 // ctx.cu — context + buffers: the thin C-ABI CUDA layer that replaces the reference's OpenCL wrapper
 // (R/Include/OpenCLUtils/CLExecutionContext.h, CLBuffer.h; R/src/OpenCLUtils/CLExecutionContext.cpp:264-293,386-403,
-//  R/src/OpenCLUtils/CLBuffer.cpp:40-130).  One in-order stream per context, like the reference's single queue.
+//  R/src/OpenCLUtils/CLBuffer.cpp:42-122).  One in-order stream per context, like the reference's single queue.
 #include "common.cuh"
 #include <stdarg.h>
 
