@@ -66,3 +66,35 @@ def test_every_exported_symbol_is_documented():
     docs = open(os.path.join(ROOT, "INTEGRATION.md")).read() + open(os.path.join(ROOT, "DESIGN.md")).read()
     assert len(names) > 60
     assert [n for n in names if n not in docs] == []
+
+
+@pytest.mark.skipif(not os.path.isdir("/root/reference"), reason="needs the reference tree")
+def test_reference_citations_point_into_existing_lines():
+    """Every `File.ext:first[-last]` citation in the headers, sources and documents names a file of the reference and lines it has."""
+    import collections
+    import re
+    index = collections.defaultdict(list)
+    for d, _, fs in os.walk("/root/reference"):
+        for f in fs:
+            index[f.lower()].append(os.path.join(d, f))
+    own = {"clrt.h", "scene.cpp", "clrt_types.h", "clrt_host.h"}            # same-named files of this repository
+    docs = ["DESIGN.md", "INTEGRATION.md", "include/clrt.h", "include/clrt_types.h", "include/clrt_host.h", "include/clrt/CLRayTracer.hpp",
+            "host/Scene.cpp", "host/OpenCLRayTracerDemo.cpp", "oracle/clrt_oracle.cpp", "oracle/ref_bridge.cpp",
+            "openclraytracer_b200/api.py", "openclraytracer_b200/frame.py"]
+    csrc = os.path.join(ROOT, "openclraytracer_b200", "csrc")
+    docs += [os.path.join("openclraytracer_b200", "csrc", f) for f in sorted(os.listdir(csrc)) if f.endswith((".cu", ".cuh"))]
+    checked, bad = 0, []
+    for doc in docs:
+        text = open(os.path.join(ROOT, doc), errors="replace").read()
+        for m in re.finditer(r"([A-Za-z_][A-Za-z0-9_]*\.(?:h|cpp|cl|txt|bat)):(\d+)(?:-(\d+))?", text):
+            name, a, b = m.group(1), int(m.group(2)), int(m.group(3) or m.group(2))
+            paths = index.get(name.lower())
+            if not paths:
+                if name.lower() not in own:
+                    bad.append((doc, m.group(0), "no such file in the reference"))
+                continue
+            checked += 1
+            lines = max(sum(1 for _ in open(p, errors="replace")) for p in paths)
+            if a > b or b > lines:
+                bad.append((doc, m.group(0), "the file has %d lines" % lines))
+    assert checked > 250 and bad == []
