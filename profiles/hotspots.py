@@ -1,20 +1,24 @@
 """profiles/hotspots.py <tag>: per-SOURCE-LINE view of the ncu full captures of the traversal kernels (no GPU needed).
 ncu's source page (`ncu -i <rep> --page source --csv`) gives warp-stall samples and executed instructions per SASS instruction;
 `nvdisasm -g` on the library's cubin gives the source line of every instruction (-lineinfo build).  Joined on the instruction
-offset (opcodes are cross-checked) and summed per line of csrc/trace.cu -> profiles/<tag>_source_hotspots.md."""
+offset (opcodes are cross-checked) and summed per source line -> profiles/<tag>_source_hotspots.md."""
 import csv, io, os, re, subprocess, sys, tempfile, collections
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 TAG = sys.argv[1] if len(sys.argv) > 1 else "r01"
 LIB = os.path.join(ROOT, "openclraytracer_b200", "libclrt_cuda.so")
-KERNELS = [("soup1m", "shadow_shade_kernel", "shadow_shade_kernelILb0"), ("soup1m", "trace_primary_kernel", "trace_primary_kernelILi1ELb0"),
-           ("clumsydragon", "shadow_shade_kernel", "shadow_shade_kernelILb0"), ("clumsydragon", "trace_primary_kernel", "trace_primary_kernelILi1ELb0")]
+# (capture label, kernel, substring of the mangled name, object file of the library)
+KERNELS = [("soup1m", "shadow_shade_kernel", "shadow_shade_kernelILb0", "trace"), ("soup1m", "trace_primary_kernel", "trace_primary_kernelILi1ELb0", "trace"),
+           ("clumsydragon", "shadow_shade_kernel", "shadow_shade_kernelILb0", "trace"),
+           ("clumsydragon", "trace_primary_kernel", "trace_primary_kernelILi1ELb0", "trace"),
+           ("blocks", "onesweep_pass_kernel", "onesweep_pass_kernelILi16ELb1", "sort"), ("soup1m", "refit_atomic_kernel", "refit_atomic_kernel", "bvh"),
+           ("soup1m", "karras_emit_kernel", "karras_emit_kernel", "bvh"), ("soup1m", "widen_kernel", "widen_kernel", "trace_tree")]
 
 
-def disassemble():
+def disassemble(obj):
     d = tempfile.mkdtemp()
-    subprocess.run(["cuobjdump", "-xelf", "trace", LIB], cwd=d, check=True, stdout=subprocess.DEVNULL)
-    cubin = [f for f in os.listdir(d) if f.startswith("trace.") and f.endswith(".cubin")][0]
+    subprocess.run(["cuobjdump", "-xelf", obj + ".", LIB], cwd=d, check=True, stdout=subprocess.DEVNULL)
+    cubin = [f for f in os.listdir(d) if f.startswith(obj + ".") and f.endswith(".cubin")][0]
     text = subprocess.run(["nvdisasm", "-g", "-c", os.path.join(d, cubin)], check=True, capture_output=True, text=True).stdout
     funcs, cur, line, inl = {}, None, None, None
     for l in text.splitlines():
@@ -49,17 +53,25 @@ def ncu_sass(rep):
 
 
 def main():
-    funcs = disassemble()
-    src = open(os.path.join(ROOT, "openclraytracer_b200", "csrc", "trace.cu")).read().splitlines()
-    rt = open(os.path.join(ROOT, "openclraytracer_b200", "csrc", "rtmath.cuh")).read().splitlines()
-    out = ["# Source-line hot spots of the traversal kernels (%s)" % TAG, "",
+    dis_cache, src_cache = {}, {}
+
+    def source_line(name, no):
+        if name not in src_cache:
+            p = os.path.join(ROOT, "openclraytracer_b200", "csrc", name)
+            src_cache[name] = open(p).read().splitlines() if os.path.exists(p) else []
+        lines = src_cache[name]
+        return lines[no - 1].strip()[:110].replace("|", "\\|") if 0 < no <= len(lines) else ""
+    out = ["# Source-line hot spots of the hot kernels (%s)" % TAG, "",
            "From the `ncu --set full --import-source on` captures of profiles/capture.sh, joined with `nvdisasm -g` of the shipped cubin "
            "(profiles/hotspots.py).  samples = warp-stall samples attributed to the line's instructions (all / not issued); "
            "inst = warp-level instructions executed; lanes = thread instructions / warp instructions.", ""]
-    for wl, kernel, mangled in KERNELS:
+    for wl, kernel, mangled, obj in KERNELS:
         rep = os.path.join(ROOT, "gpurun_out", "full_%s_%s_%s.ncu-rep" % (wl, kernel, TAG))
         if not os.path.exists(rep):
             continue
+        if obj not in dis_cache:
+            dis_cache[obj] = disassemble(obj)
+        funcs = dis_cache[obj]
         name = next(k for k in funcs if mangled in k)
         dis, sass = funcs[name], ncu_sass(rep)
         by_off = {o: (op, ln) for o, op, ln in dis}
@@ -72,9 +84,8 @@ def main():
         out += ["## [%s] %s — %d SASS instructions, %d opcodes agree with the cubin, %.0f samples, %.3g warp instructions, %.1f lanes on average"
                 % (wl, kernel, len(sass), agree, tot[0], tot[2], tot[3] / max(tot[2], 1)), "",
                 "| file:line | samples (all) | % | not issued | inst % | lanes | source |", "|---|---|---|---|---|---|---|"]
-        for ln, p in sorted(per.items(), key=lambda kv: -kv[1][0])[:22]:
-            lines = src if ln[0] == "trace.cu" else rt if ln[0] == "rtmath.cuh" else []
-            code = lines[ln[1] - 1].strip()[:110].replace("|", "\\|") if 0 < ln[1] <= len(lines) else ""
+        for ln, p in sorted(per.items(), key=lambda kv: -kv[1][0])[:(22 if obj == "trace" else 12)]:
+            code = source_line(ln[0], ln[1])
             out.append("| %s:%d | %.0f | %.1f | %.0f | %.1f | %.1f | `%s` |" % (ln[0], ln[1], p[0], 100 * p[0] / max(tot[0], 1), p[1], 100 * p[2] / max(tot[2], 1),
                                                                               p[3] / max(p[2], 1), code))
         out.append("")
