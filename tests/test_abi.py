@@ -98,3 +98,17 @@ def test_reference_citations_point_into_existing_lines():
             if a > b or b > lines:
                 bad.append((doc, m.group(0), "the file has %d lines" % lines))
     assert checked > 250 and bad == []
+
+
+def test_public_headers_compile_as_c99_and_cpp11(tmp_path):
+    """The boundary is a C ABI: include/clrt.h and clrt_host.h must be plain C (what a cgo / JNI / ctypes binding would include);
+    the C++ host mirror must be a clean C++11 header (the reference builds with VS2012)."""
+    import subprocess
+    c = tmp_path / "c.c"
+    c.write_text("#include <clrt.h>\n#include <clrt_host.h>\nint main(void) { return clrt_abi_version() > 0 ? 0 : 0; }\n")
+    subprocess.run(["gcc", "-std=c99", "-Wall", "-Wextra", "-Werror", "-pedantic", "-I", os.path.join(ROOT, "include"), "-c", str(c),
+                    "-o", str(tmp_path / "c.o")], check=True)
+    cpp = tmp_path / "h.cpp"
+    cpp.write_text("#include <clrt/CLRayTracer.hpp>\nint main() { return 0; }\n")
+    subprocess.run(["g++", "-std=c++11", "-Wall", "-Wextra", "-Werror", "-pedantic", "-I", os.path.join(ROOT, "include"), "-c", str(cpp),
+                    "-o", str(tmp_path / "h.o")], check=True)
