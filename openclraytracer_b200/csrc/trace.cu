@@ -87,6 +87,9 @@ __device__ __forceinline__ Hit traverse_ref(const TraceNode* __restrict__ tnodes
 // ---- FAST policy ---------------------------------------------------------------------------------------------------------
 // Per-lane traversal state.  ANYHIT: an occlusion query - ends at the first triangle with 0 < t < tmax; "some hit below
 // tmax exists" equals "the closest hit is below tmax", which is what the shading's shadow test asks.
+#ifndef CLRT_STACK_TOP_REG
+#define CLRT_STACK_TOP_REG 0
+#endif
 struct Lane {
   Vec3 o, d, inv;
   Hit h;
@@ -94,6 +97,9 @@ struct Lane {
   int sp;
   uint32_t visits;                // statistics mode only: inner-node visits of the current ray (-> Contact.pad[1])
   uint32_t q0, q1, q2, q3, qn;    // postponed leaves (positions in the triangle array) and their count
+#if CLRT_STACK_TOP_REG
+  uint2 top;                      // entry sp-1 of the stack (experiment, see stack_push)
+#endif
 };   // the traversal stack lives in its own local array so that these scalars stay in registers
 
 template <bool STATS, bool ANYHIT>
@@ -129,6 +135,30 @@ __device__ __forceinline__ float child_entry(float x0, float y0, float z0, float
 }
 __device__ __forceinline__ void cswap(float& ta, uint32_t& ca, float& tb, uint32_t& cb) {
   if (tb < ta) { const float t = ta; ta = tb; tb = t; const uint32_t c = ca; ca = cb; cb = c; }
+}
+
+// The stack of (entry distance, node).  CLRT_STACK_TOP_REG=1 (EXPERIMENT, off: not yet measured — the round's GPU time ended with
+// the finding that motivates it) keeps entry sp-1 in registers and loads its successor at pop time, so that the local-memory load
+// overlaps the visit of the popped node instead of heading the next pop: profiles/r01_source_hotspots.md attributes 19.5 % of the
+// primary kernel's stall samples on Soup-1M to the pop's dependent load.  Build a variant with
+//   make -C openclraytracer_b200/csrc EXTRA=-DCLRT_STACK_TOP_REG=1 BUILD=/tmp/b OUT=/tmp/libclrt_top.so   and run with CLRT_LIB_PATH.
+__device__ __forceinline__ void stack_push(Lane& L, uint2* __restrict__ stack, float t, uint32_t c) {
+#if CLRT_STACK_TOP_REG
+  if (L.sp >= FAST_STACK) return;
+  if (L.sp > 0) stack[L.sp - 1] = L.top;
+  L.top = make_uint2(__float_as_uint(t), c); L.sp++;
+#else
+  if (L.sp < FAST_STACK) stack[L.sp++] = make_uint2(__float_as_uint(t), c);
+#endif
+}
+__device__ __forceinline__ uint2 stack_pop(Lane& L, const uint2* __restrict__ stack) {      // L.sp > 0
+#if CLRT_STACK_TOP_REG
+  const uint2 e = L.top;
+  if (--L.sp > 0) L.top = stack[L.sp - 1];
+  return e;
+#else
+  return stack[--L.sp];
+#endif
 }
 
 template <bool STATS, bool ANYHIT>
@@ -171,13 +201,13 @@ __device__ __forceinline__ void lane_step(Lane& L, const WideNode* __restrict__ 
   if (t2 > L.h.cull) t2 = T_INVALID;
   if (t3 > L.h.cull) t3 = T_INVALID;
   cswap(t0, c0, t1, c1); cswap(t2, c2, t3, c3); cswap(t0, c0, t2, c2); cswap(t1, c1, t3, c3); cswap(t1, c1, t2, c2);   // ascending entry distance
-  if (t3 != T_INVALID && L.sp < FAST_STACK) stack[L.sp++] = make_uint2(__float_as_uint(t3), c3);
-  if (t2 != T_INVALID && L.sp < FAST_STACK) stack[L.sp++] = make_uint2(__float_as_uint(t2), c2);
-  if (t1 != T_INVALID && L.sp < FAST_STACK) stack[L.sp++] = make_uint2(__float_as_uint(t1), c1);
+  if (t3 != T_INVALID) stack_push(L, stack, t3, c3);
+  if (t2 != T_INVALID) stack_push(L, stack, t2, c2);
+  if (t1 != T_INVALID) stack_push(L, stack, t1, c1);
   if (t0 != T_INVALID) { L.cur = c0; return; }
   L.cur = SENTINEL;
   while (L.sp > 0) {
-    const uint2 e = stack[--L.sp];
+    const uint2 e = stack_pop(L, stack);
     if (!(__uint_as_float(e.x) > L.h.cull)) { L.cur = e.y; break; }
   }
 }
