@@ -242,6 +242,13 @@ __device__ __forceinline__ void flush_leaves(Lane& L, const clrt_triangle* __res
 #ifndef CLRT_BATCH
 #define CLRT_BATCH 32
 #endif
+// CLRT_PACKET_AHEAD=1 (EXPERIMENT, off: prepared after the round's GPU time ended): every warp claims its NEXT packet when it
+// starts the current one, so the atomic's round trip overlaps a packet's worth of tracing.  profiles/r01_source_hotspots.md: on
+// ClumsyDragon (2-4 node visits per ray) the counter's atomicAdd is the top line of both traversal kernels, 15-16 % of the stall
+// samples.  Cost: at the end a warp may sit on one claimed packet while others are idle (<= 32 units per warp).
+#ifndef CLRT_PACKET_AHEAD
+#define CLRT_PACKET_AHEAD 0
+#endif
 constexpr int WINDOW = CLRT_WINDOW;
 constexpr int REFILL_MIN = CLRT_REFILL_MIN;
 constexpr uint32_t BATCH = CLRT_BATCH;
@@ -256,6 +263,10 @@ __device__ __forceinline__ void run_jobs(Job& job, const WideNode* __restrict__ 
   uint2 stack[FAST_STACK];
   bool busy = false, exhausted = false;
   uint32_t pool_next = 0, pool_end = 0;                         // warp-uniform
+#if CLRT_PACKET_AHEAD
+  uint32_t ahead = 0;                                           // lane 0: base of the packet claimed one refill ago
+  if (lane == 0) ahead = atomicAdd(counter, BATCH);
+#endif
   while (true) {
     // window boundary, all lanes converged: rays that ended during the window are completed together (Job::finish may aim
     // the unit's next ray), then idle lanes are refilled together once enough of them wait.
@@ -265,10 +276,16 @@ __device__ __forceinline__ void run_jobs(Job& job, const WideNode* __restrict__ 
       while (idle) {
         if (pool_next >= pool_end) {
           if (exhausted) break;
+#if CLRT_PACKET_AHEAD
+          const uint32_t b = __shfl_sync(FULL, ahead, 0);
+          if (b >= total) { exhausted = true; break; }
+          if (lane == 0) ahead = atomicAdd(counter, BATCH);
+#else
           uint32_t b = 0;
           if (lane == 0) b = atomicAdd(counter, BATCH);
           b = __shfl_sync(FULL, b, 0);
           if (b >= total) { exhausted = true; break; }
+#endif
           pool_next = b; pool_end = min(b + BATCH, total);
         }
         const uint32_t avail = pool_end - pool_next;
