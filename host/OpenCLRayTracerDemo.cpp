@@ -8,6 +8,7 @@
 // framebuffer written to a binary PPM, and the keyboard / mouse callbacks (:378-451) become a script:
 //   -script "UUDLRadws"   one frame per letter: U/D/L/R = arrow keys (move 0.3 along forward / side), a/d = mouse drag
 //                         left/right, w/s = drag up/down (5 degrees per event)
+//   -scene x.bin          a packed scene buffer instead of a scene file (Scene::setHostSceneData)
 //   -out prefix           writes prefix_<frame>.ppm (default: no files);  -shadows adds the shadow pass;  -device N
 // Shading runs on the device (clrt_shade; the reference shades on the host with the same Blinn-Phong, Shading.h:74-166).
 #include <clrt/CLRayTracer.hpp>
@@ -72,7 +73,18 @@ int main(int argc, char* argv[]) {
     CLExecutionContext context(device);
     std::cout << "Loading scene: " << scenePath << std::endl;
     Scene scene;
-    CHECKED_CALL(scene.load(scenePath.c_str(), err));
+    if (scenePath.size() > 4 && scenePath.substr(scenePath.size() - 4) == ".bin") {
+      // an already packed v0.6 scene buffer (what Scene::load produces; synthetic scenes and the test fixtures come this way)
+      std::vector<unsigned char> bytes;
+      FILE* f = fopen(scenePath.c_str(), "rb");
+      if (!f) { std::cout << "cannot open " << scenePath << std::endl; return 1; }
+      unsigned char chunk[65536]; size_t got;
+      while ((got = fread(chunk, 1, sizeof(chunk), f)) > 0) bytes.insert(bytes.end(), chunk, chunk + got);
+      fclose(f);
+      CHECKED_CALL(scene.setHostSceneData(bytes.data(), bytes.size(), err));
+    } else {
+      CHECKED_CALL(scene.load(scenePath.c_str(), err));
+    }
     const SceneHeader* sceneHeader = SCENE_HEADER(scene.getHostSceneData());
     std::cout << "Scene info:\n   Bounds: Min: X=" << sceneHeader->modelsBoundingBox.bounds[0].x << " Y=" << sceneHeader->modelsBoundingBox.bounds[0].y
               << " Z=" << sceneHeader->modelsBoundingBox.bounds[0].z << "\n           Max: X=" << sceneHeader->modelsBoundingBox.bounds[1].x

@@ -107,6 +107,10 @@ int clrt_trace_primary(clrt_accel* accel, const clrt_camera* h_camera, void* dpt
 /* generateContacts(rays,contacts,rayCount)  BVHManager.cpp:292-329 -> kernel generateContacts2 (BVHKernels.cl:103-117). */
 int clrt_trace_rays(clrt_accel* accel, const void* dptr_rays, void* dptr_contacts, uint32_t ray_count);
 void* clrt_accel_primary_contacts_dptr(clrt_accel* accel);     /* getPrimaryContacts()->getCLMem() */
+/* generateContacts(Camera&) for ONE image-space stripe (ours: the reference is single-device, CLExecutionContext.cpp:264-293):
+ * tiles t = rank (mod nranks) of 32x8 pixels; contacts in stripe order (slot = local tile*256 + y*32 + x; slots outside the image
+ * carry pixelIndex = UINT_MAX), clrt_frame_stripe_pixels() slots.  Feeds the generic-ray passes of a sharded frame. */
+int clrt_trace_primary_stripe(clrt_accel* accel, const clrt_camera* h_camera, uint32_t rank, uint32_t nranks, void* dptr_contacts);
 /* Traversal policy.  FAST (default): near-child-first, t-pruned, persistent-thread kernel — same closest hit,
  * exact ties may pick another triangle.  REFERENCE_ORDER: the reference's A-before-B unpruned order
  * (R/Include/CLData/AccelerationStructs/BVH.h:344-408), bit-exact contacts; the parity vehicle. */
@@ -144,6 +148,10 @@ int clrt_accel_enable_stage_timing(clrt_accel* accel, int on);
 /* Traversal statistics mode (measurement only; the reference has none — SURVEY.md section 5): while on, the trace
  * kernels count rays traversed, inner-node visits and triangle tests.  set_stats zeroes the counters;
  * read_stats returns {rays, inner-node visits, triangle tests, leaf-box tests inside equal-key runs} accumulated since. */
+/* Traversal stacks are bounded (the reference's is `stack[32]`, R/Include/CLData/AccelerationStructs/BVH.h:352, and overflows
+ * silently).  Here a push that does not fit is counted on the device; this call waits for the context's stream and FAILS when a
+ * launch since the last check dropped a subtree.  The blocking C++ / Python generateContacts call it after their wait. */
+int clrt_accel_check(clrt_accel* accel);
 int clrt_accel_set_stats(clrt_accel* accel, int on);
 int clrt_accel_read_stats(clrt_accel* accel, uint64_t* h_out4);
 
@@ -184,6 +192,12 @@ int clrt_generate_secondary_rays(clrt_ctx* ctx, int kind, const clrt_camera* h_c
 int clrt_shade(clrt_ctx* ctx, const clrt_scene* scene, const clrt_camera* h_camera, const void* dptr_contacts,
                uint32_t n, const void* dptr_shadow_contacts, void* dptr_rgba8 /* may be NULL */,
                void* dptr_rgba_f32 /* may be NULL */);
+
+/* Bounce frame (BASELINE.json configs[3]; ours — the reference has no secondary rays, KNOWN_ISSUES_AND_TODO.txt:27-33): Blinn-Phong of
+ * contact i without shadows, each colour channel halved when the bounce ray of slot i (dptr_bounce_contacts[i], from
+ * clrt_generate_bounce_rays + clrt_trace_rays) hit something: one-sample ambient occlusion -> RGBA8 at slot i. */
+int clrt_shade_bounce(clrt_ctx* ctx, const clrt_scene* scene, const clrt_camera* h_camera, const void* dptr_contacts, uint32_t n,
+                      const void* dptr_bounce_contacts, void* dptr_rgba8);
 
 /* Shadow pass + Blinn-Phong in ONE kernel over n contacts (BVH only): per contact and light an occlusion query along the
  * shadow ray clrt_generate_shadow_rays would build, then the shading of clrt_shade -> RGBA8.  Same pixels as the

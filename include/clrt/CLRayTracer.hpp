@@ -308,7 +308,7 @@ class AccelerationStructureManager {                                      // Acc
   virtual Common::Result generateContacts(Camera& cam, Common::Errata& err) {
     if (!_accel) { CLRT_FILL_ERRATA(err, "generateContacts: initialize() was not called"); return Common::Error; }
     CLRT_CALL(clrt_trace_primary(_accel, &cam, NULL), err);
-    CLRT_CALL(clrt_ctx_sync(_context.handle()), err);
+    CLRT_CALL(clrt_accel_check(_accel), err);              // waits for the queue; fails on a traversal-stack overflow
     _primary.reset(new ContactsView(_context, clrt_accel_primary_contacts_dptr(_accel), (size_t)cam.resX * cam.resY * sizeof(Contact)));
     return Common::Success;
   }
@@ -318,7 +318,7 @@ class AccelerationStructureManager {                                      // Acc
       CLRT_FILL_ERRATA(err, "generateContacts: buffers are smaller than rayCount elements"); return Common::Error;
     }
     CLRT_CALL(clrt_trace_rays(_accel, rays.getCLMem(), contacts.getCLMem(), rayCount), err);
-    CLRT_CALL(clrt_ctx_sync(_context.handle()), err);
+    CLRT_CALL(clrt_accel_check(_accel), err);
     return Common::Success;
   }
   // The primary contacts live in a buffer the manager owns; the view exposes getCLMem / getSize / getActualSize / copyToHost.

@@ -54,6 +54,7 @@ SIGNATURES = {
     "clrt_accel_set_fused_shadows": (C.c_int, [C.c_void_p, C.c_int]),
     "clrt_accel_set_stats": (C.c_int, [C.c_void_p, C.c_int]),
     "clrt_accel_read_stats": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64)]),
+    "clrt_accel_check": (C.c_int, [C.c_void_p]),
     "clrt_bvh_export_nodes": (C.c_int, [C.c_void_p, C.c_void_p]),
     "clrt_bvh_export_pairs": (C.c_int, [C.c_void_p, C.c_void_p]),
     "clrt_tlg_sizes": (C.c_int, [C.c_void_p] + [C.POINTER(C.c_uint32)] * 4),
@@ -62,6 +63,8 @@ SIGNATURES = {
     "clrt_generate_shadow_rays": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.POINTER(C.c_uint32)]),
     "clrt_generate_bounce_rays": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint64, C.c_void_p]),
     "clrt_generate_secondary_rays": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint64, C.c_void_p]),
+    "clrt_shade_bounce": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p]),
+    "clrt_trace_primary_stripe": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p]),
     "clrt_shade": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]),
     "clrt_shadow_shade": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]),
     "clrt_frame_stripe_pixels": (C.c_int, [C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),

@@ -283,12 +283,22 @@ class AccelerationStructureManager:
             c = contacts.getCLMem() if isinstance(contacts, Buffer) else contacts
             check(self._lib.clrt_trace_rays(self.handle, C.c_void_p(r), C.c_void_p(c), rayCount))
 
+    def trace_primary_stripe(self, camera, rank, nranks, dptr_contacts):
+        """generateContacts(Camera&) for one image-space stripe, contacts in stripe order (clrt_trace_primary_stripe)."""
+        cam = np.ascontiguousarray(camera, dtype=L.CAMERA)
+        check(self._lib.clrt_trace_primary_stripe(self.handle, _ptr(cam), rank, nranks, C.c_void_p(dptr_contacts)))
+
     def getPrimaryContacts(self):
         """Device pointer of the primary contacts (the reference returns the CLBuffer)."""
         return self._lib.clrt_accel_primary_contacts_dptr(self.handle)
 
+    def check(self):
+        """Waits for the context's stream; raises if a traversal stack overflowed since the last check (clrt_accel_check)."""
+        check(self._lib.clrt_accel_check(self.handle))
+
     def download_primary_contacts(self):
         """getPrimaryContacts()->copyToHost (OpenCLRayTracerDemo.cpp:289)."""
+        self.check()
         out = np.empty(self._primary_pixels, dtype=L.CONTACT)
         self.context.enqueueReadBuffer(self.getPrimaryContacts(), out)
         return out
@@ -476,6 +486,12 @@ def shade(context, scene, camera, dptr_contacts, n, dptr_shadow=None, dptr_rgba8
                                  C.c_void_p(dptr_shadow) if dptr_shadow else None,
                                  C.c_void_p(dptr_rgba8) if dptr_rgba8 else None,
                                  C.c_void_p(dptr_rgba_f32) if dptr_rgba_f32 else None))
+
+
+def shade_bounce(context, scene, camera, dptr_contacts, n, dptr_bounce_contacts, dptr_rgba8):
+    cam = np.ascontiguousarray(camera, dtype=L.CAMERA)
+    check(_lib.load().clrt_shade_bounce(context.handle, scene.handle, _ptr(cam), C.c_void_p(dptr_contacts), n,
+                                        C.c_void_p(dptr_bounce_contacts), C.c_void_p(dptr_rgba8)))
 
 
 def frame_untile(context, dptr_stripes, resX, resY, nranks, dptr_raster):

@@ -123,6 +123,17 @@ extern "C" int clrt_trace_primary(clrt_accel* a, const clrt_camera* h_camera, vo
   return accel_trace_primary(a, *h_camera, out, 0, 0);
 }
 
+// Stripe `rank` of `nranks` of the camera's primary rays (image-space sharding): contacts in STRIPE order — slot =
+// local tile * 256 + y * 32 + x, slots outside the image get pixelIndex = UINT_MAX — for clrt_frame_stripe_pixels() slots.
+extern "C" int clrt_trace_primary_stripe(clrt_accel* a, const clrt_camera* h_camera, uint32_t rank, uint32_t nranks, void* dptr_contacts) {
+  if (!a || !h_camera || !dptr_contacts) CLRT_FAIL("clrt_trace_primary_stripe: NULL argument");
+  if (!nranks || rank >= nranks) CLRT_FAIL("clrt_trace_primary_stripe: rank %u of %u", rank, nranks);
+  if ((uintptr_t)dptr_contacts & 15) CLRT_FAIL("clrt_trace_primary_stripe: the contact buffer must be 16-byte aligned");
+  CLRT_CUDA(cudaSetDevice(a->ctx->device));
+  if ((uint64_t)h_camera->resX * h_camera->resY > 0x7FFFFFFFull) CLRT_FAIL("clrt_trace_primary_stripe: resolution too large");
+  return accel_trace_primary(a, *h_camera, (clrt_contact*)dptr_contacts, rank, nranks);
+}
+
 extern "C" void* clrt_accel_primary_contacts_dptr(clrt_accel* a) { return a ? a->d_contacts : nullptr; }
 
 extern "C" int clrt_trace_rays(clrt_accel* a, const void* dptr_rays, void* dptr_contacts, uint32_t ray_count) {
@@ -312,7 +323,7 @@ extern "C" int clrt_render_frame_host(clrt_accel* a, const clrt_camera* h_camera
     result = stripe;
   }
   CLRT_CUDA(cudaMemcpyAsync(h_rgba8, result, out_bytes, cudaMemcpyDeviceToHost, ctx->stream));
-  CLRT_CUDA(cudaStreamSynchronize(ctx->stream));
+  CLRT_TRY(clrt_accel_check(a));                               // waits for the stream; a traversal-stack overflow fails the frame
   if (out_rays) {
     // counted without re-rendering: primary = all samples; shadow = (L+1) per hit sample.  Without supersampling the hits are the
     // pixels with alpha != 0 of the frame just read back; with it, of the sample raster (a second read-back, only when asked).

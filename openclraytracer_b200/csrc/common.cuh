@@ -27,6 +27,8 @@ struct clrt_ctx {
   void* scratch = nullptr; size_t scratch_bytes = 0;
   void* sort_alt = nullptr; size_t sort_alt_bytes = 0;
   void* pinned = nullptr; size_t pinned_bytes = 0;     // staging for small host<->device transfers
+  // look-back state of the scan (scan.cu): never reset between calls — descriptors carry a generation, tickets run on
+  void* scan_state = nullptr; size_t scan_state_bytes = 0; uint32_t scan_gen = 0, scan_tickets = 0;
 };
 int clrt_ctx_scratch(clrt_ctx* ctx, size_t bytes, void** out);      // grow-only device scratch
 int clrt_ctx_sort_alt(clrt_ctx* ctx, size_t bytes, void** out);     // ping-pong buffer of the radix sort
@@ -78,6 +80,12 @@ struct __align__(16) WideNode {
   uint32_t child[4];
   uint32_t pad[4];
 };
+
+// Top table of the wide tree (trace_tree.cu: wide_top_kernel): WIDE_TOP_LEVELS levels in breadth-first order, stored behind the n
+// per-node records (index n + slot).  A child id with WIDE_TOP_BIT set is a slot of that table.  n < 2^30, so inner ids stay below 2^31.
+#define WIDE_TOP_LEVELS 5
+#define WIDE_TOP_NODES  341            /* (4^5 - 1) / 3 */
+#define WIDE_TOP_BIT    0x80000000u
 
 // Peer framebuffers of the image-space exchange (accel.cu: clrt_render_stripe_p2p): up to 8 raster-ordered RGBA8 buffers, one per
 // GPU of the box (the local one included), that the shading kernel writes its pixels into directly over NVLink.

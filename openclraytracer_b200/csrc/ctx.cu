@@ -49,6 +49,7 @@ extern "C" int clrt_ctx_destroy(clrt_ctx* c) {
   cudaStreamSynchronize(c->stream);
   if (c->scratch) cudaFree(c->scratch);
   if (c->sort_alt) cudaFree(c->sort_alt);
+  if (c->scan_state) cudaFree(c->scan_state);
   if (c->pinned) cudaFreeHost(c->pinned);
   if (c->owns_stream) cudaStreamDestroy(c->stream);
   delete c;

@@ -3,20 +3,27 @@
 // R/src/CLRayTracerEngine/PrefixSumKernels.cl:29-106 — a multi-level Blelloch scan + uniform add, one
 // synchronous launch pair per level).  Semantics kept: inclusive, out[i] = in[0]+...+in[i]; in may alias out.
 //
-// HBM roofline: 8 B per element (4 read + 4 written), one pass.  Layout: each CTA owns a tile of
-// THREADS*IPT consecutive elements, loaded as 16-byte vectors (blocked arrangement: thread t owns elements
-// [t*IPT, t*IPT+IPT) so the serial part needs no transposition), warp shuffles for the intra-CTA scan, and a
-// 64-bit {flag,value} descriptor per tile for the look-back (one relaxed 8-byte store publishes both).
-// Tile ids come from an atomic ticket so a CTA only ever waits on CTAs that already started.
+// HBM roofline: 8 B per element (4 read + 4 written), one pass.  Each CTA owns a tile of 16384 consecutive elements as
+// SCAN_VEC sub-tiles of THREADS x 4: thread t holds the uint4 at vector index k*THREADS + t of every sub-tile k, so each warp-wide
+// 16-byte load / store covers 512 contiguous bytes (round 1 loaded 4 x uint4 per thread at a 64-byte lane stride: every
+// instruction touched 32 half-used sectors, 0.33-0.45 of the HBM peak).  The CTA scan is two shuffle levels: a warp scan of the uint4
+// sums per sub-tile, then every warp scans the SCAN_VEC x WARPS warp totals from shared memory.  One 64-bit {generation|flag,
+// value} descriptor per tile drives the look-back (a single relaxed 8-byte store publishes both).  Tile ids come from an atomic
+// ticket so a CTA only ever waits on CTAs that already started.  No reset launch: descriptors carry the call's GENERATION number
+// and the ticket counter runs on (the host subtracts the tickets handed out so far), so a call is exactly one kernel.
 #include "common.cuh"
 
 namespace {
 
-constexpr int SCAN_THREADS = 256;
-constexpr int SCAN_IPT = 16;                 // 4 x uint4 per thread
-constexpr int SCAN_TILE = SCAN_THREADS * SCAN_IPT;
+constexpr int SCAN_THREADS = 1024;
+constexpr int SCAN_WARPS = SCAN_THREADS / 32;
+constexpr int SCAN_VEC = 4;                                  // uint4 per thread
+constexpr int SCAN_SUB = SCAN_THREADS * 4;                   // elements per sub-tile
+constexpr int SCAN_TILE = SCAN_SUB * SCAN_VEC;               // 16384
+constexpr int SCAN_LOOK = 4;                                 // descriptors per lane and look-back round: 128 predecessors per L2 round trip
+static_assert(SCAN_VEC * SCAN_WARPS == 128, "the warp-total scan below holds four entries per lane");
 
-constexpr unsigned long long FLAG_AGG = 1ull << 32, FLAG_PREFIX = 2ull << 32;
+constexpr unsigned FLAG_AGG = 1u, FLAG_PREFIX = 2u;          // descriptor: hi = generation << 2 | flag, lo = value
 
 __device__ __forceinline__ unsigned long long ld_relaxed_u64(const unsigned long long* p) {
   unsigned long long v; asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory"); return v;
@@ -25,94 +32,136 @@ __device__ __forceinline__ void st_relaxed_u64(unsigned long long* p, unsigned l
   asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" :: "l"(p), "l"(v) : "memory");
 }
 
+template <bool ALIGNED>
 __global__ void __launch_bounds__(SCAN_THREADS)
 scan_lookback_kernel(const uint32_t* in, uint32_t* out, uint32_t n,   /* in may alias out */
-                     unsigned long long* __restrict__ status, uint32_t* __restrict__ ticket) {
+                     unsigned long long* __restrict__ status, uint32_t* __restrict__ ticket, uint32_t ticket_base, uint32_t gen) {
   __shared__ uint32_t s_tile;
-  __shared__ uint32_t s_warp[SCAN_THREADS / 32];
+  __shared__ __align__(16) uint32_t s_part[SCAN_VEC * SCAN_WARPS];       // [sub-tile][warp] totals
   __shared__ uint32_t s_prefix;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  if (tid == 0) s_tile = atomicAdd(ticket, 1u);
+  if (tid == 0) s_tile = atomicAdd(ticket, 1u) - ticket_base;
   __syncthreads();
   const uint32_t tile = s_tile;
-  const size_t base = (size_t)tile * SCAN_TILE + (size_t)tid * SCAN_IPT;
+  const size_t tile_base = (size_t)tile * SCAN_TILE;
+  const bool full = tile_base + SCAN_TILE <= n;
 
-  uint32_t v[SCAN_IPT];
-  if (base + SCAN_IPT <= n && (((uintptr_t)in & 15) == 0)) {
-    const uint4* p = reinterpret_cast<const uint4*>(in + base);
+  uint4 v[SCAN_VEC];
 #pragma unroll
-    for (int k = 0; k < SCAN_IPT / 4; k++) { uint4 q = p[k]; v[4*k] = q.x; v[4*k+1] = q.y; v[4*k+2] = q.z; v[4*k+3] = q.w; }
-  } else {
-#pragma unroll
-    for (int k = 0; k < SCAN_IPT; k++) v[k] = (base + k < n) ? in[base + k] : 0u;
+  for (int k = 0; k < SCAN_VEC; k++) {
+    const size_t e = tile_base + (size_t)k * SCAN_SUB + 4 * (size_t)tid;
+    if (ALIGNED && full) v[k] = *reinterpret_cast<const uint4*>(in + e);
+    else {
+      v[k].x = e     < n ? in[e]     : 0u; v[k].y = e + 1 < n ? in[e + 1] : 0u;
+      v[k].z = e + 2 < n ? in[e + 2] : 0u; v[k].w = e + 3 < n ? in[e + 3] : 0u;
+    }
   }
-  // thread-serial inclusive scan
+  // inclusive scan inside each uint4, then a warp scan of the uint4 totals per sub-tile
+  uint32_t wexcl[SCAN_VEC];
 #pragma unroll
-  for (int k = 1; k < SCAN_IPT; k++) v[k] += v[k - 1];
-  // warp scan of thread totals
-  uint32_t tot = v[SCAN_IPT - 1], incl = tot;
+  for (int k = 0; k < SCAN_VEC; k++) {
+    v[k].y += v[k].x; v[k].z += v[k].y; v[k].w += v[k].z;
+    uint32_t incl = v[k].w;
 #pragma unroll
-  for (int d = 1; d < 32; d <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += t; }
-  if (lane == 31) s_warp[warp] = incl;
+    for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += t; }
+    wexcl[k] = incl - v[k].w;
+    if (lane == 31) s_part[k * SCAN_WARPS + warp] = incl;
+  }
   __syncthreads();
-  uint32_t warp_excl = 0, tile_total = 0;
+  // every warp scans the 128 (sub-tile, warp) totals: lane holds entries 4*lane .. 4*lane+3 (entry = k * WARPS + warp, tile order)
+  uint32_t tile_total;
+  {
+    const uint4 pr = *reinterpret_cast<const uint4*>(s_part + 4 * lane);
+    const uint32_t quad = pr.x + pr.y + pr.z + pr.w;
+    uint32_t incl = quad;
 #pragma unroll
-  for (int w = 0; w < SCAN_THREADS / 32; w++) { uint32_t t = s_warp[w]; if (w < warp) warp_excl += t; tile_total += t; }
-  const uint32_t thread_excl = warp_excl + incl - tot;
-
-  // decoupled look-back by warp 0: lanes inspect 32 predecessors at a time
+    for (int d = 1; d < 32; d <<= 1) { const uint32_t t = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += t; }
+    const uint32_t e0 = incl - quad, e1 = e0 + pr.x, e2 = e1 + pr.y, e3 = e2 + pr.z;      // exclusive prefixes of the lane's four entries
+    tile_total = __shfl_sync(0xffffffffu, incl, 31);
+    const uint32_t mine = (warp & 3) == 0 ? e0 : (warp & 3) == 1 ? e1 : (warp & 3) == 2 ? e2 : e3;   // entry k*32 + warp sits in lane (k*32 + warp)/4 at sub-index warp & 3
+#pragma unroll
+    for (int k = 0; k < SCAN_VEC; k++) wexcl[k] += __shfl_sync(0xffffffffu, mine, (k * SCAN_WARPS + warp) >> 2);
+  }
+  // Decoupled look-back by warp 0.  A round inspects 32 x SCAN_LOOK predecessors: the chain resolves window / round-trip tiles per
+  // unit time, and with 32 per round it — not HBM — bounded the kernel (round 1 and the first version of this one: 45-50 tiles/us).
   if (warp == 0) {
-    if (lane == 0) st_relaxed_u64(status + tile, (tile == 0 ? FLAG_PREFIX : FLAG_AGG) | tile_total);
+    const unsigned long long tag = (unsigned long long)(gen << 2) << 32;
+    if (lane == 0) st_relaxed_u64(status + tile, tag | ((unsigned long long)(tile == 0 ? FLAG_PREFIX : FLAG_AGG) << 32) | tile_total);
     uint32_t excl = 0;
     if (tile > 0) {
-      int look = (int)tile - 1 - lane;
+      long long look = (long long)tile - 1 - (long long)lane * SCAN_LOOK;       // newest descriptor of this lane; lanes and j run newest -> oldest
       while (true) {
-        unsigned long long s = 0;
-        bool have;
+        uint32_t val[SCAN_LOOK]; unsigned flag[SCAN_LOOK];
+        bool all;
         do {
-          s = look >= 0 ? ld_relaxed_u64(status + look) : FLAG_PREFIX;   // before tile 0: prefix 0
-          have = (s >> 32) != 0;
-        } while (!__all_sync(0xffffffffu, have));
-        const unsigned pmask = __ballot_sync(0xffffffffu, (s >> 32) == 2);
-        // sum the values of lanes up to and including the first PREFIX lane (lanes are ordered newest -> oldest)
-        const int first = pmask ? __ffs(pmask) - 1 : 32;
-        uint32_t val = (lane <= first) ? (uint32_t)s : 0u;
+          all = true;
 #pragma unroll
-        for (int d = 16; d > 0; d >>= 1) val += __shfl_xor_sync(0xffffffffu, val, d);
-        excl += val;
+          for (int j = 0; j < SCAN_LOOK; j++) {
+            if (look - j >= 0) {
+              const unsigned long long sd = ld_relaxed_u64(status + (look - j));
+              const uint32_t hi = (uint32_t)(sd >> 32);
+              flag[j] = (hi >> 2) == gen ? (hi & 3u) : 0u; val[j] = (uint32_t)sd;
+            } else { flag[j] = FLAG_PREFIX; val[j] = 0u; }                        // before tile 0: prefix 0
+            all = all && flag[j] != 0u;
+          }
+        } while (!__all_sync(0xffffffffu, all));
+        // the lane's sum up to and including its first PREFIX descriptor
+        uint32_t sum = 0; bool closed = false;
+#pragma unroll
+        for (int j = 0; j < SCAN_LOOK; j++) { if (!closed) sum += val[j]; closed = closed || flag[j] == FLAG_PREFIX; }
+        const unsigned pmask = __ballot_sync(0xffffffffu, closed);
+        const int first = pmask ? __ffs(pmask) - 1 : 32;
+        uint32_t v2 = (lane <= first) ? sum : 0u;
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) v2 += __shfl_xor_sync(0xffffffffu, v2, d);
+        excl += v2;
         if (pmask) break;
-        look -= 32;
+        look -= 32 * SCAN_LOOK;
       }
-      if (lane == 0) st_relaxed_u64(status + tile, FLAG_PREFIX | (unsigned long long)(uint32_t)(excl + tile_total));
+      if (lane == 0) st_relaxed_u64(status + tile, tag | ((unsigned long long)FLAG_PREFIX << 32) | (unsigned long long)(uint32_t)(excl + tile_total));
     }
     if (lane == 0) s_prefix = excl;
   }
   __syncthreads();
-  const uint32_t add = s_prefix + thread_excl;
-  if (base + SCAN_IPT <= n && (((uintptr_t)out & 15) == 0)) {
-    uint4* p = reinterpret_cast<uint4*>(out + base);
+  const uint32_t base = s_prefix;
 #pragma unroll
-    for (int k = 0; k < SCAN_IPT / 4; k++) p[k] = make_uint4(v[4*k] + add, v[4*k+1] + add, v[4*k+2] + add, v[4*k+3] + add);
-  } else {
-#pragma unroll
-    for (int k = 0; k < SCAN_IPT; k++) if (base + k < n) out[base + k] = v[k] + add;
+  for (int k = 0; k < SCAN_VEC; k++) {
+    const size_t e = tile_base + (size_t)k * SCAN_SUB + 4 * (size_t)tid;
+    const uint32_t add = base + wexcl[k];
+    const uint4 r = make_uint4(v[k].x + add, v[k].y + add, v[k].z + add, v[k].w + add);
+    if (ALIGNED && full) *reinterpret_cast<uint4*>(out + e) = r;
+    else {
+      if (e < n) out[e] = r.x;
+      if (e + 1 < n) out[e + 1] = r.y;
+      if (e + 2 < n) out[e + 2] = r.z;
+      if (e + 3 < n) out[e + 3] = r.w;
+    }
   }
 }
 
 } // namespace
 
+// Look-back state of the context: [ticket u32 | pad | status u64 x tiles], zeroed when (re)allocated and never reset afterwards.
+// A descriptor is valid only when it carries the generation of the running call; the ticket counter runs on across calls.
 int scan_inclusive(clrt_ctx* ctx, const uint32_t* in, uint32_t* out, size_t n) {
   if (n == 0) return 0;
   if (n > 0xFFFFFFFFull) CLRT_FAIL("scan: n = %zu exceeds 2^32-1", n);
   const size_t tiles = (n + SCAN_TILE - 1) / SCAN_TILE;
-  void* scratch = nullptr;
   const size_t bytes = tiles * 8 + 16;
-  CLRT_TRY(clrt_ctx_scratch(ctx, bytes, &scratch));
-  CLRT_CUDA(cudaMemsetAsync(scratch, 0, bytes, ctx->stream));
-  uint32_t* ticket = (uint32_t*)scratch;
-  unsigned long long* status = (unsigned long long*)((uint8_t*)scratch + 16);
-  scan_lookback_kernel<<<(unsigned)tiles, SCAN_THREADS, 0, ctx->stream>>>(in, out, (uint32_t)n, status, ticket);
+  if (bytes > ctx->scan_state_bytes || ctx->scan_gen >= (1u << 30) - 1u) {
+    CLRT_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (bytes > ctx->scan_state_bytes) CLRT_TRY(clrt_grow(&ctx->scan_state, &ctx->scan_state_bytes, bytes + bytes / 2));
+    CLRT_CUDA(cudaMemsetAsync(ctx->scan_state, 0, ctx->scan_state_bytes, ctx->stream));
+    ctx->scan_gen = 0; ctx->scan_tickets = 0;
+  }
+  const uint32_t gen = ++ctx->scan_gen;
+  uint32_t* ticket = (uint32_t*)ctx->scan_state;
+  unsigned long long* status = (unsigned long long*)((uint8_t*)ctx->scan_state + 16);
+  const bool aligned = (((uintptr_t)in | (uintptr_t)out) & 15) == 0;
+  if (aligned) scan_lookback_kernel<true><<<(unsigned)tiles, SCAN_THREADS, 0, ctx->stream>>>(in, out, (uint32_t)n, status, ticket, ctx->scan_tickets, gen);
+  else scan_lookback_kernel<false><<<(unsigned)tiles, SCAN_THREADS, 0, ctx->stream>>>(in, out, (uint32_t)n, status, ticket, ctx->scan_tickets, gen);
   CLRT_CHECK_LAUNCH();
+  ctx->scan_tickets += (uint32_t)tiles;                        // every CTA takes exactly one ticket (mod 2^32)
   return 0;
 }
 

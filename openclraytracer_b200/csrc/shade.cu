@@ -127,6 +127,23 @@ shade_kernel(clrt_camera cam, const clrt_contact* __restrict__ contacts, uint32_
   if (rgba_f32) __stcs(rgba_f32 + i, color);
 }
 
+// Bounce frame (BASELINE.json configs[3]: one diffuse bounce per primary hit): Blinn-Phong of the primary contact, halved when the
+// bounce ray of the same slot hit something (one-sample ambient occlusion).  Ours; the reference has no secondary rays (its TODO 2.2).
+__global__ void __launch_bounds__(256)
+shade_bounce_kernel(clrt_camera cam, const clrt_contact* __restrict__ contacts, uint32_t n, const clrt_light* __restrict__ lights,
+                    uint32_t n_lights, const clrt_material* __restrict__ materials, uint32_t n_materials,
+                    const clrt_contact* __restrict__ bounce, uint32_t* __restrict__ rgba8) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint4 head = __ldcs(reinterpret_cast<const uint4*>(contacts + i));
+  const float4 nd = __ldcs(reinterpret_cast<const float4*>(contacts + i) + 1);
+  uint32_t packed;
+  shade_contact(cam, head, nd, lights, n_lights, materials, n_materials, [](uint32_t, float) { return false; }, packed);
+  if (packed && __ldcs(&bounce[i].normalAndintersectionDistance.w) > 0.0f)
+    packed = ((packed >> 1) & 0x007F7F7Fu) | (packed & 0xFF000000u);
+  __stcs(rgba8 + i, packed);
+}
+
 // stripes (rank-major, each padded to ceil(tiles/nranks) tiles, tile-major, 256 px per tile) -> raster
 __global__ void __launch_bounds__(256)
 untile_kernel(const uint32_t* __restrict__ stripes, uint32_t resX, uint32_t resY, uint32_t nranks, uint32_t* __restrict__ raster) {
@@ -237,6 +254,17 @@ extern "C" int clrt_shade(clrt_ctx* ctx, const clrt_scene* scene, const clrt_cam
   CLRT_CUDA(cudaSetDevice(ctx->device));
   return shade_launch(ctx, scene, *h_camera, (const clrt_contact*)dptr_contacts, n, (const clrt_contact*)dptr_shadow_contacts,
                       (uint32_t*)dptr_rgba8, (float4*)dptr_rgba_f32, nullptr);
+}
+
+extern "C" int clrt_shade_bounce(clrt_ctx* ctx, const clrt_scene* scene, const clrt_camera* h_camera, const void* dptr_contacts, uint32_t n,
+                                 const void* dptr_bounce_contacts, void* dptr_rgba8) {
+  if (!ctx || !scene || !h_camera || (n && (!dptr_contacts || !dptr_bounce_contacts || !dptr_rgba8))) CLRT_FAIL("clrt_shade_bounce: NULL argument");
+  CLRT_CUDA(cudaSetDevice(ctx->device));
+  if (!n) return 0;
+  shade_bounce_kernel<<<(n + 255) / 256, 256, 0, ctx->stream>>>(*h_camera, (const clrt_contact*)dptr_contacts, n, scene->d_lights, scene->n_lights,
+      scene->d_materials, scene->n_materials, (const clrt_contact*)dptr_bounce_contacts, (uint32_t*)dptr_rgba8);
+  CLRT_CHECK_LAUNCH();
+  return 0;
 }
 
 extern "C" int clrt_frame_untile_on(clrt_ctx* ctx, void* stream, const void* dptr_stripes, uint32_t resX, uint32_t resY, uint32_t nranks,

@@ -23,8 +23,11 @@
 
 namespace {
 
-constexpr int TRACE_THREADS = 128;
-constexpr int FAST_STACK = 72;     // (entry distance, node) pairs; a visit pushes at most three
+#ifndef CLRT_TRACE_THREADS
+#define CLRT_TRACE_THREADS 128
+#endif
+constexpr int TRACE_THREADS = CLRT_TRACE_THREADS;
+constexpr int FAST_STACK = 96;     // (entry distance, node) pairs; a visit pushes at most three: 3 x wide depth, and a trace tree of 2^30 leaves is at most 60 binary = 30 wide levels deep
 constexpr int REF_STACK = 96;
 constexpr uint32_t SENTINEL = 0xFFFFFFFFu;
 
@@ -51,7 +54,7 @@ struct Stats { uint32_t rays, inner, tris, lboxes; };
 // ---- REFERENCE_ORDER policy: the reference's visiting order, one ray per thread ---------------------------------------
 template <bool STATS>
 __device__ __forceinline__ Hit traverse_ref(const TraceNode* __restrict__ tnodes, const clrt_triangle* __restrict__ tris,
-                                            uint32_t n, Vec3 o, Vec3 d, Stats& st) {
+                                            uint32_t n, Vec3 o, Vec3 d, Stats& st, uint32_t* __restrict__ overflow) {
   Hit h; h.t = RT_FLT_MAX; h.tri = SENTINEL; h.cull = RT_FLT_MAX;
   if (STATS) st.rays++;
   if (n == 0) return h;
@@ -71,7 +74,7 @@ __device__ __forceinline__ Hit traverse_ref(const TraceNode* __restrict__ tnodes
       const float tB = aabb_intersect(q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, o, inv);
       const bool aValid = tA > 0.0f || point_inside(q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, o);
       const bool bValid = tB > 0.0f || point_inside(q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, o);
-      if (aValid && bValid) { cur = q3.x; if (sp < REF_STACK) stack[sp++] = q3.y; }
+      if (aValid && bValid) { cur = q3.x; if (sp < REF_STACK) stack[sp++] = q3.y; else atomicAdd(overflow, 1u); }   // counted: clrt_accel_check fails the call
       else if (aValid) cur = q3.x;
       else if (bValid) cur = q3.y;
       else cur = stack[--sp];
@@ -87,9 +90,6 @@ __device__ __forceinline__ Hit traverse_ref(const TraceNode* __restrict__ tnodes
 // ---- FAST policy ---------------------------------------------------------------------------------------------------------
 // Per-lane traversal state.  ANYHIT: an occlusion query - ends at the first triangle with 0 < t < tmax; "some hit below
 // tmax exists" equals "the closest hit is below tmax", which is what the shading's shadow test asks.
-#ifndef CLRT_STACK_TOP_REG
-#define CLRT_STACK_TOP_REG 0
-#endif
 struct Lane {
   Vec3 o, d, inv;
   Hit h;
@@ -97,34 +97,76 @@ struct Lane {
   int sp;
   uint32_t visits;                // statistics mode only: inner-node visits of the current ray (-> Contact.pad[1])
   uint32_t q0, q1, q2, q3, qn;    // postponed leaves (positions in the triangle array) and their count
-#if CLRT_STACK_TOP_REG
-  uint2 top;                      // entry sp-1 of the stack (experiment, see stack_push)
+};
+
+// Compile-time shape of the traversal kernels (profiles/variants.sh builds and measures the alternatives):
+//   CLRT_TRACE_THREADS  threads per CTA
+//   CLRT_SSTACK         traversal-stack entries per thread kept in SHARED memory (entry-major: entry e of thread t at
+//                       [e * threads + t], 8-byte words -> conflict free); deeper entries spill to a local-memory array that a
+//                       balanced tree never reaches (Soup-1M: deepest stack 19)
+//   CLRT_TOP_STAGED     records of the top table (common.cuh: the first levels of the wide tree in breadth-first order) copied
+//                       into shared memory by ONE bulk-async (TMA) copy per CTA at kernel start: 21 = 3 levels (2.6 KB),
+//                       85 = 4 levels (10.6 KB), 341 = 5 levels (42.6 KB); 0 = the table is read from global memory
+#ifndef CLRT_TRACE_THREADS
+#define CLRT_TRACE_THREADS 128
 #endif
-};   // the traversal stack lives in its own local array so that these scalars stay in registers
+#ifndef CLRT_SSTACK
+#define CLRT_SSTACK 16
+#endif
+#ifndef CLRT_TOP_STAGED
+#define CLRT_TOP_STAGED 85
+#endif
+#ifndef CLRT_UNIFORM_STACK
+#define CLRT_UNIFORM_STACK 0
+#endif
+#ifndef CLRT_MIN_CTAS
+#define CLRT_MIN_CTAS 1          // __launch_bounds__ second argument of the FAST kernels (register cap = 65536 / (threads x CTAs))
+#endif
+#ifndef CLRT_PREFETCH_TOP
+#define CLRT_PREFETCH_TOP 0      // prefetch.global.L1 of the node on top of the stack (the one visited after the nearest child's subtree)
+#endif
+constexpr int SSTACK = CLRT_SSTACK;
+constexpr int TOP_STAGED = CLRT_TOP_STAGED;
+static_assert(TRACE_THREADS == CLRT_TRACE_THREADS, "TRACE_THREADS");
+static_assert(TOP_STAGED == 0 || TOP_STAGED == 5 || TOP_STAGED == 21 || TOP_STAGED == 85 || TOP_STAGED == 341, "CLRT_TOP_STAGED: whole levels");
+static_assert(SSTACK >= 4 && SSTACK <= FAST_STACK, "CLRT_SSTACK");
+constexpr size_t FAST_SMEM_BYTES = (size_t)TOP_STAGED * sizeof(WideNode) + (size_t)SSTACK * TRACE_THREADS * sizeof(uint2) + 16;
+
+struct StackRef {
+  uint2* s;        // shared-memory column of this thread (stride TRACE_THREADS)
+  uint2* l;        // local-memory spill [FAST_STACK - SSTACK]
+  uint32_t* overflow;
+};
 
 template <bool STATS, bool ANYHIT>
 __device__ __forceinline__ void lane_begin(Lane& L, const clrt_triangle* __restrict__ tris, uint32_t n, Vec3 o, Vec3 d, float tmax, Stats& st) {
-  L.o = o; L.d = d; L.inv = v3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+  L.o = o; L.d = d;
+  // 1/d as the reference computes it, except that an exactly zero component gives +-1e30 instead of +-inf: (bound - origin) * inv
+  // is then 0 when the origin lies ON the bound (the reference's 0 * inf = NaN is dropped by its compare-select min/max,
+  // AABB.h:126-142, i.e. the slab is accepted — same outcome) and +-huge otherwise (rejected like +-inf).  No NaN reaches the
+  // fminf/fmaxf of child_entry, which would turn it into a rejection of both boxes along a seam in the ray's plane.
+  const float big = 1.0e30f;
+  L.inv = v3(d.x == 0.0f ? copysignf(big, d.x) : 1.0f / d.x, d.y == 0.0f ? copysignf(big, d.y) : 1.0f / d.y, d.z == 0.0f ? copysignf(big, d.z) : 1.0f / d.z);
   L.h.t = tmax; L.h.tri = SENTINEL; L.h.cull = ANYHIT ? tmax * CULL_SLACK : RT_FLT_MAX;
   L.sp = 0; L.qn = 0;
-  L.cur = n >= 2 ? n : SENTINEL;
+  L.cur = n >= 2 ? WIDE_TOP_BIT : SENTINEL;                  // slot 0 of the top table = the root
   if (STATS) { st.rays++; L.visits = 0; }
   if (n == 1) { test_triangle<false>(tris, 0, o, d, L.h); if (STATS) st.tris++; }     // the reference reads past its node buffer here
 }
 
 // One visit of a 4-wide node (WideNode, common.cuh: the 2-level collapse of the binary trace structure written by
 // widen_kernel, trace_tree.cu): ONE dependent 128-byte fetch decides four boxes, which halves the length of the dependent
-// load chain a ray walks — the chain, not bandwidth, is what bounds this kernel.  Leaf children are intersected at once;
-// valid inner children are sorted by entry distance, the nearest is entered, the others go to the stack WITH their entry
+// load chain a ray walks.  Accepted leaf children go to the lane's leaf queue (tested later, warp-wide: flush_one); valid
+// inner children are sorted by entry distance, the nearest is entered, the others go to the stack WITH their entry
 // distance so that a pop can cull them against the hit found meanwhile.  Box validity is the reference's
 // (child_entry below); children beyond best_t * (1 + 1e-5) are culled.
 #define T_INVALID __int_as_float(0x7f800000)      /* +inf marks an empty / rejected slot */
 
 // Entry distance of one child box, or T_INVALID.  Same six products (bound - origin) * (1/d) as the reference's AABBIntersect
-// (AABB.h:126-142), so tn / tf are the reference's tmin / tmax bit for bit; the per-axis near/far pick is a min/max instead of
-// the sign select, the three pairwise overlap flags are `tn <= tf`, and the reference's validity `t > 0 || origin inside`
-// (AABB.h:178-184) is `tf >= 0` (origin inside <=> every axis has near <= 0 <= far).  22 instructions instead of ~50.
-// Empty slots hold NaN boxes (widen_kernel): every comparison fails.
+// (AABB.h:126-142), so for finite 1/d tn / tf are the reference's tmin / tmax bit for bit; the per-axis near/far pick is a
+// min/max instead of the sign select, the three pairwise overlap flags are `tn <= tf`, and the reference's validity
+// `t > 0 || origin inside` (AABB.h:178-184) is `tf >= 0` (origin inside <=> every axis has near <= 0 <= far).  Axis-parallel
+// rays: see lane_begin.  Empty slots hold NaN boxes (widen_kernel): every comparison fails.
 __device__ __forceinline__ float child_entry(float x0, float y0, float z0, float x1, float y1, float z1, Vec3 o, Vec3 inv, float cull) {
   const float ax = (x0 - o.x) * inv.x, bx = (x1 - o.x) * inv.x;
   const float ay = (y0 - o.y) * inv.y, by = (y1 - o.y) * inv.y;
@@ -137,50 +179,41 @@ __device__ __forceinline__ void cswap(float& ta, uint32_t& ca, float& tb, uint32
   if (tb < ta) { const float t = ta; ta = tb; tb = t; const uint32_t c = ca; ca = cb; cb = c; }
 }
 
-// The stack of (entry distance, node).  CLRT_STACK_TOP_REG=1 (EXPERIMENT, off: not yet measured — the round's GPU time ended with
-// the finding that motivates it) keeps entry sp-1 in registers and loads its successor at pop time, so that the local-memory load
-// overlaps the visit of the popped node instead of heading the next pop: profiles/r01_source_hotspots.md attributes 19.5 % of the
-// primary kernel's stall samples on Soup-1M to the pop's dependent load.  Build a variant with
-//   make -C openclraytracer_b200/csrc EXTRA=-DCLRT_STACK_TOP_REG=1 BUILD=/tmp/b OUT=/tmp/libclrt_top.so   and run with CLRT_LIB_PATH.
-__device__ __forceinline__ void stack_push(Lane& L, uint2* __restrict__ stack, float t, uint32_t c) {
-#if CLRT_STACK_TOP_REG
-  if (L.sp >= FAST_STACK) return;
-  if (L.sp > 0) stack[L.sp - 1] = L.top;
-  L.top = make_uint2(__float_as_uint(t), c); L.sp++;
-#else
-  if (L.sp < FAST_STACK) stack[L.sp++] = make_uint2(__float_as_uint(t), c);
-#endif
+// The stack of (entry distance, node): the first SSTACK entries in shared memory, the rest in local memory.  A push beyond
+// FAST_STACK cannot be honoured; it is COUNTED (clrt_accel_check fails the call) instead of silently dropping a subtree.
+__device__ __forceinline__ void stack_push(Lane& L, const StackRef& S, float t, uint32_t c) {
+  const uint2 e = make_uint2(__float_as_uint(t), c);
+  if (L.sp < SSTACK) S.s[L.sp * TRACE_THREADS] = e;
+  else if (L.sp < FAST_STACK) S.l[L.sp - SSTACK] = e;
+  else { atomicAdd(S.overflow, 1u); return; }
+  L.sp++;
 }
-__device__ __forceinline__ uint2 stack_pop(Lane& L, const uint2* __restrict__ stack) {      // L.sp > 0
-#if CLRT_STACK_TOP_REG
-  const uint2 e = L.top;
-  if (--L.sp > 0) L.top = stack[L.sp - 1];
-  return e;
-#else
-  return stack[--L.sp];
-#endif
+__device__ __forceinline__ uint2 stack_pop(Lane& L, const StackRef& S) {      // L.sp > 0
+  --L.sp;
+  return L.sp < SSTACK ? S.s[L.sp * TRACE_THREADS] : S.l[L.sp - SSTACK];
 }
 
 template <bool STATS, bool ANYHIT>
-__device__ __forceinline__ void lane_step(Lane& L, const WideNode* __restrict__ wnodes, const clrt_triangle* __restrict__ tris,
-                                          uint32_t n, Stats& st, uint2* __restrict__ stack) {
+__device__ __forceinline__ void lane_visit(Lane& L, const WideNode* __restrict__ wnodes, const WideNode* s_top, const clrt_triangle* __restrict__ tris,
+                                           uint32_t n, Stats& st, const StackRef& S) {
   if (STATS) { st.inner++; L.visits++; }
   const Vec3 o = L.o, d = L.d, inv = L.inv;
-  const float4* p = reinterpret_cast<const float4*>(wnodes + (L.cur - n));
-  const float4 lx = __ldg(p), ly = __ldg(p + 1), lz = __ldg(p + 2), hx = __ldg(p + 3), hy = __ldg(p + 4), hz = __ldg(p + 5);
-  const uint4 ch = __ldg(reinterpret_cast<const uint4*>(p + 6));
+  // top-table slots below TOP_STAGED are read from the CTA's shared-memory copy, everything else from global memory
+  const uint32_t slot = L.cur & ~WIDE_TOP_BIT;
+  const WideNode* node = (L.cur & WIDE_TOP_BIT) ? ((TOP_STAGED && slot < (uint32_t)TOP_STAGED) ? s_top + slot : wnodes + n + slot)
+                                                : wnodes + (L.cur - n);
+  const float4* p = reinterpret_cast<const float4*>(node);
+  const float4 lx = p[0], ly = p[1], lz = p[2], hx = p[3], hy = p[4], hz = p[5];
+  const uint4 ch = *reinterpret_cast<const uint4*>(p + 6);
   uint32_t c0 = ch.x, c1 = ch.y, c2 = ch.z, c3 = ch.w;
   float t0 = child_entry(lx.x, ly.x, lz.x, hx.x, hy.x, hz.x, o, inv, L.h.cull);
   float t1 = child_entry(lx.y, ly.y, lz.y, hx.y, hy.y, hz.y, o, inv, L.h.cull);
   float t2 = child_entry(lx.z, ly.z, lz.z, hx.z, hy.z, hz.z, o, inv, L.h.cull);
   float t3 = child_entry(lx.w, ly.w, lz.w, hx.w, hy.w, hz.w, o, inv, L.h.cull);
-  // Leaves.  Closest-hit rays test them on the spot, in ONE looped copy of the triangle test (a hit shrinks the cull distance
-  // before the inner children are ordered).  Occlusion queries POSTPONE them: the ids go to a four-entry queue in registers and
-  // the triangle tests of the whole warp run together at the end of the window (flush_leaves).  Tested on the spot, the
-  // Moeller-Trumbore code ran with 2.7 of 32 lanes (ncu source view: 17 % of the issue slots), because only ~9 % of the
-  // lane-steps find a leaf; an occlusion query has a fixed cull distance, so waiting costs nothing but a few extra visits
-  // (shadow pass -10 %); for closest-hit rays the late cull distance ate the gain (measured).  A fifth leaf in a window is
-  // tested at once.
+  // Leaves are POSTPONED: their ids go to a four-entry queue in registers and the triangle tests run warp-wide in flush_one once
+  // enough lanes hold one.  Tested on the spot, the Moeller-Trumbore code ran with 2.7 of 32 lanes (round-1 ncu source view:
+  // only ~9 % of the lane-steps find a leaf, but with 16+ active lanes almost every warp-step found one somewhere).  A fifth
+  // leaf is tested at once.
   {
     uint32_t leaves = (c0 < n && t0 != T_INVALID ? 1u : 0u) | (c1 < n && t1 != T_INVALID ? 2u : 0u) |
                       (c2 < n && t2 != T_INVALID ? 4u : 0u) | (c3 < n && t3 != T_INVALID ? 8u : 0u);
@@ -191,101 +224,146 @@ __device__ __forceinline__ void lane_step(Lane& L, const WideNode* __restrict__ 
     while (leaves) {
       const uint32_t id = (leaves & 1u) ? c0 : (leaves & 2u) ? c1 : (leaves & 4u) ? c2 : c3;
       leaves &= leaves - 1u;
-      if (ANYHIT && L.qn < 4u) { L.q3 = L.q2; L.q2 = L.q1; L.q1 = L.q0; L.q0 = id; L.qn++; }
+      if (L.qn < 4u) { L.q3 = L.q2; L.q2 = L.q1; L.q1 = L.q0; L.q0 = id; L.qn++; }
       else { test_triangle<true>(tris, id, o, d, L.h); if (STATS) st.tris++; }
     }
   }
-  if (ANYHIT && L.h.tri != SENTINEL) { L.cur = SENTINEL; return; }
+  if (ANYHIT && L.h.tri != SENTINEL) { L.cur = SENTINEL; L.sp = 0; L.qn = 0; return; }
   if (t0 > L.h.cull) t0 = T_INVALID;
   if (t1 > L.h.cull) t1 = T_INVALID;
   if (t2 > L.h.cull) t2 = T_INVALID;
   if (t3 > L.h.cull) t3 = T_INVALID;
   cswap(t0, c0, t1, c1); cswap(t2, c2, t3, c3); cswap(t0, c0, t2, c2); cswap(t1, c1, t3, c3); cswap(t1, c1, t2, c2);   // ascending entry distance
-  if (t3 != T_INVALID) stack_push(L, stack, t3, c3);
-  if (t2 != T_INVALID) stack_push(L, stack, t2, c2);
-  if (t1 != T_INVALID) stack_push(L, stack, t1, c1);
+#if CLRT_UNIFORM_STACK
+  // Branch-free: every valid child is pushed, farthest first (an invalid one is stored too, but the stack pointer does not move),
+  // and the next node is ALWAYS popped: the nearest child when there is one (its entry distance was just accepted, so the cull test
+  // below passes), else older entries until one survives the cull distance.  One shared-memory round trip on the critical path
+  // against four divergent branches: the push / pop code ran with 5-6 of 32 lanes (profiles/r02a_source_hotspots.md).
+  if (L.sp + 4 <= SSTACK) {
+    uint2* top = S.s + L.sp * TRACE_THREADS;
+    top[0] = make_uint2(__float_as_uint(t3), c3); top += (t3 != T_INVALID) ? TRACE_THREADS : 0; L.sp += (t3 != T_INVALID);
+    top[0] = make_uint2(__float_as_uint(t2), c2); top += (t2 != T_INVALID) ? TRACE_THREADS : 0; L.sp += (t2 != T_INVALID);
+    top[0] = make_uint2(__float_as_uint(t1), c1); top += (t1 != T_INVALID) ? TRACE_THREADS : 0; L.sp += (t1 != T_INVALID);
+    top[0] = make_uint2(__float_as_uint(t0), c0); L.sp += (t0 != T_INVALID);
+  } else {
+    if (t3 != T_INVALID) stack_push(L, S, t3, c3);
+    if (t2 != T_INVALID) stack_push(L, S, t2, c2);
+    if (t1 != T_INVALID) stack_push(L, S, t1, c1);
+    if (t0 != T_INVALID) stack_push(L, S, t0, c0);
+  }
+#else
+  if (t3 != T_INVALID) stack_push(L, S, t3, c3);
+  if (t2 != T_INVALID) stack_push(L, S, t2, c2);
+  if (t1 != T_INVALID) stack_push(L, S, t1, c1);
+#if CLRT_PREFETCH_TOP
+  if (t1 != T_INVALID && !(c1 & WIDE_TOP_BIT)) asm volatile("prefetch.global.L1 [%0];" :: "l"(wnodes + (c1 - n)));
+#endif
   if (t0 != T_INVALID) { L.cur = c0; return; }
+#endif
   L.cur = SENTINEL;
   while (L.sp > 0) {
-    const uint2 e = stack_pop(L, stack);
+    const uint2 e = stack_pop(L, S);
     if (!(__uint_as_float(e.x) > L.h.cull)) { L.cur = e.y; break; }
   }
 }
 
-// The postponed triangle tests of the warp, together (all lanes call this; lanes without a queue idle through it).
+// One postponed triangle test per lane that holds one (the queue is LIFO: q0 is the newest).  A closest-hit ray goes on with the
+// shorter cull distance; an occlusion query that hit is complete.
 template <bool STATS, bool ANYHIT>
-__device__ __forceinline__ void flush_leaves(Lane& L, const clrt_triangle* __restrict__ tris, Stats& st) {
-  while (__any_sync(0xffffffffu, L.qn != 0u)) {
-    if (L.qn != 0u) {
-      const uint32_t id = L.q0;
-      L.q0 = L.q1; L.q1 = L.q2; L.q2 = L.q3; L.qn--;
-      test_triangle<true>(tris, id, L.o, L.d, L.h);
-      if (STATS) st.tris++;
-      if (ANYHIT && L.h.tri != SENTINEL) { L.qn = 0u; L.cur = SENTINEL; }
-    }
+__device__ __forceinline__ void flush_one(Lane& L, const clrt_triangle* __restrict__ tris, Stats& st) {
+  if (L.qn != 0u) {
+    const uint32_t id = L.q0;
+    L.q0 = L.q1; L.q1 = L.q2; L.q2 = L.q3; L.qn--;
+    test_triangle<true>(tris, id, L.o, L.d, L.h);
+    if (STATS) st.tris++;
+    if (ANYHIT && L.h.tri != SENTINEL) { L.qn = 0u; L.cur = SENTINEL; L.sp = 0; }
   }
 }
 
 // Persistent-warp driver with lane refill.  A "unit" is a pixel slot / ray / contact; units come from one global atomic
-// counter in warp-private batches of BATCH consecutive indices (work stealing between all warps of the GPU).  A lane
-// whose unit is complete goes idle; when REFILL_MIN lanes are idle the warp hands them the next units of its batch, so
-// lanes do not wait for the slowest ray of a packet (rays of one warp differ several-fold in node visits).  Between
-// refill checks every lane runs WINDOW traversal steps on its own.
+// counter in warp-private batches of BATCH consecutive indices (work stealing between all warps of the GPU).  Every step
+// has two phases, each run by all lanes that have something to do in it:
+//   A  lane_visit: lanes with a current node fetch it, test its four boxes, queue accepted leaves, push / pop;
+//   B  flush_one:  once FLUSH_MIN lanes hold a postponed leaf (or a queue is QFULL deep, or no lane can do phase A) every
+//      lane with a queue tests ONE triangle.
+// A lane whose ray is complete waits; when REFILL_MIN lanes wait, they complete their units together (Job::finish may aim
+// the unit's next ray) and idle lanes are handed the next units of the warp's batch, so lanes never wait for the slowest ray
+// of a packet (rays of one warp differ several-fold in node visits).
 //   Job::start(unit, L)  -> true: a ray is ready in L;  false: the unit completed without tracing (output written)
 //   Job::finish(L)       -> true: the unit continues with another ray (L re-initialised); false: unit complete
 #ifndef CLRT_WINDOW
-#define CLRT_WINDOW 8
+#define CLRT_WINDOW 2
 #endif
 #ifndef CLRT_REFILL_MIN
-#define CLRT_REFILL_MIN 12
+#define CLRT_REFILL_MIN 8
+#endif
+#ifndef CLRT_FLUSH_MIN
+#define CLRT_FLUSH_MIN 8
+#endif
+#ifndef CLRT_QFULL
+#define CLRT_QFULL 3
 #endif
 #ifndef CLRT_BATCH
 #define CLRT_BATCH 32
 #endif
-// CLRT_PACKET_AHEAD=1 (EXPERIMENT, off: prepared after the round's GPU time ended): every warp claims its NEXT packet when it
-// starts the current one, so the atomic's round trip overlaps a packet's worth of tracing.  profiles/r01_source_hotspots.md: on
-// ClumsyDragon (2-4 node visits per ray) the counter's atomicAdd is the top line of both traversal kernels, 15-16 % of the stall
-// samples.  Cost: at the end a warp may sit on one claimed packet while others are idle (<= 32 units per warp).
-#ifndef CLRT_PACKET_AHEAD
-#define CLRT_PACKET_AHEAD 0
-#endif
 constexpr int WINDOW = CLRT_WINDOW;
 constexpr int REFILL_MIN = CLRT_REFILL_MIN;
+constexpr int FLUSH_MIN = CLRT_FLUSH_MIN;
+constexpr uint32_t QFULL = CLRT_QFULL;
 constexpr uint32_t BATCH = CLRT_BATCH;
+
+// Shared memory of a FAST kernel: [top table prefix | stack columns | mbarrier].  One thread arms the barrier and issues the
+// bulk copy (cp.async.bulk = the TMA engine's linear mode); everybody waits on the barrier's phase 0.
+__device__ __forceinline__ const WideNode* stage_top_table(unsigned char* smem, const WideNode* __restrict__ g_top, uint32_t n) {
+  WideNode* s_top = reinterpret_cast<WideNode*>(smem);
+  if (TOP_STAGED && n >= 2) {                                  // n < 2: no wide nodes exist (lane_begin answers such scenes directly)
+    unsigned long long* bar = reinterpret_cast<unsigned long long*>(smem + (size_t)TOP_STAGED * sizeof(WideNode) + (size_t)SSTACK * TRACE_THREADS * sizeof(uint2));
+    const uint32_t bar_a = (uint32_t)__cvta_generic_to_shared(bar), dst_a = (uint32_t)__cvta_generic_to_shared(s_top);
+    constexpr uint32_t bytes = (uint32_t)(TOP_STAGED * sizeof(WideNode));
+    if (threadIdx.x == 0) {
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" :: "r"(bar_a) : "memory");
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(bar_a), "r"(bytes) : "memory");
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                   :: "r"(dst_a), "l"(g_top), "r"(bytes), "r"(bar_a) : "memory");
+    }
+    uint32_t done = 0;
+    while (!done)
+      asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0; selp.u32 %0, 1, 0, p; }" : "=r"(done) : "r"(bar_a) : "memory");
+  }
+  return s_top;
+}
 
 template <class Job, bool STATS, bool ANYHIT>
 __device__ __forceinline__ void run_jobs(Job& job, const WideNode* __restrict__ wnodes, const clrt_triangle* __restrict__ tris,
-                                         uint32_t n, uint32_t total, uint32_t* __restrict__ counter, Stats& st) {
+                                         uint32_t n, uint32_t total, uint32_t* __restrict__ counter, Stats& st, uint32_t* __restrict__ overflow) {
+  extern __shared__ __align__(128) unsigned char fast_smem[];
+  const WideNode* s_top = stage_top_table(fast_smem, wnodes + n, n);
+  uint2 spill[FAST_STACK - SSTACK > 0 ? FAST_STACK - SSTACK : 1];
+  const StackRef S{reinterpret_cast<uint2*>(fast_smem + (size_t)TOP_STAGED * sizeof(WideNode)) + threadIdx.x, spill, overflow};
   const unsigned FULL = 0xffffffffu;
   const int lane = threadIdx.x & 31;
   const unsigned lt_mask = (1u << lane) - 1u;
   Lane L; L.cur = SENTINEL; L.sp = 0; L.qn = 0;
-  uint2 stack[FAST_STACK];
   bool busy = false, exhausted = false;
   uint32_t pool_next = 0, pool_end = 0;                         // warp-uniform
-#if CLRT_PACKET_AHEAD
-  uint32_t ahead = 0;                                           // lane 0: base of the packet claimed one refill ago
-  if (lane == 0) ahead = atomicAdd(counter, BATCH);
-#endif
   while (true) {
-    // window boundary, all lanes converged: rays that ended during the window are completed together (Job::finish may aim
-    // the unit's next ray), then idle lanes are refilled together once enough of them wait.
-    if (busy && L.cur == SENTINEL) busy = job.finish(L);
-    unsigned idle = __ballot_sync(FULL, !busy);
-    if (__popc(idle) >= REFILL_MIN) {
+    // all lanes converged: rays that are complete wait here; once enough lanes wait they are completed together and idle lanes
+    // are refilled together
+    const bool fin = busy && L.cur == SENTINEL && L.qn == 0u;
+    if (__popc(__ballot_sync(FULL, !busy || fin)) >= REFILL_MIN) {
+      if (fin) busy = job.finish(L);
+      unsigned idle = __ballot_sync(FULL, !busy);
       while (idle) {
         if (pool_next >= pool_end) {
           if (exhausted) break;
-#if CLRT_PACKET_AHEAD
-          const uint32_t b = __shfl_sync(FULL, ahead, 0);
-          if (b >= total) { exhausted = true; break; }
-          if (lane == 0) ahead = atomicAdd(counter, BATCH);
-#else
           uint32_t b = 0;
           if (lane == 0) b = atomicAdd(counter, BATCH);
           b = __shfl_sync(FULL, b, 0);
           if (b >= total) { exhausted = true; break; }
-#endif
           pool_next = b; pool_end = min(b + BATCH, total);
         }
         const uint32_t avail = pool_end - pool_next;
@@ -297,9 +375,15 @@ __device__ __forceinline__ void run_jobs(Job& job, const WideNode* __restrict__ 
       if (idle == FULL) break;                                  // nothing left anywhere
     }
 #pragma unroll 1
-    for (int k = 0; k < WINDOW; k++)
-      if (busy && L.cur != SENTINEL) lane_step<STATS, ANYHIT>(L, wnodes, tris, n, st, stack);
-    if (ANYHIT) flush_leaves<STATS, ANYHIT>(L, tris, st);
+    for (int k = 0; k < WINDOW; k++) {
+      const bool walking = busy && L.cur != SENTINEL;
+      if (walking) lane_visit<STATS, ANYHIT>(L, wnodes, s_top, tris, n, st, S);
+      const unsigned queued = __ballot_sync(FULL, L.qn != 0u);
+      if (queued) {
+        const bool go = __popc(queued) >= FLUSH_MIN || __any_sync(FULL, L.qn >= QFULL) || !__any_sync(FULL, busy && L.cur != SENTINEL);
+        if (go) flush_one<STATS, ANYHIT>(L, tris, st);
+      }
+    }
   }
 }
 
@@ -397,35 +481,41 @@ struct ShadowJob {
   const clrt_camera& cam; const clrt_contact* __restrict__ contacts;
   const clrt_light* __restrict__ lights; uint32_t n_lights; const clrt_material* __restrict__ materials; uint32_t n_materials;
   const clrt_triangle* __restrict__ tris; uint32_t n; uint32_t* __restrict__ rgba8; const PeerTargets& peers; Stats& st; uint32_t& live_rays;
-  uint4 head; float4 nd; Vec3 o, P; uint32_t index, l, occl;
+  // Per-lane state of a unit: five registers.  The contact's 32 bytes are read again when the unit is shaded and the primary ray
+  // is regenerated per shadow ray (40 instructions against ~9000 of a shadow ray's traversal): the 17 registers the whole contact,
+  // origin and hit point took cost the kernel a fifth of its occupancy (86 registers, 5 CTAs per SM).
+  uint32_t index, pixel, l, occl; float t;
   // peers.n == 0: the local stripe buffer at the contact's slot.  Otherwise the fused exchange: the pixel goes straight into the
   // raster-ordered framebuffer of EVERY GPU of the box (peer memory over NVLink; the local one is among them) — no all-gather,
   // no untile pass.  Slots outside the image (pixel == SENTINEL) have no raster position.
-  __device__ __forceinline__ void store_pixel(uint32_t slot, uint32_t pixel, uint32_t packed) {
+  __device__ __forceinline__ void store_pixel(uint32_t slot, uint32_t px, uint32_t packed) {
     if (peers.n == 0) { __stcs(rgba8 + slot, packed); return; }
-    if (pixel == SENTINEL) return;
+    if (px == SENTINEL) return;
 #pragma unroll
-    for (uint32_t t = 0; t < 8; t++) if (t < peers.n) peers.p[t][pixel] = packed;
+    for (uint32_t k = 0; k < 8; k++) if (k < peers.n) peers.p[k][px] = packed;
   }
   __device__ __forceinline__ void shade_and_store() {
     uint32_t packed;
     const uint32_t oc = occl;
+    const uint4 head = __ldcs(reinterpret_cast<const uint4*>(contacts + index));
+    const float4 nd = __ldcs(reinterpret_cast<const float4*>(contacts + index) + 1);
     shade_contact(cam, head, nd, lights, n_lights, materials, n_materials, [oc](uint32_t k, float) { return ((oc >> k) & 1u) != 0u; }, packed);
-    store_pixel(index, head.x, packed);
+    store_pixel(index, pixel, packed);
   }
   __device__ __forceinline__ void aim(Lane& L) {
+    Vec3 o, d; generate_ray(cam, pixel, o, d);
+    const Vec3 P = vadd(o, vscale(d, t));
     float energy; const Vec3 lp = light_position(lights, n_lights, l, o, energy);
-    const float limit = vlength(vsub(lp, P)) - SHADOW_EPS_REL * nd.w;
-    Vec3 org, dir; shadow_ray(cam, head.x, nd.w, lights, n_lights, l, org, dir);
+    const float limit = vlength(vsub(lp, P)) - SHADOW_EPS_REL * t;
+    Vec3 org, dir; shadow_ray(cam, pixel, t, lights, n_lights, l, org, dir);
     lane_begin<STATS, true>(L, tris, n, org, dir, limit, st);
   }
   __device__ __forceinline__ bool start(uint32_t i, Lane& L) {
     index = i; occl = 0; l = 0;
-    head = __ldcs(reinterpret_cast<const uint4*>(contacts + i));
-    nd = __ldcs(reinterpret_cast<const float4*>(contacts + i) + 1);
+    const uint4 head = __ldcs(reinterpret_cast<const uint4*>(contacts + i));
+    const float4 nd = __ldcs(reinterpret_cast<const float4*>(contacts + i) + 1);
+    pixel = head.x; t = nd.w;
     if (!(nd.w > 0.0f && head.x != SENTINEL)) { store_pixel(i, head.x, 0u); return false; }
-    Vec3 d; generate_ray(cam, head.x, o, d);
-    P = vadd(o, vscale(d, nd.w));
     live_rays += n_lights + 1;
     aim(L);
     return true;
@@ -440,11 +530,11 @@ struct ShadowJob {
 
 // ---- kernels ---------------------------------------------------------------------------------------------------------------
 template <int MODE, bool STATS>      // MODE 0: REFERENCE_ORDER, 1: FAST
-__global__ void __launch_bounds__(TRACE_THREADS)
+__global__ void __launch_bounds__(TRACE_THREADS, CLRT_MIN_CTAS)
 trace_primary_kernel(const clrt_camera cam, const TraceNode* __restrict__ tnodes, const WideNode* __restrict__ wnodes,
                      const clrt_triangle* __restrict__ tris, uint32_t n, clrt_contact* __restrict__ out,
                      uint32_t rank, uint32_t nranks, int raster, uint32_t* __restrict__ counter,
-                     unsigned long long* __restrict__ stats) {
+                     unsigned long long* __restrict__ stats, uint32_t* __restrict__ overflow) {
   Stats st; st.rays = st.inner = st.tris = st.lboxes = 0;
   const TileGrid g = make_tile_grid(cam.resX, cam.resY);
   const uint32_t total = stripe_tile_count(g.tiles, rank, nranks) * CLRT_TILE_PIXELS;
@@ -458,7 +548,7 @@ trace_primary_kernel(const clrt_camera cam, const TraceNode* __restrict__ tnodes
       const PixelRef r = pixel_of_unit(cam, g, pk + lane, rank, nranks, raster);
       if (r.inside) {
         Vec3 o, d; generate_ray(cam, r.pixel, o, d);
-        const Hit h = traverse_ref<STATS>(tnodes, tris, n, o, d, st);
+        const Hit h = traverse_ref<STATS>(tnodes, tris, n, o, d, st, overflow);
         write_contact(out, r.slot, r.pixel, h, tris);
       } else if (!raster) {
         Hit h; h.t = RT_FLT_MAX; h.tri = SENTINEL;
@@ -467,16 +557,16 @@ trace_primary_kernel(const clrt_camera cam, const TraceNode* __restrict__ tnodes
     }
   } else {
     PrimaryJob<STATS> job{cam, g, rank, nranks, raster, tris, n, out, st, 0u, 0u};
-    run_jobs<PrimaryJob<STATS>, STATS, false>(job, wnodes, tris, n, total, counter, st);
+    run_jobs<PrimaryJob<STATS>, STATS, false>(job, wnodes, tris, n, total, counter, st, overflow);
   }
   if (STATS) flush_stats(st, stats);
 }
 
 template <int MODE, bool STATS>
-__global__ void __launch_bounds__(TRACE_THREADS)
+__global__ void __launch_bounds__(TRACE_THREADS, CLRT_MIN_CTAS)
 trace_rays_kernel(const clrt_ray* __restrict__ rays, uint32_t count, const TraceNode* __restrict__ tnodes, const WideNode* __restrict__ wnodes,
                   const clrt_triangle* __restrict__ tris, uint32_t n, clrt_contact* __restrict__ out,
-                  uint32_t* __restrict__ counter, unsigned long long* __restrict__ stats) {
+                  uint32_t* __restrict__ counter, unsigned long long* __restrict__ stats, uint32_t* __restrict__ overflow) {
   Stats st; st.rays = st.inner = st.tris = st.lboxes = 0;
   if (MODE == 0) {
     const int lane = threadIdx.x & 31;
@@ -491,28 +581,28 @@ trace_rays_kernel(const clrt_ray* __restrict__ rays, uint32_t count, const Trace
         const float4 ro = __ldcs(p + 1), rd = __ldcs(p + 2);
         Hit h; h.t = RT_FLT_MAX; h.tri = SENTINEL; h.cull = RT_FLT_MAX;
         if (!(rd.x == 0.0f && rd.y == 0.0f && rd.z == 0.0f))
-          h = traverse_ref<STATS>(tnodes, tris, n, v3(ro.x, ro.y, ro.z), v3(rd.x, rd.y, rd.z), st);
+          h = traverse_ref<STATS>(tnodes, tris, n, v3(ro.x, ro.y, ro.z), v3(rd.x, rd.y, rd.z), st, overflow);
         write_contact(out, i, i, h, tris);
       }
     }
   } else {
     RaysJob<STATS> job{rays, tris, n, out, st, 0u};
-    run_jobs<RaysJob<STATS>, STATS, false>(job, wnodes, tris, n, count, counter, st);
+    run_jobs<RaysJob<STATS>, STATS, false>(job, wnodes, tris, n, count, counter, st, overflow);
   }
   if (STATS) flush_stats(st, stats);
 }
 
 template <bool STATS>
-__global__ void __launch_bounds__(TRACE_THREADS)
+__global__ void __launch_bounds__(TRACE_THREADS, CLRT_MIN_CTAS)
 shadow_shade_kernel(const clrt_camera cam, const clrt_contact* __restrict__ contacts, uint32_t count,
                     const clrt_light* __restrict__ lights, uint32_t n_lights, const clrt_material* __restrict__ materials, uint32_t n_materials,
                     const WideNode* __restrict__ wnodes, const clrt_triangle* __restrict__ tris, uint32_t n,
                     uint32_t* __restrict__ rgba8, const PeerTargets peers, uint32_t* __restrict__ counter, unsigned long long* __restrict__ ray_counter,
-                    unsigned long long* __restrict__ stats) {
+                    unsigned long long* __restrict__ stats, uint32_t* __restrict__ overflow) {
   Stats st; st.rays = st.inner = st.tris = st.lboxes = 0;
   uint32_t live_rays = 0;
-  ShadowJob<STATS> job{cam, contacts, lights, n_lights, materials, n_materials, tris, n, rgba8, peers, st, live_rays};
-  run_jobs<ShadowJob<STATS>, STATS, true>(job, wnodes, tris, n, count, counter, st);
+  ShadowJob<STATS> job{cam, contacts, lights, n_lights, materials, n_materials, tris, n, rgba8, peers, st, live_rays, 0u, 0u, 0u, 0u, 0.0f};
+  run_jobs<ShadowJob<STATS>, STATS, true>(job, wnodes, tris, n, count, counter, st, overflow);
   if (ray_counter) {
 #pragma unroll
     for (int dd = 16; dd > 0; dd >>= 1) live_rays += __shfl_xor_sync(0xffffffffu, live_rays, dd);
@@ -528,12 +618,14 @@ shadow_shade_kernel(const clrt_camera cam, const clrt_contact* __restrict__ cont
 // full-frame rate, 16 units per lane with 8 slots 94 %, but 24+ units per lane leave too few warps to fill the machine (86 %, 75 %).
 // So: `rays_per_lane` (16) units per lane, but never fewer warps than capacity / D (D kernels run side by side; D = the number of
 // frame slots the caller has used so far).
-template <typename K>
-int persistent_grid(clrt_accel* a, K kernel, int threads, uint32_t packets, unsigned* grid) {
-  static int per_sm = 0;                       // one instance per kernel template instantiation
+// FAST kernels take FAST_SMEM_BYTES of dynamic shared memory (top table prefix + stack columns); REFERENCE_ORDER kernels none.
+template <auto kernel>                         // the kernel itself, not its type: the statics below are per kernel instantiation
+int persistent_grid(clrt_accel* a, int threads, size_t smem, uint32_t packets, unsigned* grid) {
+  static int per_sm = 0;
   if (per_sm == 0) {
-    CLRT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, 0));
-    if (per_sm < 1) per_sm = 1;
+    if (smem > 48 * 1024) CLRT_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CLRT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, smem));
+    if (per_sm < 1) CLRT_FAIL("trace kernel does not fit an SM (%zu bytes of shared memory, %d threads)", smem, threads);
   }
   static int rays_per_lane = 0;
   if (rays_per_lane == 0) { const char* e = getenv("CLRT_RAYS_PER_LANE"); rays_per_lane = e ? atoi(e) : 16; if (rays_per_lane < 1) rays_per_lane = 1; }
@@ -558,6 +650,7 @@ int persistent_grid(clrt_accel* a, K kernel, int threads, uint32_t packets, unsi
 // frames in flight on several streams, each with a private counter and scratch).
 static inline cudaStream_t trace_stream(const clrt_accel* a) { return a->launch_stream ? a->launch_stream : a->ctx->stream; }
 static inline uint32_t* trace_counter(const clrt_accel* a) { return a->launch_counter ? a->launch_counter : a->d_tile_counter; }
+static inline uint32_t* overflow_word(const clrt_accel* a) { return a->d_tile_counter + 13; }      // sticky; read by clrt_accel_check
 
 struct TraceView { const TraceNode* tnodes; const WideNode* wnodes; const clrt_triangle* tris; };
 static TraceView trace_view(const clrt_accel* a, bool fast) {
@@ -568,20 +661,22 @@ static TraceView trace_view(const clrt_accel* a, bool fast) {
 template <int M, bool S>
 static int launch_primary(clrt_accel* a, const clrt_camera& cam, clrt_contact* out, uint32_t rank, uint32_t nranks, int raster, uint32_t packets) {
   unsigned grid = 0;
-  CLRT_TRY(persistent_grid(a, trace_primary_kernel<M, S>, TRACE_THREADS, packets, &grid));
+  const size_t smem = M ? FAST_SMEM_BYTES : 0;
+  CLRT_TRY((persistent_grid<trace_primary_kernel<M, S>>(a, TRACE_THREADS, smem, packets, &grid)));
   const TraceView v = trace_view(a, M != 0);
-  trace_primary_kernel<M, S><<<grid, TRACE_THREADS, 0, trace_stream(a)>>>(cam, v.tnodes, v.wnodes, v.tris, a->n, out, rank, nranks, raster,
-                                                                        trace_counter(a), (unsigned long long*)(a->d_tile_counter + 4));
+  trace_primary_kernel<M, S><<<grid, TRACE_THREADS, smem, trace_stream(a)>>>(cam, v.tnodes, v.wnodes, v.tris, a->n, out, rank, nranks, raster,
+                                                                           trace_counter(a), (unsigned long long*)(a->d_tile_counter + 4), overflow_word(a));
   CLRT_CHECK_LAUNCH();
   return 0;
 }
 template <int M, bool S>
 static int launch_rays(clrt_accel* a, const clrt_ray* rays, clrt_contact* out, uint32_t count, uint32_t packets) {
   unsigned grid = 0;
-  CLRT_TRY(persistent_grid(a, trace_rays_kernel<M, S>, TRACE_THREADS, packets, &grid));
+  const size_t smem = M ? FAST_SMEM_BYTES : 0;
+  CLRT_TRY((persistent_grid<trace_rays_kernel<M, S>>(a, TRACE_THREADS, smem, packets, &grid)));
   const TraceView v = trace_view(a, M != 0);
-  trace_rays_kernel<M, S><<<grid, TRACE_THREADS, 0, trace_stream(a)>>>(rays, count, v.tnodes, v.wnodes, v.tris, a->n, out,
-                                                                     trace_counter(a), (unsigned long long*)(a->d_tile_counter + 4));
+  trace_rays_kernel<M, S><<<grid, TRACE_THREADS, smem, trace_stream(a)>>>(rays, count, v.tnodes, v.wnodes, v.tris, a->n, out,
+                                                                        trace_counter(a), (unsigned long long*)(a->d_tile_counter + 4), overflow_word(a));
   CLRT_CHECK_LAUNCH();
   return 0;
 }
@@ -618,10 +713,10 @@ static int launch_shadow_shade(clrt_accel* a, const clrt_camera& cam, const clrt
                                unsigned long long* d_ray_counter, uint32_t packets) {
   const clrt_scene* sc = a->scene;
   unsigned grid = 0;
-  CLRT_TRY(persistent_grid(a, shadow_shade_kernel<S>, TRACE_THREADS, packets, &grid));
+  CLRT_TRY(persistent_grid<shadow_shade_kernel<S>>(a, TRACE_THREADS, FAST_SMEM_BYTES, packets, &grid));
   const TraceView v = trace_view(a, true);
-  shadow_shade_kernel<S><<<grid, TRACE_THREADS, 0, trace_stream(a)>>>(cam, contacts, count, sc->d_lights, sc->n_lights, sc->d_materials, sc->n_materials,
-      v.wnodes, v.tris, a->n, rgba8, a->launch_targets, trace_counter(a), d_ray_counter, (unsigned long long*)(a->d_tile_counter + 4));
+  shadow_shade_kernel<S><<<grid, TRACE_THREADS, FAST_SMEM_BYTES, trace_stream(a)>>>(cam, contacts, count, sc->d_lights, sc->n_lights, sc->d_materials, sc->n_materials,
+      v.wnodes, v.tris, a->n, rgba8, a->launch_targets, trace_counter(a), d_ray_counter, (unsigned long long*)(a->d_tile_counter + 4), overflow_word(a));
   CLRT_CHECK_LAUNCH();
   return 0;
 }
@@ -636,4 +731,21 @@ int bvh_shadow_shade(clrt_accel* a, const clrt_camera& cam, const clrt_contact* 
   CLRT_CUDA(cudaMemsetAsync(trace_counter(a), 0, 4, trace_stream(a)));
   return a->stats ? launch_shadow_shade<true>(a, cam, contacts, count, rgba8, d_ray_counter, packets)
                   : launch_shadow_shade<false>(a, cam, contacts, count, rgba8, d_ray_counter, packets);
+}
+
+// Traversal stacks are bounded (REF_STACK, FAST_STACK).  A push that does not fit is counted on the device instead of silently
+// dropping a subtree; this call synchronises the context's stream and FAILS if any launch since the last check overflowed.
+extern "C" int clrt_accel_check(clrt_accel* a) {
+  if (!a) CLRT_FAIL("clrt_accel_check: NULL accel");
+  CLRT_CUDA(cudaSetDevice(a->ctx->device));
+  void* pin = nullptr;
+  CLRT_TRY(clrt_ctx_pinned(a->ctx, 64, &pin));
+  CLRT_CUDA(cudaMemcpyAsync(pin, a->d_tile_counter + 13, 4, cudaMemcpyDeviceToHost, a->ctx->stream));
+  CLRT_CUDA(cudaStreamSynchronize(a->ctx->stream));
+  const uint32_t dropped = *(uint32_t*)pin;
+  if (dropped) {
+    CLRT_CUDA(cudaMemsetAsync(a->d_tile_counter + 13, 0, 4, a->ctx->stream));
+    CLRT_FAIL("traversal stack overflow: %u pushes did not fit (tree deeper than the %d / %d entry stacks); contacts are incomplete", dropped, REF_STACK, FAST_STACK);
+  }
+  return 0;
 }

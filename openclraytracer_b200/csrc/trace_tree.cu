@@ -170,6 +170,43 @@ widen_kernel(const TraceNode* __restrict__ tnodes, uint32_t n, WideNode* __restr
   reinterpret_cast<uint4*>(o)[7] = make_uint4(0u, 0u, 0u, 0u);
 }
 
+// Top table (the north star's "staging of the top BVH levels"): the first WIDE_TOP_LEVELS levels of the wide tree copied in
+// breadth-first order into WIDE_TOP_NODES consecutive records behind the n per-node records (slot of child j of slot s = 4s+1+j, the
+// implicit complete 4-ary layout; slots of absent children stay unused).  Child ids that stay inside the table become
+// WIDE_TOP_BIT | slot; everything else keeps its id.  The trace kernels start at WIDE_TOP_BIT | 0 and copy a prefix of the table
+// into shared memory with one bulk-async (TMA) copy per CTA (trace.cu).  One CTA, one thread per slot, level by level.
+__global__ void __launch_bounds__(WIDE_TOP_NODES <= 1024 ? 512 : 1024)
+wide_top_kernel(const WideNode* __restrict__ wnodes, uint32_t n, WideNode* __restrict__ top) {
+  __shared__ uint32_t src[WIDE_TOP_NODES];
+  for (int s = threadIdx.x; s < WIDE_TOP_NODES; s += blockDim.x) src[s] = 0xFFFFFFFFu;
+  __syncthreads();
+  if (threadIdx.x == 0) src[0] = n;                          // the root: inner node 0
+  __syncthreads();
+  int first = 0, count = 1;
+  for (int level = 0; level < WIDE_TOP_LEVELS; level++) {
+    for (int k = threadIdx.x; k < count; k += blockDim.x) {
+      const int s = first + k;
+      const uint32_t id = src[s];
+      uint4* o = reinterpret_cast<uint4*>(top + s);
+      if (id == 0xFFFFFFFFu) {                                 // unused slot: NaN boxes, empty children
+        const uint32_t q = 0x7fc00000u;
+        for (int w = 0; w < 6; w++) o[w] = make_uint4(q, q, q, q);
+        o[6] = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu); o[7] = make_uint4(0u, 0u, 0u, 0u);
+        continue;
+      }
+      const uint4* p = reinterpret_cast<const uint4*>(wnodes + (id - n));
+      for (int w = 0; w < 6; w++) o[w] = p[w];
+      uint4 ch = p[6];
+      uint32_t c[4] = {ch.x, ch.y, ch.z, ch.w};
+      for (int j = 0; j < 4; j++)
+        if (level + 1 < WIDE_TOP_LEVELS && c[j] != 0xFFFFFFFFu && c[j] >= n) { src[4 * s + 1 + j] = c[j]; c[j] = WIDE_TOP_BIT | (uint32_t)(4 * s + 1 + j); }
+      o[6] = make_uint4(c[0], c[1], c[2], c[3]); o[7] = make_uint4(0u, 0u, 0u, 0u);
+    }
+    __syncthreads();
+    first += count; count *= 4;
+  }
+}
+
 } // namespace
 
 void trace_tree_destroy(clrt_accel* a) {
@@ -200,11 +237,14 @@ int trace_tree_build(clrt_accel* a) {
   if (n < 2) return 0;
   cudaStream_t s = ctx->stream;
   const bool tm = a->timing;
-  if ((size_t)n * sizeof(WideNode) > a->wnodes_cap) CLRT_CUDA(cudaStreamSynchronize(s));
-  CLRT_TRY(clrt_grow((void**)&a->d_wnodes, &a->wnodes_cap, (size_t)n * sizeof(WideNode)));
+  const size_t wide_bytes = ((size_t)n + WIDE_TOP_NODES) * sizeof(WideNode);      // per-node records, then the top table
+  if (wide_bytes > a->wnodes_cap) CLRT_CUDA(cudaStreamSynchronize(s));
+  CLRT_TRY(clrt_grow((void**)&a->d_wnodes, &a->wnodes_cap, wide_bytes));
   if (tm) CLRT_CUDA(cudaEventRecord(a->ev[5], s));
   if (want) CLRT_TRY(trace_tree_separate(a));
   widen_kernel<<<(n + 127) / 128, 128, 0, s>>>(want ? a->d_tt_nodes : a->d_tnodes, n, a->d_wnodes);
+  CLRT_CHECK_LAUNCH();
+  wide_top_kernel<<<1, WIDE_TOP_NODES <= 1024 ? 512 : 1024, 0, s>>>(a->d_wnodes, n, a->d_wnodes + n);
   CLRT_CHECK_LAUNCH();
   if (tm) {
     CLRT_CUDA(cudaEventRecord(a->ev[6], s));

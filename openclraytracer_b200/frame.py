@@ -339,3 +339,77 @@ def orbit_camera(scene_buf, resX, resY, step, steps_per_turn=64, fov_deg=90.0):
     c, s = np.cos(-ang), np.sin(-ang)
     m = np.array([c, 0, s, pos[0], 0, 1, 0, pos[1], -s, 0, c, pos[2]], dtype=np.float32)
     return api.make_camera(resX, resY, base["FOVDistance"], m)
+
+
+class BounceRenderer:
+    """BASELINE.json configs[3]: incoherent secondary rays, image-tile sharded.  Per frame and rank: primary contacts of the rank's
+    stripe (clrt_trace_primary_stripe, stripe order) -> one cosine-weighted diffuse bounce ray per hit (clrt_generate_bounce_rays)
+    -> the generic-ray entry generateContacts(rays, contacts, n) (clrt_trace_rays; BVHManager.cpp:292-329) -> Blinn-Phong halved
+    where the bounce ray hit (clrt_shade_bounce) -> RGBA8 stripe; one all-gather of equal padded stripes + untile gives every rank
+    the frame.  Rays are independent and the structure is read-only: no other exchange exists.  One stream, one frame at a time."""
+
+    def __init__(self, scene_buf, resX, resY, rank=0, world=1, device=0, group=None):
+        import torch
+        self.torch = torch
+        self.rank, self.world, self.group = rank, world, group
+        self.resX, self.resY = resX, resY
+        torch.cuda.set_device(device)
+        self.device = torch.device("cuda", device)
+        self.stream = torch.cuda.Stream(self.device)
+        self.ctx = api.Context(device, stream=self.stream.cuda_stream)
+        self.scene = api.Scene(scene_buf)
+        self.scene.loadToGPU(self.ctx)
+        self.accel = api.BVHManager(self.ctx, self.scene)
+        self.accel.initialize()
+        self.cap, self.tiles = api.frame_stripe_pixels(resX, resY, rank, world)
+        self.slots = self.tiles * TILE_PIXELS
+        with torch.cuda.stream(self.stream):
+            self.contacts = torch.zeros(self.cap * 32, dtype=torch.uint8, device=self.device)
+            self.rays = torch.zeros(self.cap * 48, dtype=torch.uint8, device=self.device)
+            self.bounce = torch.zeros(self.cap * 32, dtype=torch.uint8, device=self.device)
+            self.stripe = torch.zeros(self.cap, dtype=torch.int32, device=self.device)
+            self.gathered = torch.zeros(self.cap * world, dtype=torch.int32, device=self.device) if world > 1 else self.stripe
+            self.raster = torch.zeros(resY * resX, dtype=torch.int32, device=self.device)
+        self.host_raster = torch.zeros(resY * resX, dtype=torch.int32).pin_memory()
+        self.stream.synchronize()
+
+    def build(self):
+        self.accel.initializeFrame()
+        self.accel.construct()
+        self.stream.synchronize()
+
+    def render_device(self, camera, seed=20161116):
+        torch = self.torch
+        with torch.cuda.stream(self.stream):
+            if self.slots:
+                self.accel.trace_primary_stripe(camera, self.rank, self.world, self.contacts.data_ptr())
+                api.generate_bounce_rays(self.ctx, camera, self.contacts.data_ptr(), self.slots, seed, self.rays.data_ptr())
+                self.accel.generateContacts(self.rays.data_ptr(), self.bounce.data_ptr(), self.slots)
+                api.shade_bounce(self.ctx, self.scene, camera, self.contacts.data_ptr(), self.slots, self.bounce.data_ptr(), self.stripe.data_ptr())
+            if self.world > 1:
+                import torch.distributed as dist
+                dist.all_gather_into_tensor(self.gathered, self.stripe, group=self.group)
+            api.frame_untile_on(self.ctx, self.stream.cuda_stream, self.gathered.data_ptr(), self.resX, self.resY, self.world, self.raster.data_ptr())
+
+    def render_host(self, camera, seed=20161116):
+        """e2e: host camera in, the frame in pinned host memory (rank 0) when the stream has passed."""
+        self.render_device(camera, seed)
+        if self.rank == 0:
+            with self.torch.cuda.stream(self.stream):
+                self.host_raster.copy_(self.raster, non_blocking=True)
+        return self.host_raster
+
+    def count_rays(self):
+        """Rays of the last frame on this rank: primary = stripe slots inside the image, bounce = primary hits (host sync)."""
+        self.stream.synchronize()
+        c = self.contacts[: self.slots * 32].view(self.torch.int32).reshape(-1, 8)
+        inside = int((c[:, 0] != -1).sum().item())
+        hits = int((c[:, 7].view(self.torch.float32) > 0).sum().item())
+        return inside + hits
+
+    def finish(self):
+        self.stream.synchronize()
+
+    def close(self):
+        self.finish()
+        self.accel.free(); self.scene.free(); self.ctx.close()

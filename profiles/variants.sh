@@ -1,34 +1,25 @@
 #!/bin/bash
-# profiles/variants.sh — build the prepared compile-time experiments of csrc/trace.cu HERE (nvcc, no GPU), then run under gpurun:
-#   bash profiles/variants.sh build            # -> gpurun_variants/libclrt_<name>.so (git-ignored, travels to the GPU box)
-#   gpurun -- 'bash profiles/variants.sh run'  # parity tests + short bench per variant through CLRT_LIB_PATH
-# Variants: base (shipped flags), top (CLRT_STACK_TOP_REG=1), ahead (CLRT_PACKET_AHEAD=1), both.
+# profiles/variants.sh — compile-time variants of the traversal kernels (csrc/trace.cu), built HERE (nvcc, no GPU) and measured under gpurun:
+#   bash profiles/variants.sh build name1:"-DCLRT_X=1 -DCLRT_Y=2" name2:...   # -> gpurun_variants/libclrt_<name>.so (git-ignored, travels)
+#   gpurun -- 'bash profiles/variants.sh run [workload ...]'                  # profiles/quick_trace.py per variant through CLRT_LIB_PATH
+#   gpurun -- 'bash profiles/variants.sh test name'                           # the traversal parity tests against one variant
 set -u
 cd "$(dirname "$0")/.."
-declare -A FLAGS=( [base]="" [top]="-DCLRT_STACK_TOP_REG=1" [ahead]="-DCLRT_PACKET_AHEAD=1" [both]="-DCLRT_STACK_TOP_REG=1 -DCLRT_PACKET_AHEAD=1" )
 case "${1:-build}" in
   build)
-    mkdir -p gpurun_variants
-    for v in base top ahead both; do
-      make -s -C openclraytracer_b200/csrc -j8 EXTRA="${FLAGS[$v]}" BUILD=/tmp/clrt_variant_$v OUT=$PWD/gpurun_variants/libclrt_$v.so || exit 1
-      echo "built gpurun_variants/libclrt_$v.so (${FLAGS[$v]:-shipped flags})"
-    done ;;
+    shift; mkdir -p gpurun_variants
+    for spec in "$@"; do
+      v="${spec%%:*}"; flags="${spec#*:}"; [ "$flags" = "$spec" ] && flags=""
+      ( rm -rf /tmp/clrt_variant_$v; mkdir -p /tmp/clrt_variant_$v
+        # only trace.cu depends on the switches: reuse the shipped objects for the rest
+        cp openclraytracer_b200/csrc/build/*.o /tmp/clrt_variant_$v/ 2>/dev/null; rm -f /tmp/clrt_variant_$v/trace.o
+        make -s -C openclraytracer_b200/csrc EXTRA="$flags" BUILD=/tmp/clrt_variant_$v OUT=$PWD/gpurun_variants/libclrt_$v.so && echo "built $v ($flags)" ) &
+    done; wait ;;
   run)
-    mkdir -p gpurun_out
-    for v in base top ahead both; do
-      export CLRT_LIB_PATH=$PWD/gpurun_variants/libclrt_$v.so
-      timeout 300 python -m pytest tests/test_gpu_bvh.py tests/test_gpu_bounce.py -q -x -m gpu -k "not spheres_10m and not full_size" 2>&1 | tail -1 | sed "s/^/[$v] /"
-      for w in soup1m clumsydragon; do
-        timeout 200 python bench.py --workload $w --steps 20 --warmup 5 --no-cpu-baseline --no-kernels 2>/dev/null | tail -1 > gpurun_out/variant_${v}_$w.json
-        python - "$v" "$w" <<'PY'
-import json, sys
-v, w = sys.argv[1:3]
-try:
-    d = json.loads(open("gpurun_out/variant_%s_%s.json" % (v, w)).read())
-    print("[%s] %s: %.0f Mrays/s, %.4f ms/frame; primary %.4f ms, shadow %.4f ms" % (v, w, d["value"], d["ms_per_step"], d["trace_kernels"]["primary"]["ms"], d["trace_kernels"]["shadow"]["ms"]))
-except Exception as e:
-    print("[%s] %s: no line (%s)" % (v, w, e))
-PY
-      done
+    shift; mkdir -p gpurun_out
+    for so in gpurun_variants/libclrt_*.so; do
+      CLRT_LIB_PATH=$PWD/$so timeout 300 python profiles/quick_trace.py "$@" 2>&1 | grep -v "^$" | tail -4
     done ;;
+  test)
+    CLRT_LIB_PATH=$PWD/gpurun_variants/libclrt_$2.so timeout 900 python -m pytest tests/test_gpu_bvh.py tests/test_gpu_bounce.py -q -x -m gpu -k "not spheres_10m" 2>&1 | tail -3 ;;
 esac
