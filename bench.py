@@ -480,9 +480,9 @@ def main():
             launches, pipeline = 5, "one frame at a time on one stream"           # primary, bounce rays, trace, shade, untile (+ NCCL's own kernel at N > 1)
             secondary = "one cosine-weighted diffuse bounce ray per hit through generateContacts(rays, contacts, n)"
         else:
-            # BVH: trace_primary_kernel, shadow_shade_kernel + untile_kernel (nccl) | push, 2 signal, 2 wait (push) | ack wait, exchange (fused)
+            # BVH: frame_kernel + untile_kernel (nccl) | push, 2 signal, 2 wait (push) | ack wait, exchange (fused)
             # GRID: primary, shadow-ray generation, generic trace, shade, untile
-            launches = {"nccl": 3, "push": 7, "fused": 4}[exchange] if args.accel == "BVH" else 5
+            launches = {"nccl": 2, "push": 6, "fused": 3}[exchange] if args.accel == "BVH" else 5
             pipeline = f"{r.DEPTH} frame(s) in flight" + (": frames traced on alternating streams (frame slots)" if r.DEPTH > 1 else "")
             secondary = "1 shadow ray per hit per light (scene light + camera light)"
         line = {

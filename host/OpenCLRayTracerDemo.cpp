@@ -23,11 +23,11 @@ using namespace CLRayTracer::Common;
 using namespace CLRayTracer::OpenCLUtils;
 using namespace CLRayTracer::AccelerationStructures;
 
-enum AccelerationStruct { INVALID = -1, BVH = 0, GRID = 1 };
+enum AccelerationStruct { INVALID = -1, BVH = 0, GRID = 1, KD = 2 };       // KD: ours (the reference's TODO 2.1)
 
 static void printUsage() {
   std::cout << "OpenCLRayTracer demo (headless, CUDA/B200 back end)\nCommand line parameters:\n"
-            << "-winH <Window Height>\n-winW <Window Width>\n-accStruct <Acceleration Structure> - valid values: BVH, GRID\n"
+            << "-winH <Window Height>\n-winW <Window Width>\n-accStruct <Acceleration Structure> - valid values: BVH, GRID (and KD, not in the reference)\n"
             << "-scene <Path to scene file>\n[-headersPath <ignored>] [-script <UDLRadws...>] [-out <ppm prefix>] [-shadows] [-device <n>]\n";
 }
 
@@ -56,7 +56,7 @@ int main(int argc, char* argv[]) {
     const char* next = i + 1 < argc ? argv[i + 1] : NULL;
     if (current == "-winH") window_height = next ? atoi(next) : 0;
     else if (current == "-winW") window_width = next ? atoi(next) : 0;
-    else if (current == "-accStruct" && next) accelerationStructInUse = std::string(next) == "BVH" ? BVH : std::string(next) == "GRID" ? GRID : INVALID;
+    else if (current == "-accStruct" && next) accelerationStructInUse = std::string(next) == "BVH" ? BVH : std::string(next) == "GRID" ? GRID : std::string(next) == "KD" ? KD : INVALID;
     else if (current == "-scene") scenePath = next ? next : "";
     else if (current == "-script") script = next ? next : "";
     else if (current == "-out") outPrefix = next ? next : "";
@@ -66,7 +66,7 @@ int main(int argc, char* argv[]) {
   if (!(window_height > 0 && window_width > 0 && accelerationStructInUse != INVALID && !scenePath.empty())) { printUsage(); return 0; }
   const size_t pixelCount = (size_t)window_width * window_height;
   std::cout << "Configuration parameters:\n    Window width: " << window_width << "\n    Window heigth: " << window_height
-            << "\n    Acceleration struct: " << (accelerationStructInUse == BVH ? "BVH" : "GRID") << "\n    Scene file: " << scenePath << std::endl;
+            << "\n    Acceleration struct: " << (accelerationStructInUse == BVH ? "BVH" : accelerationStructInUse == GRID ? "GRID" : "KD") << "\n    Scene file: " << scenePath << std::endl;
 
   Errata err;
   try {
@@ -111,7 +111,8 @@ int main(int argc, char* argv[]) {
 
     std::shared_ptr<AccelerationStructureManager> accelerationStruct;
     if (accelerationStructInUse == BVH) accelerationStruct.reset(new BVHManager(context, scene));
-    else accelerationStruct.reset(new TwoLevelGridManager(context, scene));
+    else if (accelerationStructInUse == GRID) accelerationStruct.reset(new TwoLevelGridManager(context, scene));
+    else accelerationStruct.reset(new KDTreeManager(context, scene));
     CHECKED_CALL(accelerationStruct->initialize(err));
     CHECKED_CALL(accelerationStruct->initializeFrame(err));
     CHECKED_CALL(accelerationStruct->construct(err));

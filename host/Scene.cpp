@@ -30,6 +30,8 @@
 #include <cstdlib>
 #include <fstream>
 #include <map>
+#include <stdexcept>
+#include <string>
 #include <vector>
 
 namespace {
@@ -432,7 +434,9 @@ Result pack_scene_file(const char* filename_as_given, char*& out, uint64_t& out_
       clrt_mesh_header hdr; memset(&hdr, 0, sizeof(hdr));
       hdr.dataSize = (uint64_t)ni * 2 + (uint64_t)nv * 16 + sizeof(clrt_mesh_header);
       hdr.numberOfVertices = nv; hdr.numberOfIndices = ni; hdr.numberOfTriangles = ni / 3;
-      hdr.materialIndex = (uint64_t)(int64_t)s.material_ids[0];
+      // Scene.cpp:411 reads material_ids[0] unconditionally; a shape whose faces all have fewer than three vertices has none (the
+      // reference reads past an empty vector there): such a sub-mesh gets tinyobj's "no material" id
+      hdr.materialIndex = (uint64_t)(int64_t)(s.material_ids.empty() ? -1 : s.material_ids[0]);
       memcpy(sp, &hdr, sizeof(hdr));                      // sub-mesh blocks are only 2-byte aligned: no typed stores
       modelTris += ni / 3;
       char* vp = sp + sizeof(clrt_mesh_header);
@@ -465,7 +469,13 @@ Result pack_scene_file(const char* filename_as_given, char*& out, uint64_t& out_
 namespace CLRayTracer {
 Common::Result Scene::load(const char* filename, Common::Errata& err) {
   char* buf = NULL; uint64_t size = 0;
-  if (pack_scene_file(filename, buf, size, err) != Common::Success) return Common::Error;
+  // Result + Errata is the interface's error convention: a malformed OBJ (face index outside the vertex list -> std::out_of_range) or
+  // an allocation failure is reported, not thrown through the caller
+  try {
+    if (pack_scene_file(filename, buf, size, err) != Common::Success) return Common::Error;
+  } catch (const std::exception& e) {
+    CLRT_FILL_ERRATA(err, (std::string("Scene::load: ") + e.what()).c_str()); return Common::Error;
+  }
   delete[] _hostSceneData;
   _hostSceneData = buf; _sceneDataSize = size;
   if (_device) { clrt_scene_destroy(_device); _device = NULL; }
@@ -479,7 +489,14 @@ extern "C" const char* clrt_host_last_error(void) { return g_host_error.c_str();
 extern "C" int clrt_host_scene_load(const char* scene_file, void** out_buf, uint64_t* out_bytes) {
   if (!scene_file || !out_buf || !out_bytes) { g_host_error = "clrt_host_scene_load: NULL argument"; return 1; }
   Errata err; char* buf = NULL; uint64_t size = 0;
-  if (pack_scene_file(scene_file, buf, size, err) != CLRayTracer::Common::Success) { g_host_error = err.message(); return 1; }
+  // no C++ exception may cross the C boundary (a face index outside the vertex list throws std::out_of_range, a huge scene bad_alloc)
+  try {
+    if (pack_scene_file(scene_file, buf, size, err) != CLRayTracer::Common::Success) { g_host_error = err.message(); return 1; }
+  } catch (const std::exception& e) {
+    g_host_error = std::string("clrt_host_scene_load: ") + e.what(); return 1;
+  } catch (...) {
+    g_host_error = "clrt_host_scene_load: unknown exception"; return 1;
+  }
   *out_buf = buf; *out_bytes = size;
   return 0;
 }

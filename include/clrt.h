@@ -98,6 +98,20 @@ int      clrt_scene_export_triangles(const clrt_scene* scene, void* h_out /* N*4
  * TwoLevelGridManager  R/Include/Algorithms/TwoLevelGridManager.h:61-178, R/src/CLRayTracerEngine/TwoLevelGridManager.cpp */
 int clrt_bvh_create(clrt_ctx* ctx, const clrt_scene* scene, clrt_accel** out);                  /* ctor + initialize() */
 int clrt_tlg_create(clrt_ctx* ctx, const clrt_scene* scene, float top_density, float leaf_density, clrt_accel** out);
+/* KDTreeManager (ours: the reference's TODO 2.1, /root/reference/KNOWN_ISSUES_AND_TODO.txt:24-26 "Adding KD trees - Construction may be
+ * based on method which is used to construct the BVH"): a third AccelerationStructureManager
+ * (R/Include/Algorithms/AccelerationStructureManager.h:52-78) behind the same handle — clrt_accel_init_frame / _construct,
+ * clrt_trace_primary / clrt_trace_rays, the frame entry points (three-call shadow pipeline).  Built like the LBVH (Morton codes of
+ * the cells a triangle overlaps -> sort -> Karras radix tree over the occupied cells = a kd-tree of median planes); returns the true
+ * closest hit, i.e. the BVH's contacts (openclraytracer_b200/csrc/kd.cu). */
+int clrt_kdtree_create(clrt_ctx* ctx, const clrt_scene* scene, clrt_accel** out);
+/* Inspection: out3 = {levels (2^levels cells per axis), (cell, triangle) pairs, leaves}; out_lo_cs6 = grid origin xyz, cell size xyz. */
+int clrt_kd_info(clrt_accel* accel, uint32_t* out3, float* out_lo_cs6);
+/* setTopLevelDensity / setLeafDensity (R/Include/Algorithms/TwoLevelGridManager.h:112-115): read at the next init_frame, like the
+ * reference's calculateGridData (TwoLevelGridManager.cpp:584-600, called from initializeFrame). */
+int clrt_tlg_set_densities(clrt_accel* accel, float top_density, float leaf_density);
+/* getResolution() (TwoLevelGridManager.h:129, .cpp:566-578): top-level resolution for the current densities; out_xyz[3]. */
+int clrt_tlg_resolution(clrt_accel* accel, uint32_t* out_xyz);
 int clrt_accel_destroy(clrt_accel* accel);
 int clrt_accel_init_frame(clrt_accel* accel);   /* initializeFrame()  BVHManager.cpp:122-150 / TwoLevelGridManager.cpp:160-201 */
 int clrt_accel_construct(clrt_accel* accel);    /* construct()        BVHManager.cpp:156-228 / TwoLevelGridManager.cpp:207-469 */
@@ -113,7 +127,11 @@ void* clrt_accel_primary_contacts_dptr(clrt_accel* accel);     /* getPrimaryCont
 int clrt_trace_primary_stripe(clrt_accel* accel, const clrt_camera* h_camera, uint32_t rank, uint32_t nranks, void* dptr_contacts);
 /* Traversal policy.  FAST (default): near-child-first, t-pruned, persistent-thread kernel — same closest hit,
  * exact ties may pick another triangle.  REFERENCE_ORDER: the reference's A-before-B unpruned order
- * (R/Include/CLData/AccelerationStructs/BVH.h:344-408), bit-exact contacts; the parity vehicle. */
+ * (R/Include/CLData/AccelerationStructs/BVH.h:344-408), bit-exact contacts; the parity vehicle.
+ * On a Two-Level Grid: REFERENCE_ORDER (the grid's default) is the reference's walk literally (tlg_generate_contact,
+ * R/Include/CLData/AccelerationStructs/TwoLevelGrid.h:557-678: entry t = min of the slab entries, the first leaf cell with any hit
+ * ends the walk — its contact is not always the closest hit), bit-exact; FAST is the corrected two-level DDA that
+ * returns the true closest hit, i.e. what the BVH returns (the reference's TODO, KNOWN_ISSUES_AND_TODO.txt:41-43). */
 #define CLRT_TRACE_FAST            0
 #define CLRT_TRACE_REFERENCE_ORDER 1
 int clrt_accel_set_trace_mode(clrt_accel* accel, int mode);
@@ -218,8 +236,9 @@ int clrt_render_stripe(clrt_accel* accel, const clrt_camera* h_camera, int shado
  * a slot and of dptr_rgba8 (stream order / events). */
 int clrt_render_stripe_on(clrt_accel* accel, void* stream, int slot, const clrt_camera* h_camera, int shadows, uint32_t rank,
                           uint32_t nranks, void* dptr_rgba8, uint64_t* out_rays);
-/* The frame entry points fuse the shadow pass with the shading on a BVH (occlusion queries inside one kernel).  on == 0
- * forces the three-call pipeline (clrt_generate_shadow_rays -> clrt_trace_rays -> clrt_shade); pixels are identical. */
+/* The frame entry points run a BVH frame (or stripe) as ONE kernel: primary ray, occlusion queries to the lights, shading
+ * (on == 1, the default with the FAST policy).  on == 2: two kernels (primary contacts, then shadow + shade over them);
+ * on == 0: the three-call pipeline (clrt_generate_shadow_rays -> clrt_trace_rays -> clrt_shade).  Pixels are identical. */
 int clrt_accel_set_fused_shadows(clrt_accel* accel, int on);
 int clrt_frame_untile(clrt_ctx* ctx, const void* dptr_stripes, uint32_t resX, uint32_t resY, uint32_t nranks, void* dptr_raster_rgba8);
 /* The same on a caller-chosen cudaStream_t (the frame pipeline runs gather + untile + read-back of frame k on a second
@@ -247,9 +266,12 @@ int clrt_render_stripe_peers(clrt_accel* accel, void* stream, int slot, const cl
  * (zeroed; ready at [slot*8 + writer], ack at [64 + slot*8 + writer]); seq = 1, 2, ... counts the frames of this slot.  Enqueued
  * on `stream`: wait until every GPU acked frame seq-1 of the slot (its framebuffer may be overwritten) -> trace + shade, pixels
  * to every framebuffer -> ready to all, wait for all -> h_rgba8 ? (copy this GPU's framebuffer to pinned host memory -> ack) : ack.
- * Every GPU of the box must submit the same frames in the same order. */
+ * consumer_stream != NULL: everything from "wait for all" on is enqueued THERE (behind an event of this frame's "ready"), so the
+ * trace stream of the slot never waits for the other GPUs' stripes nor for the read-back; the frame is complete on this GPU when
+ * the consumer stream has passed.  Every GPU of the box must submit the same frames in the same order. */
 int clrt_render_frame_peers(clrt_accel* accel, void* stream, int slot, const clrt_camera* h_camera, uint32_t rank, uint32_t nranks,
-                            void* const* peer_rasters, void* const* peer_words, uint32_t seq, void* h_rgba8, uint64_t* out_rays);
+                            void* const* peer_rasters, void* const* peer_words, uint32_t seq, void* h_rgba8, uint64_t* out_rays,
+                            void* consumer_stream);
 /* This GPU's stripe buffer (as written by clrt_render_stripe[_on]) -> raster position in every peer's framebuffer. */
 int clrt_frame_push(clrt_ctx* ctx, void* stream, const void* dptr_stripe, uint32_t resX, uint32_t resY, uint32_t rank,
                     uint32_t nranks, void* const* peer_rasters);

@@ -101,6 +101,9 @@ typedef clrt_contact Contact;        // CLStructs.h:112-118 (pad[0] additionally
 typedef clrt_ray Ray;                // CLStructs.h:82-87
 typedef clrt_matrix4 Matrix4;
 typedef clrt_float4 CL_FLOAT3;
+typedef float CL_FLOAT;
+struct CL_UINT3 { uint32_t x, y, z, w; };                                  // cl_uint3 occupies 16 bytes
+typedef clrt_aabb AABB;                                                    // Primitives/AABB.h:47-52
 typedef clrt_scene_header SceneHeader;
 struct Quaternion { float r, i, j, k; };                                  // Transform.h:60-70
 
@@ -307,9 +310,14 @@ class AccelerationStructureManager {                                      // Acc
   }
   virtual Common::Result generateContacts(Camera& cam, Common::Errata& err) {
     if (!_accel) { CLRT_FILL_ERRATA(err, "generateContacts: initialize() was not called"); return Common::Error; }
-    CLRT_CALL(clrt_trace_primary(_accel, &cam, NULL), err);
+    // the contacts live in a CLBuffer the manager owns and resizes per frame (BVHManager.cpp:240-244)
+    const size_t bytes = (size_t)cam.resX * cam.resY * sizeof(Contact);
+    try {
+      if (!_primaryContactsArray) _primaryContactsArray.reset(new OpenCLUtils::CLBuffer(_context, bytes ? bytes : sizeof(Contact), OpenCLUtils::CLBufferFlags::ReadWrite));
+      else _primaryContactsArray->resize(bytes);
+    } catch (const Common::CLInterfaceException& e) { err = e; return Common::Error; }
+    CLRT_CALL(clrt_trace_primary(_accel, &cam, _primaryContactsArray->getCLMem()), err);
     CLRT_CALL(clrt_accel_check(_accel), err);              // waits for the queue; fails on a traversal-stack overflow
-    _primary.reset(new ContactsView(_context, clrt_accel_primary_contacts_dptr(_accel), (size_t)cam.resX * cam.resY * sizeof(Contact)));
     return Common::Success;
   }
   virtual Common::Result generateContacts(OpenCLUtils::CLBuffer& rays, OpenCLUtils::CLBuffer& contacts, const unsigned int rayCount, Common::Errata& err) {
@@ -321,18 +329,8 @@ class AccelerationStructureManager {                                      // Acc
     CLRT_CALL(clrt_accel_check(_accel), err);
     return Common::Success;
   }
-  // The primary contacts live in a buffer the manager owns; the view exposes getCLMem / getSize / getActualSize / copyToHost.
-  class ContactsView {
-   public:
-    ContactsView(const OpenCLUtils::CLExecutionContext& c, cl_mem p, size_t bytes) : _c(c), _p(p), _bytes(bytes) {}
-    cl_mem getCLMem() const { return _p; }
-    size_t getSize() const { return _bytes; }
-    size_t getActualSize() const { return _bytes; }
-    Common::Result copyToHost(void* target, Common::Errata& err) const { return _c.enqueueReadBuffer(_p, target, _bytes, err); }
-   private:
-    const OpenCLUtils::CLExecutionContext& _c; cl_mem _p; size_t _bytes;
-  };
-  virtual const std::shared_ptr<ContactsView> getPrimaryContacts() const { return _primary; }
+  // AccelerationStructureManager.h:75, BVHManager.h:108, TwoLevelGridManager.h:120
+  virtual const std::shared_ptr<OpenCLUtils::CLBuffer> getPrimaryContacts() const { return _primaryContactsArray; }
   virtual ~AccelerationStructureManager() { if (_accel) clrt_accel_destroy(_accel); }
 
   // additions (not in the reference): traversal policy, trace tree policy, stage timings
@@ -343,7 +341,7 @@ class AccelerationStructureManager {                                      // Acc
   const OpenCLUtils::CLExecutionContext& _context;
   const Scene& _scene;
   clrt_accel* _accel;
-  std::shared_ptr<ContactsView> _primary;
+  std::shared_ptr<OpenCLUtils::CLBuffer> _primaryContactsArray;
 };
 
 class BVHManager : public AccelerationStructureManager {                   // BVHManager.h:59-126
@@ -367,18 +365,41 @@ class TwoLevelGridManager : public AccelerationStructureManager {          // Tw
     CLRT_CALL(clrt_tlg_create(_context.handle(), _scene.deviceHandle(), _topLevelDensity, _leafDensity, &_accel), err);
     return Common::Success;
   }
-  // densities take effect at the next initialize() (the reference reads them in initializeFrame; both precede construct)
-  void setTopLevelDensity(float d) { _topLevelDensity = d; }
-  void setLeafDensity(float d) { _leafDensity = d; }
-  float getTopLevelDensity() const { return _topLevelDensity; }
-  float getLeafDensity() const { return _leafDensity; }
-  Common::Result getGridData(clrt_grid_data& out, Common::Errata& err) const {        // getResolution / getBounds
+  // Properties (TwoLevelGridManager.h:112-119): plain members; like the reference's, they are read when the grid data is
+  // calculated, i.e. at the next initializeFrame() (TwoLevelGridManager.cpp:160-201 -> calculateGridData :584-600).
+  void setTopLevelDensity(CL_FLOAT value) { _topLevelDensity = value; if (_accel) clrt_tlg_set_densities(_accel, _topLevelDensity, _leafDensity); }
+  void setLeafDensity(CL_FLOAT value) { _leafDensity = value; if (_accel) clrt_tlg_set_densities(_accel, _topLevelDensity, _leafDensity); }
+  CL_FLOAT getTopLevelDensity() const { return _topLevelDensity; }
+  CL_FLOAT getLeafDensity() const { return _leafDensity; }
+  // Utility functions (TwoLevelGridManager.h:129,134; .cpp:566-578,606-609)
+  CL_UINT3 getResolution() const {
+    CL_UINT3 r; r.x = r.y = r.z = r.w = 0;
+    uint32_t v[3] = {0, 0, 0};
+    if (_accel && clrt_tlg_resolution(_accel, v) == 0) { r.x = v[0]; r.y = v[1]; r.z = v[2]; }
+    return r;
+  }
+  AABB getBounds() const { return SCENE_HEADER(_scene.getHostSceneData())->modelsBoundingBox; }
+  // ours: the grid data of the last initializeFrame() as the kernels use it (resolution, steps, box, leaf density)
+  Common::Result getGridData(clrt_grid_data& out, Common::Errata& err) const {
     CLRT_CALL(clrt_tlg_export(_accel, &out, NULL, NULL, NULL, NULL, NULL), err);
     return Common::Success;
   }
 
  private:
   float _topLevelDensity, _leafDensity;
+};
+
+// The reference's TODO 2.1 (KNOWN_ISSUES_AND_TODO.txt:24-26: "Adding KD trees - Construction may be based on method which is used to
+// construct the BVH") as a third manager behind the plug-in interface (AccelerationStructureManager.h:52-78).
+class KDTreeManager : public AccelerationStructureManager {
+ public:
+  KDTreeManager(const OpenCLUtils::CLExecutionContext& context, const Scene& scene) : AccelerationStructureManager(context, scene) {}
+  virtual Common::Result initialize(Common::Errata& err) {
+    if (!_scene.deviceHandle()) { CLRT_FILL_ERRATA(err, "KDTreeManager::initialize: Scene::loadToGPU was not called"); return Common::Error; }
+    if (_accel) { clrt_accel_destroy(_accel); _accel = NULL; }
+    CLRT_CALL(clrt_kdtree_create(_context.handle(), _scene.deviceHandle(), &_accel), err);
+    return Common::Success;
+  }
 };
 
 }  // namespace AccelerationStructures

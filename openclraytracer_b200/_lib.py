@@ -55,6 +55,10 @@ SIGNATURES = {
     "clrt_accel_set_stats": (C.c_int, [C.c_void_p, C.c_int]),
     "clrt_accel_read_stats": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint64)]),
     "clrt_accel_check": (C.c_int, [C.c_void_p]),
+    "clrt_kdtree_create": (C.c_int, [C.c_void_p, C.c_void_p, c_void_pp]),
+    "clrt_kd_info": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint32), C.POINTER(C.c_float)]),
+    "clrt_tlg_set_densities": (C.c_int, [C.c_void_p, C.c_float, C.c_float]),
+    "clrt_tlg_resolution": (C.c_int, [C.c_void_p, C.POINTER(C.c_uint32)]),
     "clrt_bvh_export_nodes": (C.c_int, [C.c_void_p, C.c_void_p]),
     "clrt_bvh_export_pairs": (C.c_int, [C.c_void_p, C.c_void_p]),
     "clrt_tlg_sizes": (C.c_int, [C.c_void_p] + [C.POINTER(C.c_uint32)] * 4),
@@ -80,7 +84,7 @@ SIGNATURES = {
     "clrt_peer_close": (C.c_int, [C.c_void_p, C.c_void_p]),
     "clrt_render_stripe_peers": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_uint32, C.c_uint32, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]),
     "clrt_render_frame_peers": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_uint32, C.c_uint32, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
-                                          C.c_uint32, C.c_void_p, C.POINTER(C.c_uint64)]),
+                                          C.c_uint32, C.c_void_p, C.POINTER(C.c_uint64), C.c_void_p]),
     "clrt_frame_push": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(C.c_void_p)]),
     "clrt_peer_signal": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p), C.c_uint32, C.c_uint32, C.c_uint32]),
     "clrt_peer_wait": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32]),

@@ -361,12 +361,14 @@ class AccelerationStructureManager:
                                                  C.byref(rays) if want_rays else None))
         return rays.value
 
-    def render_frame_peers(self, stream, slot, camera, rank, nranks, peer_rasters, peer_words, seq, h_rgba8=None, want_rays=False):
+    def render_frame_peers(self, stream, slot, camera, rank, nranks, peer_rasters, peer_words, seq, h_rgba8=None, want_rays=False,
+                           consumer_stream=None):
         """The whole per-frame protocol of the fused peer-memory exchange in one call (include/clrt.h)."""
         cam = np.ascontiguousarray(camera, dtype=L.CAMERA)
         rays = C.c_uint64()
         check(self._lib.clrt_render_frame_peers(self.handle, C.c_void_p(stream), slot, _ptr(cam), rank, nranks, peer_rasters, peer_words, seq,
-                                                C.c_void_p(h_rgba8) if h_rgba8 else None, C.byref(rays) if want_rays else None))
+                                                C.c_void_p(h_rgba8) if h_rgba8 else None, C.byref(rays) if want_rays else None,
+                                                C.c_void_p(consumer_stream) if consumer_stream else None))
         return rays.value
 
     def render_frame_host(self, camera, shadows, out_rgba8=None, want_rays=False):
@@ -415,11 +417,20 @@ class TwoLevelGridManager(AccelerationStructureManager):
         super().__init__(context, scene)
         self._top, self._leaf = float(topLevelDensity), float(leafDensity)
 
-    def setTopLevelDensity(self, v):
+    def setTopLevelDensity(self, v):                 # read at the next initializeFrame(), like the reference's calculateGridData
         self._top = float(v)
+        if self.handle:
+            check(self._lib.clrt_tlg_set_densities(self.handle, self._top, self._leaf))
 
     def setLeafDensity(self, v):
         self._leaf = float(v)
+        if self.handle:
+            check(self._lib.clrt_tlg_set_densities(self.handle, self._top, self._leaf))
+
+    def getResolution(self):                         # TwoLevelGridManager.h:129
+        v = (C.c_uint32 * 3)()
+        check(self._lib.clrt_tlg_resolution(self.handle, v))
+        return tuple(v)
 
     def getTopLevelDensity(self):
         return self._top
@@ -448,6 +459,21 @@ class TwoLevelGridManager(AccelerationStructureManager):
         lpairs = np.zeros(leaf_pairs, dtype=L.UINT2)
         check(self._lib.clrt_tlg_export(self.handle, _ptr(grid), _ptr(cells), _ptr(top_ranges), _ptr(tpairs), _ptr(leaf_ranges), _ptr(lpairs)))
         return dict(grid=grid, top_cells=cells, top_ranges=top_ranges, top_pairs=tpairs, leaf_ranges=leaf_ranges, leaf_pairs=lpairs)
+
+
+class KDTreeManager(AccelerationStructureManager):
+    """The reference's TODO 2.1 (KNOWN_ISSUES_AND_TODO.txt:24-26) as a third AccelerationStructureManager (csrc/kd.cu)."""
+
+    def initialize(self):
+        h = C.c_void_p()
+        check(self._lib.clrt_kdtree_create(self.context.handle, self.scene.handle, C.byref(h)))
+        self.handle = h
+        self.context._adopt(self)
+
+    def info(self):
+        v = (C.c_uint32 * 3)(); f = (C.c_float * 6)()
+        check(self._lib.clrt_kd_info(self.handle, v, f))
+        return dict(levels=v[0], pairs=v[1], leaves=v[2], origin=tuple(f[:3]), cell=tuple(f[3:]))
 
 
 def generate_primary_rays(context, camera, dptr_rays):

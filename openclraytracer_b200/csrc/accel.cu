@@ -11,6 +11,7 @@ int shade_launch(clrt_ctx* ctx, const clrt_scene* scene, const clrt_camera& cam,
 
 int bvh_shadow_shade(clrt_accel* a, const clrt_camera& cam, const clrt_contact* contacts, uint32_t count, uint32_t* rgba8,
                      unsigned long long* d_ray_counter);
+int bvh_frame_fused(clrt_accel* a, const clrt_camera& cam, uint32_t rank, uint32_t nranks, uint32_t* rgba8, unsigned long long* d_ray_counter);
 
 static int accel_create(clrt_ctx* ctx, const clrt_scene* scene, AccelKind kind, clrt_accel** out) {
   if (!ctx || !scene || !out) CLRT_FAIL("accel create: NULL argument");
@@ -34,7 +35,13 @@ extern "C" int clrt_tlg_create(clrt_ctx* ctx, const clrt_scene* scene, float top
   if (!(top_density > 0.0f) || !(leaf_density > 0.0f)) CLRT_FAIL("clrt_tlg_create: densities must be positive");
   CLRT_TRY(accel_create(ctx, scene, ACCEL_TLG, out));
   (*out)->top_density = top_density; (*out)->leaf_density = leaf_density;
+  (*out)->trace_mode = CLRT_TRACE_REFERENCE_ORDER;            // a grid answers like the reference's walk unless asked for the corrected one
   return 0;
+}
+
+// KDTreeManager (ours; the reference's TODO 2.1, KNOWN_ISSUES_AND_TODO.txt:24-26): a third AccelerationStructureManager, kd.cu
+extern "C" int clrt_kdtree_create(clrt_ctx* ctx, const clrt_scene* scene, clrt_accel** out) {
+  return accel_create(ctx, scene, ACCEL_KD, out);
 }
 
 extern "C" int clrt_accel_destroy(clrt_accel* a) {
@@ -42,6 +49,7 @@ extern "C" int clrt_accel_destroy(clrt_accel* a) {
   cudaSetDevice(a->ctx->device);
   cudaStreamSynchronize(a->ctx->stream);
   if (a->kind == ACCEL_TLG) tlg_destroy(a);
+  if (a->kind == ACCEL_KD) kd_destroy(a);
   if (a->d_nodes) cudaFree(a->d_nodes);
   if (a->d_pairs) cudaFree(a->d_pairs);
   if (a->d_counters) cudaFree(a->d_counters);
@@ -56,6 +64,7 @@ extern "C" int clrt_accel_destroy(clrt_accel* a) {
   if (a->d_slot_counters) cudaFree(a->d_slot_counters);
   for (int i = 0; i < clrt_accel::FRAME_SLOTS; i++) if (a->d_slot_scratch[i]) cudaFree(a->d_slot_scratch[i]);
   for (int i = 0; i <= CLRT_STAGE_COUNT; i++) if (a->ev[i]) cudaEventDestroy(a->ev[i]);
+  for (int i = 0; i < clrt_accel::FRAME_SLOTS; i++) if (a->slot_event[i]) cudaEventDestroy(a->slot_event[i]);
   delete a;
   return 0;
 }
@@ -63,12 +72,12 @@ extern "C" int clrt_accel_destroy(clrt_accel* a) {
 extern "C" int clrt_accel_init_frame(clrt_accel* a) {
   if (!a) CLRT_FAIL("clrt_accel_init_frame: NULL accel");
   CLRT_CUDA(cudaSetDevice(a->ctx->device));
-  return a->kind == ACCEL_BVH ? bvh_init_frame(a) : tlg_init_frame(a);
+  return a->kind == ACCEL_BVH ? bvh_init_frame(a) : a->kind == ACCEL_TLG ? tlg_init_frame(a) : kd_init_frame(a);
 }
 extern "C" int clrt_accel_construct(clrt_accel* a) {
   if (!a) CLRT_FAIL("clrt_accel_construct: NULL accel");
   CLRT_CUDA(cudaSetDevice(a->ctx->device));
-  return a->kind == ACCEL_BVH ? bvh_construct(a) : tlg_construct(a);
+  return a->kind == ACCEL_BVH ? bvh_construct(a) : a->kind == ACCEL_TLG ? tlg_construct(a) : kd_construct(a);
 }
 extern "C" int clrt_accel_set_trace_mode(clrt_accel* a, int mode) {
   if (!a) CLRT_FAIL("clrt_accel_set_trace_mode: NULL accel");
@@ -77,7 +86,8 @@ extern "C" int clrt_accel_set_trace_mode(clrt_accel* a, int mode) {
 }
 extern "C" int clrt_accel_set_fused_shadows(clrt_accel* a, int on) {
   if (!a) CLRT_FAIL("clrt_accel_set_fused_shadows: NULL accel");
-  a->unfused_shadows = on == 0; return 0;
+  // 0: three kernels (primary, generic shadow rays, shade); 1: the default — one frame kernel; 2: two kernels (primary, shadow + shade)
+  a->unfused_shadows = on == 0; a->two_kernel_frame = on == 2; return 0;
 }
 extern "C" int clrt_accel_enable_stage_timing(clrt_accel* a, int on) {
   if (!a) CLRT_FAIL("clrt_accel_enable_stage_timing: NULL accel");
@@ -112,6 +122,9 @@ static int ensure_contacts(clrt_accel* a, size_t count) {
 }
 
 int accel_trace_primary(clrt_accel* a, const clrt_camera& cam, clrt_contact* out, uint32_t rank, uint32_t nranks);
+static int accel_trace_rays(clrt_accel* a, const clrt_ray* rays, clrt_contact* out, uint32_t count) {
+  return a->kind == ACCEL_BVH ? bvh_trace_rays(a, rays, out, count) : a->kind == ACCEL_TLG ? tlg_trace_rays(a, rays, out, count) : kd_trace_rays(a, rays, out, count);
+}
 
 extern "C" int clrt_trace_primary(clrt_accel* a, const clrt_camera* h_camera, void* dptr_contacts) {
   if (!a || !h_camera) CLRT_FAIL("clrt_trace_primary: NULL argument");
@@ -140,8 +153,7 @@ extern "C" int clrt_trace_rays(clrt_accel* a, const void* dptr_rays, void* dptr_
   if (!a || (ray_count && (!dptr_rays || !dptr_contacts))) CLRT_FAIL("clrt_trace_rays: NULL argument");
   if (((uintptr_t)dptr_rays & 15) || ((uintptr_t)dptr_contacts & 15)) CLRT_FAIL("clrt_trace_rays: buffers must be 16-byte aligned");
   CLRT_CUDA(cudaSetDevice(a->ctx->device));
-  return a->kind == ACCEL_BVH ? bvh_trace_rays(a, (const clrt_ray*)dptr_rays, (clrt_contact*)dptr_contacts, ray_count)
-                              : tlg_trace_rays(a, (const clrt_ray*)dptr_rays, (clrt_contact*)dptr_contacts, ray_count);
+  return accel_trace_rays(a, (const clrt_ray*)dptr_rays, (clrt_contact*)dptr_contacts, ray_count);
 }
 
 // Shadow pass fused with the shading over an arbitrary contact buffer (BVH only).
@@ -203,7 +215,13 @@ static int render_stripe_impl(clrt_accel* a, const clrt_camera* h_camera, int sh
   clrt_ray* srays = (clrt_ray*)(base + contacts_bytes);
   clrt_contact* scont = (clrt_contact*)(base + contacts_bytes + srays_bytes);
   unsigned long long* counter = (unsigned long long*)(base + contacts_bytes + srays_bytes + scont_bytes);
-  if (slots) {
+  // One launch for the whole stripe (primary + shadow + shading) when the fused shadow pass applies and the FAST policy is on;
+  // REFERENCE_ORDER keeps its own primary kernel (the parity vehicle) followed by the shadow + shade kernel.
+  const bool one_kernel = fused && a->trace_mode == CLRT_TRACE_FAST && !a->two_kernel_frame;
+  if (slots && one_kernel) {
+    if (out_rays) CLRT_CUDA(cudaMemsetAsync(counter, 0, 8, stream));
+    CLRT_TRY(bvh_frame_fused(a, cam, rank, nranks, (uint32_t*)dptr_rgba8, out_rays ? counter : nullptr));
+  } else if (slots) {
     CLRT_TRY(accel_trace_primary(a, cam, contacts, rank, nranks));
     if (fused) {
       CLRT_CUDA(cudaMemsetAsync(counter, 0, 8, stream));
@@ -211,7 +229,7 @@ static int render_stripe_impl(clrt_accel* a, const clrt_camera* h_camera, int sh
     } else if (shadows) {
       CLRT_CUDA(cudaMemsetAsync(counter, 0, 8, ctx->stream));
       CLRT_TRY(shade_launch_shadow_rays(ctx, a->scene, cam, contacts, slots, srays, out_rays ? counter : nullptr));
-      CLRT_TRY(a->kind == ACCEL_BVH ? bvh_trace_rays(a, srays, scont, slots * L1) : tlg_trace_rays(a, srays, scont, slots * L1));
+      CLRT_TRY(accel_trace_rays(a, srays, scont, slots * L1));
     }
     if (!fused && shadows && slot >= 0) CLRT_FAIL("clrt_render_stripe_on: frame slots need the fused shadow pass");
     if (!fused) CLRT_TRY(shade_launch(ctx, a->scene, cam, contacts, slots, shadows ? scont : nullptr, (uint32_t*)dptr_rgba8, nullptr, stream));
@@ -272,11 +290,12 @@ int peer_launch_signal(cudaStream_t stream, const PeerTargets& flags, uint32_t w
 // writer]; seq = 1, 2, ... per slot.  Enqueues on `stream`: wait until every GPU acked seq-1 of this slot (its framebuffer is
 // free) -> trace + shade with the pixels going to every framebuffer -> ready to all, wait for all -> (copy to host ->) ack to all.
 extern "C" int clrt_render_frame_peers(clrt_accel* a, void* stream_, int slot, const clrt_camera* h_camera, uint32_t rank, uint32_t nranks,
-                                       void* const* peer_rasters, void* const* peer_words, uint32_t seq, void* h_rgba8, uint64_t* out_rays) {
+                                       void* const* peer_rasters, void* const* peer_words, uint32_t seq, void* h_rgba8, uint64_t* out_rays,
+                                       void* consumer_stream_) {
   if (!a || !h_camera || !peer_rasters || !peer_words || !nranks || nranks > 8 || rank >= nranks || !seq)
     CLRT_FAIL("clrt_render_frame_peers: bad argument");
   if (slot < 0 || slot >= clrt_accel::FRAME_SLOTS) CLRT_FAIL("clrt_render_frame_peers: slot %d of %d", slot, clrt_accel::FRAME_SLOTS);
-  cudaStream_t stream = (cudaStream_t)stream_;
+  cudaStream_t stream = (cudaStream_t)stream_, consumer = (cudaStream_t)consumer_stream_;
   PeerTargets flags; flags.n = nranks;
   for (uint32_t i = 0; i < 8; i++) flags.p[i] = i < nranks ? (uint32_t*)peer_words[i] : nullptr;
   for (uint32_t i = 0; i < nranks; i++) if (!flags.p[i]) CLRT_FAIL("clrt_render_frame_peers: peer %u is NULL", i);
@@ -285,11 +304,25 @@ extern "C" int clrt_render_frame_peers(clrt_accel* a, void* stream_, int slot, c
   const uint32_t ready = (uint32_t)slot * 8u, ack = 64u + (uint32_t)slot * 8u;
   if (seq > 1) CLRT_TRY(peer_launch_wait(stream, own + ack, nranks, seq - 1));
   CLRT_TRY(clrt_render_stripe_peers(a, stream_, slot, h_camera, rank, nranks, peer_rasters, out_rays));
-  CLRT_TRY(peer_launch_exchange(stream, flags, own, ready, h_rgba8 ? ~0u : ack, rank, seq));
-  if (h_rgba8) {
-    CLRT_CUDA(cudaMemcpyAsync(h_rgba8, peer_rasters[rank], (size_t)h_camera->resX * h_camera->resY * 4, cudaMemcpyDeviceToHost, stream));
-    CLRT_TRY(peer_launch_signal(stream, flags, ack + rank, seq));
+  const size_t bytes = (size_t)h_camera->resX * h_camera->resY * 4;
+  if (!consumer) {
+    CLRT_TRY(peer_launch_exchange(stream, flags, own, ready, h_rgba8 ? ~0u : ack, rank, seq));
+    if (h_rgba8) {
+      CLRT_CUDA(cudaMemcpyAsync(h_rgba8, peer_rasters[rank], bytes, cudaMemcpyDeviceToHost, stream));
+      CLRT_TRY(peer_launch_signal(stream, flags, ack + rank, seq));
+    }
+    return 0;
   }
+  // Trace stream: ready to all, nothing else — it goes on with the slot's next frame as soon as the acks of this one arrive.
+  // Consumer stream: behind OUR ready (an event, so that its spinning wait can never sit in front of the kernels it waits for when
+  // streams share a hardware queue), wait for everybody's ready -> read-back -> ack to all.
+  CLRT_TRY(peer_launch_signal(stream, flags, ready + rank, seq));
+  if (!a->slot_event[slot]) CLRT_CUDA(cudaEventCreateWithFlags(&a->slot_event[slot], cudaEventDisableTiming));
+  CLRT_CUDA(cudaEventRecord(a->slot_event[slot], stream));
+  CLRT_CUDA(cudaStreamWaitEvent(consumer, a->slot_event[slot], 0));
+  CLRT_TRY(peer_launch_wait(consumer, own + ready, nranks, seq));
+  if (h_rgba8) CLRT_CUDA(cudaMemcpyAsync(h_rgba8, peer_rasters[rank], bytes, cudaMemcpyDeviceToHost, consumer));
+  CLRT_TRY(peer_launch_signal(consumer, flags, ack + rank, seq));
   return 0;
 }
 
@@ -345,5 +378,6 @@ extern "C" int clrt_render_frame_host(clrt_accel* a, const clrt_camera* h_camera
 int accel_trace_primary(clrt_accel* a, const clrt_camera& cam, clrt_contact* out, uint32_t rank, uint32_t nranks) {
   // The camera travels to the kernels BY VALUE (64 bytes in the constant bank); the reference allocates and uploads a
   // CLBuffer per frame for it (BVHManager.cpp:237).
-  return a->kind == ACCEL_BVH ? bvh_trace_primary(a, cam, out, rank, nranks) : tlg_trace_primary(a, cam, out, rank, nranks);
+  return a->kind == ACCEL_BVH ? bvh_trace_primary(a, cam, out, rank, nranks)
+       : a->kind == ACCEL_TLG ? tlg_trace_primary(a, cam, out, rank, nranks) : kd_trace_primary(a, cam, out, rank, nranks);
 }

@@ -27,8 +27,8 @@ struct clrt_ctx {
   void* scratch = nullptr; size_t scratch_bytes = 0;
   void* sort_alt = nullptr; size_t sort_alt_bytes = 0;
   void* pinned = nullptr; size_t pinned_bytes = 0;     // staging for small host<->device transfers
-  // look-back state of the scan (scan.cu): never reset between calls — descriptors carry a generation, tickets run on
-  void* scan_state = nullptr; size_t scan_state_bytes = 0; uint32_t scan_gen = 0, scan_tickets = 0;
+  // look-back state of the scan (scan.cu): never reset between calls — descriptors carry a generation
+  void* scan_state = nullptr; size_t scan_state_bytes = 0; uint32_t scan_gen = 0;
 };
 int clrt_ctx_scratch(clrt_ctx* ctx, size_t bytes, void** out);      // grow-only device scratch
 int clrt_ctx_sort_alt(clrt_ctx* ctx, size_t bytes, void** out);     // ping-pong buffer of the radix sort
@@ -75,11 +75,34 @@ struct __align__(16) TraceNode {
 // 128-byte 4-wide traversal node (FAST policy): the 2-level collapse of a binary TraceNode tree, written by widen_kernel
 // (trace_tree.cu).  Wide node i stands for binary inner node i; only the nodes reachable from the root through wide links
 // are ever visited.  child < N: leaf (position in the tree-ordered triangle array); >= N: N + inner index; 0xFFFFFFFF: empty.
+#ifndef CLRT_WIDE_Q16
+#define CLRT_WIDE_Q16 1
+#endif
+#if CLRT_WIDE_Q16
+// 64-byte variant: the four child boxes as 16-bit fixed point on ONE grid for the whole structure (QFrame below: bound = lo + q * step
+// per axis; lo bounds rounded down, hi bounds up, checked against their decoding, so the stored box contains the exact one).  Halves
+// of word w of every q array belong to children 2w (low) and 2w+1 (high).  An empty slot holds an inverted box (qlo = 65535, qhi = 0).
+// Why: the traversal kernels are bound by the L1 data pipe (ncu r02a: l1tex__data_pipe_lsu_wavefronts at 82 % of peak) — every lane
+// fetches its own node, so each 16-byte load instruction costs one wavefront per active lane: 7 per visit with the 128-byte node,
+// 4 with this one.  The grid is per structure, not per node, so decoding needs no per-node set-up: (bound - origin) / d =
+// A + q * B with A = (lo - origin) / d and B = step / d computed once per RAY (trace.cu: lane_begin).
+struct __align__(16) WideNode {
+  uint32_t qlx[2], qly[2];
+  uint32_t qlz[2], qhx[2];
+  uint32_t qhy[2], qhz[2];
+  uint32_t child[4];
+};
+static_assert(sizeof(WideNode) == 64, "WideNode layout");
+#else
 struct __align__(16) WideNode {
   float lox[4], loy[4], loz[4], hix[4], hiy[4], hiz[4];
   uint32_t child[4];
   uint32_t pad[4];
 };
+#endif
+// Quantisation grid of the 64-byte nodes, written by wide_frame_kernel behind the top table (record n + WIDE_TOP_NODES): the box of
+// the structure's root, slightly enlarged, divided into 65535 steps per axis.
+struct __align__(16) QFrame { float lox, loy, loz, pad0, stepx, stepy, stepz, pad1; };
 
 // Top table of the wide tree (trace_tree.cu: wide_top_kernel): WIDE_TOP_LEVELS levels in breadth-first order, stored behind the n
 // per-node records (index n + slot).  A child id with WIDE_TOP_BIT set is a slot of that table.  n < 2^30, so inner ids stay below 2^31.
@@ -91,7 +114,7 @@ struct __align__(16) WideNode {
 // GPU of the box (the local one included), that the shading kernel writes its pixels into directly over NVLink.
 struct PeerTargets { uint32_t* p[8]; uint32_t n; };
 
-enum AccelKind { ACCEL_BVH = 0, ACCEL_TLG = 1 };
+enum AccelKind { ACCEL_BVH = 0, ACCEL_TLG = 1, ACCEL_KD = 2 };
 
 struct clrt_accel {
   AccelKind kind = ACCEL_BVH;
@@ -100,6 +123,7 @@ struct clrt_accel {
   int trace_mode = CLRT_TRACE_FAST;
   bool timing = false;
   bool unfused_shadows = false;     // frame entry points: force the three-kernel shadow pipeline (parity checks)
+  bool two_kernel_frame = false;    // frame entry points: primary kernel + shadow/shade kernel instead of the one frame kernel
   bool stats = false;               // traversal statistics mode (rays, inner visits, triangle tests)
   float stage_ms[CLRT_STAGE_COUNT] = {0};
   cudaEvent_t ev[CLRT_STAGE_COUNT + 1] = {nullptr};
@@ -132,12 +156,15 @@ struct clrt_accel {
   static constexpr int FRAME_SLOTS = 8;
   void* d_slot_scratch[FRAME_SLOTS] = {nullptr}; size_t slot_scratch_cap[FRAME_SLOTS] = {0};
   uint32_t* d_slot_counters = nullptr;            // FRAME_SLOTS x 64 B
+  cudaEvent_t slot_event[FRAME_SLOTS] = {nullptr}; // "this GPU's stripe of the slot's frame is stored everywhere" (clrt_render_frame_peers)
   int slots_seen = 0;                             // highest frame slot used so far + 1 = the caller's frames in flight (grid sizing)
   cudaStream_t launch_stream = nullptr;           // set only while a slot's launches are being enqueued
   PeerTargets launch_targets = {{nullptr}, 0};     // ditto: peer framebuffers of a p2p frame (n == 0: write the local stripe buffer)
   uint32_t* launch_counter = nullptr;
   // --- TLG --- (tlg.cu)
   struct TlgState* tlg = nullptr;
+  // --- KD-tree --- (kd.cu)
+  struct KdState* kd = nullptr;
   float top_density = 2.0f, leaf_density = 2.0f;
 };
 
@@ -155,6 +182,11 @@ int tlg_construct(clrt_accel* a);
 int tlg_trace_primary(clrt_accel* a, const clrt_camera& cam, clrt_contact* out, uint32_t rank, uint32_t nranks);
 int tlg_trace_rays(clrt_accel* a, const clrt_ray* rays, clrt_contact* out, uint32_t n);
 void tlg_destroy(clrt_accel* a);
+int kd_init_frame(clrt_accel* a);
+int kd_construct(clrt_accel* a);
+int kd_trace_primary(clrt_accel* a, const clrt_camera& cam, clrt_contact* out, uint32_t rank, uint32_t nranks);
+int kd_trace_rays(clrt_accel* a, const clrt_ray* rays, clrt_contact* out, uint32_t n);
+void kd_destroy(clrt_accel* a);
 int sort_pairs_radix(clrt_ctx* ctx, clrt_uint2* pairs, size_t n, int key_bits);
 int scan_inclusive(clrt_ctx* ctx, const uint32_t* in, uint32_t* out, size_t n);
 

@@ -44,7 +44,14 @@ radix_histogram_kernel(const uint2* __restrict__ pairs, uint32_t n, uint32_t* __
   for (int i = threadIdx.x; i < passes * BINS; i += HIST_THREADS) s_hist[i] = 0;
   __syncthreads();
   const size_t stride = (size_t)gridDim.x * HIST_THREADS;
-  // two pairs (16 B) per load where possible
+  // two pairs (16 B) per load where possible; a buffer that is only 8-byte aligned (a slice at an odd pair offset) gives its first
+  // pair to thread 0 of CTA 0 and is read as 16-byte vectors from the second one
+  const uint32_t head = (uint32_t)(((uintptr_t)pairs >> 3) & 1u) & (n ? 1u : 0u);
+  if (head && blockIdx.x == 0 && threadIdx.x == 0) {
+    const uint32_t k = pairs[0].x;
+    for (int p = 0; p < passes; p++) atomicAdd(&s_hist[p * BINS + ((k >> (p * RADIX_BITS)) & (BINS - 1))], 1u);
+  }
+  pairs += head; n -= head;
   const size_t n2 = n / 2;
   const uint4* p4 = reinterpret_cast<const uint4*>(pairs);
   for (size_t i = blockIdx.x * (size_t)HIST_THREADS + threadIdx.x; i < n2; i += stride) {

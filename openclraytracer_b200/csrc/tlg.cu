@@ -263,7 +263,7 @@ __device__ __forceinline__ bool aabb_triangle_intersect(Vec3 boxcenter, Vec3 h, 
 __global__ void __launch_bounds__(128)
 tlg_scatter_leaf_kernel(const clrt_triangle* __restrict__ tris, const uint2* __restrict__ top_pairs, uint32_t pairs,
                         const clrt_grid_data g, const clrt_top_cell* __restrict__ top, const uint32_t* __restrict__ scan,
-                        const uint32_t* __restrict__ counters, uint32_t cap, uint2* __restrict__ leaf_pairs) {
+                        const uint32_t* __restrict__ counters, uint32_t cap, uint2* __restrict__ leaf_pairs, uint32_t* __restrict__ over_budget) {
   const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
   if (p >= pairs) return;
   const uint32_t budget = counters[p];
@@ -281,7 +281,11 @@ tlg_scatter_leaf_kernel(const clrt_triangle* __restrict__ tris, const uint2* __r
       for (uint32_t x = f.x0; x <= f.x1; x++) {
         const Vec3 centre = v3(f.baseX + (float)x * f.stepX + half.x, f.baseY + (float)y * f.stepY + half.y, f.baseZ + (float)z * f.stepZ + half.z);
         if (aabb_triangle_intersect(centre, half, v0, v1, v2)) {
-          if (at + written < cap) leaf_pairs[at + written] = make_uint2(z * cell.x * cell.y + y * cell.x + x + cell.w, pr.y);
+          // The budget comes from the conservative box count (tlg_count_leaf_kernel), the writes from the exact test: should rounding
+          // ever let the exact test accept a cell the count did not see, the pair must not land in the next top pair's region (the
+          // reference has the same hole, TwoLevelGrid.h:330-365, and races there).  It is dropped and COUNTED: construct() fails.
+          if (written < budget && at + written < cap) leaf_pairs[at + written] = make_uint2(z * cell.x * cell.y + y * cell.x + x + cell.w, pr.y);
+          else atomicAdd(over_budget, 1u);
           written++;
         }
       }
@@ -370,6 +374,83 @@ __device__ __forceinline__ GridHit tlg_traverse(Vec3 o, Vec3 d, const clrt_grid_
   return none;
 }
 
+// ---- corrected walk (ours; SURVEY.md section 8 f4, KNOWN_ISSUES Q21) --------------------------------------------------------------
+// The literal walk above enters the grid at t0 = MIN of the slab entries and lets the first leaf cell with any hit end the walk, even
+// when that hit lies in a later cell: its contact can differ from the closest hit.  This one is a plain two-level 3D-DDA: entry =
+// MAX of the slab entries (clamped to 0), cells visited in ray order, the closest hit so far is kept across cells and the walk ends
+// when it lies inside the cell just finished — the true closest hit, the one the BVH returns.  Selected by CLRT_TRACE_FAST on a grid.
+struct Walk { float tx, ty, tz, dx, dy, dz; int ix, iy, iz, sx, sy, sz, ex, ey, ez; };
+__device__ __forceinline__ void walk_axis(float o, float d, float inv, float b0, float cs, int r, float p, float& tnext, float& dt, int& i, int& step, int& end) {
+  i = (int)floorf((p - b0) / cs);
+  i = i < 0 ? 0 : (i > r - 1 ? r - 1 : i);
+  if (d > 0.0f) { tnext = (b0 + (float)(i + 1) * cs - o) * inv; dt = cs * inv; step = 1; end = r; }
+  else if (d < 0.0f) { tnext = (b0 + (float)i * cs - o) * inv; dt = -cs * inv; step = -1; end = -1; }
+  else { tnext = RT_FLT_MAX; dt = 0.0f; step = 1; end = r; }
+}
+__device__ __forceinline__ void walk_setup(Walk& w, Vec3 o, Vec3 d, Vec3 inv, float b0x, float b0y, float b0z, float csx, float csy, float csz,
+                                           int rx, int ry, int rz, float t_in) {
+  walk_axis(o.x, d.x, inv.x, b0x, csx, rx, o.x + d.x * t_in, w.tx, w.dx, w.ix, w.sx, w.ex);
+  walk_axis(o.y, d.y, inv.y, b0y, csy, ry, o.y + d.y * t_in, w.ty, w.dy, w.iy, w.sy, w.ey);
+  walk_axis(o.z, d.z, inv.z, b0z, csz, rz, o.z + d.z * t_in, w.tz, w.dz, w.iz, w.sz, w.ez);
+}
+// leaves the cell through its nearest face; false when that leaves the grid
+__device__ __forceinline__ bool walk_step(Walk& w) {
+  if (w.tx <= w.ty && w.tx <= w.tz) { w.tx += w.dx; w.ix += w.sx; return w.ix != w.ex; }
+  if (w.ty <= w.tz) { w.ty += w.dy; w.iy += w.sy; return w.iy != w.ey; }
+  w.tz += w.dz; w.iz += w.sz; return w.iz != w.ez;
+}
+__device__ __forceinline__ GridHit tlg_traverse_closest(Vec3 o, Vec3 d, const clrt_grid_data& g, const clrt_top_cell* __restrict__ top,
+                                                        const uint2* __restrict__ leaf_ranges, const uint2* __restrict__ leaf_pairs,
+                                                        const clrt_triangle* __restrict__ tris) {
+  GridHit best; best.t = RT_FLT_MAX; best.tri = 0xFFFFFFFFu;
+  GridHit none; none.t = 0.0f; none.tri = 0xFFFFFFFFu;
+  const float big = 1.0e30f;
+  const Vec3 inv = v3(d.x == 0.0f ? copysignf(big, d.x) : 1.0f / d.x, d.y == 0.0f ? copysignf(big, d.y) : 1.0f / d.y, d.z == 0.0f ? copysignf(big, d.z) : 1.0f / d.z);
+  const float b0x = g.box.bounds[0].x, b0y = g.box.bounds[0].y, b0z = g.box.bounds[0].z;
+  float t_in;
+  {
+    const float ax = (b0x - o.x) * inv.x, bx = (g.box.bounds[1].x - o.x) * inv.x;
+    const float ay = (b0y - o.y) * inv.y, by = (g.box.bounds[1].y - o.y) * inv.y;
+    const float az = (b0z - o.z) * inv.z, bz = (g.box.bounds[1].z - o.z) * inv.z;
+    const float tn = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fminf(az, bz)), tf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fmaxf(az, bz));
+    if (!(tn <= tf) || tf < 0.0f) return none;
+    t_in = fmaxf(tn, 0.0f);
+  }
+  const float slack = 1.00001f;
+  Walk T;
+  walk_setup(T, o, d, inv, b0x, b0y, b0z, g.stepX, g.stepY, g.stepZ, (int)g.resX, (int)g.resY, (int)g.resZ, t_in);
+  float t_cur = t_in;
+  const uint32_t top_cap = g.resX + g.resY + g.resZ + 3u;
+  for (uint32_t it = 0; it < top_cap; it++) {
+    const uint4 cell = __ldg(reinterpret_cast<const uint4*>(top) + ((uint32_t)T.iz * g.resX * g.resY + (uint32_t)T.iy * g.resX + (uint32_t)T.ix));
+    const float t_exit = fminf(T.tx, fminf(T.ty, T.tz));
+    if (!(cell.x == 0 || cell.y == 0 || cell.z == 0)) {
+      const float c0x = b0x + (float)T.ix * g.stepX, c0y = b0y + (float)T.iy * g.stepY, c0z = b0z + (float)T.iz * g.stepZ;
+      Walk Lf;
+      walk_setup(Lf, o, d, inv, c0x, c0y, c0z, g.stepX / (float)cell.x, g.stepY / (float)cell.y, g.stepZ / (float)cell.z,
+                 (int)cell.x, (int)cell.y, (int)cell.z, t_cur);
+      const uint32_t leaf_cap = cell.x + cell.y + cell.z + 3u;
+      for (uint32_t lit = 0; lit < leaf_cap; lit++) {
+        const uint32_t leaf = (uint32_t)Lf.iz * cell.x * cell.y + (uint32_t)Lf.iy * cell.x + (uint32_t)Lf.ix + cell.w;
+        const uint2 range = __ldg(leaf_ranges + leaf);
+        for (uint32_t k = range.x; k < range.y; k++) {
+          const uint32_t id = __ldg(&leaf_pairs[k].y);
+          Vec3 a, b, c; load_tri(tris, id, a, b, c);
+          const float t = triangle_intersect(a, b, c, o, d);
+          if (t > 0.0f && (t < best.t || (t == best.t && id < best.tri))) { best.t = t; best.tri = id; }
+        }
+        const float l_exit = fminf(Lf.tx, fminf(Lf.ty, Lf.tz));
+        if (best.t <= l_exit * slack) return best;            // the closest hit lies in a cell already finished
+        if (l_exit >= t_exit || !walk_step(Lf)) break;        // the ray left the top cell
+      }
+    }
+    if (best.t <= t_exit * slack) return best;
+    t_cur = t_exit;
+    if (!walk_step(T)) break;
+  }
+  return best.tri != 0xFFFFFFFFu ? best : none;
+}
+
 __device__ __forceinline__ void tlg_write_contact(clrt_contact* __restrict__ out, uint32_t slot, uint32_t pixelIndex, const GridHit& h,
                                                   const clrt_triangle* __restrict__ tris) {
   uint4 head = make_uint4(pixelIndex, 0u, 0xFFFFFFFFu, 0u);
@@ -390,6 +471,7 @@ __device__ __forceinline__ void tlg_write_contact(clrt_contact* __restrict__ out
 constexpr int TLG_TRACE_THREADS = 128;
 
 // generateContactsKernel (.cl:228-246): persistent warps over 8x4-pixel packets (same tiling as the BVH path).
+template <bool CORRECTED>
 __global__ void __launch_bounds__(TLG_TRACE_THREADS)
 tlg_trace_primary_kernel(const clrt_camera cam, const clrt_grid_data g, const clrt_top_cell* __restrict__ top,
                          const uint2* __restrict__ leaf_ranges, const uint2* __restrict__ leaf_pairs, const clrt_triangle* __restrict__ tris,
@@ -411,7 +493,7 @@ tlg_trace_primary_kernel(const clrt_camera cam, const clrt_grid_data g, const cl
     const uint32_t pixel = ty * cam.resX + tx;
     if (inside) {
       Vec3 o, d; generate_ray(cam, pixel, o, d);
-      const GridHit h = tlg_traverse(o, d, g, top, leaf_ranges, leaf_pairs, tris);
+      const GridHit h = CORRECTED ? tlg_traverse_closest(o, d, g, top, leaf_ranges, leaf_pairs, tris) : tlg_traverse(o, d, g, top, leaf_ranges, leaf_pairs, tris);
       tlg_write_contact(out, raster ? pixel : lt * CLRT_TILE_PIXELS + inTile, pixel, h, tris);
     } else if (!raster) {
       GridHit h; h.t = 0.0f; h.tri = 0xFFFFFFFFu;
@@ -421,6 +503,7 @@ tlg_trace_primary_kernel(const clrt_camera cam, const clrt_grid_data g, const cl
 }
 
 // generateContacts2Kernel (.cl:251-267)
+template <bool CORRECTED>
 __global__ void __launch_bounds__(TLG_TRACE_THREADS)
 tlg_trace_rays_kernel(const clrt_ray* __restrict__ rays, uint32_t count, const clrt_grid_data g, const clrt_top_cell* __restrict__ top,
                       const uint2* __restrict__ leaf_ranges, const uint2* __restrict__ leaf_pairs, const clrt_triangle* __restrict__ tris,
@@ -438,7 +521,8 @@ tlg_trace_rays_kernel(const clrt_ray* __restrict__ rays, uint32_t count, const c
       const float4 ro = __ldcs(p + 1), rd = __ldcs(p + 2);
       GridHit h; h.t = 0.0f; h.tri = 0xFFFFFFFFu;
       if (!(rd.x == 0.0f && rd.y == 0.0f && rd.z == 0.0f))
-        h = tlg_traverse(v3(ro.x, ro.y, ro.z), v3(rd.x, rd.y, rd.z), g, top, leaf_ranges, leaf_pairs, tris);
+        h = CORRECTED ? tlg_traverse_closest(v3(ro.x, ro.y, ro.z), v3(rd.x, rd.y, rd.z), g, top, leaf_ranges, leaf_pairs, tris)
+                      : tlg_traverse(v3(ro.x, ro.y, ro.z), v3(rd.x, rd.y, rd.z), g, top, leaf_ranges, leaf_pairs, tris);
       tlg_write_contact(out, i, i, h, tris);
     }
   }
@@ -462,6 +546,31 @@ static int grow_sync(clrt_ctx* ctx, void** p, size_t* cap, size_t bytes) {
   return 0;
 }
 
+// getResolution (TwoLevelGridManager.cpp:566-578): float arithmetic, pow in double rounded once (Q20), truncation to uint.
+static void tlg_resolution(const clrt_accel* a, float& fx, float& fy, float& fz) {
+  const clrt_aabb& box = a->scene->header.modelsBoundingBox;
+  const float deltaX = box.bounds[1].x - box.bounds[0].x, deltaY = box.bounds[1].y - box.bounds[0].y, deltaZ = box.bounds[1].z - box.bounds[0].z;
+  const float volume = deltaX * deltaY * deltaZ;
+  const float prims = (float)a->scene->header.totalNumberOfTriangles;
+  const float av = (float)pow((double)(a->top_density * prims / volume), (double)ONE_THIRD);
+  fx = deltaX * av; fy = deltaY * av; fz = deltaZ * av;
+}
+// setTopLevelDensity / setLeafDensity (TwoLevelGridManager.h:112-115): plain members read by calculateGridData at the next initializeFrame.
+extern "C" int clrt_tlg_set_densities(clrt_accel* a, float top_density, float leaf_density) {
+  if (!a || a->kind != ACCEL_TLG) CLRT_FAIL("clrt_tlg_set_densities: not a Two-Level Grid");
+  if (!(top_density > 0.0f) || !(leaf_density > 0.0f)) CLRT_FAIL("clrt_tlg_set_densities: densities must be positive");
+  a->top_density = top_density; a->leaf_density = leaf_density;
+  return 0;
+}
+// getResolution() (TwoLevelGridManager.h:129): the top-level resolution the current densities give, truncated like the reference's
+// float -> uint conversion (0 where the reference's value is below one or not a number).
+extern "C" int clrt_tlg_resolution(clrt_accel* a, uint32_t* out_xyz) {
+  if (!a || !out_xyz || a->kind != ACCEL_TLG) CLRT_FAIL("clrt_tlg_resolution: not a Two-Level Grid / NULL argument");
+  float f[3]; tlg_resolution(a, f[0], f[1], f[2]);
+  for (int i = 0; i < 3; i++) out_xyz[i] = (f[i] >= 1.0f && f[i] < 4294967040.0f) ? (uint32_t)f[i] : 0u;
+  return 0;
+}
+
 // initializeFrame (TwoLevelGridManager.cpp:160-201): calculateGridData (:584-600) on the host, allocate + zero.
 int tlg_init_frame(clrt_accel* a) {
   clrt_ctx* ctx = a->ctx;
@@ -474,12 +583,7 @@ int tlg_init_frame(clrt_accel* a) {
   clrt_grid_data g; memset(&g, 0, sizeof g);
   g.box = sc->header.modelsBoundingBox;
   {
-    // getResolution (:566-578): float arithmetic, pow in double rounded once (Q20), truncation to uint
-    const float deltaX = g.box.bounds[1].x - g.box.bounds[0].x, deltaY = g.box.bounds[1].y - g.box.bounds[0].y, deltaZ = g.box.bounds[1].z - g.box.bounds[0].z;
-    const float volume = deltaX * deltaY * deltaZ;
-    const float prims = (float)sc->header.totalNumberOfTriangles;
-    const float av = (float)pow((double)(a->top_density * prims / volume), (double)ONE_THIRD);
-    const float fx = deltaX * av, fy = deltaY * av, fz = deltaZ * av;
+    float fx, fy, fz; tlg_resolution(a, fx, fy, fz);
     if (!(fx >= 1.0f && fy >= 1.0f && fz >= 1.0f) || !(fx < 2048.0f && fy < 2048.0f && fz < 2048.0f) || n == 0)
       CLRT_FAIL("Two-Level Grid: degenerate top-level resolution (%g x %g x %g) for %u triangles - the reference divides by zero here", fx, fy, fz, n);
     g.resX = (uint32_t)fx; g.resY = (uint32_t)fy; g.resZ = (uint32_t)fz;
@@ -552,16 +656,19 @@ int tlg_construct(clrt_accel* a) {
   CLRT_TRY(grow_sync(ctx, (void**)&t->d_leaf_ranges, &t->leaf_ranges_cap, (size_t)(t->leaf_cells ? t->leaf_cells : 1) * 8));
   CLRT_CUDA(cudaMemsetAsync(t->d_leaf_pairs, 0xFF, (size_t)t->leaf_pairs_cap * 8, s));
   CLRT_CUDA(cudaMemsetAsync(t->d_leaf_ranges, 0, (size_t)t->leaf_cells * 8, s));
-  CLRT_CUDA(cudaMemsetAsync(t->d_real, 0, 4, s));
+  CLRT_CUDA(cudaMemsetAsync(t->d_real, 0, 8, s));                                      // [0] real leaf pairs, [1] pairs beyond their budget
   t->leaf_pairs = 0;
   if (t->leaf_pairs_cap) {
     tlg_scatter_leaf_kernel<<<(t->top_pairs + 127) / 128, 128, 0, s>>>(tris, (const uint2*)t->d_top_pairs, t->top_pairs, g, t->d_top_cells,
-                                                                       t->d_scan, t->d_counters, t->leaf_pairs_cap, (uint2*)t->d_leaf_pairs);
+                                                                       t->d_scan, t->d_counters, t->leaf_pairs_cap, (uint2*)t->d_leaf_pairs, t->d_real + 1);
     CLRT_CHECK_LAUNCH();
     CLRT_TRY(sort_pairs_radix(ctx, t->d_leaf_pairs, t->leaf_pairs_cap, 32));
     extract_ranges_kernel<<<(t->leaf_pairs_cap + 255) / 256, 256, 0, s>>>((const uint2*)t->d_leaf_pairs, t->leaf_pairs_cap, (uint2*)t->d_leaf_ranges, t->d_real);
     CLRT_CHECK_LAUNCH();
     CLRT_TRY(read_u32(ctx, t->d_real, &t->leaf_pairs));
+    uint32_t over = 0;
+    CLRT_TRY(read_u32(ctx, t->d_real + 1, &over));
+    if (over) CLRT_FAIL("Two-Level Grid: the exact leaf scatter found %u pairs the conservative count did not budget for", over);
   }
   CLRT_TRY(mark());                                                                     // ev5: leaf pairs
   if (tm) {
@@ -593,9 +700,15 @@ int tlg_trace_primary(clrt_accel* a, const clrt_camera& cam, clrt_contact* out, 
   if (!packets) return 0;
   CLRT_CUDA(cudaMemsetAsync(a->d_tile_counter, 0, 4, ctx->stream));
   unsigned grid = 0;
-  CLRT_TRY(tlg_grid(ctx, tlg_trace_primary_kernel, packets, &grid));
-  tlg_trace_primary_kernel<<<grid, TLG_TRACE_THREADS, 0, ctx->stream>>>(cam, t->grid, t->d_top_cells, (const uint2*)t->d_leaf_ranges,
-      (const uint2*)t->d_leaf_pairs, a->scene->d_tris, out, rank, nranks, raster, a->d_tile_counter);
+  if (a->trace_mode == CLRT_TRACE_FAST) {                      // the corrected closest-hit walk
+    CLRT_TRY(tlg_grid(ctx, tlg_trace_primary_kernel<true>, packets, &grid));
+    tlg_trace_primary_kernel<true><<<grid, TLG_TRACE_THREADS, 0, ctx->stream>>>(cam, t->grid, t->d_top_cells, (const uint2*)t->d_leaf_ranges,
+        (const uint2*)t->d_leaf_pairs, a->scene->d_tris, out, rank, nranks, raster, a->d_tile_counter);
+  } else {                                                     // the reference's walk, literally
+    CLRT_TRY(tlg_grid(ctx, tlg_trace_primary_kernel<false>, packets, &grid));
+    tlg_trace_primary_kernel<false><<<grid, TLG_TRACE_THREADS, 0, ctx->stream>>>(cam, t->grid, t->d_top_cells, (const uint2*)t->d_leaf_ranges,
+        (const uint2*)t->d_leaf_pairs, a->scene->d_tris, out, rank, nranks, raster, a->d_tile_counter);
+  }
   CLRT_CHECK_LAUNCH();
   return 0;
 }
@@ -607,9 +720,15 @@ int tlg_trace_rays(clrt_accel* a, const clrt_ray* rays, clrt_contact* out, uint3
   const uint32_t packets = (count + 31u) / 32u;
   CLRT_CUDA(cudaMemsetAsync(a->d_tile_counter, 0, 4, ctx->stream));
   unsigned grid = 0;
-  CLRT_TRY(tlg_grid(ctx, tlg_trace_rays_kernel, packets, &grid));
-  tlg_trace_rays_kernel<<<grid, TLG_TRACE_THREADS, 0, ctx->stream>>>(rays, count, t->grid, t->d_top_cells, (const uint2*)t->d_leaf_ranges,
-      (const uint2*)t->d_leaf_pairs, a->scene->d_tris, out, a->d_tile_counter);
+  if (a->trace_mode == CLRT_TRACE_FAST) {
+    CLRT_TRY(tlg_grid(ctx, tlg_trace_rays_kernel<true>, packets, &grid));
+    tlg_trace_rays_kernel<true><<<grid, TLG_TRACE_THREADS, 0, ctx->stream>>>(rays, count, t->grid, t->d_top_cells, (const uint2*)t->d_leaf_ranges,
+        (const uint2*)t->d_leaf_pairs, a->scene->d_tris, out, a->d_tile_counter);
+  } else {
+    CLRT_TRY(tlg_grid(ctx, tlg_trace_rays_kernel<false>, packets, &grid));
+    tlg_trace_rays_kernel<false><<<grid, TLG_TRACE_THREADS, 0, ctx->stream>>>(rays, count, t->grid, t->d_top_cells, (const uint2*)t->d_leaf_ranges,
+        (const uint2*)t->d_leaf_pairs, a->scene->d_tris, out, a->d_tile_counter);
+  }
   CLRT_CHECK_LAUNCH();
   return 0;
 }

@@ -88,15 +88,23 @@ __device__ __forceinline__ Hit traverse_ref(const TraceNode* __restrict__ tnodes
 }
 
 // ---- FAST policy ---------------------------------------------------------------------------------------------------------
+// ANYHIT template argument: 0 closest hit, 1 occlusion query, 2 decided per ray (Lane::any — the fused frame kernel traces both kinds).
+#define LANE_ANY(L) (ANYHIT == 1 || (ANYHIT == 2 && (L).any))
 // Per-lane traversal state.  ANYHIT: an occlusion query - ends at the first triangle with 0 < t < tmax; "some hit below
 // tmax exists" equals "the closest hit is below tmax", which is what the shading's shadow test asks.
 struct Lane {
-  Vec3 o, d, inv;
+  Vec3 o, d;
+#if CLRT_WIDE_Q16
+  Vec3 An, Af, B;                 // slab distances of grid position q: near bounds q * B + An, far bounds q * B + Af (lane_begin)
+#else
+  Vec3 inv;
+#endif
   Hit h;
   uint32_t cur;
   int sp;
   uint32_t visits;                // statistics mode only: inner-node visits of the current ray (-> Contact.pad[1])
   uint32_t q0, q1, q2, q3, qn;    // postponed leaves (positions in the triangle array) and their count
+  bool any;                       // ANYHIT == 2 only: this ray is an occlusion query
 };
 
 // Compile-time shape of the traversal kernels (profiles/variants.sh builds and measures the alternatives):
@@ -120,7 +128,7 @@ struct Lane {
 #define CLRT_UNIFORM_STACK 0
 #endif
 #ifndef CLRT_MIN_CTAS
-#define CLRT_MIN_CTAS 1          // __launch_bounds__ second argument of the FAST kernels (register cap = 65536 / (threads x CTAs))
+#define CLRT_MIN_CTAS 6          // __launch_bounds__ second argument of the FAST kernels (register cap = 65536 / (threads x CTAs))
 #endif
 #ifndef CLRT_PREFETCH_TOP
 #define CLRT_PREFETCH_TOP 0      // prefetch.global.L1 of the node on top of the stack (the one visited after the nearest child's subtree)
@@ -138,16 +146,36 @@ struct StackRef {
   uint32_t* overflow;
 };
 
-template <bool STATS, bool ANYHIT>
-__device__ __forceinline__ void lane_begin(Lane& L, const clrt_triangle* __restrict__ tris, uint32_t n, Vec3 o, Vec3 d, float tmax, Stats& st) {
+template <bool STATS, int ANYHIT>
+__device__ __forceinline__ void lane_begin(Lane& L, const clrt_triangle* __restrict__ tris, uint32_t n, const QFrame* __restrict__ qf,
+                                           Vec3 o, Vec3 d, float tmax, Stats& st) {
   L.o = o; L.d = d;
   // 1/d as the reference computes it, except that an exactly zero component gives +-1e30 instead of +-inf: (bound - origin) * inv
   // is then 0 when the origin lies ON the bound (the reference's 0 * inf = NaN is dropped by its compare-select min/max,
   // AABB.h:126-142, i.e. the slab is accepted — same outcome) and +-huge otherwise (rejected like +-inf).  No NaN reaches the
-  // fminf/fmaxf of child_entry, which would turn it into a rejection of both boxes along a seam in the ray's plane.
+  // fminf/fmaxf of the box test, which would turn it into a rejection of both boxes along a seam in the ray's plane.
   const float big = 1.0e30f;
-  L.inv = v3(d.x == 0.0f ? copysignf(big, d.x) : 1.0f / d.x, d.y == 0.0f ? copysignf(big, d.y) : 1.0f / d.y, d.z == 0.0f ? copysignf(big, d.z) : 1.0f / d.z);
-  L.h.t = tmax; L.h.tri = SENTINEL; L.h.cull = ANYHIT ? tmax * CULL_SLACK : RT_FLT_MAX;
+  const Vec3 inv = v3(d.x == 0.0f ? copysignf(big, d.x) : 1.0f / d.x, d.y == 0.0f ? copysignf(big, d.y) : 1.0f / d.y, d.z == 0.0f ? copysignf(big, d.z) : 1.0f / d.z);
+#if CLRT_WIDE_Q16
+  // Grid position q (16 bit) on an axis lies at lo + q * step, i.e. at ray distance A + q * B with A = (lo - origin) * inv and
+  // B = step * inv.  q reaches the FMA as the float 2^23 + q (one PRMT builds its bits, no conversion), so the constant is
+  // A0 = A - 2^23 * B.  Rounding: A0 is rounded at magnitude 2^23 |B| + |A| (half a step of error), q * B exactly cancels the
+  // 2^23 * B part because the same rounded B is used, A carries 2^-23 |A|.  Near bounds are therefore moved 0.55 |B| + 2^-21 |A|
+  // earlier and far bounds as much later: the tested box still contains the stored one (which contains the exact one).
+  if (n >= 2) {
+    const float4 f0 = __ldg(reinterpret_cast<const float4*>(qf)), f1 = __ldg(reinterpret_cast<const float4*>(qf) + 1);
+    const Vec3 A = v3((f0.x - o.x) * inv.x, (f0.y - o.y) * inv.y, (f0.z - o.z) * inv.z);
+    L.B = v3(f1.x * inv.x, f1.y * inv.y, f1.z * inv.z);
+    const Vec3 A0 = v3(__fmaf_rn(-8388608.0f, L.B.x, A.x), __fmaf_rn(-8388608.0f, L.B.y, A.y), __fmaf_rn(-8388608.0f, L.B.z, A.z));
+    const float k = 1.0f / 2097152.0f;
+    const Vec3 w = v3(0.55f * fabsf(L.B.x) + k * fabsf(A.x), 0.55f * fabsf(L.B.y) + k * fabsf(A.y), 0.55f * fabsf(L.B.z) + k * fabsf(A.z));
+    L.An = v3(A0.x - w.x, A0.y - w.y, A0.z - w.z);
+    L.Af = v3(A0.x + w.x, A0.y + w.y, A0.z + w.z);
+  }
+#else
+  L.inv = inv;
+#endif
+  L.h.t = tmax; L.h.tri = SENTINEL; L.h.cull = LANE_ANY(L) ? tmax * CULL_SLACK : RT_FLT_MAX;
   L.sp = 0; L.qn = 0;
   L.cur = n >= 2 ? WIDE_TOP_BIT : SENTINEL;                  // slot 0 of the top table = the root
   if (STATS) { st.rays++; L.visits = 0; }
@@ -167,6 +195,7 @@ __device__ __forceinline__ void lane_begin(Lane& L, const clrt_triangle* __restr
 // min/max instead of the sign select, the three pairwise overlap flags are `tn <= tf`, and the reference's validity
 // `t > 0 || origin inside` (AABB.h:178-184) is `tf >= 0` (origin inside <=> every axis has near <= 0 <= far).  Axis-parallel
 // rays: see lane_begin.  Empty slots hold NaN boxes (widen_kernel): every comparison fails.
+#if !CLRT_WIDE_Q16
 __device__ __forceinline__ float child_entry(float x0, float y0, float z0, float x1, float y1, float z1, Vec3 o, Vec3 inv, float cull) {
   const float ax = (x0 - o.x) * inv.x, bx = (x1 - o.x) * inv.x;
   const float ay = (y0 - o.y) * inv.y, by = (y1 - o.y) * inv.y;
@@ -175,6 +204,7 @@ __device__ __forceinline__ float child_entry(float x0, float y0, float z0, float
   const float tf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fmaxf(az, bz));
   return (tn <= fminf(tf, cull) && tf >= 0.0f) ? tn : T_INVALID;
 }
+#endif
 __device__ __forceinline__ void cswap(float& ta, uint32_t& ca, float& tb, uint32_t& cb) {
   if (tb < ta) { const float t = ta; ta = tb; tb = t; const uint32_t c = ca; ca = cb; cb = c; }
 }
@@ -193,15 +223,49 @@ __device__ __forceinline__ uint2 stack_pop(Lane& L, const StackRef& S) {      //
   return L.sp < SSTACK ? S.s[L.sp * TRACE_THREADS] : S.l[L.sp - SSTACK];
 }
 
-template <bool STATS, bool ANYHIT>
+template <bool STATS, int ANYHIT>
 __device__ __forceinline__ void lane_visit(Lane& L, const WideNode* __restrict__ wnodes, const WideNode* s_top, const clrt_triangle* __restrict__ tris,
                                            uint32_t n, Stats& st, const StackRef& S) {
   if (STATS) { st.inner++; L.visits++; }
-  const Vec3 o = L.o, d = L.d, inv = L.inv;
+  const Vec3 o = L.o, d = L.d;
   // top-table slots below TOP_STAGED are read from the CTA's shared-memory copy, everything else from global memory
   const uint32_t slot = L.cur & ~WIDE_TOP_BIT;
   const WideNode* node = (L.cur & WIDE_TOP_BIT) ? ((TOP_STAGED && slot < (uint32_t)TOP_STAGED) ? s_top + slot : wnodes + n + slot)
                                                 : wnodes + (L.cur - n);
+#if CLRT_WIDE_Q16
+  const uint4* p = reinterpret_cast<const uint4*>(node);
+  const uint4 qa = p[0], qb = p[1], qc = p[2], ch = p[3];
+  uint32_t c0 = ch.x, c1 = ch.y, c2 = ch.z, c3 = ch.w;
+  float t0, t1, t2, t3;
+  {
+    // near / far grid positions per axis by the sign of the direction (B carries the sign of 1/d)
+    const bool nx = L.B.x < 0.0f, ny = L.B.y < 0.0f, nz = L.B.z < 0.0f;
+    const uint32_t nxa = nx ? qb.z : qa.x, nxb = nx ? qb.w : qa.y, fxa = nx ? qa.x : qb.z, fxb = nx ? qa.y : qb.w;
+    const uint32_t nya = ny ? qc.x : qa.z, nyb = ny ? qc.y : qa.w, fya = ny ? qa.z : qc.x, fyb = ny ? qa.w : qc.y;
+    const uint32_t nza = nz ? qc.z : qb.x, nzb = nz ? qc.w : qb.y, fza = nz ? qb.x : qc.z, fzb = nz ? qb.y : qc.w;
+    const float cull = L.h.cull;
+    auto entry = [&](uint32_t wnx, uint32_t wny, uint32_t wnz, uint32_t wfx, uint32_t wfy, uint32_t wfz, unsigned sel) {
+      // 0x4B000000 | q is the float 2^23 + q: bytes (q.lo, q.hi, 0x00, 0x4B) in one PRMT
+      const float tn = fmaxf(fmaxf(__fmaf_rn(__uint_as_float(__byte_perm(wnx, 0x4B000000u, sel)), L.B.x, L.An.x),
+                                   __fmaf_rn(__uint_as_float(__byte_perm(wny, 0x4B000000u, sel)), L.B.y, L.An.y)),
+                             __fmaf_rn(__uint_as_float(__byte_perm(wnz, 0x4B000000u, sel)), L.B.z, L.An.z));
+      const float tf = fminf(fminf(__fmaf_rn(__uint_as_float(__byte_perm(wfx, 0x4B000000u, sel)), L.B.x, L.Af.x),
+                                   __fmaf_rn(__uint_as_float(__byte_perm(wfy, 0x4B000000u, sel)), L.B.y, L.Af.y)),
+                             __fmaf_rn(__uint_as_float(__byte_perm(wfz, 0x4B000000u, sel)), L.B.z, L.Af.z));
+      return (tn <= fminf(tf, cull) && tf >= 0.0f) ? tn : T_INVALID;
+    };
+    t0 = entry(nxa, nya, nza, fxa, fya, fza, 0x7410u);
+    t1 = entry(nxa, nya, nza, fxa, fya, fza, 0x7432u);
+    t2 = entry(nxb, nyb, nzb, fxb, fyb, fzb, 0x7410u);
+    t3 = entry(nxb, nyb, nzb, fxb, fyb, fzb, 0x7432u);
+    // an empty slot holds an inverted box, which the test rejects for every finite ray; its id says so too
+    if (c0 == SENTINEL) t0 = T_INVALID;
+    if (c1 == SENTINEL) t1 = T_INVALID;
+    if (c2 == SENTINEL) t2 = T_INVALID;
+    if (c3 == SENTINEL) t3 = T_INVALID;
+  }
+#else
+  const Vec3 inv = L.inv;
   const float4* p = reinterpret_cast<const float4*>(node);
   const float4 lx = p[0], ly = p[1], lz = p[2], hx = p[3], hy = p[4], hz = p[5];
   const uint4 ch = *reinterpret_cast<const uint4*>(p + 6);
@@ -210,6 +274,7 @@ __device__ __forceinline__ void lane_visit(Lane& L, const WideNode* __restrict__
   float t1 = child_entry(lx.y, ly.y, lz.y, hx.y, hy.y, hz.y, o, inv, L.h.cull);
   float t2 = child_entry(lx.z, ly.z, lz.z, hx.z, hy.z, hz.z, o, inv, L.h.cull);
   float t3 = child_entry(lx.w, ly.w, lz.w, hx.w, hy.w, hz.w, o, inv, L.h.cull);
+#endif
   // Leaves are POSTPONED: their ids go to a four-entry queue in registers and the triangle tests run warp-wide in flush_one once
   // enough lanes hold one.  Tested on the spot, the Moeller-Trumbore code ran with 2.7 of 32 lanes (round-1 ncu source view:
   // only ~9 % of the lane-steps find a leaf, but with 16+ active lanes almost every warp-step found one somewhere).  A fifth
@@ -228,7 +293,7 @@ __device__ __forceinline__ void lane_visit(Lane& L, const WideNode* __restrict__
       else { test_triangle<true>(tris, id, o, d, L.h); if (STATS) st.tris++; }
     }
   }
-  if (ANYHIT && L.h.tri != SENTINEL) { L.cur = SENTINEL; L.sp = 0; L.qn = 0; return; }
+  if (LANE_ANY(L) && L.h.tri != SENTINEL) { L.cur = SENTINEL; L.sp = 0; L.qn = 0; return; }
   if (t0 > L.h.cull) t0 = T_INVALID;
   if (t1 > L.h.cull) t1 = T_INVALID;
   if (t2 > L.h.cull) t2 = T_INVALID;
@@ -269,14 +334,14 @@ __device__ __forceinline__ void lane_visit(Lane& L, const WideNode* __restrict__
 
 // One postponed triangle test per lane that holds one (the queue is LIFO: q0 is the newest).  A closest-hit ray goes on with the
 // shorter cull distance; an occlusion query that hit is complete.
-template <bool STATS, bool ANYHIT>
+template <bool STATS, int ANYHIT>
 __device__ __forceinline__ void flush_one(Lane& L, const clrt_triangle* __restrict__ tris, Stats& st) {
   if (L.qn != 0u) {
     const uint32_t id = L.q0;
     L.q0 = L.q1; L.q1 = L.q2; L.q2 = L.q3; L.qn--;
     test_triangle<true>(tris, id, L.o, L.d, L.h);
     if (STATS) st.tris++;
-    if (ANYHIT && L.h.tri != SENTINEL) { L.qn = 0u; L.cur = SENTINEL; L.sp = 0; }
+    if (LANE_ANY(L) && L.h.tri != SENTINEL) { L.qn = 0u; L.cur = SENTINEL; L.sp = 0; }
   }
 }
 
@@ -295,7 +360,7 @@ __device__ __forceinline__ void flush_one(Lane& L, const clrt_triangle* __restri
 #define CLRT_WINDOW 2
 #endif
 #ifndef CLRT_REFILL_MIN
-#define CLRT_REFILL_MIN 8
+#define CLRT_REFILL_MIN 12
 #endif
 #ifndef CLRT_FLUSH_MIN
 #define CLRT_FLUSH_MIN 8
@@ -337,7 +402,7 @@ __device__ __forceinline__ const WideNode* stage_top_table(unsigned char* smem, 
   return s_top;
 }
 
-template <class Job, bool STATS, bool ANYHIT>
+template <class Job, bool STATS, int ANYHIT>
 __device__ __forceinline__ void run_jobs(Job& job, const WideNode* __restrict__ wnodes, const clrt_triangle* __restrict__ tris,
                                          uint32_t n, uint32_t total, uint32_t* __restrict__ counter, Stats& st, uint32_t* __restrict__ overflow) {
   extern __shared__ __align__(128) unsigned char fast_smem[];
@@ -439,7 +504,7 @@ __device__ __forceinline__ PixelRef pixel_of_unit(const clrt_camera& cam, const 
 template <bool STATS>
 struct PrimaryJob {
   const clrt_camera& cam; TileGrid g; uint32_t rank, nranks; int raster;
-  const clrt_triangle* __restrict__ tris; uint32_t n; clrt_contact* __restrict__ out; Stats& st;
+  const clrt_triangle* __restrict__ tris; uint32_t n; const QFrame* __restrict__ qf; clrt_contact* __restrict__ out; Stats& st;
   uint32_t pixel, slot;
   __device__ __forceinline__ bool start(uint32_t u, Lane& L) {
     const PixelRef r = pixel_of_unit(cam, g, u, rank, nranks, raster);
@@ -449,7 +514,7 @@ struct PrimaryJob {
     }
     pixel = r.pixel; slot = r.slot;
     Vec3 o, d; generate_ray(cam, pixel, o, d);
-    lane_begin<STATS, false>(L, tris, n, o, d, RT_FLT_MAX, st);
+    lane_begin<STATS, 0>(L, tris, n, qf, o, d, RT_FLT_MAX, st);
     return true;
   }
   __device__ __forceinline__ bool finish(Lane& L) { write_contact(out, slot, pixel, L.h, tris, STATS ? L.visits : 0u); return false; }
@@ -459,14 +524,14 @@ struct PrimaryJob {
 // anything in the reference either (det == 0 for every triangle); it is answered without traversal.
 template <bool STATS>
 struct RaysJob {
-  const clrt_ray* __restrict__ rays; const clrt_triangle* __restrict__ tris; uint32_t n; clrt_contact* __restrict__ out; Stats& st;
+  const clrt_ray* __restrict__ rays; const clrt_triangle* __restrict__ tris; uint32_t n; const QFrame* __restrict__ qf; clrt_contact* __restrict__ out; Stats& st;
   uint32_t index;
   __device__ __forceinline__ bool start(uint32_t i, Lane& L) {
     const float4* p = reinterpret_cast<const float4*>(rays + i);
     const float4 ro = __ldcs(p + 1), rd = __ldcs(p + 2);
     if (rd.x == 0.0f && rd.y == 0.0f && rd.z == 0.0f) { Hit h; h.t = RT_FLT_MAX; h.tri = SENTINEL; write_contact(out, i, i, h, tris); return false; }
     index = i;
-    lane_begin<STATS, false>(L, tris, n, v3(ro.x, ro.y, ro.z), v3(rd.x, rd.y, rd.z), RT_FLT_MAX, st);
+    lane_begin<STATS, 0>(L, tris, n, qf, v3(ro.x, ro.y, ro.z), v3(rd.x, rd.y, rd.z), RT_FLT_MAX, st);
     return true;
   }
   __device__ __forceinline__ bool finish(Lane& L) { write_contact(out, index, index, L.h, tris); return false; }
@@ -480,7 +545,7 @@ template <bool STATS>
 struct ShadowJob {
   const clrt_camera& cam; const clrt_contact* __restrict__ contacts;
   const clrt_light* __restrict__ lights; uint32_t n_lights; const clrt_material* __restrict__ materials; uint32_t n_materials;
-  const clrt_triangle* __restrict__ tris; uint32_t n; uint32_t* __restrict__ rgba8; const PeerTargets& peers; Stats& st; uint32_t& live_rays;
+  const clrt_triangle* __restrict__ tris; uint32_t n; const QFrame* __restrict__ qf; uint32_t* __restrict__ rgba8; const PeerTargets& peers; Stats& st; uint32_t& live_rays;
   // Per-lane state of a unit: five registers.  The contact's 32 bytes are read again when the unit is shaded and the primary ray
   // is regenerated per shadow ray (40 instructions against ~9000 of a shadow ray's traversal): the 17 registers the whole contact,
   // origin and hit point took cost the kernel a fifth of its occupancy (86 registers, 5 CTAs per SM).
@@ -508,7 +573,7 @@ struct ShadowJob {
     float energy; const Vec3 lp = light_position(lights, n_lights, l, o, energy);
     const float limit = vlength(vsub(lp, P)) - SHADOW_EPS_REL * t;
     Vec3 org, dir; shadow_ray(cam, pixel, t, lights, n_lights, l, org, dir);
-    lane_begin<STATS, true>(L, tris, n, org, dir, limit, st);
+    lane_begin<STATS, 1>(L, tris, n, qf, org, dir, limit, st);
   }
   __device__ __forceinline__ bool start(uint32_t i, Lane& L) {
     index = i; occl = 0; l = 0;
@@ -524,6 +589,65 @@ struct ShadowJob {
     occl |= (L.h.tri != SENTINEL ? 1u : 0u) << l;
     if (++l <= n_lights) { aim(L); return true; }
     shade_and_store();
+    return false;
+  }
+};
+
+// The whole frame in ONE persistent kernel (ours): unit = pixel slot of the stripe; its primary ray (closest hit), then — when it
+// hit — one occlusion query per light from the hit point, then Blinn-Phong -> RGBA8.  Same rays, same arithmetic and same pixels as
+// trace_primary_kernel + shadow_shade_kernel, without the 32-byte contacts going through memory and without the second kernel's
+// launch and drain: a frame (or a 1/8 stripe of one at 8 GPUs) has one tail instead of two.  Lanes of a warp are in either phase.
+template <bool STATS>
+struct FrameJob {
+  const clrt_camera& cam; TileGrid g; uint32_t rank, nranks;
+  const clrt_light* __restrict__ lights; uint32_t n_lights; const clrt_material* __restrict__ materials; uint32_t n_materials;
+  const clrt_triangle* __restrict__ tris; uint32_t n; const QFrame* __restrict__ qf; uint32_t* __restrict__ rgba8; const PeerTargets& peers;
+  Stats& st; uint32_t& live_rays;
+  uint32_t pixel, slot, l, occl, tri; float t;      // l == 0: the primary ray is on its way; l >= 1: shadow ray of light l - 1
+  __device__ __forceinline__ void store_pixel(uint32_t sl, uint32_t px, uint32_t packed) {
+    if (peers.n == 0) { __stcs(rgba8 + sl, packed); return; }
+    if (px == SENTINEL) return;
+#pragma unroll
+    for (uint32_t k = 0; k < 8; k++) if (k < peers.n) peers.p[k][px] = packed;
+  }
+  __device__ __forceinline__ void aim(Lane& L) {
+    Vec3 o, d; generate_ray(cam, pixel, o, d);
+    const Vec3 P = vadd(o, vscale(d, t));
+    float energy; const Vec3 lp = light_position(lights, n_lights, l - 1u, o, energy);
+    const float limit = vlength(vsub(lp, P)) - SHADOW_EPS_REL * t;
+    Vec3 org, dir; shadow_ray(cam, pixel, t, lights, n_lights, l - 1u, org, dir);
+    L.any = true;
+    lane_begin<STATS, 2>(L, tris, n, qf, org, dir, limit, st);
+  }
+  __device__ __forceinline__ bool start(uint32_t u, Lane& L) {
+    const PixelRef r = pixel_of_unit(cam, g, u, rank, nranks, 0);
+    if (!r.inside) { store_pixel(r.slot, SENTINEL, 0u); return false; }
+    pixel = r.pixel; slot = r.slot; l = 0;
+    Vec3 o, d; generate_ray(cam, pixel, o, d);
+    L.any = false;
+    lane_begin<STATS, 2>(L, tris, n, qf, o, d, RT_FLT_MAX, st);
+    return true;
+  }
+  __device__ __forceinline__ bool finish(Lane& L) {
+    if (l == 0) {                                          // the primary ray is complete
+      if (L.h.tri == SENTINEL) { store_pixel(slot, pixel, 0u); return false; }
+      tri = L.h.tri; t = L.h.t; occl = 0; l = 1;
+      live_rays += n_lights + 1;
+      aim(L);
+      return true;
+    }
+    occl |= (L.h.tri != SENTINEL ? 1u : 0u) << (l - 1u);
+    if (++l <= n_lights + 1u) { aim(L); return true; }
+    // shade: the contact write_contact would have stored (normal of the winning triangle, material, t)
+    const float4* p = reinterpret_cast<const float4*>(tris + tri);
+    const float4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
+    const Vec3 nrm = triangle_normal(v3(a.x, a.y, a.z), v3(b.x, b.y, b.z), v3(c.x, c.y, c.z));
+    const uint4 head = make_uint4(pixel, __float_as_uint(a.w), __float_as_uint(b.w), 0u);
+    const float4 nd = make_float4(nrm.x, nrm.y, nrm.z, t);
+    uint32_t packed;
+    const uint32_t oc = occl;
+    shade_contact(cam, head, nd, lights, n_lights, materials, n_materials, [oc](uint32_t k, float) { return ((oc >> k) & 1u) != 0u; }, packed);
+    store_pixel(slot, pixel, packed);
     return false;
   }
 };
@@ -556,8 +680,8 @@ trace_primary_kernel(const clrt_camera cam, const TraceNode* __restrict__ tnodes
       }
     }
   } else {
-    PrimaryJob<STATS> job{cam, g, rank, nranks, raster, tris, n, out, st, 0u, 0u};
-    run_jobs<PrimaryJob<STATS>, STATS, false>(job, wnodes, tris, n, total, counter, st, overflow);
+    PrimaryJob<STATS> job{cam, g, rank, nranks, raster, tris, n, reinterpret_cast<const QFrame*>(wnodes + n + WIDE_TOP_NODES), out, st, 0u, 0u};
+    run_jobs<PrimaryJob<STATS>, STATS, 0>(job, wnodes, tris, n, total, counter, st, overflow);
   }
   if (STATS) flush_stats(st, stats);
 }
@@ -586,8 +710,8 @@ trace_rays_kernel(const clrt_ray* __restrict__ rays, uint32_t count, const Trace
       }
     }
   } else {
-    RaysJob<STATS> job{rays, tris, n, out, st, 0u};
-    run_jobs<RaysJob<STATS>, STATS, false>(job, wnodes, tris, n, count, counter, st, overflow);
+    RaysJob<STATS> job{rays, tris, n, reinterpret_cast<const QFrame*>(wnodes + n + WIDE_TOP_NODES), out, st, 0u};
+    run_jobs<RaysJob<STATS>, STATS, 0>(job, wnodes, tris, n, count, counter, st, overflow);
   }
   if (STATS) flush_stats(st, stats);
 }
@@ -601,8 +725,30 @@ shadow_shade_kernel(const clrt_camera cam, const clrt_contact* __restrict__ cont
                     unsigned long long* __restrict__ stats, uint32_t* __restrict__ overflow) {
   Stats st; st.rays = st.inner = st.tris = st.lboxes = 0;
   uint32_t live_rays = 0;
-  ShadowJob<STATS> job{cam, contacts, lights, n_lights, materials, n_materials, tris, n, rgba8, peers, st, live_rays, 0u, 0u, 0u, 0u, 0.0f};
-  run_jobs<ShadowJob<STATS>, STATS, true>(job, wnodes, tris, n, count, counter, st, overflow);
+  ShadowJob<STATS> job{cam, contacts, lights, n_lights, materials, n_materials, tris, n, reinterpret_cast<const QFrame*>(wnodes + n + WIDE_TOP_NODES), rgba8, peers, st, live_rays, 0u, 0u, 0u, 0u, 0.0f};
+  run_jobs<ShadowJob<STATS>, STATS, 1>(job, wnodes, tris, n, count, counter, st, overflow);
+  if (ray_counter) {
+#pragma unroll
+    for (int dd = 16; dd > 0; dd >>= 1) live_rays += __shfl_xor_sync(0xffffffffu, live_rays, dd);
+    if ((threadIdx.x & 31) == 0 && live_rays) atomicAdd(ray_counter, (unsigned long long)live_rays);
+  }
+  if (STATS) flush_stats(st, stats);
+}
+
+template <bool STATS>
+__global__ void __launch_bounds__(TRACE_THREADS, CLRT_MIN_CTAS)
+frame_kernel(const clrt_camera cam, uint32_t rank, uint32_t nranks,
+             const clrt_light* __restrict__ lights, uint32_t n_lights, const clrt_material* __restrict__ materials, uint32_t n_materials,
+             const WideNode* __restrict__ wnodes, const clrt_triangle* __restrict__ tris, uint32_t n,
+             uint32_t* __restrict__ rgba8, const PeerTargets peers, uint32_t* __restrict__ counter, unsigned long long* __restrict__ ray_counter,
+             unsigned long long* __restrict__ stats, uint32_t* __restrict__ overflow) {
+  Stats st; st.rays = st.inner = st.tris = st.lboxes = 0;
+  uint32_t live_rays = 0;
+  const TileGrid g = make_tile_grid(cam.resX, cam.resY);
+  const uint32_t total = stripe_tile_count(g.tiles, rank, nranks) * CLRT_TILE_PIXELS;
+  FrameJob<STATS> job{cam, g, rank, nranks, lights, n_lights, materials, n_materials, tris, n, reinterpret_cast<const QFrame*>(wnodes + n + WIDE_TOP_NODES),
+                      rgba8, peers, st, live_rays, 0u, 0u, 0u, 0u, 0u, 0.0f};
+  run_jobs<FrameJob<STATS>, STATS, 2>(job, wnodes, tris, n, total, counter, st, overflow);
   if (ray_counter) {
 #pragma unroll
     for (int dd = 16; dd > 0; dd >>= 1) live_rays += __shfl_xor_sync(0xffffffffu, live_rays, dd);
@@ -731,6 +877,31 @@ int bvh_shadow_shade(clrt_accel* a, const clrt_camera& cam, const clrt_contact* 
   CLRT_CUDA(cudaMemsetAsync(trace_counter(a), 0, 4, trace_stream(a)));
   return a->stats ? launch_shadow_shade<true>(a, cam, contacts, count, rgba8, d_ray_counter, packets)
                   : launch_shadow_shade<false>(a, cam, contacts, count, rgba8, d_ray_counter, packets);
+}
+
+template <bool S>
+static int launch_frame(clrt_accel* a, const clrt_camera& cam, uint32_t rank, uint32_t nranks, uint32_t* rgba8, unsigned long long* d_ray_counter, uint32_t packets) {
+  const clrt_scene* sc = a->scene;
+  unsigned grid = 0;
+  CLRT_TRY(persistent_grid<frame_kernel<S>>(a, TRACE_THREADS, FAST_SMEM_BYTES, packets, &grid));
+  const TraceView v = trace_view(a, true);
+  frame_kernel<S><<<grid, TRACE_THREADS, FAST_SMEM_BYTES, trace_stream(a)>>>(cam, rank, nranks, sc->d_lights, sc->n_lights, sc->d_materials, sc->n_materials,
+      v.wnodes, v.tris, a->n, rgba8, a->launch_targets, trace_counter(a), d_ray_counter, (unsigned long long*)(a->d_tile_counter + 4), overflow_word(a));
+  CLRT_CHECK_LAUNCH();
+  return 0;
+}
+
+// One stripe of a frame — primary rays, shadow rays, shading — in one launch (BVH, FAST policy; stripe-ordered RGBA8 or, with peer
+// targets, raster-ordered stores into every framebuffer).  d_ray_counter (may be NULL) accumulates the live shadow rays.
+int bvh_frame_fused(clrt_accel* a, const clrt_camera& cam, uint32_t rank, uint32_t nranks, uint32_t* rgba8, unsigned long long* d_ray_counter) {
+  if (!a->built) CLRT_FAIL("frame: the BVH was not constructed");
+  if (a->scene->n_lights + 1 > 32) CLRT_FAIL("fused frame supports at most 31 scene lights");
+  const TileGrid g = make_tile_grid(cam.resX, cam.resY);
+  const uint32_t packets = stripe_tile_count(g.tiles, rank, nranks) * 8u;
+  if (!packets) return 0;
+  CLRT_CUDA(cudaMemsetAsync(trace_counter(a), 0, 4, trace_stream(a)));
+  return a->stats ? launch_frame<true>(a, cam, rank, nranks, rgba8, d_ray_counter, packets)
+                  : launch_frame<false>(a, cam, rank, nranks, rgba8, d_ray_counter, packets);
 }
 
 // Traversal stacks are bounded (REF_STACK, FAST_STACK).  A push that does not fit is counted on the device instead of silently

@@ -150,6 +150,32 @@ __device__ __forceinline__ Slot2 wn_expand(const TraceNode* __restrict__ tnodes,
   s.lo1 = make_float4(q1.z, q1.w, q2.x, 0.0f); s.hi1 = make_float4(q2.y, q2.z, q2.w, 0.0f); s.c1 = q3.y;
   return s;
 }
+#if CLRT_WIDE_Q16
+// The quantisation grid: the root's box (union of its two child boxes in tnodes[0]) enlarged by a sliver, 65535 steps per axis.
+__global__ void wide_frame_kernel(const TraceNode* __restrict__ tnodes, QFrame* __restrict__ frame) {
+  const float4* p = reinterpret_cast<const float4*>(tnodes);
+  const float4 q0 = p[0], q1 = p[1], q2 = p[2];
+  const float lo[3] = {fminf(q0.x, q1.z), fminf(q0.y, q1.w), fminf(q0.z, q2.x)}, hi[3] = {fmaxf(q0.w, q2.y), fmaxf(q1.x, q2.z), fmaxf(q1.y, q2.w)};
+  float flo[3], step[3];
+  for (int a = 0; a < 3; a++) {
+    const float pad = (hi[a] - lo[a]) * (1.0f / 4096.0f) + (fabsf(lo[a]) + fabsf(hi[a])) * (1.0f / 1048576.0f) + 1.0e-30f;
+    flo[a] = lo[a] - pad;
+    step[a] = ((hi[a] + pad) - flo[a]) * (1.0f / 65535.0f) * 1.000002f;
+  }
+  frame->lox = flo[0]; frame->loy = flo[1]; frame->loz = flo[2]; frame->pad0 = 0.0f;
+  frame->stepx = step[0]; frame->stepy = step[1]; frame->stepz = step[2]; frame->pad1 = 0.0f;
+}
+// One bound pair on one axis -> 16-bit grid positions whose decoding lo + q * step (one fused rounding) contains [lo, hi].
+__device__ __forceinline__ void q16_pair(float flo, float step, float lo, float hi, bool valid, uint32_t& ql, uint32_t& qh) {
+  if (!valid) { ql = 65535u; qh = 0u; return; }
+  const float inv = 1.0f / step;
+  float l = fminf(fmaxf(floorf((lo - flo) * inv), 0.0f), 65535.0f), h = fminf(fmaxf(ceilf((hi - flo) * inv), 0.0f), 65535.0f);
+  while (l > 0.0f && fmaf(l, step, flo) > lo) l -= 1.0f;
+  while (h < 65535.0f && fmaf(h, step, flo) < hi) h += 1.0f;
+  ql = (uint32_t)l; qh = (uint32_t)h;
+}
+#endif
+
 __global__ void __launch_bounds__(128)
 widen_kernel(const TraceNode* __restrict__ tnodes, uint32_t n, WideNode* __restrict__ wnodes) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -159,6 +185,24 @@ widen_kernel(const TraceNode* __restrict__ tnodes, uint32_t n, WideNode* __restr
   const uint4 q3 = __ldg(reinterpret_cast<const uint4*>(p + 3));
   const Slot2 a = wn_expand(tnodes, n, q3.x, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y);
   const Slot2 b = wn_expand(tnodes, n, q3.y, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w);
+#if CLRT_WIDE_Q16
+  const QFrame f = *reinterpret_cast<const QFrame*>(wnodes + n + WIDE_TOP_NODES);
+  const uint32_t c[4] = {a.c0, a.c1, b.c0, b.c1};
+  const float4 lo[4] = {a.lo0, a.lo1, b.lo0, b.lo1}, hi[4] = {a.hi0, a.hi1, b.hi0, b.hi1};
+  uint32_t ql[3][4], qh[3][4];
+#pragma unroll
+  for (int j = 0; j < 4; j++) {
+    const bool valid = c[j] != 0xFFFFFFFFu;
+    q16_pair(f.lox, f.stepx, lo[j].x, hi[j].x, valid, ql[0][j], qh[0][j]);
+    q16_pair(f.loy, f.stepy, lo[j].y, hi[j].y, valid, ql[1][j], qh[1][j]);
+    q16_pair(f.loz, f.stepz, lo[j].z, hi[j].z, valid, ql[2][j], qh[2][j]);
+  }
+  uint4* o = reinterpret_cast<uint4*>(wnodes + i);
+  o[0] = make_uint4(ql[0][0] | (ql[0][1] << 16), ql[0][2] | (ql[0][3] << 16), ql[1][0] | (ql[1][1] << 16), ql[1][2] | (ql[1][3] << 16));
+  o[1] = make_uint4(ql[2][0] | (ql[2][1] << 16), ql[2][2] | (ql[2][3] << 16), qh[0][0] | (qh[0][1] << 16), qh[0][2] | (qh[0][3] << 16));
+  o[2] = make_uint4(qh[1][0] | (qh[1][1] << 16), qh[1][2] | (qh[1][3] << 16), qh[2][0] | (qh[2][1] << 16), qh[2][2] | (qh[2][3] << 16));
+  o[3] = make_uint4(c[0], c[1], c[2], c[3]);
+#else
   float4* o = reinterpret_cast<float4*>(wnodes + i);
   o[0] = make_float4(a.lo0.x, a.lo1.x, b.lo0.x, b.lo1.x);
   o[1] = make_float4(a.lo0.y, a.lo1.y, b.lo0.y, b.lo1.y);
@@ -168,6 +212,7 @@ widen_kernel(const TraceNode* __restrict__ tnodes, uint32_t n, WideNode* __restr
   o[5] = make_float4(a.hi0.z, a.hi1.z, b.hi0.z, b.hi1.z);
   reinterpret_cast<uint4*>(o)[6] = make_uint4(a.c0, a.c1, b.c0, b.c1);
   reinterpret_cast<uint4*>(o)[7] = make_uint4(0u, 0u, 0u, 0u);
+#endif
 }
 
 // Top table (the north star's "staging of the top BVH levels"): the first WIDE_TOP_LEVELS levels of the wide tree copied in
@@ -188,19 +233,25 @@ wide_top_kernel(const WideNode* __restrict__ wnodes, uint32_t n, WideNode* __res
       const int s = first + k;
       const uint32_t id = src[s];
       uint4* o = reinterpret_cast<uint4*>(top + s);
-      if (id == 0xFFFFFFFFu) {                                 // unused slot: NaN boxes, empty children
+      constexpr int CH = sizeof(WideNode) / 16 - (CLRT_WIDE_Q16 ? 1 : 2);     // index of the 16 bytes holding the four child ids
+      if (id == 0xFFFFFFFFu) {                                 // unused slot: boxes no ray enters, empty children
+#if CLRT_WIDE_Q16
+        o[0] = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu); o[1] = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0u, 0u); o[2] = make_uint4(0u, 0u, 0u, 0u);
+#else
         const uint32_t q = 0x7fc00000u;
         for (int w = 0; w < 6; w++) o[w] = make_uint4(q, q, q, q);
-        o[6] = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu); o[7] = make_uint4(0u, 0u, 0u, 0u);
+        o[7] = make_uint4(0u, 0u, 0u, 0u);
+#endif
+        o[CH] = make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu);
         continue;
       }
       const uint4* p = reinterpret_cast<const uint4*>(wnodes + (id - n));
-      for (int w = 0; w < 6; w++) o[w] = p[w];
-      uint4 ch = p[6];
+      for (int w = 0; w < (int)(sizeof(WideNode) / 16); w++) o[w] = p[w];
+      const uint4 ch = p[CH];
       uint32_t c[4] = {ch.x, ch.y, ch.z, ch.w};
       for (int j = 0; j < 4; j++)
         if (level + 1 < WIDE_TOP_LEVELS && c[j] != 0xFFFFFFFFu && c[j] >= n) { src[4 * s + 1 + j] = c[j]; c[j] = WIDE_TOP_BIT | (uint32_t)(4 * s + 1 + j); }
-      o[6] = make_uint4(c[0], c[1], c[2], c[3]); o[7] = make_uint4(0u, 0u, 0u, 0u);
+      o[CH] = make_uint4(c[0], c[1], c[2], c[3]);
     }
     __syncthreads();
     first += count; count *= 4;
@@ -237,11 +288,15 @@ int trace_tree_build(clrt_accel* a) {
   if (n < 2) return 0;
   cudaStream_t s = ctx->stream;
   const bool tm = a->timing;
-  const size_t wide_bytes = ((size_t)n + WIDE_TOP_NODES) * sizeof(WideNode);      // per-node records, then the top table
+  const size_t wide_bytes = ((size_t)n + WIDE_TOP_NODES + 1) * sizeof(WideNode);  // per-node records, the top table, the quantisation grid
   if (wide_bytes > a->wnodes_cap) CLRT_CUDA(cudaStreamSynchronize(s));
   CLRT_TRY(clrt_grow((void**)&a->d_wnodes, &a->wnodes_cap, wide_bytes));
   if (tm) CLRT_CUDA(cudaEventRecord(a->ev[5], s));
   if (want) CLRT_TRY(trace_tree_separate(a));
+#if CLRT_WIDE_Q16
+  wide_frame_kernel<<<1, 1, 0, s>>>(want ? a->d_tt_nodes : a->d_tnodes, reinterpret_cast<QFrame*>(a->d_wnodes + n + WIDE_TOP_NODES));
+  CLRT_CHECK_LAUNCH();
+#endif
   widen_kernel<<<(n + 127) / 128, 128, 0, s>>>(want ? a->d_tt_nodes : a->d_tnodes, n, a->d_wnodes);
   CLRT_CHECK_LAUNCH();
   wide_top_kernel<<<1, WIDE_TOP_NODES <= 1024 ? 512 : 1024, 0, s>>>(a->d_wnodes, n, a->d_wnodes + n);

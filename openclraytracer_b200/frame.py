@@ -91,19 +91,25 @@ def slot_sequence(frame_no, depth):
     return frame_no % depth, frame_no // depth + 1
 
 
-def peer_frame_ops(frame_no, depth, rank, world):
-    """The stream-ordered steps one GPU enqueues for one frame, as (op, ...) tuples — what clrt_render_frame_peers launches.
+def peer_frame_ops(frame_no, depth, rank, world, split=True):
+    """The stream-ordered steps one GPU enqueues for one frame, as (stream, op, ...) tuples — what clrt_render_frame_peers launches.
+    stream = ("trace", slot) or ("consumer",).  split: the waiting half of the exchange (everybody's ready -> consume -> ack) runs on
+    the consumer stream behind an event of this frame's own "ready"; otherwise everything is on the slot's trace stream.
     tests/test_frame_host.py runs these for all ranks under random interleavings: no deadlock, no framebuffer overwritten
     before every GPU consumed it, every consumed frame complete."""
     k, seq = slot_sequence(frame_no, depth)
+    t, c = ("trace", k), (("consumer",) if split else ("trace", k))
     ops = []
     if seq > 1:
-        ops.append(("wait", [peer_word(PEER_ACK, k, w) for w in range(world)], seq - 1))
-    ops.append(("store_pixels", k, frame_no))                          # into every GPU's framebuffer k
-    ops.append(("signal", peer_word(PEER_READY, k, rank), seq))       # on every GPU
-    ops.append(("wait", [peer_word(PEER_READY, k, w) for w in range(world)], seq))
-    ops.append(("consume", k, frame_no))                               # read-back / display
-    ops.append(("signal", peer_word(PEER_ACK, k, rank), seq))
+        ops.append((t, "wait", [peer_word(PEER_ACK, k, w) for w in range(world)], seq - 1))
+    ops.append((t, "store_pixels", k, frame_no))                          # into every GPU's framebuffer k
+    ops.append((t, "signal", peer_word(PEER_READY, k, rank), seq))       # on every GPU
+    if split:
+        ops.append((t, "record", frame_no))
+        ops.append((c, "wait_event", frame_no))
+    ops.append((c, "wait", [peer_word(PEER_READY, k, w) for w in range(world)], seq))
+    ops.append((c, "consume", k, frame_no))                               # read-back / display
+    ops.append((c, "signal", peer_word(PEER_ACK, k, rank), seq))
     return ops
 
 
@@ -152,6 +158,7 @@ class FrameRenderer:
         if self.exchange not in ("nccl", "push", "fused"):
             raise ValueError("CLRT_EXCHANGE=%r (nccl, push or fused)" % self.exchange)
         self._peer_block = None
+        self.split_exchange = os.environ.get("CLRT_SPLIT_EXCHANGE", "1") != "0"
         if self.exchange != "nccl":
             self._setup_peers()
         self.stripe, self.gathered, self.raster, self.host_raster = self.stripes[0], self.gathereds[0], self.rasters[0], self.host_rasters[0]
@@ -229,9 +236,12 @@ class FrameRenderer:
         s = ts.cuda_stream
         if self.exchange == "fused" and shadows:          # the whole protocol below in one C call
             host = self.host_rasters[k].data_ptr() if (to_host and self.rank == 0) else None
-            rays = self.accel.render_frame_peers(s, k, camera, self.rank, self.world, self._peer_rasters[k], self._peer_flags, seq, host, want_rays)
+            # the exchange's waiting half (everybody's ready -> read-back -> ack) runs on the `comm` stream: the slot's trace stream
+            # never waits for the other GPUs' stripes, nor for rank 0's 8 MB read-back
+            rays = self.accel.render_frame_peers(s, k, camera, self.rank, self.world, self._peer_rasters[k], self._peer_flags, seq, host, want_rays,
+                                                 consumer_stream=self.comm.cuda_stream if self.split_exchange else None)
             if to_host:
-                self.ev_host[k].record(ts)
+                self.ev_host[k].record(self.comm if self.split_exchange else ts)
             self.stripe, self.raster, self.host_raster = self.stripes[k], self.rasters[k], self.host_rasters[k]
             return rays
         with torch.cuda.stream(ts):

@@ -66,8 +66,8 @@ def test_orbit_camera_step0_is_the_demo_camera():
     assert np.allclose(a["viewTransform"], b["viewTransform"], atol=1e-6) and a["FOVDistance"] == b["FOVDistance"]
 
 
-def _simulate_peer_frames(world, depth, frames, seed, skip_ack_wait=False):
-    """Discrete model of the peer-memory exchange: every GPU has `depth` in-order streams, 128 flag words and `depth`
+def _simulate_peer_frames(world, depth, frames, seed, skip_ack_wait=False, split=True):
+    """Discrete model of the peer-memory exchange: every GPU has `depth` in-order trace streams (+ one consumer stream when split), 128 flag words and `depth`
     framebuffers holding, per writer, the frame number last stored.  A random scheduler picks any stream whose head op can run.
     Returns None, or a string naming the first violated invariant."""
     import random
@@ -75,25 +75,31 @@ def _simulate_peer_frames(world, depth, frames, seed, skip_ack_wait=False):
     flags = [[0] * frame.PEER_WORDS for _ in range(world)]
     fb = [[[-1] * world for _ in range(depth)] for _ in range(world)]          # fb[gpu][slot][writer] = frame
     consumed = [[-1] * depth for _ in range(world)]                            # last frame consumed from fb[gpu][slot]
-    streams = [[[] for _ in range(depth)] for _ in range(world)]
+    streams = [dict() for _ in range(world)]                      # per GPU: stream name -> queue of ops
+    recorded = [set() for _ in range(world)]
     for f in range(frames):
         for r in range(world):
-            ops = frame.peer_frame_ops(f, depth, r, world)
-            if skip_ack_wait:
-                ops = [o for o in ops if not (o[0] == "wait" and o[1][0] >= frame.PEER_ACK)]
-            streams[r][f % depth].extend(ops)
-    pending = sum(len(q) for s in streams for q in s)
+            for op in frame.peer_frame_ops(f, depth, r, world, split=split):
+                if skip_ack_wait and op[1] == "wait" and op[2][0] >= frame.PEER_ACK:
+                    continue
+                streams[r].setdefault(op[0], []).append(op[1:])
+    pending = sum(len(q) for s in streams for q in s.values())
     while pending:
         ready = []
         for r in range(world):
-            for k in range(depth):
-                q = streams[r][k]
-                if q and (q[0][0] != "wait" or all(flags[r][w] >= q[0][2] for w in q[0][1])):
-                    ready.append((r, k))
+            for name, q in streams[r].items():
+                if not q:
+                    continue
+                op = q[0]
+                if op[0] == "wait" and not all(flags[r][w] >= op[2] for w in op[1]):
+                    continue
+                if op[0] == "wait_event" and op[1] not in recorded[r]:
+                    continue
+                ready.append((r, name))
         if not ready:
             return "deadlock with %d ops pending" % pending
-        r, k = rng.choice(ready)
-        op = streams[r][k].pop(0)
+        r, name = rng.choice(ready)
+        op = streams[r][name].pop(0)
         pending -= 1
         if op[0] == "store_pixels":
             _, slot, f = op
@@ -104,6 +110,8 @@ def _simulate_peer_frames(world, depth, frames, seed, skip_ack_wait=False):
         elif op[0] == "signal":
             for g in range(world):
                 flags[g][op[1]] = op[2]
+        elif op[0] == "record":
+            recorded[r].add(op[1])
         elif op[0] == "consume":
             _, slot, f = op
             if fb[r][slot] != [f] * world:
@@ -117,10 +125,11 @@ def test_peer_exchange_protocol_under_random_interleavings(world, depth):
     """The N > 1 path has no collective to run over gloo: its host-side logic IS the flag protocol (frame.peer_frame_ops = what
     clrt_render_frame_peers enqueues).  Random schedules of all GPUs' streams: never a deadlock, never a framebuffer overwritten
     before every GPU consumed it, never a torn frame.  Control: without the ack wait the model must catch an overwrite."""
-    for seed in range(25):
-        assert _simulate_peer_frames(world, depth, 5 * depth + 3, seed) is None
-    caught = [_simulate_peer_frames(world, depth, 5 * depth + 3, seed, skip_ack_wait=True) for seed in range(25)]
-    assert any(c is not None and "overwrote" in c for c in caught)
+    for split in (True, False):
+        for seed in range(25):
+            assert _simulate_peer_frames(world, depth, 5 * depth + 3, seed, split=split) is None
+        caught = [_simulate_peer_frames(world, depth, 5 * depth + 3, seed, skip_ack_wait=True, split=split) for seed in range(25)]
+        assert any(c is not None and "overwrote" in c for c in caught)
 
 
 def test_peer_flag_words_do_not_collide():

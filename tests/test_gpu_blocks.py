@@ -29,6 +29,18 @@ def test_radix_sort_matches_stable_oracle(ctx, O, n):
     buf.free()
 
 
+@pytest.mark.parametrize("n", [1, 2, 1001, 70_000])
+def test_radix_sort_of_a_slice_at_an_odd_pair_offset(ctx, O, n):
+    """The interface asks for 8-byte alignment (a uint2); a slice that starts at an odd pair is not 16-byte aligned."""
+    p = make_pairs(n + 3, seed=n)
+    buf = api.Buffer.from_array(ctx, p)
+    api.BitonicSort(ctx).sort(buf.getCLMem() + 8, n)
+    got = buf.copyToHost(L.UINT2, n + 3)
+    assert np.array_equal(got[1:1 + n], O.sort_pairs_stable(p[1:1 + n]))
+    assert np.array_equal(got[:1], p[:1]) and np.array_equal(got[1 + n:], p[1 + n:])
+    buf.free()
+
+
 def test_radix_sort_few_distinct_keys_and_extremes(ctx, O):
     n = 200_000
     p = make_pairs(n, 5)

@@ -273,13 +273,15 @@ def test_fused_shadow_pass_equals_three_kernel_pipeline(ctx, name):
     buf = scenes.soup_scene(60_000, seed=5) if name == "soup" else scenes.load_bundled(name)
     scene, bvh = build_gpu(ctx, buf)
     for cam in (api.demo_camera(buf, 320, 180), api.demo_camera(buf, 97, 61)):
-        bvh.set_fused_shadows(True)
-        a, ra = bvh.render_frame_host(cam, shadows=True, want_rays=True)
-        a = a.copy()
         bvh.set_fused_shadows(False)
         b, rb = bvh.render_frame_host(cam, shadows=True, want_rays=True)
-        assert np.array_equal(a, b) and ra == rb
-        assert (a[..., 3] == 255).any()
+        b = b.copy()
+        for mode in (1, 2):                     # 1: the one-kernel frame (default); 2: primary kernel + fused shadow/shade kernel
+            bvh.set_fused_shadows(mode)
+            a, ra = bvh.render_frame_host(cam, shadows=True, want_rays=True)
+            assert np.array_equal(a, b) and ra == rb, mode
+        assert (b[..., 3] == 255).any()
+    bvh.set_fused_shadows(True)
     # stand-alone entry point over the primary contacts
     cam = api.demo_camera(buf, 160, 90)
     n = 160 * 90

@@ -122,3 +122,28 @@ def test_tlg_degenerate_scene_is_an_error(ctx):
     with pytest.raises(api.ClrtError, match="degenerate"):
         tlg.initializeFrame()
     tlg.free(); scene.free()
+
+
+@pytest.mark.parametrize("name", ["cube", "tenryuu", "clumsydragon", "soup"])
+def test_corrected_grid_walk_returns_the_bvh_closest_hits(ctx, O, name):
+    """Row f4 (KNOWN_ISSUES Q21): CLRT_TRACE_FAST on a grid selects the corrected two-level DDA (entry = max of the slab entries, the
+    closest hit kept across cells, the walk ends when it lies in a finished cell).  Its contacts must be the TRUE closest hits —
+    the oracle's BVH contacts — by the north-star tolerances, for camera rays and for generic rays; the default stays the literal walk."""
+    from test_gpu_bvh import compare_fast
+    buf = scenes.soup_scene(40_000, seed=11, tris_per_mesh=8192) if name == "soup" else scenes.load_bundled(name)
+    scene, tlg = build_gpu(ctx, buf)
+    b = O.bvh_build(buf)
+    for cam in (api.demo_camera(buf, 320, 200), api.demo_camera(buf, 97, 61)):
+        want = O.bvh_trace_primary(cam, b)
+        tlg.set_trace_mode(api.TRACE_FAST)
+        tlg.generateContacts(cam)
+        got = tlg.download_primary_contacts()
+        compare_fast(got, want, b["tris"])
+        assert np.array_equal(got["materialIndex"][want["nd"][:, 3] > 0], want["materialIndex"][want["nd"][:, 3] > 0])
+    n = 320 * 200
+    cam = api.demo_camera(buf, 320, 200)
+    rays = api.Buffer(ctx, n * 48); contacts = api.Buffer(ctx, n * 32)
+    api.generate_primary_rays(ctx, cam, rays.getCLMem())
+    tlg.generateContacts(rays, contacts, n)
+    compare_fast(contacts.copyToHost(L.CONTACT, n), O.bvh_trace_primary(cam, b), b["tris"])
+    rays.free(); contacts.free(); tlg.free(); scene.free()
