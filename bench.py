@@ -43,6 +43,7 @@ WORKLOADS = {
     "clumsydragon": ("Mrays/s (primary+shadow, 1080p)", (1920, 1080), "bundled mesh, synthetic camera path"),
     "spheres10m": ("Mrays/s (primary+diffuse bounce, 4K)", (3840, 2160), "synthetic"),
 }
+ACCEL_NAME = {"BVH": "LBVH", "GRID": "Two-Level Grid (corrected closest-hit walk)", "KD": "KD-tree (ours; the reference's TODO 2.1)"}
 LANE_OPS_PER_WIDE_VISIT = 120.0      # ~60 lane-ops per binary inner-node visit (two slab tests); a 4-wide visit = two of them
 LANE_OPS_PER_TRI_TEST = 75.0         # Moeller-Trumbore incl. normal
 
@@ -118,11 +119,16 @@ class CpuReference:
     oracle/_ref/libclrt_ref.so (the reference's headers compiled in place, OpenMP over work-items) when present ("reference"), else the
     oracle port ("port")."""
 
-    def __init__(self, scene_buf, accel="BVH"):
+    def __init__(self, scene_buf, accel="BVH", force_port=False):
         from oracle import oracle_py as O
         O.build(("oracle",))
         self.O, self.scene, self.accel = O, scene_buf, accel
-        self.kind = "reference" if O.have_ref() else "port"
+        # force_port: Spheres-10M has 2000 sub-meshes and the reference fetches a triangle by walking the sub-mesh headers
+        # (SceneBufferParser.h:253-293, O(#sub-meshes) per fetch): its literal code needs minutes per 4K frame.  The oracle port reads the
+        # flattened triangle array instead (validated against the literal walk on small scenes) — same arithmetic, bounded time.
+        self.kind = "reference" if (O.have_ref() and not force_port) else "port"
+        if accel == "KD":
+            accel = self.accel = "BVH"                  # the reference has no KD-tree: its BVH is the CPU arm of that workload
         if accel == "GRID" and self.kind != "reference":
             raise SystemExit("the Two-Level Grid has no oracle port: oracle/_ref/libclrt_ref.so (the reference's own code) is required")
         # all the host cores this process may run on — torchrun exports OMP_NUM_THREADS=1 to its workers, which would time the
@@ -220,10 +226,16 @@ def cpu_frame_fn(ref, workload):
     return ref.bounce_frame if workload == "spheres10m" else ref.frame
 
 
+def cpu_sample_resolution(workload, res):
+    """The CPU arm's frame: the bench resolution, except Spheres-10M (a quarter of 4K per axis: a 4K frame is minutes of CPU work)."""
+    return (res[0] // 4, res[1] // 4) if workload == "spheres10m" else res
+
+
 def cpu_baseline(scene_buf, res, workload, accel, budget_s=14.0, single_thread_budget_s=4.0):
-    """Bounded sample of the same workload on the host cores: whole frames of the bench resolution and camera path for ~budget_s."""
+    """Bounded sample of the same workload on the host cores: whole frames of the bench camera path for ~budget_s."""
     from openclraytracer_b200 import frame
-    ref = CpuReference(scene_buf, accel)
+    ref = CpuReference(scene_buf, accel, force_port=(workload == "spheres10m"))
+    res = cpu_sample_resolution(workload, res)
     fn = cpu_frame_fn(ref, workload)
     rays, secs, frames = 0, 0.0, 0
     while frames < 1 or (secs < budget_s and frames < 64):
@@ -248,7 +260,9 @@ def run_reference(args, workload_desc, scene_buf, n_tris):
         return
     from openclraytracer_b200 import frame
     metric, res, data = WORKLOADS[args.workload]
-    ref = CpuReference(scene_buf, args.accel)
+    full_res = res
+    res = cpu_sample_resolution(args.workload, res)
+    ref = CpuReference(scene_buf, args.accel, force_port=(args.workload == "spheres10m"))
     fn = cpu_frame_fn(ref, args.workload)
     rays, secs = 0, 0.0
     for i in range(args.warmup + args.steps):
@@ -260,8 +274,8 @@ def run_reference(args, workload_desc, scene_buf, n_tris):
     line = {"impl": "reference", "metric": metric, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": secs / args.steps * 1e3, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": data,
-            "config": {"workload": workload_desc, "resolution": "%dx%d" % res, "accel": "LBVH" if args.accel == "BVH" else "Two-Level Grid",
-                       "triangles": n_tris, "rays_per_step": rays // max(args.steps, 1)},
+            "config": {"workload": workload_desc, "resolution": "%dx%d" % full_res + ("" if res == full_res else " (bounded sample: %dx%d frames)" % res),
+                       "accel": ACCEL_NAME[args.accel], "triangles": n_tris, "rays_per_step": rays // max(args.steps, 1)},
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": ref.cores, "kind": ref.kind, "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "build_ms_per_Mtri": ref.build_ms / (n_tris / 1e6)}
@@ -347,7 +361,8 @@ def main():
     ap.add_argument("--workload", default="soup1m", choices=sorted(WORKLOADS),
                     help="soup1m = BASELINE.json configs[2] (the config the metric is quoted on at 1/2/4/8 GPUs; default), clumsydragon = configs[1], "
                          "spheres10m = configs[3] (4K, primary + diffuse bounce)")
-    ap.add_argument("--accel", default="BVH", choices=["BVH", "GRID"], help="acceleration structure (-accStruct of the reference's demo)")
+    ap.add_argument("--accel", default="BVH", choices=["BVH", "GRID", "KD"],
+                    help="acceleration structure (-accStruct of the reference's demo; KD = the KD-tree manager, the reference's TODO 2.1)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-kernels", action="store_true", help="skip the per-kernel build/sort/scan roofline section")
     args = ap.parse_args()
@@ -386,7 +401,7 @@ def main():
     # ---- build (once; timed separately, median of several) ------------------------------------------------
     r.accel.enable_stage_timing(True)
     build_ms, stages = [], []
-    stage_ids = (0, 1, 2, 3, api.STAGE_TRACE_TREE) if args.accel == "BVH" else (8, 9, 10, 11, 12)
+    stage_ids = (0, 1, 2, 3, api.STAGE_TRACE_TREE) if args.accel == "BVH" else (8, 9, 10, 11, 12) if args.accel == "GRID" else (api.STAGE_TOTAL,)
     for i in range(8):
         r.build()
         build_ms.append(r.accel.stage_ms(api.STAGE_TOTAL))
@@ -480,16 +495,17 @@ def main():
             launches, pipeline = 5, "one frame at a time on one stream"           # primary, bounce rays, trace, shade, untile (+ NCCL's own kernel at N > 1)
             secondary = "one cosine-weighted diffuse bounce ray per hit through generateContacts(rays, contacts, n)"
         else:
-            # BVH: frame_kernel + untile_kernel (nccl) | push, 2 signal, 2 wait (push) | ack wait, exchange (fused)
+            # BVH: trace_primary_kernel, shadow_shade_kernel (or frame_kernel alone) + untile_kernel (nccl) | push, 2 signal, 2 wait (push) |
+            # ack wait, ready signal, ready wait, ack signal (fused, split exchange)
             # GRID: primary, shadow-ray generation, generic trace, shade, untile
-            launches = {"nccl": 2, "push": 6, "fused": 3}[exchange] if args.accel == "BVH" else 5
+            launches = ({"nccl": 3, "push": 7, "fused": 5}[exchange] - (1 if r.one_kernel else 0)) if args.accel == "BVH" else 5
             pipeline = f"{r.DEPTH} frame(s) in flight" + (": frames traced on alternating streams (frame slots)" if r.DEPTH > 1 else "")
             secondary = "1 shadow ray per hit per light (scene light + camera light)"
         line = {
             "metric": metric, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f32", "data": data,
-            "config": {"workload": workload_desc, "resolution": "%dx%d" % RES, "accel": "LBVH" if args.accel == "BVH" else "Two-Level Grid",
+            "config": {"workload": workload_desc, "resolution": "%dx%d" % RES, "accel": ACCEL_NAME[args.accel],
                        "triangles": n_tris, "rays_per_step": total_rays // args.steps, "secondary": secondary,
                        "parallelism": f"image-space tile stripes x{world}, redundant build, " + EXCHANGE_DESC[exchange],
                        "l2": "inputs larger than L2: the per-step working set (contacts, rays, framebuffers: > 130 MB at 1080p with frames in "
@@ -502,7 +518,8 @@ def main():
             "pipeline": pipeline,
             "build_ms": build_med, "build_ms_per_Mtri": build_med / (n_tris / 1e6),
             "build_stage_ms": dict(zip(["morton", "sort", "emit", "refit", "trace_structure"] if args.accel == "BVH" else
-                                       ["count_top", "top_pairs", "leaf_cells", "leaf_count", "leaf_pairs"], [float(x) for x in stage_med])),
+                                       ["count_top", "top_pairs", "leaf_cells", "leaf_count", "leaf_pairs"] if args.accel == "GRID" else ["total"],
+                                       [float(x) for x in stage_med])),
             "clocks": clocks,
         }
         if args.accel == "BVH":
@@ -516,9 +533,9 @@ def main():
                                          "wide_visits_per_ray": v["inner_per_ray"], "tri_tests_per_ray": v["tris_per_ray"],
                                          "issue_frac": issue_roofline(v, args.workload, sm_count, float(clock), peak_src)["frac"]} for k, v in kt.items()}
         else:
-            line["roofline"] = {"bound": "issue", "kernel": "tlg_trace_primary_kernel / tlg_trace_rays_kernel", "achieved": None, "peak": None,
+            line["roofline"] = {"bound": "issue", "kernel": "tlg_trace_*_kernel" if args.accel == "GRID" else "kd_trace_*_kernel", "achieved": None, "peak": None,
                                 "unit": "Tlane-op/s", "frac": None, "traffic": None,
-                                "note": "the grid walk has no statistics mode (cells stepped per ray are not counted): kernel-only rate under 'value'"}
+                                "note": "this walk has no statistics mode (cells / nodes stepped per ray are not counted): see 'value'"}
         if not args.no_kernels:
             line["kernels"] = kernel_rooflines(r, hbm_peak, n_tris, stage_med, args.accel)
         if not args.no_cpu_baseline and world == 1:          # the CPU baseline is reported at N = 1 only

@@ -236,9 +236,9 @@ int clrt_render_stripe(clrt_accel* accel, const clrt_camera* h_camera, int shado
  * a slot and of dptr_rgba8 (stream order / events). */
 int clrt_render_stripe_on(clrt_accel* accel, void* stream, int slot, const clrt_camera* h_camera, int shadows, uint32_t rank,
                           uint32_t nranks, void* dptr_rgba8, uint64_t* out_rays);
-/* The frame entry points run a BVH frame (or stripe) as ONE kernel: primary ray, occlusion queries to the lights, shading
- * (on == 1, the default with the FAST policy).  on == 2: two kernels (primary contacts, then shadow + shade over them);
- * on == 0: the three-call pipeline (clrt_generate_shadow_rays -> clrt_trace_rays -> clrt_shade).  Pixels are identical. */
+/* The frame entry points fuse the shadow pass with the shading on a BVH: on == 1 (default) two kernels — primary contacts, then
+ * occlusion queries + Blinn-Phong over them; on == 2 ONE kernel for the whole stripe (primary ray, occlusion queries, shading; FAST
+ * policy); on == 0 the three-call pipeline (clrt_generate_shadow_rays -> clrt_trace_rays -> clrt_shade).  Pixels are identical. */
 int clrt_accel_set_fused_shadows(clrt_accel* accel, int on);
 int clrt_frame_untile(clrt_ctx* ctx, const void* dptr_stripes, uint32_t resX, uint32_t resY, uint32_t nranks, void* dptr_raster_rgba8);
 /* The same on a caller-chosen cudaStream_t (the frame pipeline runs gather + untile + read-back of frame k on a second

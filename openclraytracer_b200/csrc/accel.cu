@@ -86,8 +86,8 @@ extern "C" int clrt_accel_set_trace_mode(clrt_accel* a, int mode) {
 }
 extern "C" int clrt_accel_set_fused_shadows(clrt_accel* a, int on) {
   if (!a) CLRT_FAIL("clrt_accel_set_fused_shadows: NULL accel");
-  // 0: three kernels (primary, generic shadow rays, shade); 1: the default — one frame kernel; 2: two kernels (primary, shadow + shade)
-  a->unfused_shadows = on == 0; a->two_kernel_frame = on == 2; return 0;
+  // 0: three kernels (primary, generic shadow rays, shade); 1: the default — two kernels (primary, shadow + shade); 2: one frame kernel
+  a->unfused_shadows = on == 0; a->one_kernel_frame = on == 2; return 0;
 }
 extern "C" int clrt_accel_enable_stage_timing(clrt_accel* a, int on) {
   if (!a) CLRT_FAIL("clrt_accel_enable_stage_timing: NULL accel");
@@ -215,9 +215,10 @@ static int render_stripe_impl(clrt_accel* a, const clrt_camera* h_camera, int sh
   clrt_ray* srays = (clrt_ray*)(base + contacts_bytes);
   clrt_contact* scont = (clrt_contact*)(base + contacts_bytes + srays_bytes);
   unsigned long long* counter = (unsigned long long*)(base + contacts_bytes + srays_bytes + scont_bytes);
-  // One launch for the whole stripe (primary + shadow + shading) when the fused shadow pass applies and the FAST policy is on;
-  // REFERENCE_ORDER keeps its own primary kernel (the parity vehicle) followed by the shadow + shade kernel.
-  const bool one_kernel = fused && a->trace_mode == CLRT_TRACE_FAST && !a->two_kernel_frame;
+  // Two launches by default: primary contacts, then shadow + shade over them.  clrt_accel_set_fused_shadows(2) runs the whole stripe
+  // as ONE launch (FAST policy only): one drain instead of two, no contacts through memory — but warps that mix closest-hit and
+  // occlusion rays lose coherence: measured on Soup-1M at 1080p, one GPU, 2.45 ms per frame against 2.31 (profiles/r02_experiments.md).
+  const bool one_kernel = fused && a->trace_mode == CLRT_TRACE_FAST && a->one_kernel_frame;
   if (slots && one_kernel) {
     if (out_rays) CLRT_CUDA(cudaMemsetAsync(counter, 0, 8, stream));
     CLRT_TRY(bvh_frame_fused(a, cam, rank, nranks, (uint32_t*)dptr_rgba8, out_rays ? counter : nullptr));

@@ -123,7 +123,7 @@ struct clrt_accel {
   int trace_mode = CLRT_TRACE_FAST;
   bool timing = false;
   bool unfused_shadows = false;     // frame entry points: force the three-kernel shadow pipeline (parity checks)
-  bool two_kernel_frame = false;    // frame entry points: primary kernel + shadow/shade kernel instead of the one frame kernel
+  bool one_kernel_frame = false;    // frame entry points: the whole stripe in one launch (frame_kernel) instead of primary + shadow/shade
   bool stats = false;               // traversal statistics mode (rays, inner visits, triangle tests)
   float stage_ms[CLRT_STAGE_COUNT] = {0};
   cudaEvent_t ev[CLRT_STAGE_COUNT + 1] = {nullptr};

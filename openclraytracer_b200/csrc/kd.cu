@@ -36,7 +36,7 @@ struct KdState {
 
 namespace {
 
-struct KdGrid { float lox, loy, loz, csx, csy, csz; int levels; };
+struct KdGrid { float lox, loy, loz, csx, csy, csz; int levels; clrt_aabb box; };   // box: the scene box (tie-break by the reference's order)
 
 __device__ __forceinline__ uint32_t kd_expand_bits(uint32_t v) {
   v = (v * 0x00010001u) & 0xFF0000FFu;
@@ -204,7 +204,8 @@ __device__ __forceinline__ KdHit kd_traverse(Vec3 o, Vec3 d, const KdGrid& g, co
       const float4* t4 = reinterpret_cast<const float4*>(tris + id);
       const float4 a = __ldg(t4), b = __ldg(t4 + 1), c = __ldg(t4 + 2);
       const float t = triangle_intersect(v3(a.x, a.y, a.z), v3(b.x, b.y, b.z), v3(c.x, c.y, c.z), o, d);
-      if (t > 0.0f && (t < best.t || (t == best.t && id < best.tri))) { best.t = t; best.tri = id; }
+      // bit-equal t: the reference's traversal keeps the triangle that comes first in its sorted (Morton code, index) order
+      if (t > 0.0f && (t < best.t || (t == best.t && reference_order_before(tris, id, best.tri, g.box)))) { best.t = t; best.tri = id; }
     }
     if (best.t <= tmax * slack) return best;                       // the closest hit lies in a region already finished
     if (sp == 0) break;
@@ -301,8 +302,8 @@ static int kd_grow(clrt_ctx* ctx, void** p, size_t* cap, size_t bytes) {
   if (bytes > *cap || !*p) { CLRT_CUDA(cudaStreamSynchronize(ctx->stream)); CLRT_TRY(clrt_grow(p, cap, bytes ? bytes : 16)); }
   return 0;
 }
-static KdGrid kd_grid_of(const KdState* k) {
-  KdGrid g; g.lox = k->lo[0]; g.loy = k->lo[1]; g.loz = k->lo[2]; g.csx = k->cs[0]; g.csy = k->cs[1]; g.csz = k->cs[2]; g.levels = k->levels;
+static KdGrid kd_grid_of(const KdState* k, const clrt_accel* a) {
+  KdGrid g; g.box = a->scene->header.modelsBoundingBox; g.lox = k->lo[0]; g.loy = k->lo[1]; g.loz = k->lo[2]; g.csx = k->cs[0]; g.csy = k->cs[1]; g.csz = k->cs[2]; g.levels = k->levels;
   return g;
 }
 
@@ -343,7 +344,7 @@ int kd_construct(clrt_accel* a) {
   const uint32_t n = a->n;
   if (n != a->scene->n_tris) CLRT_FAIL("KD-tree construct: scene changed since initializeFrame");
   cudaStream_t s = ctx->stream;
-  const KdGrid g = kd_grid_of(k);
+  const KdGrid g = kd_grid_of(k, a);
   const bool tm = a->timing;
   if (tm) CLRT_CUDA(cudaEventRecord(a->ev[0], s));
   k->pairs = 0; k->leaves = 0;
@@ -403,7 +404,7 @@ int kd_trace_primary(clrt_accel* a, const clrt_camera& cam, clrt_contact* out, u
   CLRT_CUDA(cudaMemsetAsync(a->d_tile_counter, 0, 4, ctx->stream));
   unsigned grid = 0;
   CLRT_TRY(kd_grid_size<kd_trace_primary_kernel>(ctx, packets, &grid));
-  kd_trace_primary_kernel<<<grid, KD_THREADS, 0, ctx->stream>>>(cam, kd_grid_of(k), k->d_nodes, k->leaves, (const uint2*)k->d_ranges,
+  kd_trace_primary_kernel<<<grid, KD_THREADS, 0, ctx->stream>>>(cam, kd_grid_of(k, a), k->d_nodes, k->leaves, (const uint2*)k->d_ranges,
       (const uint2*)k->d_pairs, a->scene->d_tris, out, rank, nranks, raster, a->d_tile_counter, a->d_tile_counter + 13);
   CLRT_CHECK_LAUNCH();
   return 0;
@@ -417,7 +418,7 @@ int kd_trace_rays(clrt_accel* a, const clrt_ray* rays, clrt_contact* out, uint32
   CLRT_CUDA(cudaMemsetAsync(a->d_tile_counter, 0, 4, ctx->stream));
   unsigned grid = 0;
   CLRT_TRY(kd_grid_size<kd_trace_rays_kernel>(ctx, packets, &grid));
-  kd_trace_rays_kernel<<<grid, KD_THREADS, 0, ctx->stream>>>(rays, count, kd_grid_of(k), k->d_nodes, k->leaves, (const uint2*)k->d_ranges,
+  kd_trace_rays_kernel<<<grid, KD_THREADS, 0, ctx->stream>>>(rays, count, kd_grid_of(k, a), k->d_nodes, k->leaves, (const uint2*)k->d_ranges,
       (const uint2*)k->d_pairs, a->scene->d_tris, out, a->d_tile_counter, a->d_tile_counter + 13);
   CLRT_CHECK_LAUNCH();
   return 0;

@@ -90,3 +90,42 @@ __device__ __forceinline__ float triangle_intersect(Vec3 v0, Vec3 v1, Vec3 v2, V
 __device__ __forceinline__ Vec3 triangle_normal(Vec3 v0, Vec3 v1, Vec3 v2) {
   return vnormalize(vcross(vsub(v1, v0), vsub(v2, v0)));
 }
+
+// expandBits / morton3D (BVH.h:49-73)
+__device__ __forceinline__ uint32_t expand_bits(uint32_t v) {
+  v = (v * 0x00010001u) & 0xFF0000FFu;
+  v = (v * 0x00000101u) & 0x0F00F00Fu;
+  v = (v * 0x00000011u) & 0xC30C30C3u;
+  v = (v * 0x00000005u) & 0x49249249u;
+  return v;
+}
+__device__ __forceinline__ uint32_t morton3d(float x, float y, float z) {
+  x = rmin(rmax(x * 1024.0f, 0.0f), 1023.0f);
+  y = rmin(rmax(y * 1024.0f, 0.0f), 1023.0f);
+  z = rmin(rmax(z * 1024.0f, 0.0f), 1023.0f);
+  return expand_bits((uint32_t)x) * 4 + expand_bits((uint32_t)y) * 2 + expand_bits((uint32_t)z);
+}
+// normalizeScale -> translateScale(oldMin, oldMax, value, 0, 1)  (RTKernelUtils.h:63-81): no min subtraction (Q6)
+__device__ __forceinline__ float normalize_scale(float oldMin, float oldMax, float value) {
+  const float oldLen = oldMax - oldMin;
+  const float percentage = value / oldLen;
+  const float newLen = 1.0f - 0.0f;
+  return percentage * newLen + 0.0f;
+}
+// calculateMorton (BVH.h:83-130): centroid (v1+v2+v3)/3.0f normalised to the scene box WITHOUT subtracting its minimum (Q6), 10 bits
+// per axis.  Shared by the LBVH build (bvh.cu) and by the tie-break of the structures the reference does not have (kd.cu, the corrected
+// grid walk): among hits with bit-equal t the reference's traversal keeps the triangle that comes first in ITS sorted order, i.e. the
+// smaller (Morton code, triangle index).
+__device__ __forceinline__ uint32_t reference_morton(float4 a, float4 b, float4 c, const clrt_aabb& sceneBB) {
+  const float cx = (a.x + b.x + c.x) / 3.0f, cy = (a.y + b.y + c.y) / 3.0f, cz = (a.z + b.z + c.z) / 3.0f;
+  const float nx = normalize_scale(sceneBB.bounds[0].x, sceneBB.bounds[1].x, cx);
+  const float ny = normalize_scale(sceneBB.bounds[0].y, sceneBB.bounds[1].y, cy);
+  const float nz = normalize_scale(sceneBB.bounds[0].z, sceneBB.bounds[1].z, cz);
+  return morton3d(nx, ny, nz);
+}
+// true when triangle `id` precedes triangle `other` in the reference's sorted (Morton code, index) order
+__device__ __forceinline__ bool reference_order_before(const clrt_triangle* __restrict__ tris, uint32_t id, uint32_t other, const clrt_aabb& sceneBB) {
+  const float4* p = reinterpret_cast<const float4*>(tris + id); const float4* q = reinterpret_cast<const float4*>(tris + other);
+  const uint32_t ci = reference_morton(__ldg(p), __ldg(p + 1), __ldg(p + 2), sceneBB), co = reference_morton(__ldg(q), __ldg(q + 1), __ldg(q + 2), sceneBB);
+  return ci < co || (ci == co && id < other);
+}

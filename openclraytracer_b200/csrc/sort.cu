@@ -21,6 +21,9 @@
 
 namespace {
 
+#ifndef CLRT_SORT_BIG_TILES_FROM
+#define CLRT_SORT_BIG_TILES_FROM (1u << 19)     /* 4096-pair tiles above this size, 1024-pair tiles (more CTAs in flight) below */
+#endif
 constexpr int RADIX_BITS = 8;
 constexpr int BINS = 1 << RADIX_BITS;
 constexpr int SORT_THREADS = 256;
@@ -250,7 +253,7 @@ int sort_pairs_radix(clrt_ctx* ctx, clrt_uint2* pairs, size_t n, int key_bits) {
   if (n >= (1ull << 30)) CLRT_FAIL("sort: n = %zu exceeds 2^30-1", n);
   if (key_bits <= 0 || key_bits > 32) key_bits = 32;
   int passes = (key_bits + RADIX_BITS - 1) / RADIX_BITS;
-  const bool big = n > (1u << 19);
+  const bool big = n > (size_t)CLRT_SORT_BIG_TILES_FROM;
   const int ipt = big ? 16 : 4;
   const size_t tile = (size_t)SORT_THREADS * ipt;
   const unsigned tiles = (unsigned)((n + tile - 1) / tile);

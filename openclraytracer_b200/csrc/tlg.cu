@@ -437,7 +437,8 @@ __device__ __forceinline__ GridHit tlg_traverse_closest(Vec3 o, Vec3 d, const cl
           const uint32_t id = __ldg(&leaf_pairs[k].y);
           Vec3 a, b, c; load_tri(tris, id, a, b, c);
           const float t = triangle_intersect(a, b, c, o, d);
-          if (t > 0.0f && (t < best.t || (t == best.t && id < best.tri))) { best.t = t; best.tri = id; }
+          // bit-equal t: the reference's traversal keeps the triangle that comes first in its sorted (Morton code, index) order
+          if (t > 0.0f && (t < best.t || (t == best.t && reference_order_before(tris, id, best.tri, g.box)))) { best.t = t; best.tri = id; }
         }
         const float l_exit = fminf(Lf.tx, fminf(Lf.ty, Lf.tz));
         if (best.t <= l_exit * slack) return best;            // the closest hit lies in a cell already finished

@@ -131,11 +131,18 @@ class FrameRenderer:
         self.ctx = api.Context(device, stream=self.stream.cuda_stream)
         self.scene = api.Scene(scene_buf)
         self.scene.loadToGPU(self.ctx)
-        if accel.upper() == "BVH":                     # -accStruct {BVH,GRID} (OpenCLRayTracerDemo.cpp:66-73)
+        if accel.upper() == "BVH":                     # -accStruct {BVH,GRID} (OpenCLRayTracerDemo.cpp:66-73); KD is ours
             self.accel = api.BVHManager(self.ctx, self.scene)
+        elif accel.upper() == "KD":
+            self.accel = api.KDTreeManager(self.ctx, self.scene)
         else:
             self.accel = api.TwoLevelGridManager(self.ctx, self.scene, topLevelDensity, leafDensity)
         self.accel.initialize()
+        if accel.upper() == "GRID" and os.environ.get("CLRT_GRID_WALK", "corrected") == "corrected":
+            self.accel.set_trace_mode(api.TRACE_FAST)  # the corrected closest-hit walk (the literal one is the grid's default)
+        self.one_kernel = accel.upper() == "BVH" and os.environ.get("CLRT_FRAME_KERNELS", "2") == "1"
+        if self.one_kernel:                            # the whole stripe in one launch (clrt_accel_set_fused_shadows: 2)
+            self.accel.set_fused_shadows(2)
         self.cap = stripe_capacity(resX, resY, world)
         torch.cuda.synchronize()
         # DEPTH frames in flight.  Frame k is traced on trace stream k % DEPTH with frame slot k % DEPTH of the C ABI (private

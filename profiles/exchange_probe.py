@@ -18,10 +18,11 @@ for wl in sys.argv[1:] or ("soup1m",):
     buf, _ = bench.make_scene(wl)
     cams = [frame.orbit_camera(buf, RES[0], RES[1], i) for i in range(64)]
     golden = None
-    for mode in ("nccl", "push", "fused"):
-        os.environ["CLRT_EXCHANGE"] = mode
+    for mode in os.environ.get("PROBE_MODES", "nccl,push,fused,fused-split").split(","):
+        os.environ["CLRT_EXCHANGE"] = mode.split("-")[0]
+        os.environ["CLRT_SPLIT_EXCHANGE"] = "1" if mode.endswith("-split") else "0"      # waiting half of the exchange on its own stream
         r = frame.FrameRenderer(buf, RES[0], RES[1], "BVH", rank, world, local)
-        assert r.exchange == mode
+        assert r.exchange == mode.split("-")[0]
         r.build()
         # parity: frame by frame on every rank (the frames of a pipeline of DEPTH slots, twice around)
         frames = []

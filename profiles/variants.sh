@@ -24,7 +24,7 @@ case "${1:-build}" in
     done ;;
   runcmd)                                                                       # any command per variant, e.g. the sort / scan probe
     shift
-    for so in gpurun_variants/libclrt_*.so; do
+    for so in gpurun_variants/libclrt_${VARIANT_FILTER:-}*.so; do
       echo "== $so"; CLRT_LIB_PATH=$PWD/$so timeout 300 bash -c "$*" 2>&1 | tail -8
     done ;;
   test)

@@ -276,7 +276,7 @@ def test_fused_shadow_pass_equals_three_kernel_pipeline(ctx, name):
         bvh.set_fused_shadows(False)
         b, rb = bvh.render_frame_host(cam, shadows=True, want_rays=True)
         b = b.copy()
-        for mode in (1, 2):                     # 1: the one-kernel frame (default); 2: primary kernel + fused shadow/shade kernel
+        for mode in (1, 2):                     # 1: primary kernel + fused shadow/shade kernel (default); 2: the one-kernel frame
             bvh.set_fused_shadows(mode)
             a, ra = bvh.render_frame_host(cam, shadows=True, want_rays=True)
             assert np.array_equal(a, b) and ra == rb, mode
