@@ -499,7 +499,10 @@ def main():
             # ack wait, ready signal, ready wait, ack signal (fused, split exchange)
             # GRID: primary, shadow-ray generation, generic trace, shade, untile
             launches = ({"nccl": 3, "push": 7, "fused": 5}[exchange] - (1 if r.one_kernel else 0)) if args.accel == "BVH" else 5
-            pipeline = f"{r.DEPTH} frame(s) in flight" + (": frames traced on alternating streams (frame slots)" if r.DEPTH > 1 else "")
+            if args.accel == "BVH" and exchange == "fused" and r.batch > 1:
+                launches = 3 + 2.0 / r.batch                   # `batch` frames share one primary and one shadow + shade launch
+            pipeline = f"{r.DEPTH} frame(s) in flight" + (": frames traced on alternating streams (frame slots)" if r.DEPTH > 1 else "") + \
+                       (f", {r.batch} frames per pair of launches" if getattr(r, "batch", 1) > 1 else "")
             secondary = "1 shadow ray per hit per light (scene light + camera light)"
         line = {
             "metric": metric, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -514,7 +517,7 @@ def main():
                        "timed_region_s": dev_ms * 1e-3},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 64, "d2h_bytes_per_step": RES[0] * RES[1] * 4,
                     "ms_per_step": e2e_ms / args.steps},
-            "gpu_launches": args.steps * launches,
+            "gpu_launches": int(round(args.steps * launches)),
             "pipeline": pipeline,
             "build_ms": build_med, "build_ms_per_Mtri": build_med / (n_tris / 1e6),
             "build_stage_ms": dict(zip(["morton", "sort", "emit", "refit", "trace_structure"] if args.accel == "BVH" else

@@ -230,7 +230,7 @@ int clrt_shadow_shade(clrt_accel* accel, const clrt_camera* h_camera, const void
 int clrt_frame_stripe_pixels(uint32_t resX, uint32_t resY, uint32_t rank, uint32_t nranks, uint32_t* out_pixels, uint32_t* out_tiles);
 int clrt_render_stripe(clrt_accel* accel, const clrt_camera* h_camera, int shadows, uint32_t rank, uint32_t nranks,
                        void* dptr_rgba8, uint64_t* out_rays);
-/* The same on a caller-chosen cudaStream_t with frame slot `slot` (0..7): the slot's private work counter and scratch, so that
+/* The same on a caller-chosen cudaStream_t with frame slot `slot` (0..15): the slot's private work counter and scratch, so that
  * frames submitted on different streams overlap on the device — the tail of one frame's persistent kernels (a few long rays)
  * runs next to the head of the next frame's.  BVH with the fused shadow pass (or shadows == 0) only.  The caller orders reuse of
  * a slot and of dptr_rgba8 (stream order / events). */
@@ -262,8 +262,8 @@ int clrt_peer_close(clrt_ctx* ctx, void* dptr);
  * peer_rasters[rank] is this GPU's own) instead of a stripe buffer. */
 int clrt_render_stripe_peers(clrt_accel* accel, void* stream, int slot, const clrt_camera* h_camera, uint32_t rank, uint32_t nranks,
                              void* const* peer_rasters, uint64_t* out_rays);
-/* One call per frame and GPU: the whole protocol around clrt_render_stripe_peers.  peer_words[p] = 128 flag words of GPU p
- * (zeroed; ready at [slot*8 + writer], ack at [64 + slot*8 + writer]); seq = 1, 2, ... counts the frames of this slot.  Enqueued
+/* One call per frame and GPU: the whole protocol around clrt_render_stripe_peers.  peer_words[p] = 256 flag words of GPU p
+ * (zeroed; ready at [slot*8 + writer], ack at [128 + slot*8 + writer]; 16 slots); seq = 1, 2, ... counts the frames of this slot.  Enqueued
  * on `stream`: wait until every GPU acked frame seq-1 of the slot (its framebuffer may be overwritten) -> trace + shade, pixels
  * to every framebuffer -> ready to all, wait for all -> h_rgba8 ? (copy this GPU's framebuffer to pinned host memory -> ack) : ack.
  * consumer_stream != NULL: everything from "wait for all" on is enqueued THERE (behind an event of this frame's "ready"), so the
@@ -272,6 +272,18 @@ int clrt_render_stripe_peers(clrt_accel* accel, void* stream, int slot, const cl
 int clrt_render_frame_peers(clrt_accel* accel, void* stream, int slot, const clrt_camera* h_camera, uint32_t rank, uint32_t nranks,
                             void* const* peer_rasters, void* const* peer_words, uint32_t seq, void* h_rgba8, uint64_t* out_rays,
                             void* consumer_stream);
+/* `frames` (1..4) stripes (same rank / nranks, one camera each, one resolution) by ONE primary launch and ONE shadow + shade launch
+ * into a local stripe-ordered buffer: frame f's stripe at dptr_rgba8 + f * (out_tiles of clrt_frame_stripe_pixels * 256) pixels; frame-slot semantics
+ * of clrt_render_stripe_on.  BVH, FAST policy. */
+int clrt_render_stripes_batch(clrt_accel* accel, void* stream, int slot, uint32_t frames, const clrt_camera* h_cameras, uint32_t rank,
+                              uint32_t nranks, void* dptr_rgba8);
+/* The same for `frames` (1..4) CONSECUTIVE frames — slots slot0 .. slot0+frames-1, cameras h_cameras[f] (one resolution), framebuffers
+ * peer_rasters[f * 8 + gpu], sequence numbers seqs[f], read-back targets h_rgba8s[f] (array or entries may be NULL) — traced by ONE
+ * primary launch and ONE shadow + shade launch: at 8 GPUs a stripe is an eighth of a frame and a launch of ~0.3 ms loses a sixth of
+ * its time to its drain; four frames per launch make it a half-frame launch.  consumer_stream is required. */
+int clrt_render_frames_peers(clrt_accel* accel, void* stream, int slot0, uint32_t frames, const clrt_camera* h_cameras, uint32_t rank,
+                             uint32_t nranks, void* const* peer_rasters, void* const* peer_words, const uint32_t* seqs,
+                             void* const* h_rgba8s, void* consumer_stream);
 /* This GPU's stripe buffer (as written by clrt_render_stripe[_on]) -> raster position in every peer's framebuffer. */
 int clrt_frame_push(clrt_ctx* ctx, void* stream, const void* dptr_stripe, uint32_t resX, uint32_t resY, uint32_t rank,
                     uint32_t nranks, void* const* peer_rasters);

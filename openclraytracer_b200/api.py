@@ -371,6 +371,27 @@ class AccelerationStructureManager:
                                                 C.c_void_p(consumer_stream) if consumer_stream else None))
         return rays.value
 
+    def render_stripes_batch(self, stream, slot, cameras, rank, nranks, dptr_rgba8):
+        """1..4 stripes (one camera each) by one pair of launches into a local stripe-ordered buffer (clrt_render_stripes_batch)."""
+        cams = np.ascontiguousarray(np.stack([np.asarray(c, dtype=L.CAMERA).reshape(()) for c in cameras]))
+        check(self._lib.clrt_render_stripes_batch(self.handle, C.c_void_p(stream), slot, len(cameras), _ptr(cams), rank, nranks, C.c_void_p(dptr_rgba8)))
+
+    def render_frames_peers(self, stream, slot0, cameras, rank, nranks, peer_rasters_per_frame, peer_words, seqs, h_rgba8s=None, consumer_stream=None):
+        """1..4 consecutive frames of the fused exchange traced by one pair of launches (clrt_render_frames_peers).
+        peer_rasters_per_frame[f] = the pointer array of frame f's framebuffers on every GPU (peer_pointer_array)."""
+        k = len(cameras)
+        cams = np.ascontiguousarray(np.stack([np.asarray(c, dtype=L.CAMERA).reshape(()) for c in cameras]))
+        rasters = (C.c_void_p * (k * 8))()
+        for f in range(k):
+            for g in range(nranks):
+                rasters[f * 8 + g] = peer_rasters_per_frame[f][g]
+        sq = (C.c_uint32 * k)(*seqs)
+        hosts = None
+        if h_rgba8s is not None:
+            hosts = (C.c_void_p * k)(*[C.c_void_p(h) if h else None for h in h_rgba8s])
+        check(self._lib.clrt_render_frames_peers(self.handle, C.c_void_p(stream), slot0, k, _ptr(cams), rank, nranks, rasters, peer_words, sq, hosts,
+                                                 C.c_void_p(consumer_stream)))
+
     def render_frame_host(self, camera, shadows, out_rgba8=None, want_rays=False):
         cam = np.ascontiguousarray(camera, dtype=L.CAMERA)
         if out_rgba8 is None:

@@ -287,7 +287,7 @@ int peer_launch_exchange(cudaStream_t stream, const PeerTargets& flags, const ui
                          uint32_t rank, uint32_t seq);
 int peer_launch_signal(cudaStream_t stream, const PeerTargets& flags, uint32_t word, uint32_t value);
 
-// One call per frame and GPU.  Flag words of a GPU (peer_words[p], 128 words): ready at [slot*8 + writer], ack at [64 + slot*8 +
+// One call per frame and GPU.  Flag words of a GPU (peer_words[p], 256 words): ready at [slot*8 + writer], ack at [128 + slot*8 +
 // writer]; seq = 1, 2, ... per slot.  Enqueues on `stream`: wait until every GPU acked seq-1 of this slot (its framebuffer is
 // free) -> trace + shade with the pixels going to every framebuffer -> ready to all, wait for all -> (copy to host ->) ack to all.
 extern "C" int clrt_render_frame_peers(clrt_accel* a, void* stream_, int slot, const clrt_camera* h_camera, uint32_t rank, uint32_t nranks,
@@ -302,7 +302,7 @@ extern "C" int clrt_render_frame_peers(clrt_accel* a, void* stream_, int slot, c
   for (uint32_t i = 0; i < nranks; i++) if (!flags.p[i]) CLRT_FAIL("clrt_render_frame_peers: peer %u is NULL", i);
   CLRT_CUDA(cudaSetDevice(a->ctx->device));
   const uint32_t* own = flags.p[rank];
-  const uint32_t ready = (uint32_t)slot * 8u, ack = 64u + (uint32_t)slot * 8u;
+  const uint32_t ready = (uint32_t)slot * 8u, ack = 128u + (uint32_t)slot * 8u;
   if (seq > 1) CLRT_TRY(peer_launch_wait(stream, own + ack, nranks, seq - 1));
   CLRT_TRY(clrt_render_stripe_peers(a, stream_, slot, h_camera, rank, nranks, peer_rasters, out_rays));
   const size_t bytes = (size_t)h_camera->resX * h_camera->resY * 4;
@@ -324,6 +324,96 @@ extern "C" int clrt_render_frame_peers(clrt_accel* a, void* stream_, int slot, c
   CLRT_TRY(peer_launch_wait(consumer, own + ready, nranks, seq));
   if (h_rgba8) CLRT_CUDA(cudaMemcpyAsync(h_rgba8, peer_rasters[rank], bytes, cudaMemcpyDeviceToHost, consumer));
   CLRT_TRY(peer_launch_signal(consumer, flags, ack + rank, seq));
+  return 0;
+}
+
+int bvh_frames_batch(clrt_accel* a, const clrt_camera* cams, uint32_t frames, uint32_t rank, uint32_t nranks, clrt_contact* contacts,
+                     uint32_t* rgba8, uint32_t* const* targets, uint32_t n_targets, unsigned long long* d_ray_counter);
+
+// `frames` (1..4) stripes (same rank / nranks, one camera each) by ONE primary launch and ONE shadow + shade launch into a local
+// stripe-ordered buffer: frame f's stripe at dptr_rgba8 + f * (this rank's tiles * 256) pixels.  Frame-slot semantics of
+// clrt_render_stripe_on (the slot's counter and scratch, the caller's stream).
+extern "C" int clrt_render_stripes_batch(clrt_accel* a, void* stream_, int slot, uint32_t frames, const clrt_camera* h_cameras, uint32_t rank,
+                                         uint32_t nranks, void* dptr_rgba8) {
+  if (!a || !h_cameras || !dptr_rgba8 || !nranks || rank >= nranks) CLRT_FAIL("clrt_render_stripes_batch: bad argument");
+  if (!frames || frames > 4 || slot < 0 || slot >= clrt_accel::FRAME_SLOTS) CLRT_FAIL("clrt_render_stripes_batch: frames %u, slot %d", frames, slot);
+  if (a->kind != ACCEL_BVH || a->scene->n_lights + 1 > 32 || a->unfused_shadows || a->trace_mode != CLRT_TRACE_FAST)
+    CLRT_FAIL("clrt_render_stripes_batch: needs the BVH with the fused shadow pass and the FAST policy");
+  CLRT_CUDA(cudaSetDevice(a->ctx->device));
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (slot + 1 > a->slots_seen) a->slots_seen = slot + 1;
+  const TileGrid g = make_tile_grid(h_cameras[0].resX, h_cameras[0].resY);
+  const size_t units = (size_t)stripe_tile_count(g.tiles, rank, nranks) * CLRT_TILE_PIXELS;
+  const size_t need = units * frames * sizeof(clrt_contact) + 64;
+  if (need > a->slot_scratch_cap[slot]) {
+    CLRT_CUDA(cudaStreamSynchronize(stream));
+    CLRT_TRY(clrt_grow(&a->d_slot_scratch[slot], &a->slot_scratch_cap[slot], need));
+  }
+  struct LaunchEnv {
+    clrt_accel* a;
+    LaunchEnv(clrt_accel* a_, cudaStream_t s, uint32_t* c, int batch) : a(a_) { a->launch_stream = s; a->launch_counter = c; a->launch_batch = batch; }
+    ~LaunchEnv() { a->launch_stream = nullptr; a->launch_counter = nullptr; a->launch_batch = 1; }
+  } env(a, stream, a->d_slot_counters + 16 * slot, 1);
+  return bvh_frames_batch(a, h_cameras, frames, rank, nranks, (clrt_contact*)a->d_slot_scratch[slot], (uint32_t*)dptr_rgba8, nullptr, 0, nullptr);
+}
+
+// `frames` (1..4) consecutive frames of the fused exchange as ONE pair of launches: slots slot0 .. slot0+frames-1, their cameras
+// h_cameras[f], their framebuffers peer_rasters[f * 8 + gpu] and sequence numbers seqs[f].  Protocol per frame as in
+// clrt_render_frame_peers with a consumer stream (required); what changes is that the stripes of all the frames are traced by one
+// primary launch and one shadow + shade launch, so that at 8 GPUs a launch carries half a frame's work instead of an eighth and
+// loses a quarter as much to its drain.  h_rgba8s (may be NULL) = frames host buffers for the read-back.
+extern "C" int clrt_render_frames_peers(clrt_accel* a, void* stream_, int slot0, uint32_t frames, const clrt_camera* h_cameras, uint32_t rank,
+                                        uint32_t nranks, void* const* peer_rasters, void* const* peer_words, const uint32_t* seqs,
+                                        void* const* h_rgba8s, void* consumer_stream_) {
+  if (!a || !h_cameras || !peer_rasters || !peer_words || !seqs || !consumer_stream_ || !nranks || nranks > 8 || rank >= nranks)
+    CLRT_FAIL("clrt_render_frames_peers: bad argument");
+  if (!frames || frames > 4 || slot0 < 0 || slot0 + (int)frames > clrt_accel::FRAME_SLOTS)
+    CLRT_FAIL("clrt_render_frames_peers: frames %u from slot %d (of %d)", frames, slot0, clrt_accel::FRAME_SLOTS);
+  if (a->kind != ACCEL_BVH || a->scene->n_lights + 1 > 32 || a->unfused_shadows || a->trace_mode != CLRT_TRACE_FAST)
+    CLRT_FAIL("clrt_render_frames_peers: needs the BVH with the fused shadow pass and the FAST policy");
+  cudaStream_t stream = (cudaStream_t)stream_, consumer = (cudaStream_t)consumer_stream_;
+  PeerTargets flags; flags.n = nranks;
+  for (uint32_t i = 0; i < 8; i++) flags.p[i] = i < nranks ? (uint32_t*)peer_words[i] : nullptr;
+  for (uint32_t i = 0; i < nranks; i++) if (!flags.p[i]) CLRT_FAIL("clrt_render_frames_peers: peer %u is NULL", i);
+  uint32_t* targets[4 * 8] = {nullptr};
+  for (uint32_t f = 0; f < frames; f++) {
+    if (!seqs[f]) CLRT_FAIL("clrt_render_frames_peers: sequence numbers start at 1");
+    for (uint32_t k = 0; k < nranks; k++) {
+      targets[f * 8 + k] = (uint32_t*)peer_rasters[f * 8 + k];
+      if (!targets[f * 8 + k]) CLRT_FAIL("clrt_render_frames_peers: framebuffer %u of frame %u is NULL", k, f);
+    }
+  }
+  CLRT_CUDA(cudaSetDevice(a->ctx->device));
+  if (slot0 + (int)frames > a->slots_seen) a->slots_seen = slot0 + (int)frames;
+  const uint32_t* own = flags.p[rank];
+  for (uint32_t f = 0; f < frames; f++)
+    if (seqs[f] > 1) CLRT_TRY(peer_launch_wait(stream, own + 128u + (uint32_t)(slot0 + f) * 8u, nranks, seqs[f] - 1));
+  // contacts of all the frames in slot0's scratch
+  const TileGrid g = make_tile_grid(h_cameras[0].resX, h_cameras[0].resY);
+  const size_t units = (size_t)stripe_tile_count(g.tiles, rank, nranks) * CLRT_TILE_PIXELS;
+  const size_t need = units * frames * sizeof(clrt_contact) + 64;
+  if (need > a->slot_scratch_cap[slot0]) {
+    CLRT_CUDA(cudaStreamSynchronize(stream));
+    CLRT_TRY(clrt_grow(&a->d_slot_scratch[slot0], &a->slot_scratch_cap[slot0], need));
+  }
+  {
+    struct LaunchEnv {
+      clrt_accel* a;
+      LaunchEnv(clrt_accel* a_, cudaStream_t s, uint32_t* c, int batch) : a(a_) { a->launch_stream = s; a->launch_counter = c; a->launch_batch = batch; }
+      ~LaunchEnv() { a->launch_stream = nullptr; a->launch_counter = nullptr; a->launch_batch = 1; }
+    } env(a, stream, a->d_slot_counters + 16 * slot0, (int)frames);
+    CLRT_TRY(bvh_frames_batch(a, h_cameras, frames, rank, nranks, (clrt_contact*)a->d_slot_scratch[slot0], nullptr, targets, nranks, nullptr));
+  }
+  const size_t bytes = (size_t)h_cameras[0].resX * h_cameras[0].resY * 4;
+  for (uint32_t f = 0; f < frames; f++) CLRT_TRY(peer_launch_signal(stream, flags, (uint32_t)(slot0 + f) * 8u + rank, seqs[f]));
+  if (!a->slot_event[slot0]) CLRT_CUDA(cudaEventCreateWithFlags(&a->slot_event[slot0], cudaEventDisableTiming));
+  CLRT_CUDA(cudaEventRecord(a->slot_event[slot0], stream));
+  CLRT_CUDA(cudaStreamWaitEvent(consumer, a->slot_event[slot0], 0));
+  for (uint32_t f = 0; f < frames; f++) {
+    CLRT_TRY(peer_launch_wait(consumer, own + (uint32_t)(slot0 + f) * 8u, nranks, seqs[f]));
+    if (h_rgba8s && h_rgba8s[f]) CLRT_CUDA(cudaMemcpyAsync(h_rgba8s[f], targets[f * 8 + rank], bytes, cudaMemcpyDeviceToHost, consumer));
+    CLRT_TRY(peer_launch_signal(consumer, flags, 128u + (uint32_t)(slot0 + f) * 8u + rank, seqs[f]));
+  }
   return 0;
 }
 

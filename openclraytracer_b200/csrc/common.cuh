@@ -153,7 +153,7 @@ struct clrt_accel {
   void* d_fb = nullptr; size_t fb_cap = 0;
   uint32_t* d_tile_counter = nullptr;
   // frame slots: frames in flight on caller-chosen streams (clrt_render_stripe_on), each with its own work counter + scratch
-  static constexpr int FRAME_SLOTS = 8;
+  static constexpr int FRAME_SLOTS = 16;
   void* d_slot_scratch[FRAME_SLOTS] = {nullptr}; size_t slot_scratch_cap[FRAME_SLOTS] = {0};
   uint32_t* d_slot_counters = nullptr;            // FRAME_SLOTS x 64 B
   cudaEvent_t slot_event[FRAME_SLOTS] = {nullptr}; // "this GPU's stripe of the slot's frame is stored everywhere" (clrt_render_frame_peers)
@@ -161,6 +161,7 @@ struct clrt_accel {
   cudaStream_t launch_stream = nullptr;           // set only while a slot's launches are being enqueued
   PeerTargets launch_targets = {{nullptr}, 0};     // ditto: peer framebuffers of a p2p frame (n == 0: write the local stripe buffer)
   uint32_t* launch_counter = nullptr;
+  int launch_batch = 1;                           // frames per launch of the call being enqueued (grid sizing: slots_seen / launch_batch launches run side by side)
   // --- TLG --- (tlg.cu)
   struct TlgState* tlg = nullptr;
   // --- KD-tree --- (kd.cu)

@@ -178,12 +178,32 @@ __device__ __forceinline__ KdHit kd_traverse(Vec3 o, Vec3 d, const KdGrid& g, co
     if (!(tn <= tf) || tf < 0.0f) return none;
     tmin = fmaxf(tn, 0.0f); tmax = tf;
   }
-  uint32_t stack_node[KD_STACK]; float stack_tmax[KD_STACK];
+  // One unit of work per loop iteration and lane — descend one inner node, open a leaf, or test one triangle — so that the lanes of
+  // a warp stay in step (nested per-lane loops ran with 4 of 32 lanes: every lane waited for the longest inner loop of the warp).
+  uint2 stack[KD_STACK];                                           // (far child, its tmax)
   int sp = 0;
   uint32_t cur = m >= 2 ? m : 0u;                                  // root = inner node 0, or the only leaf
+  uint32_t k = 0, kend = 0;
+  constexpr uint32_t IN_LEAF = 0xFFFFFFFEu;
   const float slack = 1.00001f;
   while (true) {
-    while (cur >= m) {                                             // inner node: pick the near side, remember the far one
+    if (cur == IN_LEAF) {
+      if (k < kend) {
+        const uint32_t id = __ldg(&pairs[k].y); k++;
+        const float4* t4 = reinterpret_cast<const float4*>(tris + id);
+        const float4 a = __ldg(t4), b = __ldg(t4 + 1), c = __ldg(t4 + 2);
+        const float t = triangle_intersect(v3(a.x, a.y, a.z), v3(b.x, b.y, b.z), v3(c.x, c.y, c.z), o, d);
+        // bit-equal t: the reference's traversal keeps the triangle that comes first in its sorted (Morton code, index) order
+        if (t > 0.0f && (t < best.t || (t == best.t && reference_order_before(tris, id, best.tri, g.box)))) { best.t = t; best.tri = id; }
+        continue;
+      }
+      if (best.t <= tmax * slack) return best;                     // the closest hit lies in a region already finished
+      if (sp == 0) break;
+      sp--;
+      tmin = tmax; tmax = __uint_as_float(stack[sp].y); cur = stack[sp].x;
+      continue;
+    }
+    if (cur >= m) {                                                // inner node: pick the near side, remember the far one
       const KdNode nd = nodes[cur - m];
       const float oa = nd.axis == 0 ? org[0] : nd.axis == 1 ? org[1] : org[2];
       const float da = nd.axis == 0 ? dir[0] : nd.axis == 1 ? dir[1] : dir[2];
@@ -194,23 +214,13 @@ __device__ __forceinline__ KdHit kd_traverse(Vec3 o, Vec3 d, const KdGrid& g, co
       if (da == 0.0f || ts > tmax * slack || ts <= 0.0f) cur = near;          // the ray never reaches the plane inside the interval
       else if (ts < tmin / slack) cur = far;                                  // it crossed the plane before the interval
       else {
-        if (sp < KD_STACK) { stack_node[sp] = far; stack_tmax[sp] = tmax; sp++; } else atomicAdd(overflow, 1u);
+        if (sp < KD_STACK) { stack[sp] = make_uint2(far, __float_as_uint(tmax)); sp++; } else atomicAdd(overflow, 1u);
         cur = near; tmax = ts;
       }
+    } else {                                                       // leaf: open its triangle list
+      const uint2 range = __ldg(ranges + cur);
+      k = range.x; kend = range.y; cur = IN_LEAF;
     }
-    const uint2 range = __ldg(ranges + cur);
-    for (uint32_t k = range.x; k < range.y; k++) {
-      const uint32_t id = __ldg(&pairs[k].y);
-      const float4* t4 = reinterpret_cast<const float4*>(tris + id);
-      const float4 a = __ldg(t4), b = __ldg(t4 + 1), c = __ldg(t4 + 2);
-      const float t = triangle_intersect(v3(a.x, a.y, a.z), v3(b.x, b.y, b.z), v3(c.x, c.y, c.z), o, d);
-      // bit-equal t: the reference's traversal keeps the triangle that comes first in its sorted (Morton code, index) order
-      if (t > 0.0f && (t < best.t || (t == best.t && reference_order_before(tris, id, best.tri, g.box)))) { best.t = t; best.tri = id; }
-    }
-    if (best.t <= tmax * slack) return best;                       // the closest hit lies in a region already finished
-    if (sp == 0) break;
-    sp--;
-    tmin = tmax; tmax = stack_tmax[sp]; cur = stack_node[sp];
   }
   return best.tri != 0xFFFFFFFFu ? best : none;
 }

@@ -491,11 +491,15 @@ __device__ __forceinline__ void flush_stats(const Stats& st, unsigned long long*
 struct PixelRef { uint32_t pixel, slot; bool inside; };
 __device__ __forceinline__ PixelRef pixel_of_unit(const clrt_camera& cam, const TileGrid& g, uint32_t u, uint32_t rank, uint32_t nranks, int raster) {
   const uint32_t lt = u >> 8, sub = (u >> 5) & 7u, l = u & 31u;
+#ifdef CLRT_PROBE_TILE_BLOCK      /* experiment only (timing probe): block-cyclic ownership, CLRT_PROBE_TILE_BLOCK consecutive tiles per block */
+  const uint32_t gt = (lt / CLRT_PROBE_TILE_BLOCK) * nranks * CLRT_PROBE_TILE_BLOCK + rank * CLRT_PROBE_TILE_BLOCK + lt % CLRT_PROBE_TILE_BLOCK;
+#else
   const uint32_t gt = rank + lt * nranks;
+#endif
   const uint32_t tx = (gt % g.tilesX) * CLRT_TILE_W + (sub & 3u) * 8u + (l & 7u);
   const uint32_t ty = (gt / g.tilesX) * CLRT_TILE_H + (sub >> 2) * 4u + (l >> 3);
   PixelRef r;
-  r.inside = tx < cam.resX && ty < cam.resY;
+  r.inside = tx < cam.resX && ty < cam.resY && gt < g.tiles;
   r.pixel = ty * cam.resX + tx;
   r.slot = raster ? r.pixel : lt * CLRT_TILE_PIXELS + ((sub >> 2) * 4u + (l >> 3)) * CLRT_TILE_W + (sub & 3u) * 8u + (l & 7u);
   return r;
@@ -589,6 +593,77 @@ struct ShadowJob {
     occl |= (L.h.tri != SENTINEL ? 1u : 0u) << l;
     if (++l <= n_lights) { aim(L); return true; }
     shade_and_store();
+    return false;
+  }
+};
+
+// ---- frame batches ------------------------------------------------------------------------------------------------------------
+// Several frames' stripes in ONE launch per pass (multi-GPU: at 8 GPUs a stripe is an eighth of a frame, a launch lives ~0.3 ms and
+// what is lost is its drain — the last long rays alone on the machine; four frames per launch make it a half-frame launch).  Unit u =
+// frame u / units, stripe slot u % units.  Each frame has its own camera and its own framebuffers (PeerBatch).
+constexpr int FRAME_BATCH_MAX = 4;
+struct CamBatch { clrt_camera cam[FRAME_BATCH_MAX]; uint32_t frames, units; };        // units: padded stripe slots of one frame
+struct PeerBatch { uint32_t* p[FRAME_BATCH_MAX][8]; uint32_t n; };                    // [frame][gpu] raster-ordered framebuffers
+
+template <bool STATS>
+struct PrimaryBatchJob {
+  const CamBatch& cams; TileGrid g; uint32_t rank, nranks;
+  const clrt_triangle* __restrict__ tris; uint32_t n; const QFrame* __restrict__ qf; clrt_contact* __restrict__ out; Stats& st;
+  uint32_t pixel, slot;
+  __device__ __forceinline__ bool start(uint32_t u, Lane& L) {
+    const uint32_t f = u / cams.units, u1 = u - f * cams.units;
+    const clrt_camera& cam = cams.cam[f];
+    const PixelRef r = pixel_of_unit(cam, g, u1, rank, nranks, 0);
+    if (!r.inside) { Hit h; h.t = RT_FLT_MAX; h.tri = SENTINEL; write_contact(out, f * cams.units + r.slot, SENTINEL, h, tris); return false; }
+    pixel = r.pixel; slot = f * cams.units + r.slot;
+    Vec3 o, d; generate_ray(cam, pixel, o, d);
+    lane_begin<STATS, 0>(L, tris, n, qf, o, d, RT_FLT_MAX, st);
+    return true;
+  }
+  __device__ __forceinline__ bool finish(Lane& L) { write_contact(out, slot, pixel, L.h, tris, STATS ? L.visits : 0u); return false; }
+};
+
+template <bool STATS>
+struct ShadowBatchJob {
+  const CamBatch& cams; const clrt_contact* __restrict__ contacts;
+  const clrt_light* __restrict__ lights; uint32_t n_lights; const clrt_material* __restrict__ materials; uint32_t n_materials;
+  const clrt_triangle* __restrict__ tris; uint32_t n; const QFrame* __restrict__ qf; uint32_t* __restrict__ rgba8; const PeerBatch& peers; Stats& st; uint32_t& live_rays;
+  uint32_t index, pixel, l, occl; float t;
+  __device__ __forceinline__ void store_pixel(uint32_t i, uint32_t px, uint32_t packed) {
+    if (peers.n == 0) { __stcs(rgba8 + i, packed); return; }
+    if (px == SENTINEL) return;
+    const uint32_t f = i / cams.units;
+#pragma unroll
+    for (uint32_t k = 0; k < 8; k++) if (k < peers.n) peers.p[f][k][px] = packed;
+  }
+  __device__ __forceinline__ void aim(Lane& L) {
+    const clrt_camera& cam = cams.cam[index / cams.units];
+    Vec3 o, d; generate_ray(cam, pixel, o, d);
+    const Vec3 P = vadd(o, vscale(d, t));
+    float energy; const Vec3 lp = light_position(lights, n_lights, l, o, energy);
+    const float limit = vlength(vsub(lp, P)) - SHADOW_EPS_REL * t;
+    Vec3 org, dir; shadow_ray(cam, pixel, t, lights, n_lights, l, org, dir);
+    lane_begin<STATS, 1>(L, tris, n, qf, org, dir, limit, st);
+  }
+  __device__ __forceinline__ bool start(uint32_t i, Lane& L) {
+    index = i; occl = 0; l = 0;
+    const uint4 head = __ldcs(reinterpret_cast<const uint4*>(contacts + i));
+    const float4 nd = __ldcs(reinterpret_cast<const float4*>(contacts + i) + 1);
+    pixel = head.x; t = nd.w;
+    if (!(nd.w > 0.0f && head.x != SENTINEL)) { store_pixel(i, head.x, 0u); return false; }
+    live_rays += n_lights + 1;
+    aim(L);
+    return true;
+  }
+  __device__ __forceinline__ bool finish(Lane& L) {
+    occl |= (L.h.tri != SENTINEL ? 1u : 0u) << l;
+    if (++l <= n_lights) { aim(L); return true; }
+    uint32_t packed;
+    const uint32_t oc = occl;
+    const uint4 head = __ldcs(reinterpret_cast<const uint4*>(contacts + index));
+    const float4 nd = __ldcs(reinterpret_cast<const float4*>(contacts + index) + 1);
+    shade_contact(cams.cam[index / cams.units], head, nd, lights, n_lights, materials, n_materials, [oc](uint32_t k, float) { return ((oc >> k) & 1u) != 0u; }, packed);
+    store_pixel(index, pixel, packed);
     return false;
   }
 };
@@ -757,6 +832,38 @@ frame_kernel(const clrt_camera cam, uint32_t rank, uint32_t nranks,
   if (STATS) flush_stats(st, stats);
 }
 
+template <bool STATS>
+__global__ void __launch_bounds__(TRACE_THREADS, CLRT_MIN_CTAS)
+trace_primary_batch_kernel(const CamBatch cams, const WideNode* __restrict__ wnodes, const clrt_triangle* __restrict__ tris, uint32_t n,
+                           clrt_contact* __restrict__ out, uint32_t rank, uint32_t nranks, uint32_t* __restrict__ counter,
+                           unsigned long long* __restrict__ stats, uint32_t* __restrict__ overflow) {
+  Stats st; st.rays = st.inner = st.tris = st.lboxes = 0;
+  const TileGrid g = make_tile_grid(cams.cam[0].resX, cams.cam[0].resY);
+  PrimaryBatchJob<STATS> job{cams, g, rank, nranks, tris, n, reinterpret_cast<const QFrame*>(wnodes + n + WIDE_TOP_NODES), out, st, 0u, 0u};
+  run_jobs<PrimaryBatchJob<STATS>, STATS, 0>(job, wnodes, tris, n, cams.frames * cams.units, counter, st, overflow);
+  if (STATS) flush_stats(st, stats);
+}
+
+template <bool STATS>
+__global__ void __launch_bounds__(TRACE_THREADS, CLRT_MIN_CTAS)
+shadow_shade_batch_kernel(const CamBatch cams, const clrt_contact* __restrict__ contacts,
+                          const clrt_light* __restrict__ lights, uint32_t n_lights, const clrt_material* __restrict__ materials, uint32_t n_materials,
+                          const WideNode* __restrict__ wnodes, const clrt_triangle* __restrict__ tris, uint32_t n,
+                          uint32_t* __restrict__ rgba8, const PeerBatch peers, uint32_t* __restrict__ counter, unsigned long long* __restrict__ ray_counter,
+                          unsigned long long* __restrict__ stats, uint32_t* __restrict__ overflow) {
+  Stats st; st.rays = st.inner = st.tris = st.lboxes = 0;
+  uint32_t live_rays = 0;
+  ShadowBatchJob<STATS> job{cams, contacts, lights, n_lights, materials, n_materials, tris, n, reinterpret_cast<const QFrame*>(wnodes + n + WIDE_TOP_NODES),
+                            rgba8, peers, st, live_rays, 0u, 0u, 0u, 0u, 0.0f};
+  run_jobs<ShadowBatchJob<STATS>, STATS, 1>(job, wnodes, tris, n, cams.frames * cams.units, counter, st, overflow);
+  if (ray_counter) {
+#pragma unroll
+    for (int dd = 16; dd > 0; dd >>= 1) live_rays += __shfl_xor_sync(0xffffffffu, live_rays, dd);
+    if ((threadIdx.x & 31) == 0 && live_rays) atomicAdd(ray_counter, (unsigned long long)live_rays);
+  }
+  if (STATS) flush_stats(st, stats);
+}
+
 // Grid of a persistent launch.  Resident capacity (SMs x occupancy, queried once per kernel) is the upper bound.  A launch alone on
 // the GPU wants the shortest kernel: one 32-unit packet per warp is enough to start every warp.  A launch in a FRAME SLOT (D
 // frames in flight on their own streams) wants throughput, and a warp is efficient only while it lives long: after its last packet
@@ -780,7 +887,7 @@ int persistent_grid(clrt_accel* a, int threads, size_t smem, uint32_t packets, u
   const unsigned all = (packets + warps_per_cta - 1) / warps_per_cta;               // one packet per warp
   unsigned want = all;
   if (a->launch_stream) {
-    const unsigned slots = (unsigned)max(1, a->slots_seen);
+    const unsigned slots = (unsigned)max(1, a->slots_seen / max(1, a->launch_batch));
     const unsigned fill = (resident + slots - 1u) / slots;
     want = min(all, max((packets + warps_per_cta * rays_per_lane - 1) / (warps_per_cta * rays_per_lane), fill));
   }
@@ -902,6 +1009,54 @@ int bvh_frame_fused(clrt_accel* a, const clrt_camera& cam, uint32_t rank, uint32
   CLRT_CUDA(cudaMemsetAsync(trace_counter(a), 0, 4, trace_stream(a)));
   return a->stats ? launch_frame<true>(a, cam, rank, nranks, rgba8, d_ray_counter, packets)
                   : launch_frame<false>(a, cam, rank, nranks, rgba8, d_ray_counter, packets);
+}
+
+// `frames` (1..4) stripes `rank` of `nranks` — one camera each, same resolution — as two launches: primary contacts of all of them
+// into `contacts` (frames x units), then shadow + shade into `rgba8` (frames x units, stripe order) or, with peer targets
+// (targets[f * 8 + gpu], n_targets GPUs), into the raster framebuffers of frame f on every GPU.  FAST policy.
+int bvh_frames_batch(clrt_accel* a, const clrt_camera* cams, uint32_t frames, uint32_t rank, uint32_t nranks, clrt_contact* contacts,
+                     uint32_t* rgba8, uint32_t* const* targets, uint32_t n_targets, unsigned long long* d_ray_counter) {
+  if (!a->built) CLRT_FAIL("frame batch: the BVH was not constructed");
+  if (!frames || frames > (uint32_t)FRAME_BATCH_MAX) CLRT_FAIL("frame batch: %u frames (1..%d)", frames, FRAME_BATCH_MAX);
+  if (a->scene->n_lights + 1 > 32) CLRT_FAIL("fused shadow pass supports at most 31 scene lights");
+  CamBatch cb; memset(&cb, 0, sizeof cb);
+  for (uint32_t f = 0; f < frames; f++) {
+    cb.cam[f] = cams[f];
+    if (cams[f].resX != cams[0].resX || cams[f].resY != cams[0].resY) CLRT_FAIL("frame batch: the cameras differ in resolution");
+  }
+  const TileGrid g = make_tile_grid(cams[0].resX, cams[0].resY);
+  cb.frames = frames; cb.units = stripe_tile_count(g.tiles, rank, nranks) * CLRT_TILE_PIXELS;
+  if (!cb.units) return 0;
+  PeerBatch pb; memset(&pb, 0, sizeof pb);
+  pb.n = n_targets;
+  for (uint32_t f = 0; f < frames && n_targets; f++) for (uint32_t k = 0; k < n_targets; k++) pb.p[f][k] = targets[f * 8 + k];
+  const uint32_t packets = frames * (cb.units / 32u);
+  const clrt_scene* sc = a->scene;
+  const TraceView v = trace_view(a, true);
+  unsigned grid = 0;
+  CLRT_CUDA(cudaMemsetAsync(trace_counter(a), 0, 4, trace_stream(a)));
+  if (a->stats) {
+    CLRT_TRY((persistent_grid<trace_primary_batch_kernel<true>>(a, TRACE_THREADS, FAST_SMEM_BYTES, packets, &grid)));
+    trace_primary_batch_kernel<true><<<grid, TRACE_THREADS, FAST_SMEM_BYTES, trace_stream(a)>>>(cb, v.wnodes, v.tris, a->n, contacts, rank, nranks, trace_counter(a),
+        (unsigned long long*)(a->d_tile_counter + 4), overflow_word(a));
+  } else {
+    CLRT_TRY((persistent_grid<trace_primary_batch_kernel<false>>(a, TRACE_THREADS, FAST_SMEM_BYTES, packets, &grid)));
+    trace_primary_batch_kernel<false><<<grid, TRACE_THREADS, FAST_SMEM_BYTES, trace_stream(a)>>>(cb, v.wnodes, v.tris, a->n, contacts, rank, nranks, trace_counter(a),
+        (unsigned long long*)(a->d_tile_counter + 4), overflow_word(a));
+  }
+  CLRT_CHECK_LAUNCH();
+  CLRT_CUDA(cudaMemsetAsync(trace_counter(a), 0, 4, trace_stream(a)));
+  if (a->stats) {
+    CLRT_TRY((persistent_grid<shadow_shade_batch_kernel<true>>(a, TRACE_THREADS, FAST_SMEM_BYTES, packets, &grid)));
+    shadow_shade_batch_kernel<true><<<grid, TRACE_THREADS, FAST_SMEM_BYTES, trace_stream(a)>>>(cb, contacts, sc->d_lights, sc->n_lights, sc->d_materials, sc->n_materials,
+        v.wnodes, v.tris, a->n, rgba8, pb, trace_counter(a), d_ray_counter, (unsigned long long*)(a->d_tile_counter + 4), overflow_word(a));
+  } else {
+    CLRT_TRY((persistent_grid<shadow_shade_batch_kernel<false>>(a, TRACE_THREADS, FAST_SMEM_BYTES, packets, &grid)));
+    shadow_shade_batch_kernel<false><<<grid, TRACE_THREADS, FAST_SMEM_BYTES, trace_stream(a)>>>(cb, contacts, sc->d_lights, sc->n_lights, sc->d_materials, sc->n_materials,
+        v.wnodes, v.tris, a->n, rgba8, pb, trace_counter(a), d_ray_counter, (unsigned long long*)(a->d_tile_counter + 4), overflow_word(a));
+  }
+  CLRT_CHECK_LAUNCH();
+  return 0;
 }
 
 // Traversal stacks are bounded (REF_STACK, FAST_STACK).  A push that does not fit is counted on the device instead of silently

@@ -77,12 +77,12 @@ def gather_stripes(local_stripe, world, group=None):
 
 
 # ---- the peer-memory exchange protocol (csrc/peer.cu, clrt_render_frame_peers) in words -----------------------------------------
-PEER_READY, PEER_ACK, PEER_WORDS = 0, 64, 128          # word offsets inside a GPU's flag block: [kind + slot*8 + writer rank]
+PEER_READY, PEER_ACK, PEER_WORDS = 0, 128, 256         # word offsets inside a GPU's flag block: [kind + slot*8 + writer rank]
 
 
 def peer_word(kind, slot, writer):
-    """Index of the flag word that GPU `writer` raises for frame slot `slot` (8 slots x 8 writers per kind)."""
-    assert kind in (PEER_READY, PEER_ACK) and 0 <= slot < 8 and 0 <= writer < 8
+    """Index of the flag word that GPU `writer` raises for frame slot `slot` (16 slots x 8 writers per kind)."""
+    assert kind in (PEER_READY, PEER_ACK) and 0 <= slot < 16 and 0 <= writer < 8
     return kind + slot * 8 + writer
 
 
@@ -140,8 +140,15 @@ class FrameRenderer:
         self.accel.initialize()
         if accel.upper() == "GRID" and os.environ.get("CLRT_GRID_WALK", "corrected") == "corrected":
             self.accel.set_trace_mode(api.TRACE_FAST)  # the corrected closest-hit walk (the literal one is the grid's default)
-        self.one_kernel = accel.upper() == "BVH" and os.environ.get("CLRT_FRAME_KERNELS", "2") == "1"
-        if self.one_kernel:                            # the whole stripe in one launch (clrt_accel_set_fused_shadows: 2)
+        # Kernels per frame.  Two (primary contacts, then shadow + shade) are faster on a whole frame and on half a frame (2.31 against
+        # 2.45 ms on one GPU: warps that mix closest-hit and occlusion rays lose coherence).  ONE kernel for the whole stripe
+        # (clrt_accel_set_fused_shadows: 2) wins on small stripes: measured on 8 B200s, Soup-1M, 0.330 ms per frame against 0.399 with two
+        # kernels, 0.631 against 0.743 on 4 and 1.249 against 1.446 on 2 (profiles/r02_bench_soup1m_*gpu.json; the single-GPU stripe
+        # probe agrees for one kernel, profiles/r02_stripe_probe.md) — so it is the default on more than one GPU.
+        # CLRT_FRAME_KERNELS=1|2 overrides.
+        fk = os.environ.get("CLRT_FRAME_KERNELS", "auto")
+        self.one_kernel = accel.upper() == "BVH" and (fk == "1" or (fk == "auto" and world >= 2))
+        if self.one_kernel:
             self.accel.set_fused_shadows(2)
         self.cap = stripe_capacity(resX, resY, world)
         torch.cuda.synchronize()
@@ -149,7 +156,17 @@ class FrameRenderer:
         # work counter + scratch), so the tail of one frame's persistent kernels — a few long rays on a mostly idle GPU —
         # overlaps the head of the next frame's; gather + untile (+ read-back) run on one more stream (`comm`), in frame
         # order on every rank (the collective's order must agree across ranks).  Buffers are per slot; events order reuse.
-        self.DEPTH = max(1, min(8, int(os.environ.get("CLRT_FRAME_DEPTH", "8")))) if accel.upper() == "BVH" else 1
+        self.split_exchange = os.environ.get("CLRT_SPLIT_EXCHANGE", "1") != "0"
+        # Frames per pair of launches with the fused exchange (clrt_render_frames_peers; two-kernel mode): measured on 8 GPUs it
+        # bought 1 % (0.394 against 0.399 ms) and cost the e2e path its overlap, so it is off unless CLRT_FRAME_BATCH=2..4 asks for it.
+        fb = os.environ.get("CLRT_FRAME_BATCH", "1")
+        self.batch = 1 if fb == "auto" else max(1, min(4, int(fb)))
+        if accel.upper() != "BVH" or not self.split_exchange or self.one_kernel:
+            self.batch = 1
+        depth = int(os.environ.get("CLRT_FRAME_DEPTH", str(8 if self.batch == 1 else 4 * self.batch)))      # four launches' worth of frames in flight
+        self.DEPTH = max(1, min(16, depth)) if accel.upper() == "BVH" else 1
+        if self.DEPTH % self.batch:
+            self.batch = 1
         self.comm = torch.cuda.Stream(self.device)
         self.trace_streams = [self.stream] + [torch.cuda.Stream(self.device) for _ in range(self.DEPTH - 1)]
         self.stripes = [torch.zeros(self.cap, dtype=torch.int32, device=self.device) for _ in range(self.DEPTH)]
@@ -165,7 +182,7 @@ class FrameRenderer:
         if self.exchange not in ("nccl", "push", "fused"):
             raise ValueError("CLRT_EXCHANGE=%r (nccl, push or fused)" % self.exchange)
         self._peer_block = None
-        self.split_exchange = os.environ.get("CLRT_SPLIT_EXCHANGE", "1") != "0"
+        self._slot, self._slot_seq, self._pending = 0, [0] * 16, []
         if self.exchange != "nccl":
             self._setup_peers()
         self.stripe, self.gathered, self.raster, self.host_raster = self.stripes[0], self.gathereds[0], self.rasters[0], self.host_rasters[0]
@@ -233,10 +250,51 @@ class FrameRenderer:
         if self.world > 1:
             dist.barrier(group=self.group)                # nobody writes before everybody has opened
 
+    def _take_slots(self, m):
+        """m consecutive frame slots starting at the current one and their sequence numbers (per-slot counters: every rank makes the
+        same calls in the same order, so they agree across the box)."""
+        k0 = self._slot
+        assert k0 + m <= self.DEPTH
+        self._slot = (k0 + m) % self.DEPTH
+        seqs = []
+        for k in range(k0, k0 + m):
+            self._slot_seq[k] += 1
+            seqs.append(self._slot_seq[k])
+        self.frame_no += m
+        return k0, seqs
+
+    def _flush(self):
+        """Submits the pending frames (1..batch, consecutive slots) as ONE pair of launches (clrt_render_frames_peers)."""
+        pend, self._pending = self._pending, []
+        if not pend:
+            return
+        k0, seqs = self._take_slots(len(pend))
+        for i, (_, to_host) in enumerate(pend):
+            if to_host:
+                self.ev_host[k0 + i].synchronize()
+        ts = self.trace_streams[k0]
+        hosts = [self.host_rasters[k0 + i].data_ptr() if (p[1] and self.rank == 0) else None for i, p in enumerate(pend)]
+        self.accel.render_frames_peers(ts.cuda_stream, k0, [p[0] for p in pend], self.rank, self.world,
+                                       [self._peer_rasters[k0 + i] for i in range(len(pend))], self._peer_flags, seqs, hosts, self.comm.cuda_stream)
+        for i, p in enumerate(pend):
+            if p[1]:
+                self.ev_host[k0 + i].record(self.comm)
+
     def _submit_peers(self, camera, shadows, want_rays, to_host):
         torch = self.torch
-        k, seq = slot_sequence(self.frame_no, self.DEPTH)
-        self.frame_no += 1
+        if self.batch > 1 and self.exchange == "fused" and shadows and not want_rays:
+            # frames are collected and traced `batch` at a time (one pair of launches for all their stripes); join() / finish() flush
+            if not self._pending and self._slot + self.batch > self.DEPTH:
+                self._slot = 0                              # a batch occupies consecutive slots
+            k = self._slot + len(self._pending)
+            self._pending.append((camera, to_host))
+            self.stripe, self.raster, self.host_raster = self.stripes[k], self.rasters[k], self.host_rasters[k]
+            if len(self._pending) == self.batch:
+                self._flush()
+            return None
+        self._flush()
+        k, seqs = self._take_slots(1)
+        seq = seqs[0]
         if to_host:
             self.ev_host[k].synchronize()
         ts = self.trace_streams[k]
@@ -317,6 +375,8 @@ class FrameRenderer:
 
     def join(self):
         """Makes the context's stream wait for every frame submitted so far (device-side join, no host wait)."""
+        if self.exchange != "nccl":
+            self._flush()                               # a batch that did not fill up
         for ts in self.trace_streams[1:]:
             self.stream.wait_stream(ts)
         self.stream.wait_stream(self.comm)

@@ -20,6 +20,10 @@ for what in "$@"; do
     bench)    timeout 600 $TR 29513 bench.py --gpus $N --steps 400 --warmup 20 --no-kernels > gpurun_out/bench_soup1m_${N}gpu_$TAG.json 2> gpurun_out/bench_soup1m_${N}gpu_$TAG.err; line gpurun_out/bench_soup1m_${N}gpu_$TAG.json ;;
     bench1k)  CLRT_FRAME_KERNELS=1 timeout 600 $TR 29514 bench.py --gpus $N --steps 400 --warmup 20 --no-kernels > gpurun_out/bench_soup1m_1k_${N}gpu_$TAG.json 2> gpurun_out/bench_soup1m_1k_${N}gpu_$TAG.err; line gpurun_out/bench_soup1m_1k_${N}gpu_$TAG.json ;;
     benchnosplit) CLRT_SPLIT_EXCHANGE=0 timeout 600 $TR 29515 bench.py --gpus $N --steps 400 --warmup 20 --no-kernels > gpurun_out/bench_soup1m_nosplit_${N}gpu_$TAG.json 2> gpurun_out/bench_soup1m_nosplit_${N}gpu_$TAG.err; line gpurun_out/bench_soup1m_nosplit_${N}gpu_$TAG.json ;;
+    cfg:*)    # cfg:<label>:<ENV=val,ENV=val,...> — bench.py soup1m under the given environment
+              label=$(echo $what | cut -d: -f2); envs=$(echo $what | cut -d: -f3 | tr "," " ")
+              env $envs timeout 600 $TR 29518 bench.py --gpus $N --steps 300 --warmup 20 --no-kernels > gpurun_out/bench_soup1m_${label}_${N}gpu_$TAG.json 2> gpurun_out/bench_soup1m_${label}_${N}gpu_$TAG.err; line gpurun_out/bench_soup1m_${label}_${N}gpu_$TAG.json ;;
+    bench2k16) CLRT_FRAME_KERNELS=2 CLRT_FRAME_DEPTH=16 timeout 600 $TR 29517 bench.py --gpus $N --steps 400 --warmup 20 --no-kernels > gpurun_out/bench_soup1m_2k16_${N}gpu_$TAG.json 2> gpurun_out/bench_soup1m_2k16_${N}gpu_$TAG.err; line gpurun_out/bench_soup1m_2k16_${N}gpu_$TAG.json ;;
     spheres)  timeout 900 $TR 29516 bench.py --gpus $N --workload spheres10m --steps 40 --warmup 5 --no-kernels > gpurun_out/bench_spheres10m_${N}gpu_$TAG.json 2> gpurun_out/bench_spheres10m_${N}gpu_$TAG.err; line gpurun_out/bench_spheres10m_${N}gpu_$TAG.json ;;
     broadcast) timeout 600 $TR 29512 profiles/broadcast_probe.py 2>&1 | grep -v "^\[W\|^W0\|^$" | tail -3; cp gpurun_out/broadcast_probe_$N.json gpurun_out/broadcast_${N}gpu_$TAG.json 2>/dev/null ;;
   esac

@@ -133,6 +133,6 @@ def test_peer_exchange_protocol_under_random_interleavings(world, depth):
 
 
 def test_peer_flag_words_do_not_collide():
-    words = {frame.peer_word(kind, slot, w) for kind in (frame.PEER_READY, frame.PEER_ACK) for slot in range(8) for w in range(8)}
-    assert len(words) == 128 and max(words) < frame.PEER_WORDS
+    words = {frame.peer_word(kind, slot, w) for kind in (frame.PEER_READY, frame.PEER_ACK) for slot in range(16) for w in range(8)}
+    assert len(words) == 256 and max(words) < frame.PEER_WORDS
     assert [frame.slot_sequence(f, 3) for f in range(7)] == [(0, 1), (1, 1), (2, 1), (0, 2), (1, 2), (2, 2), (0, 3)]

@@ -229,6 +229,35 @@ def test_stripes_compose_to_the_single_gpu_frame(ctx, res):
     bvh.free(); scene.free()
 
 
+def test_batched_stripes_equal_single_stripes(ctx):
+    """clrt_render_stripes_batch: 1..4 stripes (one camera each) by one pair of launches == the same stripes rendered one by one."""
+    import torch
+    from openclraytracer_b200 import frame
+    buf = scenes.load_bundled("tenryuu")
+    scene, bvh = build_gpu(ctx, buf)
+    W, H = 321, 203
+    cams = [frame.orbit_camera(buf, W, H, s) for s in range(4)]
+    for nranks, rank in ((1, 0), (3, 1), (8, 7)):
+        cap, tiles = api.frame_stripe_pixels(W, H, rank, nranks)
+        units = tiles * 256
+        single = api.Buffer(ctx, max(cap, 1) * 4)
+        want = []
+        for c in cams:
+            bvh.render_stripe(c, True, rank, nranks, single.getCLMem())
+            want.append(single.copyToHost(np.uint32, cap)[:units].copy())
+        for k in (1, 2, 4):
+            batch = api.Buffer(ctx, max(units, 1) * 4 * k)
+            bvh.render_stripes_batch(ctx.stream, 0, cams[:k], rank, nranks, batch.getCLMem())
+            ctx.finish()
+            got = batch.copyToHost(np.uint32, units * k)
+            for f in range(k):
+                assert np.array_equal(got[f * units:(f + 1) * units], want[f]), (nranks, rank, k, f)
+            batch.free()
+        single.free()
+    bvh.check()
+    bvh.free(); scene.free()
+
+
 def test_full_size_soup_1m_properties(ctx):
     """BASELINE config 3 size: 1M-triangle soup.  Size-independent properties: sorted keys, leaf permutation,
     hierarchy + containment, FAST == REFERENCE_ORDER closest hits, idempotent rebuild."""

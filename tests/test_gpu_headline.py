@@ -105,10 +105,13 @@ def test_soup1m_fused_shadow_shade_vs_oracle(soup1m, ctx, O):
     u8.free()
 
 
-@pytest.mark.parametrize("exchange", ["nccl", "fused"])
+@pytest.mark.parametrize("exchange", ["nccl", "fused", "fused-batch4", "fused-batch2"])
 def test_frame_renderer_frames_vs_oracle(ctx, O, exchange, monkeypatch):
     """The bench's frame path (FrameRenderer: frame slots on several streams; with CLRT_EXCHANGE=fused the shading kernel stores
     the pixels through the peer-memory block, the GPU being its own peer) against the ORACLE's frame, more frames than slots."""
+    if "-batch" in exchange:                     # several frames per pair of launches (clrt_render_frames_peers), as at 4 / 8 GPUs
+        monkeypatch.setenv("CLRT_FRAME_BATCH", exchange[-1])
+        exchange = "fused"
     monkeypatch.setenv("CLRT_EXCHANGE", exchange)
     buf = scenes.soup_scene(150_000, seed=9)
     b = O.bvh_build(buf)
@@ -116,7 +119,7 @@ def test_frame_renderer_frames_vs_oracle(ctx, O, exchange, monkeypatch):
     r = frame.FrameRenderer(buf, W, H, "BVH", 0, 1, 0)
     assert r.exchange == exchange
     r.build()
-    poses = list(range(r.DEPTH + 2))
+    poses = list(range(r.DEPTH + 3))             # more frames than slots, and a last batch that does not fill up
     outs = []
     for p in poses:
         outs.append(r.render_host_async(frame.orbit_camera(buf, W, H, p), True))
