@@ -25,7 +25,7 @@ case "${1:-build}" in
   runcmd)                                                                       # any command per variant, e.g. the sort / scan probe
     shift
     for so in gpurun_variants/libclrt_${VARIANT_FILTER:-}*.so; do
-      echo "== $so"; CLRT_LIB_PATH=$PWD/$so timeout 300 bash -c "$*" 2>&1 | tail -8
+      echo "== $so"; CLRT_LIB_PATH=$PWD/$so timeout ${VARIANT_TIMEOUT:-300} bash -c "$*" 2>&1 | tail -8
     done ;;
   test)
     CLRT_LIB_PATH=$PWD/gpurun_variants/libclrt_$2.so timeout 900 python -m pytest tests/test_gpu_bvh.py tests/test_gpu_bounce.py -q -x -m gpu -k "not spheres_10m" 2>&1 | tail -3 ;;

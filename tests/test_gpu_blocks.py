@@ -69,7 +69,10 @@ def test_bitonic_compat_rejects_non_pow2(ctx):
     buf.free()
 
 
-@pytest.mark.parametrize("n", [0, 1, 2, 31, 4095, 4096, 4097, 65536, 1_000_003, 1 << 24])
+# sizes around the tile sizes of the staged kernel (8192 below 2^21 elements, 16384 from there), one tile, one wave of 148 CTAs, a few
+# waves with a ragged last tile, and the switch of tile size
+@pytest.mark.parametrize("n", [0, 1, 2, 31, 4095, 4096, 4097, 8191, 8192, 8193, 16385, 65536, 1_000_003, 8192 * 296 + 17, (1 << 21) - 1, 1 << 21,
+                               (1 << 21) + 1, 16384 * 148 + 1, 16384 * 148 * 3 + 5, 1 << 24])
 def test_scan_matches_oracle(ctx, O, n):
     a = (scenes.splitmix64(np.arange(n, dtype=np.uint64)) & np.uint64(7)).astype(np.uint32)
     bi = api.Buffer(ctx, max(a.nbytes, 16)); bo = api.Buffer(ctx, max(a.nbytes, 16))
@@ -84,6 +87,49 @@ def test_scan_matches_oracle(ctx, O, n):
     if n:
         assert want[-1] == a.sum(dtype=np.uint64) % (1 << 32)
     bi.free(); bo.free()
+
+
+@pytest.mark.parametrize("n", [5, 8192 * 3 + 1, 3_000_001])
+def test_scan_buffers_aligned_to_4_bytes_only(ctx, O, n):
+    """Odd offsets take the register-prefetch kernel with the classic look-back (scan.cu kernel 1); in place and out of place."""
+    a = (scenes.splitmix64(np.arange(n, dtype=np.uint64)) & np.uint64(15)).astype(np.uint32)
+    want = O.scan_inclusive(a)
+    bi = api.Buffer(ctx, a.nbytes + 32); bo = api.Buffer(ctx, a.nbytes + 32)
+    pad = np.zeros(n + 3, dtype=np.uint32); pad[3:] = a
+    bi.upload(pad)
+    ps = api.PrefixSum(ctx)
+    ps.computePrefixSum(bi.getCLMem() + 12, bo.getCLMem() + 4, n)
+    assert np.array_equal(bo.copyToHost(np.uint32, n + 1)[1:], want)
+    ps.computePrefixSum(bi.getCLMem() + 12, bi.getCLMem() + 12, n)
+    assert np.array_equal(bi.copyToHost(np.uint32, n + 3)[3:], want)
+    bi.free(); bo.free()
+
+
+def test_scan_repeated_calls_reuse_descriptors(ctx, O):
+    """Descriptors are never reset: a call is told from the previous ones by its generation number.  Alternating sizes and tile sizes
+    on one context must not see stale aggregates."""
+    ps = api.PrefixSum(ctx)
+    for rep, n in enumerate([3_000_000, 100_000, 3_000_000, 2_500_000, 16384 * 148 * 2, 3_000_000]):
+        a = (scenes.splitmix64(np.arange(n, dtype=np.uint64) + np.uint64(rep)) & np.uint64(7)).astype(np.uint32)
+        b = api.Buffer.from_array(ctx, a)
+        ps.computePrefixSum(b.getCLMem(), b.getCLMem(), n)
+        assert np.array_equal(b.copyToHost(np.uint32, n), O.scan_inclusive(a)), (rep, n)
+        b.free()
+
+
+def test_scan_full_size_property(ctx):
+    """BASELINE config 5's largest size, 2^28 elements: scan of ones = 1, 2, 3, ... (size-independent property)."""
+    n = 1 << 28
+    b = api.Buffer.from_array(ctx, np.ones(n, dtype=np.uint32))
+    api.PrefixSum(ctx).computePrefixSum(b.getCLMem(), b.getCLMem(), n)
+    got = b.copyToHost(np.uint32, n)
+    b.free()
+    assert got[0] == 1 and got[-1] == n
+    assert (np.diff(got[:: 4099].astype(np.int64)) == 4099).all()
+    assert np.array_equal(got[-70_000:], np.arange(n - 70_000 + 1, n + 1, dtype=np.uint32))
+    assert np.array_equal(got[: 70_000], np.arange(1, 70_001, dtype=np.uint32))
+    mid = 148 * 16384 * 37                                              # a wave boundary
+    assert np.array_equal(got[mid - 20_000: mid + 20_000], np.arange(mid - 20_000 + 1, mid + 20_000 + 1, dtype=np.uint32))
 
 
 def test_scan_wraps_like_uint32(ctx, O):
