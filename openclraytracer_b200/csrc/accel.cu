@@ -52,7 +52,7 @@ extern "C" int clrt_accel_destroy(clrt_accel* a) {
   if (a->kind == ACCEL_KD) kd_destroy(a);
   if (a->d_nodes) cudaFree(a->d_nodes);
   if (a->d_pairs) cudaFree(a->d_pairs);
-  if (a->d_counters) cudaFree(a->d_counters);
+  if (a->d_pyr) cudaFree(a->d_pyr);
   if (a->d_tnodes) cudaFree(a->d_tnodes);
   if (a->d_refpos) cudaFree(a->d_refpos);
   trace_tree_destroy(a);

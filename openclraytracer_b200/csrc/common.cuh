@@ -131,7 +131,7 @@ struct clrt_accel {
   uint32_t n = 0;                 // leaves
   clrt_bvh_node* d_nodes = nullptr; size_t nodes_cap = 0;     // (2N-1) x 48 B, reference layout
   clrt_uint2* d_pairs = nullptr;  size_t pairs_cap = 0;       // pow2ceil(N) x 8 B (padding = UINT_MAX pairs)
-  uint32_t* d_counters = nullptr; size_t counters_cap = 0;    // N x 4 B
+  void* d_pyr = nullptr; size_t pyr_cap = 0;                  // box pyramid (boxpyr.cuh): 2 x pow2ceil(N) x 32 B
   TraceNode* d_tnodes = nullptr;  size_t tnodes_cap = 0;      // (N-1) x 64 B
   clrt_triangle* d_tris_sorted = nullptr; size_t tris_sorted_cap = 0;   // N x 48 B, sorted-leaf order, v1.w = triangle id
   uint32_t* d_refpos = nullptr; size_t refpos_cap = 0;                  // N x 4 B: triangle -> position in the reference's sorted order
@@ -144,9 +144,7 @@ struct clrt_accel {
   bool tt_built = false;
   TraceNode* d_tt_nodes = nullptr; size_t tt_nodes_cap = 0;             // (N-1) x 64 B
   clrt_triangle* d_tt_tris = nullptr; size_t tt_tris_cap = 0;           // N x 48 B in trace-tree order; v1.w = triangle id, v2.w = reference sorted position
-  float4* d_tt_leafbox = nullptr; size_t tt_leafbox_cap = 0;            // leaf boxes in trace-tree order (tt_emit_kernel -> tt_refit_kernel)
   clrt_uint2* d_tt_pairs = nullptr; size_t tt_pairs_cap = 0;            // N x 8 B (fine Morton code, triangle)
-  uint32_t* d_tt_parent = nullptr; size_t tt_parent_cap = 0;            // (2N) x 4 B: parent link | side bit
   // --- primary contacts / frame scratch ---
   clrt_contact* d_contacts = nullptr; size_t contacts_cap = 0;
   void* d_frame_scratch = nullptr; size_t frame_scratch_cap = 0;

@@ -13,10 +13,11 @@
 // winner (trace.cu).  Traversal kernels take it through the same TraceNode / clrt_triangle layouts.
 //
 // Kernels: tt_morton_kernel (48 B in, 8 B out per triangle) -> onesweep sort (sort.cu) -> tt_emit_kernel (Karras
-// ranges + gather of the triangles in tree order, ~110 B per triangle) -> tt_refit_kernel (bottom-up with arrival
-// counters; a child's box is stored INSIDE its parent's TraceNode, so no separate box array exists: 64 B per node).
+// ranges + gather of the triangles in tree order; both child boxes of a node by range queries on the box pyramid of the
+// leaf boxes in this tree's order, boxpyr.cuh — no bottom-up pass; a child's box is stored INSIDE its parent's TraceNode: 64 B per node).
 #include "common.cuh"
 #include "rtmath.cuh"
+#include "boxpyr.cuh"
 
 namespace {
 
@@ -52,13 +53,22 @@ __device__ __forceinline__ int tt_delta(const uint2* __restrict__ list, int n, u
   return ki != kj ? __clz(ki ^ kj) : 32 + __clz((uint32_t)i ^ (uint32_t)j);
 }
 
-// One thread per sorted position p: gathers triangle + leaf box into tree order; threads p < n-1 also emit inner node p.
-// parent[] holds, for inner node i at [i] and leaf p at [n + p], (parent inner index << 1) | side (0 = child A, 1 = child B);
-// the root's entry is 0xFFFFFFFF.
+// Leaf boxes in this tree's order for the pyramid: the box morton_leaves_kernel stored in the leaf's reference node.
+struct TtLeafBox {
+  const uint2* list; const clrt_bvh_node* ref_nodes;
+  __device__ __forceinline__ Box6 operator()(uint32_t p) const {
+    const float4* lb = reinterpret_cast<const float4*>(ref_nodes + __ldg(&list[p].y)) + 1;
+    const float4 lo = __ldg(lb), hi = __ldg(lb + 1);
+    Box6 b; b.lx = lo.x; b.ly = lo.y; b.lz = lo.z; b.hx = hi.x; b.hy = hi.y; b.hz = hi.z;
+    return b;
+  }
+};
+
+// One thread per sorted position p: gathers the triangle into tree order; threads p < n-1 also emit inner node p — children, and both
+// child boxes as range queries on the pyramid.
 __global__ void __launch_bounds__(256)
-tt_emit_kernel(const uint2* __restrict__ list, uint32_t n_, const clrt_triangle* __restrict__ tris, const clrt_bvh_node* __restrict__ ref_nodes,
-               const uint32_t* __restrict__ refpos, clrt_triangle* __restrict__ tris_out, float4* __restrict__ leafbox_out,
-               TraceNode* __restrict__ tnodes, uint32_t* __restrict__ parent) {
+tt_emit_kernel(const uint2* __restrict__ list, uint32_t n_, const clrt_triangle* __restrict__ tris,
+               const uint32_t* __restrict__ refpos, clrt_triangle* __restrict__ tris_out, TraceNode* __restrict__ tnodes, const PyrView pv) {
   const int n = (int)n_;
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
@@ -70,8 +80,6 @@ tt_emit_kernel(const uint2* __restrict__ list, uint32_t n_, const clrt_triangle*
     c.w = __uint_as_float(__ldg(refpos + leaf));
     float4* dst = reinterpret_cast<float4*>(tris_out + i);
     dst[0] = a; dst[1] = b; dst[2] = c;
-    const float4* lb = reinterpret_cast<const float4*>(ref_nodes + leaf) + 1;      // leaf box of morton_leaves_kernel (reference arithmetic)
-    leafbox_out[2 * (size_t)i] = __ldg(lb); leafbox_out[2 * (size_t)i + 1] = __ldg(lb + 1);
   }
   if (i + 1 >= n) return;
   const uint32_t ki = __ldg(&list[i].x);
@@ -94,38 +102,13 @@ tt_emit_kernel(const uint2* __restrict__ list, uint32_t n_, const clrt_triangle*
   const bool aLeaf = first == gamma, bLeaf = last == gamma + 1;
   const uint32_t cA = aLeaf ? (uint32_t)gamma : (uint32_t)gamma + n_;
   const uint32_t cB = bLeaf ? (uint32_t)gamma + 1u : (uint32_t)gamma + 1u + n_;
-  reinterpret_cast<uint4*>(tnodes + i)[3] = make_uint4(cA, cB, 0u, 0u);        // no runs in this tree
-  parent[aLeaf ? n_ + (uint32_t)gamma : (uint32_t)gamma] = ((uint32_t)i << 1);
-  parent[bLeaf ? n_ + (uint32_t)gamma + 1u : (uint32_t)gamma + 1u] = ((uint32_t)i << 1) | 1u;
-  if (i == 0) parent[0] = 0xFFFFFFFFu;
-}
-
-// One thread per leaf: writes its box into its parent's TraceNode slot, then climbs; the second thread to arrive at a node
-// reads the sibling box from the same TraceNode (written before the first arrival's atomic), merges and goes on.
-__device__ __forceinline__ void tt_store_child_box(TraceNode* node, uint32_t side, float4 lo, float4 hi) {
-  float* f = reinterpret_cast<float*>(node);
-  if (side == 0) { __stcg(f + 0, lo.x); __stcg(f + 1, lo.y); __stcg(f + 2, lo.z); __stcg(f + 3, hi.x); __stcg(f + 4, hi.y); __stcg(f + 5, hi.z); }
-  else           { __stcg(f + 6, lo.x); __stcg(f + 7, lo.y); __stcg(f + 8, lo.z); __stcg(f + 9, hi.x); __stcg(f + 10, hi.y); __stcg(f + 11, hi.z); }
-}
-__global__ void __launch_bounds__(256)
-tt_refit_kernel(const float4* __restrict__ leafbox, const uint32_t* __restrict__ parent, uint32_t* __restrict__ counters, uint32_t n,
-                TraceNode* __restrict__ tnodes) {
-  const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
-  if (p >= n) return;
-  float4 lo = __ldg(leafbox + 2 * (size_t)p), hi = __ldg(leafbox + 2 * (size_t)p + 1);
-  uint32_t link = __ldg(parent + n + p);
-  while (link != 0xFFFFFFFFu) {
-    const uint32_t node = link >> 1, side = link & 1u;
-    tt_store_child_box(tnodes + node, side, lo, hi);
-    uint32_t arrived;                                         // release our box / acquire the sibling's (one acq_rel atomic, no fences)
-    asm volatile("atom.add.acq_rel.gpu.global.u32 %0, [%1], 1;" : "=r"(arrived) : "l"(counters + node) : "memory");
-    if (arrived == 0) return;                                 // the sibling subtree is not done yet
-    const float* f = reinterpret_cast<const float*>(tnodes + node) + (side ? 0 : 6);     // the sibling's box
-    const float sx0 = __ldcg(f), sy0 = __ldcg(f + 1), sz0 = __ldcg(f + 2), sx1 = __ldcg(f + 3), sy1 = __ldcg(f + 4), sz1 = __ldcg(f + 5);
-    lo.x = fminf(lo.x, sx0); lo.y = fminf(lo.y, sy0); lo.z = fminf(lo.z, sz0);
-    hi.x = fmaxf(hi.x, sx1); hi.y = fmaxf(hi.y, sy1); hi.z = fmaxf(hi.z, sz1);
-    link = __ldg(parent + node);
-  }
+  const Box6 A = aLeaf ? pyr_load(pv, 0, (uint32_t)gamma) : pyr_query(pv, (uint32_t)first, (uint32_t)gamma);
+  const Box6 B = bLeaf ? pyr_load(pv, 0, (uint32_t)gamma + 1u) : pyr_query(pv, (uint32_t)gamma + 1u, (uint32_t)last);
+  float4* tn = reinterpret_cast<float4*>(tnodes + i);
+  __stcg(tn,     make_float4(A.lx, A.ly, A.lz, A.hx));
+  __stcg(tn + 1, make_float4(A.hy, A.hz, B.lx, B.ly));
+  __stcg(tn + 2, make_float4(B.lz, B.hx, B.hy, B.hz));
+  reinterpret_cast<uint4*>(tn)[3] = make_uint4(cA, cB, 0u, 0u);                // no runs in this tree
 }
 
 // 2-level collapse: wide node i = the grandchildren of binary node i (a leaf child stays as it is).  One thread per binary
@@ -263,12 +246,10 @@ wide_top_kernel(const WideNode* __restrict__ wnodes, uint32_t n, WideNode* __res
 void trace_tree_destroy(clrt_accel* a) {
   if (a->d_tt_nodes) cudaFree(a->d_tt_nodes);
   if (a->d_tt_tris) cudaFree(a->d_tt_tris);
-  if (a->d_tt_leafbox) cudaFree(a->d_tt_leafbox);
   if (a->d_tt_pairs) cudaFree(a->d_tt_pairs);
-  if (a->d_tt_parent) cudaFree(a->d_tt_parent);
   if (a->d_wnodes) cudaFree(a->d_wnodes);
   a->d_wnodes = nullptr;
-  a->d_tt_nodes = nullptr; a->d_tt_tris = nullptr; a->d_tt_leafbox = nullptr; a->d_tt_pairs = nullptr; a->d_tt_parent = nullptr;
+  a->d_tt_nodes = nullptr; a->d_tt_tris = nullptr; a->d_tt_pairs = nullptr;
 }
 
 // Called at the end of bvh_construct (a->max_run is known).  Auto policy: build when the reference tree holds an equal-key
@@ -316,23 +297,20 @@ static int trace_tree_separate(clrt_accel* a) {
   const uint32_t n = a->n;
   const clrt_aabb bb = a->scene->header.modelsBoundingBox;
   cudaStream_t s = ctx->stream;
-  if ((size_t)n * sizeof(TraceNode) > a->tt_nodes_cap || (size_t)n * sizeof(clrt_triangle) > a->tt_tris_cap || (size_t)n * 32 > a->tt_leafbox_cap ||
-      (size_t)n * 8 > a->tt_pairs_cap || (size_t)n * 8 > a->tt_parent_cap)
+  if ((size_t)n * sizeof(TraceNode) > a->tt_nodes_cap || (size_t)n * sizeof(clrt_triangle) > a->tt_tris_cap || (size_t)n * 8 > a->tt_pairs_cap ||
+      pyr_bytes(n) > a->pyr_cap)
     CLRT_CUDA(cudaStreamSynchronize(s));
   CLRT_TRY(clrt_grow((void**)&a->d_tt_nodes, &a->tt_nodes_cap, (size_t)n * sizeof(TraceNode)));
   CLRT_TRY(clrt_grow((void**)&a->d_tt_tris, &a->tt_tris_cap, (size_t)n * sizeof(clrt_triangle)));
-  CLRT_TRY(clrt_grow((void**)&a->d_tt_leafbox, &a->tt_leafbox_cap, (size_t)n * 32));
   CLRT_TRY(clrt_grow((void**)&a->d_tt_pairs, &a->tt_pairs_cap, (size_t)n * 8));
-  CLRT_TRY(clrt_grow((void**)&a->d_tt_parent, &a->tt_parent_cap, (size_t)n * 8));
+  CLRT_TRY(clrt_grow((void**)&a->d_pyr, &a->pyr_cap, pyr_bytes(n)));             // the reference tree's pyramid is done with: reused
   const unsigned grid = (n + 255) / 256;
   tt_morton_kernel<<<grid, 256, 0, s>>>(a->scene->d_tris, n, bb, reinterpret_cast<uint2*>(a->d_tt_pairs));
   CLRT_CHECK_LAUNCH();
   CLRT_TRY(sort_pairs_radix(ctx, a->d_tt_pairs, n, 30));
-  CLRT_CUDA(cudaMemsetAsync(a->d_counters, 0, (size_t)n * 4, s));              // the reference refit is done with them
-  tt_emit_kernel<<<grid, 256, 0, s>>>(reinterpret_cast<const uint2*>(a->d_tt_pairs), n, a->scene->d_tris, a->d_nodes, a->d_refpos,
-                                      a->d_tt_tris, a->d_tt_leafbox, a->d_tt_nodes, a->d_tt_parent);
-  CLRT_CHECK_LAUNCH();
-  tt_refit_kernel<<<grid, 256, 0, s>>>(a->d_tt_leafbox, a->d_tt_parent, a->d_counters, n, a->d_tt_nodes);
+  const PyrView pv = pyr_view(a->d_pyr, n);
+  CLRT_TRY(pyr_build(ctx, pv, TtLeafBox{reinterpret_cast<const uint2*>(a->d_tt_pairs), a->d_nodes}));
+  tt_emit_kernel<<<grid, 256, 0, s>>>(reinterpret_cast<const uint2*>(a->d_tt_pairs), n, a->scene->d_tris, a->d_refpos, a->d_tt_tris, a->d_tt_nodes, pv);
   CLRT_CHECK_LAUNCH();
   return 0;
 }
