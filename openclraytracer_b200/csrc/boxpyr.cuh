@@ -18,6 +18,10 @@
 #include "common.cuh"
 #include "rtmath.cuh"
 
+#ifndef CLRT_PYR_LDG
+#define CLRT_PYR_LDG 1
+#endif
+
 struct Box6 { float lx, ly, lz, hx, hy, hz; };
 __device__ __forceinline__ Box6 box_join(const Box6& L, const Box6& R) {      // L = lower sorted positions, R = higher
   Box6 o;
@@ -45,7 +49,11 @@ __host__ __device__ __forceinline__ size_t pyr_index(const PyrView& pv, int k, u
 }
 __device__ __forceinline__ Box6 pyr_load(const PyrView& pv, int k, uint32_t j) {
   const float4* p = pv.e + 2 * pyr_index(pv, k, j);
+#if CLRT_PYR_LDG
+  const float4 lo = __ldg(p), hi = __ldg(p + 1);       // entries are written by EARLIER launches only: the read-only path is safe
+#else
   const float4 lo = __ldcg(p), hi = __ldcg(p + 1);
+#endif
   Box6 b; b.lx = lo.x; b.ly = lo.y; b.lz = lo.z; b.hx = hi.x; b.hy = hi.y; b.hz = hi.z;
   return b;
 }

@@ -24,6 +24,12 @@ namespace {
 #ifndef CLRT_SORT_BIG_TILES_FROM
 #define CLRT_SORT_BIG_TILES_FROM (1u << 19)     /* 4096-pair tiles above this size, 1024-pair tiles (more CTAs in flight) below */
 #endif
+#ifndef CLRT_SORT_DEBUG
+#define CLRT_SORT_DEBUG 0            /* experiments only (wrong results): 1 = no look-back, 2 = no look-back and no ranking */
+#endif
+#ifndef CLRT_SORT_LOOK
+#define CLRT_SORT_LOOK 4
+#endif
 constexpr int RADIX_BITS = 8;
 constexpr int BINS = 1 << RADIX_BITS;
 constexpr int SORT_THREADS = 256;
@@ -136,6 +142,7 @@ onesweep_pass_kernel(const uint2* __restrict__ in, uint2* __restrict__ out, uint
     const uint32_t local = warp_base + j * 32 + lane;
     const bool valid = FULL || local < tile_items;
     const uint32_t digit = (item[j].x >> shift) & (BINS - 1);
+    if (CLRT_SORT_DEBUG == 2) { rank[j] = 0; if (lane == 0 && j == 0) s_warp_hist[warp][digit] = 32 * IPT; continue; }
     uint32_t m = FULL ? 0xffffffffu : __ballot_sync(0xffffffffu, valid);
 #pragma unroll
     for (int b = 0; b < RADIX_BITS; b++) {
@@ -171,10 +178,10 @@ onesweep_pass_kernel(const uint2* __restrict__ in, uint2* __restrict__ out, uint
     s_tile_excl[tid] = off + incl - count;
   }
   uint32_t excl = 0;
-  if (tile > 0) {
+  if (tile > 0 && CLRT_SORT_DEBUG == 0) {
     // decoupled look-back, one thread per digit; LOOK descriptors are fetched together (independent L2 round trips) and
     // consumed in order — the walk was 18 % of the stall samples with one dependent load per predecessor.
-    constexpr int LOOK = 4;
+    constexpr int LOOK = CLRT_SORT_LOOK;
     int t = (int)tile - 1;
     bool done = false;
     while (!done) {
