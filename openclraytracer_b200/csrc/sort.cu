@@ -27,6 +27,9 @@ namespace {
 #ifndef CLRT_SORT_DEBUG
 #define CLRT_SORT_DEBUG 0            /* experiments only (wrong results): 1 = no look-back, 2 = no look-back and no ranking */
 #endif
+#ifndef CLRT_SORT_MIN_CTAS
+#define CLRT_SORT_MIN_CTAS 4
+#endif
 #ifndef CLRT_SORT_LOOK
 #define CLRT_SORT_LOOK 4
 #endif
@@ -100,7 +103,7 @@ radix_scan_hist_kernel(uint32_t* __restrict__ hist, int passes) {
 
 // ---- one onesweep pass ---------------------------------------------------------------------------------
 template <int IPT, bool FULL>
-__global__ void __launch_bounds__(SORT_THREADS, 4)
+__global__ void __launch_bounds__(SORT_THREADS, CLRT_SORT_MIN_CTAS)
 onesweep_pass_kernel(const uint2* __restrict__ in, uint2* __restrict__ out, uint32_t n, int shift,
                      const uint32_t* __restrict__ digit_base,   // [BINS] exclusive global offsets of this pass
                      uint32_t* __restrict__ status,             // [tiles][BINS] look-back descriptors (zeroed)

@@ -111,28 +111,6 @@ tt_emit_kernel(const uint2* __restrict__ list, uint32_t n_, const clrt_triangle*
   reinterpret_cast<uint4*>(tn)[3] = make_uint4(cA, cB, 0u, 0u);                // no runs in this tree
 }
 
-// 2-level collapse: wide node i = the grandchildren of binary node i (a leaf child stays as it is).  One thread per binary
-// inner node, 3 x 64 B in, 128 B out; no ordering between nodes is needed because EVERY binary node gets a wide node —
-// the ones not reachable through wide links are never visited.
-// Slots 0,1 come from child A, slots 2,3 from child B (a leaf child fills one slot, the other stays empty): static slot
-// indices keep the node in registers (a running slot index put it in local memory: lg_throttle = 174 in the first capture).
-struct Slot2 { float4 lo0, hi0, lo1, hi1; uint32_t c0, c1; };     // .xyz used
-__device__ __forceinline__ Slot2 wn_expand(const TraceNode* __restrict__ tnodes, uint32_t n, uint32_t child,
-                                           float x0, float y0, float z0, float x1, float y1, float z1) {
-  const float qnan = __int_as_float(0x7fc00000);          // empty slot: a NaN box fails every comparison of the slab test
-  Slot2 s;
-  if (child < n) {
-    s.lo0 = make_float4(x0, y0, z0, 0.0f); s.hi0 = make_float4(x1, y1, z1, 0.0f); s.c0 = child;
-    s.lo1 = make_float4(qnan, qnan, qnan, 0.0f); s.hi1 = s.lo1; s.c1 = 0xFFFFFFFFu;
-    return s;
-  }
-  const float4* p = reinterpret_cast<const float4*>(tnodes + (child - n));
-  const float4 q0 = __ldg(p), q1 = __ldg(p + 1), q2 = __ldg(p + 2);
-  const uint4 q3 = __ldg(reinterpret_cast<const uint4*>(p + 3));
-  s.lo0 = make_float4(q0.x, q0.y, q0.z, 0.0f); s.hi0 = make_float4(q0.w, q1.x, q1.y, 0.0f); s.c0 = q3.x;
-  s.lo1 = make_float4(q1.z, q1.w, q2.x, 0.0f); s.hi1 = make_float4(q2.y, q2.z, q2.w, 0.0f); s.c1 = q3.y;
-  return s;
-}
 #if CLRT_WIDE_Q16
 // The quantisation grid: the root's box (union of its two child boxes in tnodes[0]) enlarged by a sliver, 65535 steps per axis.
 __global__ void wide_frame_kernel(const TraceNode* __restrict__ tnodes, QFrame* __restrict__ frame) {
@@ -159,19 +137,61 @@ __device__ __forceinline__ void q16_pair(float flo, float step, float lo, float 
 }
 #endif
 
+// Collapse of the binary trace structure into 4-wide nodes.  One thread per binary inner node i: wide node i starts from i's two
+// children and twice replaces the INNER slot with the largest surface area by that child's two children (the usual greedy collapse:
+// the child most likely to be entered anyway is opened).  Round 2a opened both children unconditionally — the grandchildren — so a
+// leaf child left a slot empty and nodes near the leaves, where a ray spends most of its visits, held two or three boxes.  3 x 64 B
+// in, 64 B out; no ordering between nodes is needed because EVERY binary node gets a wide node — the ones not reachable through
+// wide links are never visited.  Slots are named registers moved by selects: a running slot index put the node in local memory.
+#ifndef CLRT_WIDEN_GREEDY
+#define CLRT_WIDEN_GREEDY 1
+#endif
+struct WSlot { float4 lo, hi; uint32_t c; };                       // .xyz used; c: leaf (< n), inner (n + index) or 0xFFFFFFFF = empty
+__device__ __forceinline__ WSlot wslot_empty() {
+  const float qnan = __int_as_float(0x7fc00000);                   // empty slot: a NaN box fails every comparison of the slab test
+  WSlot s; s.lo = make_float4(qnan, qnan, qnan, 0.0f); s.hi = s.lo; s.c = 0xFFFFFFFFu; return s;
+}
+__device__ __forceinline__ float wslot_area(const WSlot& s, uint32_t n) {          // -1 for slots that cannot be opened
+  if (s.c < n || s.c == 0xFFFFFFFFu) return -1.0f;
+  const float dx = s.hi.x - s.lo.x, dy = s.hi.y - s.lo.y, dz = s.hi.z - s.lo.z;
+  return fmaxf(dx * dy + dy * dz + dz * dx, 0.0f);
+}
+__device__ __forceinline__ void wslot_children(const TraceNode* __restrict__ tnodes, uint32_t n, uint32_t inner, WSlot& x, WSlot& y) {
+  const float4* p = reinterpret_cast<const float4*>(tnodes + (inner - n));
+  const float4 q0 = __ldg(p), q1 = __ldg(p + 1), q2 = __ldg(p + 2);
+  const uint4 q3 = __ldg(reinterpret_cast<const uint4*>(p + 3));
+  x.lo = make_float4(q0.x, q0.y, q0.z, 0.0f); x.hi = make_float4(q0.w, q1.x, q1.y, 0.0f); x.c = q3.x;
+  y.lo = make_float4(q1.z, q1.w, q2.x, 0.0f); y.hi = make_float4(q2.y, q2.z, q2.w, 0.0f); y.c = q3.y;
+}
+__device__ __forceinline__ void wslot_swap_if(bool c, WSlot& a, WSlot& b) { if (c) { const WSlot t = a; a = b; b = t; } }
+
 __global__ void __launch_bounds__(128)
 widen_kernel(const TraceNode* __restrict__ tnodes, uint32_t n, WideNode* __restrict__ wnodes) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i + 1 >= n) return;
-  const float4* p = reinterpret_cast<const float4*>(tnodes + i);
-  const float4 q0 = __ldg(p), q1 = __ldg(p + 1), q2 = __ldg(p + 2);
-  const uint4 q3 = __ldg(reinterpret_cast<const uint4*>(p + 3));
-  const Slot2 a = wn_expand(tnodes, n, q3.x, q0.x, q0.y, q0.z, q0.w, q1.x, q1.y);
-  const Slot2 b = wn_expand(tnodes, n, q3.y, q1.z, q1.w, q2.x, q2.y, q2.z, q2.w);
+  WSlot s0, s1, s2 = wslot_empty(), s3 = wslot_empty();
+  wslot_children(tnodes, n, n + i, s0, s1);
+#if CLRT_WIDEN_GREEDY
+  // first opening: the larger inner child of the two goes to s1, its children take s1 and s2
+  wslot_swap_if(wslot_area(s0, n) > wslot_area(s1, n), s0, s1);
+  if (wslot_area(s1, n) >= 0.0f) {
+    wslot_children(tnodes, n, s1.c, s1, s2);
+    // second opening: the largest inner slot of the three goes to s2, its children take s2 and s3
+    wslot_swap_if(wslot_area(s0, n) > wslot_area(s2, n), s0, s2);
+    wslot_swap_if(wslot_area(s1, n) > wslot_area(s2, n), s1, s2);
+    if (wslot_area(s2, n) >= 0.0f) wslot_children(tnodes, n, s2.c, s2, s3);
+  }
+#else
+  // the grandchildren: both children opened whatever their size
+  { const WSlot b = s1;
+    if (s0.c >= n) wslot_children(tnodes, n, s0.c, s0, s1); else s1 = wslot_empty();
+    s2 = b;
+    if (b.c >= n) wslot_children(tnodes, n, b.c, s2, s3); }
+#endif
 #if CLRT_WIDE_Q16
   const QFrame f = *reinterpret_cast<const QFrame*>(wnodes + n + WIDE_TOP_NODES);
-  const uint32_t c[4] = {a.c0, a.c1, b.c0, b.c1};
-  const float4 lo[4] = {a.lo0, a.lo1, b.lo0, b.lo1}, hi[4] = {a.hi0, a.hi1, b.hi0, b.hi1};
+  const uint32_t c[4] = {s0.c, s1.c, s2.c, s3.c};
+  const float4 lo[4] = {s0.lo, s1.lo, s2.lo, s3.lo}, hi[4] = {s0.hi, s1.hi, s2.hi, s3.hi};
   uint32_t ql[3][4], qh[3][4];
 #pragma unroll
   for (int j = 0; j < 4; j++) {
@@ -187,13 +207,13 @@ widen_kernel(const TraceNode* __restrict__ tnodes, uint32_t n, WideNode* __restr
   o[3] = make_uint4(c[0], c[1], c[2], c[3]);
 #else
   float4* o = reinterpret_cast<float4*>(wnodes + i);
-  o[0] = make_float4(a.lo0.x, a.lo1.x, b.lo0.x, b.lo1.x);
-  o[1] = make_float4(a.lo0.y, a.lo1.y, b.lo0.y, b.lo1.y);
-  o[2] = make_float4(a.lo0.z, a.lo1.z, b.lo0.z, b.lo1.z);
-  o[3] = make_float4(a.hi0.x, a.hi1.x, b.hi0.x, b.hi1.x);
-  o[4] = make_float4(a.hi0.y, a.hi1.y, b.hi0.y, b.hi1.y);
-  o[5] = make_float4(a.hi0.z, a.hi1.z, b.hi0.z, b.hi1.z);
-  reinterpret_cast<uint4*>(o)[6] = make_uint4(a.c0, a.c1, b.c0, b.c1);
+  o[0] = make_float4(s0.lo.x, s1.lo.x, s2.lo.x, s3.lo.x);
+  o[1] = make_float4(s0.lo.y, s1.lo.y, s2.lo.y, s3.lo.y);
+  o[2] = make_float4(s0.lo.z, s1.lo.z, s2.lo.z, s3.lo.z);
+  o[3] = make_float4(s0.hi.x, s1.hi.x, s2.hi.x, s3.hi.x);
+  o[4] = make_float4(s0.hi.y, s1.hi.y, s2.hi.y, s3.hi.y);
+  o[5] = make_float4(s0.hi.z, s1.hi.z, s2.hi.z, s3.hi.z);
+  reinterpret_cast<uint4*>(o)[6] = make_uint4(s0.c, s1.c, s2.c, s3.c);
   reinterpret_cast<uint4*>(o)[7] = make_uint4(0u, 0u, 0u, 0u);
 #endif
 }

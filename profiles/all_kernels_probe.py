@@ -23,15 +23,19 @@ keys = torch.randint(0, 1 << 30, (1 << e,), dtype=torch.int32, device="cuda")
 pairs = torch.stack([keys, torch.arange(1 << e, dtype=torch.int32, device="cuda")], dim=1).contiguous()
 api.BitonicSort(ctx).sort(pairs.data_ptr(), 1 << e)              # radix_histogram, radix_scan_hist, onesweep_pass x4
 vals = torch.randint(0, 8, (1 << e,), dtype=torch.int32, device="cuda"); out = torch.empty_like(vals)
-api.PrefixSum(ctx).computePrefixSum(vals.data_ptr(), out.data_ptr(), 1 << e)      # scan_lookback_kernel
+api.PrefixSum(ctx).computePrefixSum(vals.data_ptr(), out.data_ptr(), 1 << e)      # scan_window_kernel<4>
 small = pairs[: 1 << 12].clone()
 api.BitonicSort(ctx, mode=api.SORT_BITONIC_COMPAT).sort(small.data_ptr(), 1 << 12)  # bitonic_stage_kernel
-del keys, pairs, vals, out, small
+odd = torch.zeros((1 << 20) + 1, dtype=torch.int32, device="cuda")
+api.PrefixSum(ctx).computePrefixSum(odd[1:].data_ptr(), odd[1:].data_ptr(), 1 << 20)    # scan_lookback_kernel (4-byte aligned only)
+smallv = torch.ones(1 << 19, dtype=torch.int32, device="cuda")
+api.PrefixSum(ctx).computePrefixSum(smallv.data_ptr(), smallv.data_ptr(), 1 << 19)    # scan_window_kernel<2>
+del keys, pairs, vals, out, small, odd, smallv
 
 # ---- LBVH: build (reference tree + separate trace tree), traversal, shading ----------------------------------------------------------
 bvh = api.BVHManager(ctx, scene); bvh.initialize()
-bvh.set_trace_tree(api.TRACE_TREE_ALWAYS); bvh.initializeFrame(); bvh.construct()    # + tt_morton, tt_emit, tt_refit
-bvh.set_trace_tree(api.TRACE_TREE_AUTO); bvh.initializeFrame(); bvh.construct()      # morton_leaves, karras_emit, chain_suffix, refit_atomic, wide_frame, widen, wide_top
+bvh.set_trace_tree(api.TRACE_TREE_ALWAYS); bvh.initializeFrame(); bvh.construct()    # + tt_morton, pyr_levels (trace-tree order), tt_emit
+bvh.set_trace_tree(api.TRACE_TREE_AUTO); bvh.initializeFrame(); bvh.construct()      # morton_leaves, pyr_levels, karras_emit, wide_frame, widen, wide_top
 contacts = torch.empty(n * 32, dtype=torch.uint8, device="cuda"); rgba = torch.empty(n, dtype=torch.int32, device="cuda")
 L1 = scene.num_lights() + 1
 rays = torch.empty(n * L1 * 48, dtype=torch.uint8, device="cuda"); scont = torch.empty(n * L1 * 32, dtype=torch.uint8, device="cuda")

@@ -31,6 +31,6 @@ ms_b = timed(lambda: bvh.generateContacts(rays, contacts, n))
 med = np.median(np.array(st[1:]), axis=0)
 print(json.dumps({"workload": "Spheres-10M (2000 tessellated spheres, 10e6 triangles), 3840x2160", "build_ms": float(np.median(tot[1:])),
                   "build_ms_per_Mtri": float(np.median(tot[1:])) / 10.0,
-                  "stages_ms": dict(zip(("morton", "sort", "emit", "refit", "trace_structure"), [float(x) for x in med])),
+                  "stages_ms": dict(zip(("morton", "sort", "emit", "box_pyramid", "trace_structure"), [float(x) for x in med])),
                   "trace_tree": bvh.has_trace_tree(), "primary_ms": ms_p, "primary_Mrays_per_s": n / ms_p / 1e3, "primary_hits": hits,
                   "bounce_ms": ms_b, "bounce_live_rays": hits, "bounce_Mrays_per_s": hits / ms_b / 1e3}))

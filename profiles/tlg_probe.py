@@ -26,7 +26,7 @@ for wl in sys.argv[1:] or ("clumsydragon", "soup1m"):
             r.render_device(c, True)
         r.join(); e1.record(r.stream); r.finish()
         ms = e0.elapsed_time(e1) / 10
-        names = ("morton", "sort", "emit", "refit", "trace_structure") if acc == "BVH" else ("count_top", "top_pairs", "leaf_cells", "leaf_count", "leaf_pairs")
+        names = ("morton", "sort", "emit", "box_pyramid", "trace_structure") if acc == "BVH" else ("count_top", "top_pairs", "leaf_cells", "leaf_count", "leaf_pairs")
         out[acc] = {"build_ms": float(np.median(tot[1:])), "stages_ms": dict(zip(names, [float(x) for x in np.median(np.array(st[1:]), axis=0)])),
                     "frame_ms": ms, "Mrays_per_s": rays / 10 / ms / 1e3}
         if acc == "GRID":

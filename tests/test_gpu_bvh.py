@@ -1,4 +1,4 @@
-"""GPU parity: scene flattening, LBVH build (Morton, sort, Karras emit, refit), traversal, shading — through the C ABI,
+"""GPU parity: scene flattening, LBVH build (Morton, sort, box pyramid, Karras emit + boxes), traversal, shading — through the C ABI,
 against the committed golden vectors (reference's own code) and the oracle.  Integer/index work bit-exact; hit t /
 normals bit-exact in REFERENCE_ORDER mode, FAST mode by the north-star tolerances."""
 import numpy as np
