@@ -43,7 +43,11 @@ bvh.set_trace_mode(api.TRACE_FAST)
 bvh.generateContacts(cam, contacts.data_ptr())                                     # trace_primary_kernel<FAST>
 bvh.shadow_shade(cam, contacts.data_ptr(), n, rgba.data_ptr())                     # shadow_shade_kernel
 stripe = torch.empty(frame.stripe_capacity(W, H, 1), dtype=torch.int32, device="cuda")
-bvh.render_stripe(cam, True, 0, 1, stripe.data_ptr())                              # frame_kernel
+bvh.render_stripe(cam, True, 0, 1, stripe.data_ptr())                              # trace_primary + shadow_shade (two-kernel frame)
+bvh.set_fused_shadows(2)
+bvh.render_stripe(cam, True, 0, 1, stripe.data_ptr())                              # frame_kernel (primary + occlusion + shading in one launch)
+bvh.set_fused_shadows(1)
+bvh.render_stripes_batch(S.cuda_stream, 0, [cam, frame.orbit_camera(buf, W, H, 6)], 0, 1, torch.empty(2 * frame.stripe_capacity(W, H, 1), dtype=torch.int32, device="cuda").data_ptr())   # trace_primary_batch, shadow_shade_batch
 api.frame_untile(ctx, stripe.data_ptr(), W, H, 1, rgba.data_ptr())                 # untile_kernel
 api.generate_shadow_rays(ctx, scene, cam, contacts.data_ptr(), n, rays.data_ptr())   # shadow_rays_kernel
 bvh.generateContacts(rays.data_ptr(), scont.data_ptr(), n * L1)                    # trace_rays_kernel<FAST>

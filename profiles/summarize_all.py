@@ -5,8 +5,21 @@ one row per launch) and writes profiles/<tag>_all_kernels.md (one row per KERNEL
 import csv, json, os, re, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 TAG = sys.argv[1] if len(sys.argv) > 1 else "r02"
-rows = list(csv.reader(open(os.path.join(ROOT, "gpurun_out", f"all_{TAG}.csv"))))
-hdr, units, rows = rows[0], rows[1], rows[2:]
+import glob
+# all_<tag>.csv, plus all_<tag>_*.csv from filtered passes over the same probe (profiles/capture_all.sh <tag> <kernel regex>): rows are
+# re-ordered to the first file's columns
+hdr = units = None
+rows = []
+for path in sorted(glob.glob(os.path.join(ROOT, "gpurun_out", f"all_{TAG}.csv")) + glob.glob(os.path.join(ROOT, "gpurun_out", f"all_{TAG}_*.csv"))):
+    part = list(csv.reader(open(path)))
+    if len(part) < 3:
+        continue
+    if hdr is None:
+        hdr, units = part[0], part[1]
+        rows += part[2:]
+    else:
+        pos = {h: i for i, h in enumerate(part[0])}
+        rows += [[r[pos[h]] if h in pos and pos[h] < len(r) else "" for h in hdr] for r in part[2:]]
 idx = {h: i for i, h in enumerate(hdr)}
 SCALE = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "nsecond": 1e-3, "ns": 1e-3, "usecond": 1, "us": 1, "msecond": 1e3, "ms": 1e3, "second": 1e6}
 
