@@ -82,6 +82,17 @@ int clrt_sort_pairs_u32(clrt_ctx* ctx, void* dptr_pairs, size_t n, int mode);
 /* PrefixSum::computePrefixSum(in,out,n)  R/Include/Algorithms/PrefixSum.h:48-83, R/src/CLRayTracerEngine/PrefixSum.cpp:94-133.
  *   INCLUSIVE scan of n uint32; in may equal out; any n. */
 int clrt_scan_inclusive_u32(clrt_ctx* ctx, const void* dptr_in, void* dptr_out, size_t n);
+/* The same scan for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ *   cudaMalloc).  NO counterpart in the reference.  No context: `stream` is a
+ *   cudaStream_t (NULL = the default stream) on the calling thread's CURRENT device; in / out are device pointers to n uint32,
+ *   4-byte aligned, in may equal out.  The call makes no cudaMalloc / cudaFree / allocating library call: the tile descriptors
+ *   (its only scratch memory) live in a static 128 KB device array inside the library, which limits n to
+ *   CLRT_SCAN_NOALLOC_MAX_ELEMENTS — larger n fails with an error (use clrt_scan_inclusive_u32).  The first call on a device
+ *   does the one-time set-up (make it outside stream capture).  Every call on a device shares that array: calls ordered on one
+ *   stream or by events are fine, calls that OVERLAP on the GPU race and give undefined results.  Results are identical to
+ *   clrt_scan_inclusive_u32. */
+#define CLRT_SCAN_NOALLOC_MAX_ELEMENTS (1u << 28)
+int clrt_scan_inclusive_u32_noalloc(void* stream, const void* dptr_in, void* dptr_out, size_t n);
 
 /* ---- scene: Scene::loadToGPU (R/src/CLRayTracerEngine/Scene.cpp:451-456) ------------------------------
  * Uploads the packed v0.6 scene buffer (format: R/Include/CLData/SceneBufferParser.h) unchanged and

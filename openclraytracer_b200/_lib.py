@@ -32,6 +32,7 @@ SIGNATURES = {
     "clrt_memcpy_dtoh": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]),
     "clrt_sort_pairs_u32": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int]),
     "clrt_scan_inclusive_u32": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]),
+    "clrt_scan_inclusive_u32_noalloc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]),
     "clrt_scene_upload": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, c_void_pp]),
     "clrt_scene_destroy": (C.c_int, [C.c_void_p]),
     "clrt_scene_triangle_count": (C.c_uint64, [C.c_void_p]),

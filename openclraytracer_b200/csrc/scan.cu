@@ -17,6 +17,7 @@
 //                       bandwidth at 2^28 elements (profiles/r02_experiments.md section 4).
 //   scan_lookback_kernel (buffers that are only 4-byte aligned): register prefetch + classic decoupled look-back (round 2a's kernel).
 #include "common.cuh"
+#include <mutex>
 
 namespace {
 
@@ -369,4 +370,95 @@ extern "C" int clrt_scan_inclusive_u32(clrt_ctx* ctx, const void* dptr_in, void*
   if (((uintptr_t)dptr_in & 3) || ((uintptr_t)dptr_out & 3)) CLRT_FAIL("clrt_scan_inclusive_u32: buffers must be 4-byte aligned");
   CLRT_CUDA(cudaSetDevice(ctx->device));
   return scan_inclusive(ctx, (const uint32_t*)dptr_in, (uint32_t*)dptr_out, n);
+}
+
+// ---- scan without any allocation ----------------------------------------------------------------------------------------------------
+// clrt_scan_inclusive_u32_noalloc: the same kernels as above for callers that cannot call cudaMalloc (code under CUDA graph capture,
+// tight serving loops, harnesses that forbid it).  It has no counterpart in the reference.
+// Differences from clrt_scan_inclusive_u32:
+//   * no context: the caller passes a stream; the device is the calling thread's current device;
+//   * the tile descriptors — the only scratch memory a scan needs, 8 bytes per tile — live in the file-scope array below instead of
+//     the context's grown buffer: 128 KB that every GPU which loads this library holds until the process exits.  That bounds n to
+//     CLRT_SCAN_NOALLOC_MAX_ELEMENTS = 2^28; larger sizes are rejected;
+//   * the call makes no cudaMalloc / cudaFree / allocating library call.  Per device, the FIRST call does the set-up (address of the
+//     array on that device, shared-memory attribute and occupancy of the kernels): make that call outside stream capture;
+//   * the array is shared by every call on the device and keeps the previous call's contents, so each call clears the descriptors it is
+//     going to use with a cudaMemsetAsync on the caller's stream (a fixed generation number: a captured graph can be replayed).
+//     Calls that OVERLAP on one GPU (different streams, no ordering between them) race on the descriptors — undefined results; calls
+//     ordered on one stream, or by events, are fine.
+constexpr size_t SCAN_NOALLOC_MAX = (size_t)CLRT_SCAN_NOALLOC_MAX_ELEMENTS;
+// descriptors needed: 16K-element tiles from 2^21 elements up (and for buffers that are only 4-byte aligned), 8K-element tiles below
+constexpr size_t SCAN_NOALLOC_TILES_BIG = (SCAN_NOALLOC_MAX + (size_t)SCAN_SUB * 4 - 1) / ((size_t)SCAN_SUB * 4);
+constexpr size_t SCAN_NOALLOC_TILES_SMALL = ((size_t)(1u << 21) + (size_t)SCAN_SUB * 2 - 1) / ((size_t)SCAN_SUB * 2);
+constexpr size_t SCAN_NOALLOC_TILES = SCAN_NOALLOC_TILES_BIG > SCAN_NOALLOC_TILES_SMALL ? SCAN_NOALLOC_TILES_BIG : SCAN_NOALLOC_TILES_SMALL;   // 16384 = 128 KB
+static_assert(SCAN_NOALLOC_TILES * (size_t)SCAN_SUB * 4 >= SCAN_NOALLOC_MAX, "descriptor array too small for the stated maximum");
+static __device__ __align__(256) unsigned long long g_scan_noalloc_status[SCAN_NOALLOC_TILES];
+
+namespace {
+struct ScanNoallocDevice {              // per device, filled once with that device current
+  bool ready = false;
+  unsigned long long* status = nullptr; // DEVICE address of g_scan_noalloc_status on this device (the name itself is a host-side stand-in)
+  int sm_count = 0, per_sm_w4 = 0, per_sm_w2 = 0, per_sm_lb = 0;
+};
+constexpr int SCAN_NOALLOC_MAX_DEVICES = 64;
+ScanNoallocDevice g_scan_noalloc_dev[SCAN_NOALLOC_MAX_DEVICES];
+std::mutex g_scan_noalloc_mutex;
+
+template <int VEC> constexpr size_t scan_window_smem() { return SCAN_STAGES * (size_t)SCAN_SUB * VEC * 4 + 8 * SCAN_STAGES; }
+
+int scan_noalloc_setup(int device, ScanNoallocDevice** out) {
+  if (device < 0 || device >= SCAN_NOALLOC_MAX_DEVICES) CLRT_FAIL("clrt_scan_inclusive_u32_noalloc: device %d out of range", device);
+  ScanNoallocDevice& d = g_scan_noalloc_dev[device];
+  std::lock_guard<std::mutex> lock(g_scan_noalloc_mutex);
+  if (!d.ready) {
+    void* p = nullptr;
+    CLRT_CUDA(cudaGetSymbolAddress(&p, g_scan_noalloc_status));          // the array's address ON THE CURRENT DEVICE
+    if (!p) CLRT_FAIL("clrt_scan_inclusive_u32_noalloc: cudaGetSymbolAddress returned NULL on device %d", device);
+    CLRT_CUDA(cudaDeviceGetAttribute(&d.sm_count, cudaDevAttrMultiProcessorCount, device));
+    CLRT_CUDA(cudaFuncSetAttribute(scan_window_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)scan_window_smem<4>()));
+    CLRT_CUDA(cudaFuncSetAttribute(scan_window_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)scan_window_smem<2>()));
+    CLRT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&d.per_sm_w4, scan_window_kernel<4>, SCAN_THREADS, scan_window_smem<4>()));
+    CLRT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&d.per_sm_w2, scan_window_kernel<2>, SCAN_THREADS, scan_window_smem<2>()));
+    CLRT_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&d.per_sm_lb, scan_lookback_kernel, SCAN_THREADS, 0));
+    if (d.per_sm_w4 < 1 || d.per_sm_w2 < 1 || d.per_sm_lb < 1 || d.sm_count < 1)
+      CLRT_FAIL("clrt_scan_inclusive_u32_noalloc: the scan kernels do not fit an SM of device %d", device);
+    d.status = (unsigned long long*)p;
+    d.ready = true;
+  }
+  *out = &d;
+  return 0;
+}
+} // namespace
+
+extern "C" int clrt_scan_inclusive_u32_noalloc(void* stream_, const void* dptr_in, void* dptr_out, size_t n) {
+  if (n == 0) return 0;
+  if (!dptr_in || !dptr_out) CLRT_FAIL("clrt_scan_inclusive_u32_noalloc: NULL buffer");
+  if (((uintptr_t)dptr_in & 3) || ((uintptr_t)dptr_out & 3)) CLRT_FAIL("clrt_scan_inclusive_u32_noalloc: buffers must be 4-byte aligned");
+  if (n > SCAN_NOALLOC_MAX)
+    CLRT_FAIL("clrt_scan_inclusive_u32_noalloc: n = %zu exceeds CLRT_SCAN_NOALLOC_MAX_ELEMENTS = %zu (the static descriptor array); "
+              "use clrt_scan_inclusive_u32", n, SCAN_NOALLOC_MAX);
+  int device = -1;
+  CLRT_CUDA(cudaGetDevice(&device));
+  ScanNoallocDevice* d = nullptr;
+  CLRT_TRY(scan_noalloc_setup(device, &d));
+  cudaStream_t stream = (cudaStream_t)stream_;
+  const uint32_t* in = (const uint32_t*)dptr_in;
+  uint32_t* out = (uint32_t*)dptr_out;
+  const uint32_t gen = 1u;                                                // descriptors are cleared below: any fixed non-zero generation
+  const bool aligned = (((uintptr_t)in | (uintptr_t)out) & 15) == 0;
+  const int vec = aligned ? (n >= (1u << 21) ? 4 : 2) : SCAN_VEC_UNALIGNED;
+  const size_t tile = (size_t)SCAN_SUB * vec, tiles = (n + tile - 1) / tile;
+  if (tiles > SCAN_NOALLOC_TILES) CLRT_FAIL("clrt_scan_inclusive_u32_noalloc: %zu tiles exceed the descriptor array (%zu)", tiles, SCAN_NOALLOC_TILES);
+  CLRT_CUDA(cudaMemsetAsync(d->status, 0, tiles * sizeof(unsigned long long), stream));      // what must start at zero
+  if (aligned) {
+    const int per_sm = vec == 4 ? d->per_sm_w4 : d->per_sm_w2;
+    const unsigned grid = (unsigned)min(min(tiles, (size_t)d->sm_count * per_sm), (size_t)SCAN_WIN * SCAN_THREADS);
+    if (vec == 4) scan_window_kernel<4><<<grid, SCAN_THREADS, scan_window_smem<4>(), stream>>>(in, out, (uint32_t)n, d->status, (uint32_t)tiles, gen);
+    else          scan_window_kernel<2><<<grid, SCAN_THREADS, scan_window_smem<2>(), stream>>>(in, out, (uint32_t)n, d->status, (uint32_t)tiles, gen);
+  } else {
+    const unsigned grid = (unsigned)min(tiles, (size_t)d->sm_count * d->per_sm_lb);
+    scan_lookback_kernel<<<grid, SCAN_THREADS, 0, stream>>>(in, out, (uint32_t)n, d->status, (uint32_t)tiles, gen);
+  }
+  CLRT_CHECK_LAUNCH();
+  return 0;
 }
