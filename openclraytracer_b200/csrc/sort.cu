@@ -22,10 +22,16 @@
 namespace {
 
 #ifndef CLRT_SORT_BIG_TILES_FROM
-#define CLRT_SORT_BIG_TILES_FROM (1u << 19)     /* 4096-pair tiles above this size, 1024-pair tiles (more CTAs in flight) below */
+#define CLRT_SORT_BIG_TILES_FROM (1u << 18)     /* 1024-pair tiles (more CTAs in flight) up to this size */
 #endif
 #ifndef CLRT_SORT_DEBUG
 #define CLRT_SORT_DEBUG 0            /* experiments only (wrong results): 1 = no look-back, 2 = no look-back and no ranking */
+#endif
+#ifndef CLRT_SORT_MID_TILES_TO
+#define CLRT_SORT_MID_TILES_TO (1u << 19)    /* 2048-pair tiles between BIG_TILES_FROM and this size, 4096-pair tiles above (measured: profiles/r02_experiments.md section 6) */
+#endif
+#ifndef CLRT_SORT_HUGE_TILES_FROM
+#define CLRT_SORT_HUGE_TILES_FROM (1u << 22)   /* 8192-pair tiles (512 threads) above this size */
 #endif
 #ifndef CLRT_SORT_MIN_CTAS
 #define CLRT_SORT_MIN_CTAS 4
@@ -35,8 +41,6 @@ namespace {
 #endif
 constexpr int RADIX_BITS = 8;
 constexpr int BINS = 1 << RADIX_BITS;
-constexpr int SORT_THREADS = 256;
-constexpr int SORT_WARPS = SORT_THREADS / 32;
 constexpr int HIST_THREADS = 256;
 constexpr int MAX_PASSES = 4;
 
@@ -102,19 +106,23 @@ radix_scan_hist_kernel(uint32_t* __restrict__ hist, int passes) {
 }
 
 // ---- one onesweep pass ---------------------------------------------------------------------------------
-template <int IPT, bool FULL>
-__global__ void __launch_bounds__(SORT_THREADS, CLRT_SORT_MIN_CTAS)
+// THREADS x IPT pairs per tile (CTA): 256 x 16 = 4096 (4 CTAs per SM), 512 x 16 = 8192 (2 CTAs per SM: longer digit runs in the
+// write-out, half as many descriptors and look-back chains), 256 x 4 for small inputs.  Threads 0..255 own one digit each.
+template <int THREADS, int IPT, bool FULL>
+__global__ void __launch_bounds__(THREADS, (THREADS * IPT >= 8192 ? 2 : CLRT_SORT_MIN_CTAS))
 onesweep_pass_kernel(const uint2* __restrict__ in, uint2* __restrict__ out, uint32_t n, int shift,
                      const uint32_t* __restrict__ digit_base,   // [BINS] exclusive global offsets of this pass
                      uint32_t* __restrict__ status,             // [tiles][BINS] look-back descriptors (zeroed)
                      uint32_t* __restrict__ ticket) {
-  constexpr int TILE = SORT_THREADS * IPT;
-  __shared__ uint32_t s_warp_hist[SORT_WARPS][BINS];   // per-warp digit counts -> per-warp exclusive offsets
+  constexpr int TILE = THREADS * IPT;
+  constexpr int WARPS = THREADS / 32, DIGIT_WARPS = BINS / 32;
+  static_assert(THREADS >= BINS, "one thread per digit");
+  __shared__ uint32_t s_warp_hist[WARPS][BINS];   // per-warp digit counts -> per-warp exclusive offsets
   __shared__ uint32_t s_tile_excl[BINS];               // exclusive scan of the tile's digit counts
   __shared__ uint32_t s_delta[BINS];                   // global position = s_delta[digit] + local position
-  __shared__ uint32_t s_scan_warp[SORT_WARPS];
+  __shared__ uint32_t s_scan_warp[DIGIT_WARPS];
   __shared__ uint32_t s_tile;
-  __shared__ uint2 s_staged[TILE];
+  extern __shared__ __align__(16) uint2 s_staged[];     // TILE pairs
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (tid == 0) s_tile = atomicAdd(ticket, 1u);
@@ -161,53 +169,56 @@ onesweep_pass_kernel(const uint2* __restrict__ in, uint2* __restrict__ out, uint
     rank[j] = prior + __popc(m & lt_mask);
   }
   __syncthreads();
-  // 3. per digit: exclusive offsets of the warps, tile count (thread d owns digit d; SORT_THREADS == BINS)
+  // 3. per digit: exclusive offsets of the warps, tile count (thread d < 256 owns digit d)
+  const bool owner = tid < BINS;
   uint32_t count = 0;
+  uint32_t* my_status = status + (size_t)tile * BINS + (owner ? tid : 0);
+  if (owner) {
 #pragma unroll
-  for (int w = 0; w < SORT_WARPS; w++) { const uint32_t t = s_warp_hist[w][tid]; s_warp_hist[w][tid] = count; count += t; }
-  // 4. publish the tile aggregate, then look back (one thread per digit)
-  uint32_t* my_status = status + (size_t)tile * BINS + tid;
-  st_relaxed_u32(my_status, (tile == 0 ? ST_PREFIX : ST_AGG) | count);
+    for (int w = 0; w < WARPS; w++) { const uint32_t t = s_warp_hist[w][tid]; s_warp_hist[w][tid] = count; count += t; }
+    // 4. publish the tile aggregate, then look back (one thread per digit)
+    st_relaxed_u32(my_status, (tile == 0 ? ST_PREFIX : ST_AGG) | count);
+  }
   // 5. exclusive scan of the tile's digit counts (for the shared-memory staging order)
-  {
-    uint32_t incl = count;
+  uint32_t incl = count;
 #pragma unroll
-    for (int d = 1; d < 32; d <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += t; }
-    if (lane == 31) s_scan_warp[warp] = incl;
-    __syncthreads();
+  for (int d = 1; d < 32; d <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += t; }
+  if (owner && lane == 31) s_scan_warp[warp] = incl;
+  __syncthreads();
+  if (owner) {
     uint32_t off = 0;
 #pragma unroll
-    for (int w = 0; w < SORT_WARPS; w++) if (w < warp) off += s_scan_warp[w];
+    for (int w = 0; w < DIGIT_WARPS; w++) if (w < warp) off += s_scan_warp[w];
     s_tile_excl[tid] = off + incl - count;
-  }
-  uint32_t excl = 0;
-  if (tile > 0 && CLRT_SORT_DEBUG == 0) {
-    // decoupled look-back, one thread per digit; LOOK descriptors are fetched together (independent L2 round trips) and
-    // consumed in order — the walk was 18 % of the stall samples with one dependent load per predecessor.
-    constexpr int LOOK = CLRT_SORT_LOOK;
-    int t = (int)tile - 1;
-    bool done = false;
-    while (!done) {
-      uint32_t sv[LOOK];
+    uint32_t excl = 0;
+    if (tile > 0 && CLRT_SORT_DEBUG == 0) {
+      // decoupled look-back, one thread per digit; LOOK descriptors are fetched together (independent L2 round trips) and
+      // consumed in order — the walk was 18 % of the stall samples with one dependent load per predecessor.
+      constexpr int LOOK = CLRT_SORT_LOOK;
+      int t = (int)tile - 1;
+      bool done = false;
+      while (!done) {
+        uint32_t sv[LOOK];
 #pragma unroll
-      for (int w = 0; w < LOOK; w++) sv[w] = (t - w >= 0) ? ld_relaxed_u32(my_status - (size_t)(tile - (uint32_t)(t - w)) * BINS) : ST_PREFIX;
+        for (int w = 0; w < LOOK; w++) sv[w] = (t - w >= 0) ? ld_relaxed_u32(my_status - (size_t)(tile - (uint32_t)(t - w)) * BINS) : ST_PREFIX;
 #pragma unroll
-      for (int w = 0; w < LOOK; w++) {
-        if (!done) {
-          uint32_t sx = sv[w];
-          if (t - w >= 0) {
-            const uint32_t* look = my_status - (size_t)(tile - (uint32_t)(t - w)) * BINS;
-            while ((sx >> 30) == 0) sx = ld_relaxed_u32(look);
+        for (int w = 0; w < LOOK; w++) {
+          if (!done) {
+            uint32_t sx = sv[w];
+            if (t - w >= 0) {
+              const uint32_t* look = my_status - (size_t)(tile - (uint32_t)(t - w)) * BINS;
+              while ((sx >> 30) == 0) sx = ld_relaxed_u32(look);
+            }
+            excl += sx & ST_MASK;
+            done = (sx >> 30) == 2;
           }
-          excl += sx & ST_MASK;
-          done = (sx >> 30) == 2;
         }
+        t -= LOOK;
       }
-      t -= LOOK;
+      st_relaxed_u32(my_status, ST_PREFIX | (excl + count));
     }
-    st_relaxed_u32(my_status, ST_PREFIX | (excl + count));
+    s_delta[tid] = digit_base[tid] + excl - s_tile_excl[tid];
   }
-  s_delta[tid] = digit_base[tid] + excl - s_tile_excl[tid];
   __syncthreads();
   // 6. stage in digit order
 #pragma unroll
@@ -222,7 +233,7 @@ onesweep_pass_kernel(const uint2* __restrict__ in, uint2* __restrict__ out, uint
   // 7. coalesced write-out
 #pragma unroll
   for (int j = 0; j < IPT; j++) {
-    const uint32_t k = j * SORT_THREADS + tid;
+    const uint32_t k = j * THREADS + tid;
     if (FULL || k < tile_items) {
       const uint2 it = s_staged[k];
       out[s_delta[(it.x >> shift) & (BINS - 1)] + k] = it;
@@ -248,12 +259,19 @@ __global__ void bitonic_stage_kernel(uint2* __restrict__ data, uint32_t half_n, 
 
 } // namespace
 
-template <int IPT>
+template <int THREADS, int IPT>
 static int launch_pass(clrt_ctx* ctx, const uint2* in, uint2* out, uint32_t n, int shift, const uint32_t* base,
                        uint32_t* status, uint32_t* ticket, unsigned tiles) {
+  constexpr size_t SMEM = (size_t)THREADS * IPT * sizeof(uint2);
+  static bool attr_set = false;
+  if (!attr_set) {
+    CLRT_CUDA(cudaFuncSetAttribute(onesweep_pass_kernel<THREADS, IPT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
+    CLRT_CUDA(cudaFuncSetAttribute(onesweep_pass_kernel<THREADS, IPT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
+    attr_set = true;
+  }
   // FULL: every tile is complete (n is a multiple of the tile: every power-of-two size the reference's callers use) -> no bounds checks
-  if (n % (SORT_THREADS * IPT) == 0) onesweep_pass_kernel<IPT, true><<<tiles, SORT_THREADS, 0, ctx->stream>>>(in, out, n, shift, base, status, ticket);
-  else onesweep_pass_kernel<IPT, false><<<tiles, SORT_THREADS, 0, ctx->stream>>>(in, out, n, shift, base, status, ticket);
+  if (n % (THREADS * IPT) == 0) onesweep_pass_kernel<THREADS, IPT, true><<<tiles, THREADS, SMEM, ctx->stream>>>(in, out, n, shift, base, status, ticket);
+  else onesweep_pass_kernel<THREADS, IPT, false><<<tiles, THREADS, SMEM, ctx->stream>>>(in, out, n, shift, base, status, ticket);
   CLRT_CHECK_LAUNCH();
   return 0;
 }
@@ -263,9 +281,9 @@ int sort_pairs_radix(clrt_ctx* ctx, clrt_uint2* pairs, size_t n, int key_bits) {
   if (n >= (1ull << 30)) CLRT_FAIL("sort: n = %zu exceeds 2^30-1", n);
   if (key_bits <= 0 || key_bits > 32) key_bits = 32;
   int passes = (key_bits + RADIX_BITS - 1) / RADIX_BITS;
-  const bool big = n > (size_t)CLRT_SORT_BIG_TILES_FROM;
-  const int ipt = big ? 16 : 4;
-  const size_t tile = (size_t)SORT_THREADS * ipt;
+  // tile size by n: 1024 pairs up to 2^19, 4096 up to CLRT_SORT_HUGE_TILES_FROM, 8192 above
+  const int cls = n > (size_t)CLRT_SORT_HUGE_TILES_FROM ? 2 : n > (size_t)CLRT_SORT_MID_TILES_TO ? 1 : n > (size_t)CLRT_SORT_BIG_TILES_FROM ? 3 : 0;
+  const size_t tile = cls == 2 ? 8192 : cls == 1 ? 4096 : cls == 3 ? 2048 : 1024;
   const unsigned tiles = (unsigned)((n + tile - 1) / tile);
   // scratch: [hist passes*BINS][tickets 4 (+pad)][status passes*tiles*BINS]
   const size_t hist_bytes = (size_t)MAX_PASSES * BINS * 4, ticket_bytes = 64;
@@ -289,8 +307,10 @@ int sort_pairs_radix(clrt_ctx* ctx, clrt_uint2* pairs, size_t n, int key_bits) {
   uint2* src = (uint2*)pairs; uint2* dst = (uint2*)alt;
   for (int p = 0; p < passes; p++) {
     uint32_t* st = status + (size_t)p * tiles * BINS;
-    if (big) CLRT_TRY(launch_pass<16>(ctx, src, dst, (uint32_t)n, p * RADIX_BITS, hist + p * BINS, st, tickets + p, tiles));
-    else     CLRT_TRY(launch_pass<4>(ctx, src, dst, (uint32_t)n, p * RADIX_BITS, hist + p * BINS, st, tickets + p, tiles));
+    if (cls == 2)      CLRT_TRY((launch_pass<512, 16>(ctx, src, dst, (uint32_t)n, p * RADIX_BITS, hist + p * BINS, st, tickets + p, tiles)));
+    else if (cls == 3) CLRT_TRY((launch_pass<256, 8>(ctx, src, dst, (uint32_t)n, p * RADIX_BITS, hist + p * BINS, st, tickets + p, tiles)));
+    else if (cls == 1) CLRT_TRY((launch_pass<256, 16>(ctx, src, dst, (uint32_t)n, p * RADIX_BITS, hist + p * BINS, st, tickets + p, tiles)));
+    else               CLRT_TRY((launch_pass<256, 4>(ctx, src, dst, (uint32_t)n, p * RADIX_BITS, hist + p * BINS, st, tickets + p, tiles)));
     uint2* t = src; src = dst; dst = t;
   }
   if (src != (uint2*)pairs)
