@@ -529,6 +529,177 @@ tlg_trace_rays_kernel(const clrt_ray* __restrict__ rays, uint32_t count, const c
   }
 }
 
+// ---- the corrected walk on persistent warps with lane refill ------------------------------------------------------------------------
+// tlg_traverse_closest above runs one ray per thread to the end: rays end after one top cell or after fifty, so a warp ran with 8-9 of
+// 32 lanes (ncu, profiles/r02_all_kernels.md).  Here the SAME walk (same arithmetic, same order of operations per ray, hence the same
+// hits) is resumable between TOP CELLS: one step = one whole top cell of the ray (its leaf walk and triangle loops as compact nested
+// loops), lanes meet again between top cells, and complete rays wait until enough lanes wait, then write their contacts and are
+// refilled together from an atomic counter (the LBVH kernels' scheme, trace.cu run_jobs).  A finer state machine — separate warp-wide
+// phases for "advance to the next leaf cell" and "test one triangle" — was measured slower than no refill at all (6.3 ms against
+// 4.76 ms per Soup-1M frame; this scheme: 4.10 ms): its 100 registers and branchy steps cost more than the lanes it recovered
+// (profiles/r02_experiments.md section 7).
+#ifndef CLRT_TLG_REFILL
+#define CLRT_TLG_REFILL 1            /* 0: the corrected walk runs one ray per thread (tlg_trace_*_kernel<true>) */
+#endif
+#ifndef CLRT_TLG_WINDOW
+#define CLRT_TLG_WINDOW 1            /* top cells per lane between refill checks */
+#endif
+#ifndef CLRT_TLG_REFILL_MIN
+#define CLRT_TLG_REFILL_MIN 8
+#endif
+#ifndef CLRT_TLG_MIN_CTAS
+#define CLRT_TLG_MIN_CTAS 6
+#endif
+struct GLane {
+  Vec3 o, d, inv;
+  GridHit best;
+  Walk T;
+  float t_cur;
+  uint32_t it;
+  bool done;
+  uint32_t slot, pixel;
+};
+struct GridView {
+  clrt_grid_data g; const clrt_top_cell* top; const uint2* leaf_ranges; const uint2* leaf_pairs; const clrt_triangle* tris;
+};
+
+// true when the ray enters the grid; false: the contact is "none" already
+__device__ __forceinline__ bool glane_begin(GLane& L, const GridView& V, Vec3 o, Vec3 d) {
+  const clrt_grid_data& g = V.g;
+  L.o = o; L.d = d;
+  L.best.t = RT_FLT_MAX; L.best.tri = 0xFFFFFFFFu;
+  const float big = 1.0e30f;
+  L.inv = v3(d.x == 0.0f ? copysignf(big, d.x) : 1.0f / d.x, d.y == 0.0f ? copysignf(big, d.y) : 1.0f / d.y, d.z == 0.0f ? copysignf(big, d.z) : 1.0f / d.z);
+  const float b0x = g.box.bounds[0].x, b0y = g.box.bounds[0].y, b0z = g.box.bounds[0].z;
+  const float ax = (b0x - o.x) * L.inv.x, bx = (g.box.bounds[1].x - o.x) * L.inv.x;
+  const float ay = (b0y - o.y) * L.inv.y, by = (g.box.bounds[1].y - o.y) * L.inv.y;
+  const float az = (b0z - o.z) * L.inv.z, bz = (g.box.bounds[1].z - o.z) * L.inv.z;
+  const float tn = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fminf(az, bz)), tf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fmaxf(az, bz));
+  if (!(tn <= tf) || tf < 0.0f) { L.done = true; return false; }
+  const float t_in = fmaxf(tn, 0.0f);
+  walk_setup(L.T, o, d, L.inv, b0x, b0y, b0z, g.stepX, g.stepY, g.stepZ, (int)g.resX, (int)g.resY, (int)g.resZ, t_in);
+  L.t_cur = t_in; L.it = 0; L.done = false;
+  return true;
+}
+// One step: one whole top cell of the ray (its leaf walk and triangle loops exactly as in tlg_traverse_closest).
+__device__ __forceinline__ void glane_top_cell(GLane& L, const GridView& V) {
+  const clrt_grid_data& g = V.g;
+  const float slack = 1.00001f;
+  const uint4 cell = __ldg(reinterpret_cast<const uint4*>(V.top) + ((uint32_t)L.T.iz * g.resX * g.resY + (uint32_t)L.T.iy * g.resX + (uint32_t)L.T.ix));
+  const float t_exit = fminf(L.T.tx, fminf(L.T.ty, L.T.tz));
+  if (!(cell.x == 0 || cell.y == 0 || cell.z == 0)) {
+    const float c0x = g.box.bounds[0].x + (float)L.T.ix * g.stepX, c0y = g.box.bounds[0].y + (float)L.T.iy * g.stepY, c0z = g.box.bounds[0].z + (float)L.T.iz * g.stepZ;
+    Walk Lf;
+    walk_setup(Lf, L.o, L.d, L.inv, c0x, c0y, c0z, g.stepX / (float)cell.x, g.stepY / (float)cell.y, g.stepZ / (float)cell.z,
+               (int)cell.x, (int)cell.y, (int)cell.z, L.t_cur);
+    const uint32_t leaf_cap = cell.x + cell.y + cell.z + 3u;
+    for (uint32_t lit = 0; lit < leaf_cap; lit++) {
+      const uint32_t leaf = (uint32_t)Lf.iz * cell.x * cell.y + (uint32_t)Lf.iy * cell.x + (uint32_t)Lf.ix + cell.w;
+      const uint2 range = __ldg(V.leaf_ranges + leaf);
+      for (uint32_t k = range.x; k < range.y; k++) {
+        const uint32_t id = __ldg(&V.leaf_pairs[k].y);
+        Vec3 a, b, c; load_tri(V.tris, id, a, b, c);
+        const float t = triangle_intersect(a, b, c, L.o, L.d);
+        if (t > 0.0f && (t < L.best.t || (t == L.best.t && reference_order_before(V.tris, id, L.best.tri, g.box)))) { L.best.t = t; L.best.tri = id; }
+      }
+      const float l_exit = fminf(Lf.tx, fminf(Lf.ty, Lf.tz));
+      if (L.best.t <= l_exit * slack) { L.done = true; return; }
+      if (l_exit >= t_exit || !walk_step(Lf)) break;
+    }
+  }
+  if (L.best.t <= t_exit * slack) { L.done = true; return; }
+  L.t_cur = t_exit;
+  L.it++;
+  if (!walk_step(L.T) || L.it >= g.resX + g.resY + g.resZ + 3u) L.done = true;
+}
+
+// Job: start(unit, L) -> the lane is busy; the contact of a ray that never enters the grid (or of a slot outside the image) is written at once
+template <class Job>
+__device__ __forceinline__ void tlg_run_jobs(Job& job, const GridView& V, uint32_t total, uint32_t* __restrict__ counter, clrt_contact* __restrict__ out) {
+  const unsigned FULL = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  const unsigned lt_mask = (1u << lane) - 1u;
+  GLane L; L.done = true;
+  bool busy = false, exhausted = false;
+  uint32_t pool_next = 0, pool_end = 0;
+  while (true) {
+    const bool fin = busy && L.done;
+    const unsigned waiting = __ballot_sync(FULL, !busy || fin);
+    if (__popc(waiting) >= CLRT_TLG_REFILL_MIN || !__any_sync(FULL, busy && !fin)) {
+      if (fin) {
+        GridHit h = L.best; if (h.tri == 0xFFFFFFFFu) h.t = 0.0f;
+        tlg_write_contact(out, L.slot, L.pixel, h, V.tris);
+        busy = false;
+      }
+      unsigned idle = __ballot_sync(FULL, !busy);
+      while (idle) {
+        if (pool_next >= pool_end) {
+          if (exhausted) break;
+          uint32_t b = 0;
+          if (lane == 0) b = atomicAdd(counter, 32u);
+          b = __shfl_sync(FULL, b, 0);
+          if (b >= total) { exhausted = true; break; }
+          pool_next = b; pool_end = min(b + 32u, total);
+        }
+        const uint32_t avail = pool_end - pool_next;
+        const uint32_t rnk = __popc(idle & lt_mask);
+        if (!busy && rnk < avail) busy = job.start(pool_next + rnk, L, V, out);
+        pool_next += min(avail, (uint32_t)__popc(idle));
+        idle = __ballot_sync(FULL, !busy);
+      }
+      if (idle == FULL) break;                                   // nothing left anywhere
+    }
+#pragma unroll 1
+    for (int w = 0; w < CLRT_TLG_WINDOW; w++) if (busy && !L.done) glane_top_cell(L, V);
+  }
+}
+
+struct GridPrimaryJob {
+  clrt_camera cam; TileGrid tg; uint32_t rank, nranks; int raster;
+  __device__ __forceinline__ bool start(uint32_t unit, GLane& L, const GridView& V, clrt_contact* __restrict__ out) const {
+    const uint32_t pk = unit >> 5, ln = unit & 31u;
+    const uint32_t lt = pk >> 3, sub = pk & 7u;
+    const uint32_t gt = rank + lt * nranks;
+    const uint32_t tx = (gt % tg.tilesX) * CLRT_TILE_W + (sub & 3u) * 8u + (ln & 7u);
+    const uint32_t ty = (gt / tg.tilesX) * CLRT_TILE_H + (sub >> 2) * 4u + (ln >> 3);
+    const uint32_t inTile = ((sub >> 2) * 4u + (ln >> 3)) * CLRT_TILE_W + (sub & 3u) * 8u + (ln & 7u);
+    const bool inside = tx < cam.resX && ty < cam.resY;
+    const uint32_t pixel = ty * cam.resX + tx;
+    GridHit none; none.t = 0.0f; none.tri = 0xFFFFFFFFu;
+    if (!inside) { if (!raster) tlg_write_contact(out, lt * CLRT_TILE_PIXELS + inTile, 0xFFFFFFFFu, none, V.tris); return false; }
+    L.slot = raster ? pixel : lt * CLRT_TILE_PIXELS + inTile; L.pixel = pixel;
+    Vec3 o, d; generate_ray(cam, pixel, o, d);
+    if (!glane_begin(L, V, o, d)) { tlg_write_contact(out, L.slot, pixel, none, V.tris); return false; }
+    return true;
+  }
+};
+struct GridRaysJob {
+  const clrt_ray* rays;
+  __device__ __forceinline__ bool start(uint32_t i, GLane& L, const GridView& V, clrt_contact* __restrict__ out) const {
+    const float4* p = reinterpret_cast<const float4*>(rays + i);
+    const float4 ro = __ldcs(p + 1), rd = __ldcs(p + 2);
+    GridHit none; none.t = 0.0f; none.tri = 0xFFFFFFFFu;
+    L.slot = i; L.pixel = i;
+    if ((rd.x == 0.0f && rd.y == 0.0f && rd.z == 0.0f) || !glane_begin(L, V, v3(ro.x, ro.y, ro.z), v3(rd.x, rd.y, rd.z))) {
+      tlg_write_contact(out, i, i, none, V.tris); return false;
+    }
+    return true;
+  }
+};
+
+__global__ void __launch_bounds__(TLG_TRACE_THREADS, CLRT_TLG_MIN_CTAS)
+tlg_walk_primary_kernel(const clrt_camera cam, const GridView V, clrt_contact* __restrict__ out, uint32_t rank, uint32_t nranks, int raster,
+                        uint32_t* __restrict__ counter) {
+  GridPrimaryJob job{cam, make_tile_grid(cam.resX, cam.resY), rank, nranks, raster};
+  const uint32_t total = stripe_tile_count(job.tg.tiles, rank, nranks) * 8u * 32u;
+  tlg_run_jobs(job, V, total, counter, out);
+}
+__global__ void __launch_bounds__(TLG_TRACE_THREADS, CLRT_TLG_MIN_CTAS)
+tlg_walk_rays_kernel(const clrt_ray* __restrict__ rays, uint32_t count, const GridView V, clrt_contact* __restrict__ out, uint32_t* __restrict__ counter) {
+  GridRaysJob job{rays};
+  tlg_run_jobs(job, V, count, counter, out);
+}
+
 } // namespace
 
 // ---- manager ---------------------------------------------------------------------------------------------------------
@@ -701,7 +872,11 @@ int tlg_trace_primary(clrt_accel* a, const clrt_camera& cam, clrt_contact* out, 
   if (!packets) return 0;
   CLRT_CUDA(cudaMemsetAsync(a->d_tile_counter, 0, 4, ctx->stream));
   unsigned grid = 0;
-  if (a->trace_mode == CLRT_TRACE_FAST) {                      // the corrected closest-hit walk
+  if (a->trace_mode == CLRT_TRACE_FAST && CLRT_TLG_REFILL) {   // the corrected closest-hit walk, lanes refilled
+    const GridView V{t->grid, t->d_top_cells, (const uint2*)t->d_leaf_ranges, (const uint2*)t->d_leaf_pairs, a->scene->d_tris};
+    CLRT_TRY(tlg_grid(ctx, tlg_walk_primary_kernel, packets, &grid));
+    tlg_walk_primary_kernel<<<grid, TLG_TRACE_THREADS, 0, ctx->stream>>>(cam, V, out, rank, nranks, raster, a->d_tile_counter);
+  } else if (a->trace_mode == CLRT_TRACE_FAST) {               // the corrected closest-hit walk, one ray per thread
     CLRT_TRY(tlg_grid(ctx, tlg_trace_primary_kernel<true>, packets, &grid));
     tlg_trace_primary_kernel<true><<<grid, TLG_TRACE_THREADS, 0, ctx->stream>>>(cam, t->grid, t->d_top_cells, (const uint2*)t->d_leaf_ranges,
         (const uint2*)t->d_leaf_pairs, a->scene->d_tris, out, rank, nranks, raster, a->d_tile_counter);
@@ -721,7 +896,11 @@ int tlg_trace_rays(clrt_accel* a, const clrt_ray* rays, clrt_contact* out, uint3
   const uint32_t packets = (count + 31u) / 32u;
   CLRT_CUDA(cudaMemsetAsync(a->d_tile_counter, 0, 4, ctx->stream));
   unsigned grid = 0;
-  if (a->trace_mode == CLRT_TRACE_FAST) {
+  if (a->trace_mode == CLRT_TRACE_FAST && CLRT_TLG_REFILL) {
+    const GridView V{t->grid, t->d_top_cells, (const uint2*)t->d_leaf_ranges, (const uint2*)t->d_leaf_pairs, a->scene->d_tris};
+    CLRT_TRY(tlg_grid(ctx, tlg_walk_rays_kernel, packets, &grid));
+    tlg_walk_rays_kernel<<<grid, TLG_TRACE_THREADS, 0, ctx->stream>>>(rays, count, V, out, a->d_tile_counter);
+  } else if (a->trace_mode == CLRT_TRACE_FAST) {
     CLRT_TRY(tlg_grid(ctx, tlg_trace_rays_kernel<true>, packets, &grid));
     tlg_trace_rays_kernel<true><<<grid, TLG_TRACE_THREADS, 0, ctx->stream>>>(rays, count, t->grid, t->d_top_cells, (const uint2*)t->d_leaf_ranges,
         (const uint2*)t->d_leaf_pairs, a->scene->d_tris, out, a->d_tile_counter);

@@ -71,9 +71,9 @@ ctx.finish()
 tlg = api.TwoLevelGridManager(ctx, scene); tlg.initialize(); tlg.initializeFrame(); tlg.construct()   # tlg_* build kernels, extract_ranges
 tlg.generateContacts(cam, contacts.data_ptr())                                     # tlg_trace_primary_kernel<literal>
 tlg.set_trace_mode(api.TRACE_FAST)
-tlg.generateContacts(cam, contacts.data_ptr())                                     # tlg_trace_primary_kernel<corrected>
+tlg.generateContacts(cam, contacts.data_ptr())                                     # tlg_walk_primary_kernel (corrected walk, lanes refilled)
 api.generate_primary_rays(ctx, cam, rays.data_ptr())
-tlg.generateContacts(rays.data_ptr(), scont.data_ptr(), n)                         # tlg_trace_rays_kernel<corrected>
+tlg.generateContacts(rays.data_ptr(), scont.data_ptr(), n)                         # tlg_walk_rays_kernel
 tlg.set_trace_mode(api.TRACE_REFERENCE_ORDER)
 tlg.generateContacts(rays.data_ptr(), scont.data_ptr(), n)                         # tlg_trace_rays_kernel<literal>
 kd = api.KDTreeManager(ctx, scene); kd.initialize(); kd.initializeFrame(); kd.construct()             # kd_* build kernels
