@@ -159,6 +159,16 @@ struct KdHit { float t; uint32_t tri; };
 constexpr int KD_STACK = 40;          // far children: at most one per level, 3L <= 30 levels
 constexpr int KD_THREADS = 128;
 
+#ifndef CLRT_KD_REFILL
+#define CLRT_KD_REFILL 1             /* 0: kd_trace_*_kernel (one ray per thread to the end) */
+#endif
+#ifndef CLRT_KD_REFILL_MIN
+#define CLRT_KD_REFILL_MIN 12
+#endif
+#ifndef CLRT_KD_MIN_CTAS
+#define CLRT_KD_MIN_CTAS 6
+#endif
+#if !CLRT_KD_REFILL
 __device__ __forceinline__ KdHit kd_traverse(Vec3 o, Vec3 d, const KdGrid& g, const KdNode* __restrict__ nodes, uint32_t m,
                                              const uint2* __restrict__ ranges, const uint2* __restrict__ pairs,
                                              const clrt_triangle* __restrict__ tris, uint32_t* __restrict__ overflow) {
@@ -225,6 +235,8 @@ __device__ __forceinline__ KdHit kd_traverse(Vec3 o, Vec3 d, const KdGrid& g, co
   return best.tri != 0xFFFFFFFFu ? best : none;
 }
 
+#endif
+
 __device__ __forceinline__ void kd_write_contact(clrt_contact* __restrict__ out, uint32_t slot, uint32_t pixelIndex, const KdHit& h,
                                                  const clrt_triangle* __restrict__ tris) {
   uint4 head = make_uint4(pixelIndex, 0u, 0xFFFFFFFFu, 0u);
@@ -242,6 +254,7 @@ __device__ __forceinline__ void kd_write_contact(clrt_contact* __restrict__ out,
   __stcs(reinterpret_cast<float4*>(o) + 1, nd);
 }
 
+#if !CLRT_KD_REFILL
 // generateContacts(Camera&): persistent warps over 8x4-pixel packets (the tiling of the other two structures: stripes of 32x8 tiles)
 __global__ void __launch_bounds__(KD_THREADS)
 kd_trace_primary_kernel(const clrt_camera cam, const KdGrid g, const KdNode* __restrict__ nodes, uint32_t m, const uint2* __restrict__ ranges,
@@ -295,6 +308,159 @@ kd_trace_rays_kernel(const clrt_ray* __restrict__ rays, uint32_t count, const Kd
       kd_write_contact(out, i, i, h, tris);
     }
   }
+}
+
+#endif
+
+// ---- the same walk on persistent warps with lane refill ------------------------------------------------------------------------------
+// kd_traverse runs one ray per thread as a single-loop state machine (4 of 32 lanes per instruction in ncu: three branch bodies per
+// iteration and rays of very different lengths).  What worked for the grid (profiles/r02_experiments.md section 7) is applied here:
+// compact nested loops, resumable between LEAVES — one step of a lane = descend to the next leaf, test its triangles, decide, pop —
+// and lanes that are complete wait until enough lanes wait, write their contacts and take new rays together.  Same arithmetic and
+// order of operations per ray as kd_traverse, hence the same hits.  The stack of far children (local memory) is part of the lane.
+struct KdView { KdGrid g; const KdNode* nodes; uint32_t m; const uint2* ranges; const uint2* pairs; const clrt_triangle* tris; uint32_t* overflow; };
+struct KLane {
+  Vec3 o, d, inv;
+  KdHit best;
+  float tmin, tmax;
+  uint32_t cur;
+  int sp;
+  bool done;
+  uint32_t slot, pixel;
+  uint2 stack[KD_STACK];
+};
+__device__ __forceinline__ bool klane_begin(KLane& L, const KdView& V, Vec3 o, Vec3 d) {
+  const KdGrid& g = V.g;
+  L.o = o; L.d = d; L.best.t = RT_FLT_MAX; L.best.tri = 0xFFFFFFFFu; L.done = true;
+  if (V.m == 0) return false;
+  const float big = 1.0e30f;
+  L.inv = v3(d.x == 0.0f ? copysignf(big, d.x) : 1.0f / d.x, d.y == 0.0f ? copysignf(big, d.y) : 1.0f / d.y, d.z == 0.0f ? copysignf(big, d.z) : 1.0f / d.z);
+  const float ext = (float)(1 << g.levels);
+  const float ax = (g.lox - o.x) * L.inv.x, bx = (g.lox + ext * g.csx - o.x) * L.inv.x;
+  const float ay = (g.loy - o.y) * L.inv.y, by = (g.loy + ext * g.csy - o.y) * L.inv.y;
+  const float az = (g.loz - o.z) * L.inv.z, bz = (g.loz + ext * g.csz - o.z) * L.inv.z;
+  const float tn = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fminf(az, bz)), tf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fmaxf(az, bz));
+  if (!(tn <= tf) || tf < 0.0f) return false;
+  L.tmin = fmaxf(tn, 0.0f); L.tmax = tf;
+  L.sp = 0; L.cur = V.m >= 2 ? V.m : 0u;
+  L.done = false;
+  return true;
+}
+__device__ __forceinline__ void klane_leaf_step(KLane& L, const KdView& V) {
+  const float slack = 1.00001f;
+  const uint32_t m = V.m;
+  uint32_t cur = L.cur;
+  float tmin = L.tmin, tmax = L.tmax;
+  while (cur >= m) {                                             // inner nodes: pick the near side, remember the far one
+    const KdNode nd = V.nodes[cur - m];
+    const float oa = nd.axis == 0 ? L.o.x : nd.axis == 1 ? L.o.y : L.o.z;
+    const float da = nd.axis == 0 ? L.d.x : nd.axis == 1 ? L.d.y : L.d.z;
+    const float ia = nd.axis == 0 ? L.inv.x : nd.axis == 1 ? L.inv.y : L.inv.z;
+    const float ts = (nd.plane - oa) * ia;
+    const bool below = oa < nd.plane || (oa == nd.plane && da <= 0.0f);
+    const uint32_t near = below ? nd.childA : nd.childB, far = below ? nd.childB : nd.childA;
+    if (da == 0.0f || ts > tmax * slack || ts <= 0.0f) cur = near;
+    else if (ts < tmin / slack) cur = far;
+    else {
+      if (L.sp < KD_STACK) { L.stack[L.sp] = make_uint2(far, __float_as_uint(tmax)); L.sp++; } else atomicAdd(V.overflow, 1u);
+      cur = near; tmax = ts;
+    }
+  }
+  const uint2 range = __ldg(V.ranges + cur);
+  for (uint32_t k = range.x; k < range.y; k++) {
+    const uint32_t id = __ldg(&V.pairs[k].y);
+    const float4* t4 = reinterpret_cast<const float4*>(V.tris + id);
+    const float4 a = __ldg(t4), b = __ldg(t4 + 1), c = __ldg(t4 + 2);
+    const float t = triangle_intersect(v3(a.x, a.y, a.z), v3(b.x, b.y, b.z), v3(c.x, c.y, c.z), L.o, L.d);
+    if (t > 0.0f && (t < L.best.t || (t == L.best.t && reference_order_before(V.tris, id, L.best.tri, V.g.box)))) { L.best.t = t; L.best.tri = id; }
+  }
+  if (L.best.t <= tmax * slack || L.sp == 0) { L.done = true; return; }      // the closest hit lies in a region already finished / nothing left
+  L.sp--;
+  L.tmin = tmax; L.tmax = __uint_as_float(L.stack[L.sp].y); L.cur = L.stack[L.sp].x;
+}
+
+template <class Job>
+__device__ __forceinline__ void kd_run_jobs(Job& job, const KdView& V, uint32_t total, uint32_t* __restrict__ counter, clrt_contact* __restrict__ out) {
+  const unsigned FULL = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  const unsigned lt_mask = (1u << lane) - 1u;
+  KLane L; L.done = true;
+  bool busy = false, exhausted = false;
+  uint32_t pool_next = 0, pool_end = 0;
+  while (true) {
+    const bool fin = busy && L.done;
+    const unsigned waiting = __ballot_sync(FULL, !busy || fin);
+    if (__popc(waiting) >= CLRT_KD_REFILL_MIN || !__any_sync(FULL, busy && !fin)) {
+      if (fin) {
+        KdHit h = L.best; if (h.tri == 0xFFFFFFFFu) h.t = 0.0f;
+        kd_write_contact(out, L.slot, L.pixel, h, V.tris);
+        busy = false;
+      }
+      unsigned idle = __ballot_sync(FULL, !busy);
+      while (idle) {
+        if (pool_next >= pool_end) {
+          if (exhausted) break;
+          uint32_t b = 0;
+          if (lane == 0) b = atomicAdd(counter, 32u);
+          b = __shfl_sync(FULL, b, 0);
+          if (b >= total) { exhausted = true; break; }
+          pool_next = b; pool_end = min(b + 32u, total);
+        }
+        const uint32_t avail = pool_end - pool_next;
+        const uint32_t rnk = __popc(idle & lt_mask);
+        if (!busy && rnk < avail) busy = job.start(pool_next + rnk, L, V, out);
+        pool_next += min(avail, (uint32_t)__popc(idle));
+        idle = __ballot_sync(FULL, !busy);
+      }
+      if (idle == FULL) break;
+    }
+    if (busy && !L.done) klane_leaf_step(L, V);
+  }
+}
+
+struct KdPrimaryJob {
+  clrt_camera cam; TileGrid tg; uint32_t rank, nranks; int raster;
+  __device__ __forceinline__ bool start(uint32_t unit, KLane& L, const KdView& V, clrt_contact* __restrict__ out) const {
+    const uint32_t pk = unit >> 5, ln = unit & 31u;
+    const uint32_t lt = pk >> 3, sub = pk & 7u;
+    const uint32_t gt = rank + lt * nranks;
+    const uint32_t tx = (gt % tg.tilesX) * CLRT_TILE_W + (sub & 3u) * 8u + (ln & 7u);
+    const uint32_t ty = (gt / tg.tilesX) * CLRT_TILE_H + (sub >> 2) * 4u + (ln >> 3);
+    const uint32_t inTile = ((sub >> 2) * 4u + (ln >> 3)) * CLRT_TILE_W + (sub & 3u) * 8u + (ln & 7u);
+    const bool inside = tx < cam.resX && ty < cam.resY;
+    const uint32_t pixel = ty * cam.resX + tx;
+    KdHit none; none.t = 0.0f; none.tri = 0xFFFFFFFFu;
+    if (!inside) { if (!raster) kd_write_contact(out, lt * CLRT_TILE_PIXELS + inTile, 0xFFFFFFFFu, none, V.tris); return false; }
+    L.slot = raster ? pixel : lt * CLRT_TILE_PIXELS + inTile; L.pixel = pixel;
+    Vec3 o, d; generate_ray(cam, pixel, o, d);
+    if (!klane_begin(L, V, o, d)) { kd_write_contact(out, L.slot, pixel, none, V.tris); return false; }
+    return true;
+  }
+};
+struct KdRaysJob {
+  const clrt_ray* rays;
+  __device__ __forceinline__ bool start(uint32_t i, KLane& L, const KdView& V, clrt_contact* __restrict__ out) const {
+    const float4* p = reinterpret_cast<const float4*>(rays + i);
+    const float4 ro = __ldcs(p + 1), rd = __ldcs(p + 2);
+    KdHit none; none.t = 0.0f; none.tri = 0xFFFFFFFFu;
+    L.slot = i; L.pixel = i;
+    if ((rd.x == 0.0f && rd.y == 0.0f && rd.z == 0.0f) || !klane_begin(L, V, v3(ro.x, ro.y, ro.z), v3(rd.x, rd.y, rd.z))) {
+      kd_write_contact(out, i, i, none, V.tris); return false;
+    }
+    return true;
+  }
+};
+__global__ void __launch_bounds__(KD_THREADS, CLRT_KD_MIN_CTAS)
+kd_walk_primary_kernel(const clrt_camera cam, const KdView V, clrt_contact* __restrict__ out, uint32_t rank, uint32_t nranks, int raster,
+                       uint32_t* __restrict__ counter) {
+  KdPrimaryJob job{cam, make_tile_grid(cam.resX, cam.resY), rank, nranks, raster};
+  const uint32_t total = stripe_tile_count(job.tg.tiles, rank, nranks) * 8u * 32u;
+  kd_run_jobs(job, V, total, counter, out);
+}
+__global__ void __launch_bounds__(KD_THREADS, CLRT_KD_MIN_CTAS)
+kd_walk_rays_kernel(const clrt_ray* __restrict__ rays, uint32_t count, const KdView V, clrt_contact* __restrict__ out, uint32_t* __restrict__ counter) {
+  KdRaysJob job{rays};
+  kd_run_jobs(job, V, count, counter, out);
 }
 
 } // namespace
@@ -413,9 +579,18 @@ int kd_trace_primary(clrt_accel* a, const clrt_camera& cam, clrt_contact* out, u
   if (!packets) return 0;
   CLRT_CUDA(cudaMemsetAsync(a->d_tile_counter, 0, 4, ctx->stream));
   unsigned grid = 0;
+#if CLRT_KD_REFILL
+  {
+    const KdView V{kd_grid_of(k, a), k->d_nodes, k->leaves, (const uint2*)k->d_ranges, (const uint2*)k->d_pairs, a->scene->d_tris, a->d_tile_counter + 13};
+    CLRT_TRY(kd_grid_size<kd_walk_primary_kernel>(ctx, packets, &grid));
+    kd_walk_primary_kernel<<<grid, KD_THREADS, 0, ctx->stream>>>(cam, V, out, rank, nranks, raster, a->d_tile_counter);
+    CLRT_CHECK_LAUNCH();
+  }
+#else
   CLRT_TRY(kd_grid_size<kd_trace_primary_kernel>(ctx, packets, &grid));
   kd_trace_primary_kernel<<<grid, KD_THREADS, 0, ctx->stream>>>(cam, kd_grid_of(k, a), k->d_nodes, k->leaves, (const uint2*)k->d_ranges,
       (const uint2*)k->d_pairs, a->scene->d_tris, out, rank, nranks, raster, a->d_tile_counter, a->d_tile_counter + 13);
+#endif
   CLRT_CHECK_LAUNCH();
   return 0;
 }
@@ -427,9 +602,18 @@ int kd_trace_rays(clrt_accel* a, const clrt_ray* rays, clrt_contact* out, uint32
   const uint32_t packets = (count + 31u) / 32u;
   CLRT_CUDA(cudaMemsetAsync(a->d_tile_counter, 0, 4, ctx->stream));
   unsigned grid = 0;
+#if CLRT_KD_REFILL
+  {
+    const KdView V{kd_grid_of(k, a), k->d_nodes, k->leaves, (const uint2*)k->d_ranges, (const uint2*)k->d_pairs, a->scene->d_tris, a->d_tile_counter + 13};
+    CLRT_TRY(kd_grid_size<kd_walk_rays_kernel>(ctx, packets, &grid));
+    kd_walk_rays_kernel<<<grid, KD_THREADS, 0, ctx->stream>>>(rays, count, V, out, a->d_tile_counter);
+    CLRT_CHECK_LAUNCH();
+  }
+#else
   CLRT_TRY(kd_grid_size<kd_trace_rays_kernel>(ctx, packets, &grid));
   kd_trace_rays_kernel<<<grid, KD_THREADS, 0, ctx->stream>>>(rays, count, kd_grid_of(k, a), k->d_nodes, k->leaves, (const uint2*)k->d_ranges,
       (const uint2*)k->d_pairs, a->scene->d_tris, out, a->d_tile_counter, a->d_tile_counter + 13);
+#endif
   CLRT_CHECK_LAUNCH();
   return 0;
 }

@@ -77,8 +77,8 @@ tlg.generateContacts(rays.data_ptr(), scont.data_ptr(), n)                      
 tlg.set_trace_mode(api.TRACE_REFERENCE_ORDER)
 tlg.generateContacts(rays.data_ptr(), scont.data_ptr(), n)                         # tlg_trace_rays_kernel<literal>
 kd = api.KDTreeManager(ctx, scene); kd.initialize(); kd.initializeFrame(); kd.construct()             # kd_* build kernels
-kd.generateContacts(cam, contacts.data_ptr())                                      # kd_trace_primary_kernel
-kd.generateContacts(rays.data_ptr(), scont.data_ptr(), n)                          # kd_trace_rays_kernel
+kd.generateContacts(cam, contacts.data_ptr())                                      # kd_walk_primary_kernel
+kd.generateContacts(rays.data_ptr(), scont.data_ptr(), n)                          # kd_walk_rays_kernel
 ctx.finish()
 for m in (kd, tlg, bvh):
     m.free()
