@@ -47,12 +47,20 @@ morton_leaves_kernel(const clrt_triangle* __restrict__ tris, const uint32_t* __r
   reinterpret_cast<uint2*>(pairs)[i] = make_uint2(code, i);
 }
 
-typedef const uint2* __restrict__ KeyList;      // sorted (code, leaf) pairs; a packed 4-byte copy of the codes made the searches no faster
-__device__ __forceinline__ uint32_t key_at(KeyList k, int i) { return k[i].x; }
+// Sorted codes for the searches of the emit stage: the CTA's own neighbourhood [lo, hi) sits in shared memory (most nodes are small: their
+// dependent probes — ~40 L2 round trips per thread otherwise — stay on the SM), everything else comes from the sorted (code, leaf) pairs.
+#ifndef CLRT_EMIT_KEY_WINDOW
+#define CLRT_EMIT_KEY_WINDOW 256     /* positions staged on either side of the CTA's 256; 0: no staging */
+#endif
+struct KeyList { const uint2* list; const uint32_t* s; int lo, hi; };
+__device__ __forceinline__ uint32_t key_at(const KeyList& k, int i) {
+  if (CLRT_EMIT_KEY_WINDOW && i >= k.lo && i < k.hi) return k.s[i - k.lo];
+  return k.list[i].x;
+}
 
 // ---- stage 3: Karras radix tree with the reference's duplicate-key chains ------------------------------------
 // findSplit (BVH.h:138-182)
-__device__ __forceinline__ int find_split(KeyList list, int first, int last) {
+__device__ __forceinline__ int find_split(const KeyList& list, int first, int last) {
   const uint32_t firstCode = key_at(list, first), lastCode = key_at(list, last);
   if (firstCode == lastCode) return first;
   const int commonPrefix = __clz(firstCode ^ lastCode);
@@ -68,7 +76,7 @@ __device__ __forceinline__ int find_split(KeyList list, int first, int last) {
   return split;
 }
 // determineRange (BVH.h:190-282)
-__device__ __forceinline__ int2 determine_range(KeyList list, int index, uint32_t size) {
+__device__ __forceinline__ int2 determine_range(const KeyList& list, int index, uint32_t size) {
   const int lso = (int)size - 1;
   if (index == 0) return make_int2(0, lso);
   const int initialindex = index;
@@ -112,30 +120,40 @@ __device__ __forceinline__ int2 determine_range(KeyList list, int index, uint32_
 //   neighbours in the tree are neighbours in memory, and TraceNode child ids (leaf -> sorted position p, inner -> N + i).
 // Leaf ids in sorted-position space make "smaller id" == "visited earlier by the reference's A-before-B traversal",
 // which is the tie-break the FAST traversal uses to pick the reference's winner on exact ties.
+#ifndef CLRT_EMIT_DEBUG
+#define CLRT_EMIT_DEBUG 0           /* experiments only (wrong results): bit 0 skip the triangle copy, bit 1 skip the boxes, bit 2 skip the parent links, bit 3 skip the searches */
+#endif
 #ifndef CLRT_EMIT_MIN_CTAS
 #define CLRT_EMIT_MIN_CTAS 1
 #endif
 __global__ void __launch_bounds__(256, CLRT_EMIT_MIN_CTAS)
 karras_emit_kernel(const clrt_uint2* __restrict__ pairs_, uint32_t n, clrt_bvh_node* __restrict__ nodes,
                    const clrt_triangle* __restrict__ tris, clrt_triangle* __restrict__ tris_sorted,
-                   TraceNode* __restrict__ tnodes, uint32_t* __restrict__ max_run, uint32_t* __restrict__ refpos, const PyrView pv) {
+                   TraceNode* __restrict__ tnodes, uint32_t* __restrict__ max_run, const PyrView pv) {
   const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= n) return;
   const uint2* list = reinterpret_cast<const uint2*>(pairs_);
-  {
+  __shared__ uint32_t s_keys[256 + 2 * CLRT_EMIT_KEY_WINDOW + 1];
+  KeyList keys;
+  keys.list = list; keys.s = s_keys;
+  keys.lo = max((int)(blockIdx.x * blockDim.x) - CLRT_EMIT_KEY_WINDOW, 0);
+  keys.hi = (int)min((size_t)blockIdx.x * blockDim.x + 256 + CLRT_EMIT_KEY_WINDOW, (size_t)n);
+  if (CLRT_EMIT_KEY_WINDOW) {
+    for (int i = keys.lo + (int)threadIdx.x; i < keys.hi; i += 256) s_keys[i - keys.lo] = __ldg(&list[i].x);
+    __syncthreads();
+  }
+  if (idx >= n) return;
+  if (!(CLRT_EMIT_DEBUG & 1)) {
     const uint32_t leaf = list[idx].y;
     const float4* src = reinterpret_cast<const float4*>(tris + leaf);
     float4 a = __ldg(src), b = __ldg(src + 1), c = __ldg(src + 2);
     b.w = __uint_as_float(leaf);
     c.w = __uint_as_float(idx);                 // position in the reference's sorted order: the tie-break key of the traversal
-    refpos[leaf] = idx;
     float4* dst = reinterpret_cast<float4*>(tris_sorted + idx);
     dst[0] = a; dst[1] = b; dst[2] = c;
   }
   if (idx + 1 >= n) return;
-  KeyList keys = list;
-  const int2 range = determine_range(keys, (int)idx, n);
-  const int split = find_split(keys, range.x, range.y);
+  const int2 range = (CLRT_EMIT_DEBUG & 8) ? make_int2((int)idx, (int)idx + 1) : determine_range(keys, (int)idx, n);
+  const int split = (CLRT_EMIT_DEBUG & 8) ? (int)idx : find_split(keys, range.x, range.y);
   const uint32_t self = idx + n;
   const bool aIsLeaf = (range.x == split);
   const bool bIsLeaf = (range.y == split + 1);
@@ -144,8 +162,10 @@ karras_emit_kernel(const clrt_uint2* __restrict__ pairs_, uint32_t n, clrt_bvh_n
   uint32_t* d = nodes[self].data;
   if (idx == 0) d[0] = 0xFFFFFFFFu;
   d[1] = child_A; d[2] = child_B; d[3] = 0u;
-  nodes[child_A].data[0] = self;
-  nodes[child_B].data[0] = self;
+  if (!(CLRT_EMIT_DEBUG & 4)) {
+    nodes[child_A].data[0] = self;
+    nodes[child_B].data[0] = self;
+  }
   // Equal-key runs (the reference's right-leaning chains, Q8): an inner child whose whole range carries one key is a
   // chain of its leaves in sorted order.  The traversal may treat it as ONE multi-triangle leaf [start, start+count):
   // pad0 = start of child A's run, pad1 = countA | countB << 16 (0 = not a run; child B's run starts at split+1).
@@ -155,6 +175,7 @@ karras_emit_kernel(const clrt_uint2* __restrict__ pairs_, uint32_t n, clrt_bvh_n
   if (max(cntA, cntB) >= 2) atomicMax(max_run, max(cntA, cntB));
   // Boxes (computeBoundingBoxes, BVH.h:328-334: merge3(childA, childB, self) with self = (FLT_MAX.., INNER = 0.0f), (FLT_MIN.., 0.0f)):
   // each child's box is the union of the leaf boxes of its range — a leaf's own box, or the clamped range query of an inner child.
+  if (CLRT_EMIT_DEBUG & 2) return;
   const Box6 A = aIsLeaf ? pyr_load(pv, 0, (uint32_t)split) : box_clamped(pyr_query(pv, (uint32_t)range.x, (uint32_t)split));
   const Box6 B = bIsLeaf ? pyr_load(pv, 0, (uint32_t)split + 1u) : box_clamped(pyr_query(pv, (uint32_t)split + 1u, (uint32_t)range.y));
   const Box6 U = box_clamped(box_join(A, B));
@@ -240,7 +261,7 @@ int bvh_construct(clrt_accel* a) {
   if (tm) CLRT_CUDA(cudaEventRecord(a->ev[3], s));
   CLRT_CUDA(cudaMemsetAsync(a->d_tile_counter + 12, 0, 4, s));
   if (n) {
-    karras_emit_kernel<<<(n + 255) / 256, 256, 0, s>>>(a->d_pairs, n, a->d_nodes, a->scene->d_tris, a->d_tris_sorted, a->d_tnodes, a->d_tile_counter + 12, a->d_refpos, pv);
+    karras_emit_kernel<<<(n + 255) / 256, 256, 0, s>>>(a->d_pairs, n, a->d_nodes, a->scene->d_tris, a->d_tris_sorted, a->d_tnodes, a->d_tile_counter + 12, pv);
     CLRT_CHECK_LAUNCH();
   }
   if (tm) {

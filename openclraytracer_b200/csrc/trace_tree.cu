@@ -53,6 +53,14 @@ __device__ __forceinline__ int tt_delta(const uint2* __restrict__ list, int n, u
   return ki != kj ? __clz(ki ^ kj) : 32 + __clz((uint32_t)i ^ (uint32_t)j);
 }
 
+// triangle -> position in the REFERENCE tree's sorted order (the tie-break key every traversal-side triangle carries).  Only this tree
+// needs the table (the reference tree's own triangle copy gets the position directly), so the scatter is paid only when it is built.
+__global__ void __launch_bounds__(256)
+tt_refpos_kernel(const uint2* __restrict__ ref_list, uint32_t n, uint32_t* __restrict__ refpos) {
+  const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p < n) refpos[__ldg(&ref_list[p].y)] = p;
+}
+
 // Leaf boxes in this tree's order for the pyramid: the box morton_leaves_kernel stored in the leaf's reference node.
 struct TtLeafBox {
   const uint2* list; const clrt_bvh_node* ref_nodes;
@@ -328,6 +336,8 @@ static int trace_tree_separate(clrt_accel* a) {
   tt_morton_kernel<<<grid, 256, 0, s>>>(a->scene->d_tris, n, bb, reinterpret_cast<uint2*>(a->d_tt_pairs));
   CLRT_CHECK_LAUNCH();
   CLRT_TRY(sort_pairs_radix(ctx, a->d_tt_pairs, n, 30));
+  tt_refpos_kernel<<<grid, 256, 0, s>>>(reinterpret_cast<const uint2*>(a->d_pairs), n, a->d_refpos);
+  CLRT_CHECK_LAUNCH();
   const PyrView pv = pyr_view(a->d_pyr, n);
   CLRT_TRY(pyr_build(ctx, pv, TtLeafBox{reinterpret_cast<const uint2*>(a->d_tt_pairs), a->d_nodes}));
   tt_emit_kernel<<<grid, 256, 0, s>>>(reinterpret_cast<const uint2*>(a->d_tt_pairs), n, a->scene->d_tris, a->d_refpos, a->d_tt_tris, a->d_tt_nodes, pv);
