@@ -50,7 +50,7 @@ morton_leaves_kernel(const clrt_triangle* __restrict__ tris, const uint32_t* __r
 // Sorted codes for the searches of the emit stage: the CTA's own neighbourhood [lo, hi) sits in shared memory (most nodes are small: their
 // dependent probes — ~40 L2 round trips per thread otherwise — stay on the SM), everything else comes from the sorted (code, leaf) pairs.
 #ifndef CLRT_EMIT_KEY_WINDOW
-#define CLRT_EMIT_KEY_WINDOW 256     /* positions staged on either side of the CTA's 256; 0: no staging */
+#define CLRT_EMIT_KEY_WINDOW 0       /* positions staged on either side of the CTA's 256 (measured: no effect, profiles/r02_experiments.md 5b); 0: no staging */
 #endif
 struct KeyList { const uint2* list; const uint32_t* s; int lo, hi; };
 __device__ __forceinline__ uint32_t key_at(const KeyList& k, int i) {
