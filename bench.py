@@ -429,8 +429,7 @@ def main():
             r.render_device(cams[s], True)
 
     def join():
-        if not bounce:
-            r.join()
+        r.join()
 
     # rays per frame (counted once, untimed): primary = pixels of the stripe, shadow / bounce = live secondary rays.  The camera path
     # has a period of 64 steps: count one period, reuse it.
@@ -492,7 +491,7 @@ def main():
         e2e_value = total_rays / (e2e_ms * 1e-3) / 1e6
         exchange = "nccl" if bounce else r.exchange
         if bounce:
-            launches, pipeline = 5, "one frame at a time on one stream"           # primary, bounce rays, trace, shade, untile (+ NCCL's own kernel at N > 1)
+            launches, pipeline = 5, f"{r.DEPTH} frames in flight (frame slots: own stream, counter and buffers each)"   # primary, bounce rays, trace, shade, untile (+ NCCL's own kernel at N > 1)
             secondary = "one cosine-weighted diffuse bounce ray per hit through generateContacts(rays, contacts, n)"
         else:
             # BVH: trace_primary_kernel, shadow_shade_kernel (or frame_kernel alone) + untile_kernel (nccl) | push, 2 signal, 2 wait (push) |

@@ -227,6 +227,13 @@ int clrt_shade(clrt_ctx* ctx, const clrt_scene* scene, const clrt_camera* h_came
  * clrt_generate_bounce_rays + clrt_trace_rays) hit something: one-sample ambient occlusion -> RGBA8 at slot i. */
 int clrt_shade_bounce(clrt_ctx* ctx, const clrt_scene* scene, const clrt_camera* h_camera, const void* dptr_contacts, uint32_t n,
                       const void* dptr_bounce_contacts, void* dptr_rgba8);
+/* One rank's frame of BASELINE.json configs[3] on a frame slot (ours; the reference has no secondary rays — KNOWN_ISSUES_AND_TODO.txt:27-30 —
+ * and renders one frame at a time): clrt_trace_primary_stripe -> clrt_generate_bounce_rays -> clrt_trace_rays -> clrt_shade_bounce, enqueued
+ * on `stream` (a cudaStream_t) with the slot's private work counter (slot 0 .. 15), so that frames can be in flight on several streams.
+ * Buffers are the caller's, sized for the rank's stripe (clrt_frame_stripe_pixels): contacts and bounce contacts 32 B, rays 48 B, rgba8
+ * 4 B per stripe slot; results identical to the four calls made one after the other.  BVH only. */
+int clrt_render_bounce_stripe_on(clrt_accel* accel, void* stream, int slot, const clrt_camera* h_camera, uint32_t rank, uint32_t nranks,
+                                 uint64_t seed, void* dptr_contacts, void* dptr_rays, void* dptr_bounce_contacts, void* dptr_rgba8);
 
 /* Shadow pass + Blinn-Phong in ONE kernel over n contacts (BVH only): per contact and light an occlusion query along the
  * shadow ray clrt_generate_shadow_rays would build, then the shading of clrt_shade -> RGBA8.  Same pixels as the

@@ -371,6 +371,12 @@ class AccelerationStructureManager:
                                                 C.c_void_p(consumer_stream) if consumer_stream else None))
         return rays.value
 
+    def render_bounce_stripe_on(self, stream, slot, camera, rank, nranks, seed, dptr_contacts, dptr_rays, dptr_bounce, dptr_rgba8):
+        """configs[3] frame of one rank on a frame slot: primary stripe -> diffuse bounce rays -> generic-ray walk -> shading (clrt_render_bounce_stripe_on)."""
+        cam = np.ascontiguousarray(camera, dtype=L.CAMERA)
+        check(self._lib.clrt_render_bounce_stripe_on(self.handle, C.c_void_p(stream), slot, _ptr(cam), rank, nranks, seed, C.c_void_p(dptr_contacts),
+                                                     C.c_void_p(dptr_rays), C.c_void_p(dptr_bounce), C.c_void_p(dptr_rgba8)))
+
     def render_stripes_batch(self, stream, slot, cameras, rank, nranks, dptr_rgba8):
         """1..4 stripes (one camera each) by one pair of launches into a local stripe-ordered buffer (clrt_render_stripes_batch)."""
         cams = np.ascontiguousarray(np.stack([np.asarray(c, dtype=L.CAMERA).reshape(()) for c in cameras]))

@@ -156,6 +156,34 @@ extern "C" int clrt_trace_rays(clrt_accel* a, const void* dptr_rays, void* dptr_
   return accel_trace_rays(a, (const clrt_ray*)dptr_rays, (clrt_contact*)dptr_contacts, ray_count);
 }
 
+// configs[3] frame of one rank on a frame slot: primary contacts of the rank's stripe -> one diffuse bounce ray per hit -> the generic-ray
+// walk -> shading, all enqueued on `stream` with the slot's private work counter, so that several frames can be in flight on several
+// streams (frame.BounceRenderer).  The four steps are the public calls clrt_trace_primary_stripe, clrt_generate_bounce_rays,
+// clrt_trace_rays, clrt_shade_bounce, unchanged; only where they are enqueued differs.  Ours (the reference renders one frame at a time).
+extern "C" int clrt_render_bounce_stripe_on(clrt_accel* a, void* stream_, int slot, const clrt_camera* h_camera, uint32_t rank, uint32_t nranks,
+                                            uint64_t seed, void* dptr_contacts, void* dptr_rays, void* dptr_bounce_contacts, void* dptr_rgba8) {
+  if (!a || !h_camera || !dptr_contacts || !dptr_rays || !dptr_bounce_contacts || !dptr_rgba8) CLRT_FAIL("clrt_render_bounce_stripe_on: NULL argument");
+  if (a->kind != ACCEL_BVH) CLRT_FAIL("clrt_render_bounce_stripe_on: frame slots exist for the BVH only");
+  if (slot < 0 || slot >= clrt_accel::FRAME_SLOTS) CLRT_FAIL("clrt_render_bounce_stripe_on: slot %d of %d", slot, clrt_accel::FRAME_SLOTS);
+  if (!nranks || rank >= nranks) CLRT_FAIL("clrt_render_bounce_stripe_on: rank %u of %u", rank, nranks);
+  clrt_ctx* ctx = a->ctx;
+  CLRT_CUDA(cudaSetDevice(ctx->device));
+  if (slot + 1 > a->slots_seen) a->slots_seen = slot + 1;
+  struct Env {                                    // lends the stream to everything the four calls enqueue, and the slot's counter to the trace launches
+    clrt_accel* a; cudaStream_t saved;
+    Env(clrt_accel* a_, cudaStream_t s, uint32_t* c) : a(a_), saved(a_->ctx->stream) { a->ctx->stream = s; a->launch_stream = s; a->launch_counter = c; }
+    ~Env() { a->ctx->stream = saved; a->launch_stream = nullptr; a->launch_counter = nullptr; }
+  } env(a, (cudaStream_t)stream_, a->d_slot_counters + 16 * slot);
+  const TileGrid g = make_tile_grid(h_camera->resX, h_camera->resY);
+  const uint32_t units = stripe_tile_count(g.tiles, rank, nranks) * CLRT_TILE_PIXELS;
+  if (!units) return 0;
+  CLRT_TRY(clrt_trace_primary_stripe(a, h_camera, rank, nranks, dptr_contacts));
+  CLRT_TRY(clrt_generate_bounce_rays(ctx, h_camera, dptr_contacts, units, seed, dptr_rays));
+  CLRT_TRY(clrt_trace_rays(a, dptr_rays, dptr_bounce_contacts, units));
+  CLRT_TRY(clrt_shade_bounce(ctx, a->scene, h_camera, dptr_contacts, units, dptr_bounce_contacts, dptr_rgba8));
+  return 0;
+}
+
 // Shadow pass fused with the shading over an arbitrary contact buffer (BVH only).
 extern "C" int clrt_shadow_shade(clrt_accel* a, const clrt_camera* h_camera, const void* dptr_contacts, uint32_t n, void* dptr_rgba8) {
   if (!a || !h_camera || (n && (!dptr_contacts || !dptr_rgba8))) CLRT_FAIL("clrt_shadow_shade: NULL argument");

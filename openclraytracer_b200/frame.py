@@ -420,10 +420,12 @@ def orbit_camera(scene_buf, resX, resY, step, steps_per_turn=64, fov_deg=90.0):
 
 class BounceRenderer:
     """BASELINE.json configs[3]: incoherent secondary rays, image-tile sharded.  Per frame and rank: primary contacts of the rank's
-    stripe (clrt_trace_primary_stripe, stripe order) -> one cosine-weighted diffuse bounce ray per hit (clrt_generate_bounce_rays)
-    -> the generic-ray entry generateContacts(rays, contacts, n) (clrt_trace_rays; BVHManager.cpp:292-329) -> Blinn-Phong halved
-    where the bounce ray hit (clrt_shade_bounce) -> RGBA8 stripe; one all-gather of equal padded stripes + untile gives every rank
-    the frame.  Rays are independent and the structure is read-only: no other exchange exists.  One stream, one frame at a time."""
+    stripe -> one cosine-weighted diffuse bounce ray per hit -> the generic-ray entry generateContacts(rays, contacts, n)
+    (BVHManager.cpp:292-329) -> Blinn-Phong halved where the bounce ray hit -> RGBA8 stripe (clrt_render_bounce_stripe_on = the four
+    public calls on a frame slot); one all-gather of equal padded stripes + untile gives every rank the frame.  Rays are independent and
+    the structure is read-only: no other exchange exists.  DEPTH frames are in flight (CLRT_BOUNCE_DEPTH, default 3): every frame slot has
+    its own stream, work counter and buffers, so the all-gather and the kernel tails of one frame overlap the tracing of the next; the
+    collectives are issued in frame order on every rank."""
 
     def __init__(self, scene_buf, resX, resY, rank=0, world=1, device=0, group=None):
         import torch
@@ -440,51 +442,78 @@ class BounceRenderer:
         self.accel.initialize()
         self.cap, self.tiles = api.frame_stripe_pixels(resX, resY, rank, world)
         self.slots = self.tiles * TILE_PIXELS
-        with torch.cuda.stream(self.stream):
-            self.contacts = torch.zeros(self.cap * 32, dtype=torch.uint8, device=self.device)
-            self.rays = torch.zeros(self.cap * 48, dtype=torch.uint8, device=self.device)
-            self.bounce = torch.zeros(self.cap * 32, dtype=torch.uint8, device=self.device)
-            self.stripe = torch.zeros(self.cap, dtype=torch.int32, device=self.device)
-            self.gathered = torch.zeros(self.cap * world, dtype=torch.int32, device=self.device) if world > 1 else self.stripe
-            self.raster = torch.zeros(resY * resX, dtype=torch.int32, device=self.device)
-        self.host_raster = torch.zeros(resY * resX, dtype=torch.int32).pin_memory()
+        self.DEPTH = max(1, min(8, int(os.environ.get("CLRT_BOUNCE_DEPTH", "3"))))
+        self.frames = []
+        for k in range(self.DEPTH):
+            st = torch.cuda.Stream(self.device)
+            with torch.cuda.stream(st):
+                f = {"stream": st, "event": torch.cuda.Event(),
+                     "contacts": torch.zeros(self.cap * 32, dtype=torch.uint8, device=self.device),
+                     "rays": torch.zeros(self.cap * 48, dtype=torch.uint8, device=self.device),
+                     "bounce": torch.zeros(self.cap * 32, dtype=torch.uint8, device=self.device),
+                     "stripe": torch.zeros(self.cap, dtype=torch.int32, device=self.device),
+                     "raster": torch.zeros(resY * resX, dtype=torch.int32, device=self.device),
+                     "host_raster": torch.zeros(resY * resX, dtype=torch.int32).pin_memory() if rank == 0 else None}
+                f["gathered"] = torch.zeros(self.cap * world, dtype=torch.int32, device=self.device) if world > 1 else f["stripe"]
+            st.synchronize()
+            self.frames.append(f)
+        self._next, self._last = 0, 0
         self.stream.synchronize()
 
+    # the buffers of the frame submitted last (bench.py's per-kernel timing and ray count read them)
+    contacts = property(lambda self: self.frames[self._last]["contacts"])
+    rays = property(lambda self: self.frames[self._last]["rays"])
+    bounce = property(lambda self: self.frames[self._last]["bounce"])
+    raster = property(lambda self: self.frames[self._last]["raster"])
+    host_raster = property(lambda self: self.frames[self._last]["host_raster"])
+
     def build(self):
+        self.finish()
         self.accel.initializeFrame()
         self.accel.construct()
         self.stream.synchronize()
 
     def render_device(self, camera, seed=20161116):
         torch = self.torch
-        with torch.cuda.stream(self.stream):
+        k = self._next
+        self._next, self._last = (k + 1) % self.DEPTH, k
+        f = self.frames[k]
+        with torch.cuda.stream(f["stream"]):
             if self.slots:
-                self.accel.trace_primary_stripe(camera, self.rank, self.world, self.contacts.data_ptr())
-                api.generate_bounce_rays(self.ctx, camera, self.contacts.data_ptr(), self.slots, seed, self.rays.data_ptr())
-                self.accel.generateContacts(self.rays.data_ptr(), self.bounce.data_ptr(), self.slots)
-                api.shade_bounce(self.ctx, self.scene, camera, self.contacts.data_ptr(), self.slots, self.bounce.data_ptr(), self.stripe.data_ptr())
+                self.accel.render_bounce_stripe_on(f["stream"].cuda_stream, k, camera, self.rank, self.world, seed, f["contacts"].data_ptr(),
+                                                   f["rays"].data_ptr(), f["bounce"].data_ptr(), f["stripe"].data_ptr())
             if self.world > 1:
                 import torch.distributed as dist
-                dist.all_gather_into_tensor(self.gathered, self.stripe, group=self.group)
-            api.frame_untile_on(self.ctx, self.stream.cuda_stream, self.gathered.data_ptr(), self.resX, self.resY, self.world, self.raster.data_ptr())
+                dist.all_gather_into_tensor(f["gathered"], f["stripe"], group=self.group)
+            api.frame_untile_on(self.ctx, f["stream"].cuda_stream, f["gathered"].data_ptr(), self.resX, self.resY, self.world, f["raster"].data_ptr())
+            f["event"].record(f["stream"])
+        return f
 
     def render_host(self, camera, seed=20161116):
-        """e2e: host camera in, the frame in pinned host memory (rank 0) when the stream has passed."""
-        self.render_device(camera, seed)
+        """e2e: host camera in, the frame in pinned host memory (rank 0) when the frame's stream has passed."""
+        f = self.render_device(camera, seed)
         if self.rank == 0:
-            with self.torch.cuda.stream(self.stream):
-                self.host_raster.copy_(self.raster, non_blocking=True)
-        return self.host_raster
+            with self.torch.cuda.stream(f["stream"]):
+                f["host_raster"].copy_(f["raster"], non_blocking=True)
+                f["event"].record(f["stream"])
+        return f["host_raster"]
+
+    def join(self):
+        """Device-side join: the renderer's own stream waits for every frame in flight."""
+        for f in self.frames:
+            self.stream.wait_event(f["event"])
 
     def count_rays(self):
         """Rays of the last frame on this rank: primary = stripe slots inside the image, bounce = primary hits (host sync)."""
-        self.stream.synchronize()
+        self.finish()
         c = self.contacts[: self.slots * 32].view(self.torch.int32).reshape(-1, 8)
         inside = int((c[:, 0] != -1).sum().item())
         hits = int((c[:, 7].view(self.torch.float32) > 0).sum().item())
         return inside + hits
 
     def finish(self):
+        for f in self.frames:
+            f["stream"].synchronize()
         self.stream.synchronize()
 
     def close(self):

@@ -214,3 +214,47 @@ def test_reflection_depth_loop(ctx, O, name):
     for x in (prays, contacts, *bufs):
         x.free()
     bvh.free(); scene.free()
+
+
+@pytest.mark.parametrize("depth", ["1", "3"])
+def test_bounce_renderer_frames_in_flight_equal_the_four_calls(ctx, depth, monkeypatch):
+    """frame.BounceRenderer (what bench.py --workload spheres10m times: clrt_render_bounce_stripe_on on frame slots, several frames in
+    flight on several streams, untile) against the four public calls made one after the other on the context's stream — the path the
+    tests above check against the oracle.  More frames than slots; every raster must be identical."""
+    from openclraytracer_b200 import frame
+    monkeypatch.setenv("CLRT_BOUNCE_DEPTH", depth)
+    buf = scenes.soup_scene(60_000, seed=4)
+    W, H = 448, 264                                                     # not a multiple of the 32x8 tiles in y
+    r = frame.BounceRenderer(buf, W, H, 0, 1, 0)
+    assert r.DEPTH == int(depth)
+    r.build()
+    poses = list(range(2 * r.DEPTH + 1))
+    got = []
+    for p in poses:
+        got.append(r.render_host(frame.orbit_camera(buf, W, H, p)))
+        if (p + 1) % r.DEPTH == 0:                                       # host rasters are about to be reused: collect
+            r.finish()
+            got = [g.numpy().copy() if hasattr(g, "numpy") else g for g in got]
+    r.finish()
+    got = [g.numpy().copy() if hasattr(g, "numpy") else g for g in got]
+    r.close()
+    # the same frames by single calls
+    scene, bvh = build_gpu(ctx, buf)
+    cap, tiles = api.frame_stripe_pixels(W, H, 0, 1)
+    n = tiles * frame.TILE_PIXELS
+    contacts = api.Buffer(ctx, cap * 32); rays = api.Buffer(ctx, cap * 48); bnc = api.Buffer(ctx, cap * 32)
+    stripe = api.Buffer(ctx, cap * 4); raster = api.Buffer(ctx, W * H * 4)
+    bvh.set_trace_mode(api.TRACE_FAST)
+    for p, g in zip(poses, got):
+        cam = frame.orbit_camera(buf, W, H, p)
+        bvh.trace_primary_stripe(cam, 0, 1, contacts.getCLMem())
+        api.generate_bounce_rays(ctx, cam, contacts.getCLMem(), n, SEED, rays.getCLMem())
+        bvh.generateContacts(rays.getCLMem(), bnc.getCLMem(), n)
+        api.shade_bounce(ctx, scene, cam, contacts.getCLMem(), n, bnc.getCLMem(), stripe.getCLMem())
+        api.frame_untile(ctx, stripe.getCLMem(), W, H, 1, raster.getCLMem())
+        want = raster.copyToHost(np.int32, W * H)
+        assert np.array_equal(np.asarray(g).reshape(-1), want), f"pose {p}"
+        assert (want != 0).mean() > 0.2
+    for b in (contacts, rays, bnc, stripe, raster):
+        b.free()
+    bvh.free(); scene.free()
