@@ -327,8 +327,7 @@ struct KLane {
   int sp;
   bool done;
   uint32_t slot, pixel;
-  uint2 stack[KD_STACK];
-};
+};                                    // the stack of far children is a separate local array: inside the struct it dragged every field into local memory
 __device__ __forceinline__ bool klane_begin(KLane& L, const KdView& V, Vec3 o, Vec3 d) {
   const KdGrid& g = V.g;
   L.o = o; L.d = d; L.best.t = RT_FLT_MAX; L.best.tri = 0xFFFFFFFFu; L.done = true;
@@ -346,7 +345,7 @@ __device__ __forceinline__ bool klane_begin(KLane& L, const KdView& V, Vec3 o, V
   L.done = false;
   return true;
 }
-__device__ __forceinline__ void klane_leaf_step(KLane& L, const KdView& V) {
+__device__ __forceinline__ void klane_leaf_step(KLane& L, uint2* __restrict__ stack, const KdView& V) {
   const float slack = 1.00001f;
   const uint32_t m = V.m;
   uint32_t cur = L.cur;
@@ -362,7 +361,7 @@ __device__ __forceinline__ void klane_leaf_step(KLane& L, const KdView& V) {
     if (da == 0.0f || ts > tmax * slack || ts <= 0.0f) cur = near;
     else if (ts < tmin / slack) cur = far;
     else {
-      if (L.sp < KD_STACK) { L.stack[L.sp] = make_uint2(far, __float_as_uint(tmax)); L.sp++; } else atomicAdd(V.overflow, 1u);
+      if (L.sp < KD_STACK) { stack[L.sp] = make_uint2(far, __float_as_uint(tmax)); L.sp++; } else atomicAdd(V.overflow, 1u);
       cur = near; tmax = ts;
     }
   }
@@ -376,7 +375,8 @@ __device__ __forceinline__ void klane_leaf_step(KLane& L, const KdView& V) {
   }
   if (L.best.t <= tmax * slack || L.sp == 0) { L.done = true; return; }      // the closest hit lies in a region already finished / nothing left
   L.sp--;
-  L.tmin = tmax; L.tmax = __uint_as_float(L.stack[L.sp].y); L.cur = L.stack[L.sp].x;
+  const uint2 e = stack[L.sp];
+  L.tmin = tmax; L.tmax = __uint_as_float(e.y); L.cur = e.x;
 }
 
 template <class Job>
@@ -385,6 +385,7 @@ __device__ __forceinline__ void kd_run_jobs(Job& job, const KdView& V, uint32_t 
   const int lane = threadIdx.x & 31;
   const unsigned lt_mask = (1u << lane) - 1u;
   KLane L; L.done = true;
+  uint2 stack[KD_STACK];                                           // (far child, its tmax) of the lane's ray
   bool busy = false, exhausted = false;
   uint32_t pool_next = 0, pool_end = 0;
   while (true) {
@@ -414,7 +415,7 @@ __device__ __forceinline__ void kd_run_jobs(Job& job, const KdView& V, uint32_t 
       }
       if (idle == FULL) break;
     }
-    if (busy && !L.done) klane_leaf_step(L, V);
+    if (busy && !L.done) klane_leaf_step(L, stack, V);
   }
 }
 
