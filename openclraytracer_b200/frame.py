@@ -9,11 +9,17 @@ stripes, 8.3 MB per 1080p frame) follows, and an untile kernel restores raster o
 the path.  Eight frames are in flight: frames are traced on alternating streams (frame slots of the C ABI) so that the
 latency-bound tail of one frame overlaps the next, and the collective, the untile and the read-back run on one more stream.
 
-CLRT_EXCHANGE selects the exchange (BVH): "nccl" (the above; the default on one GPU), "fused" (the default at world > 1;
-measured 8 GPUs, Soup-1M: 0.40 ms/frame against 0.49 with NCCL) or "push" — both over peer memory
-(csrc/peer.cu): every rank exports its raster framebuffers + a block of flag words (cudaIpc), and a frame's pixels are stored
-straight into EVERY GPU's framebuffer over NVLink, by one pass over the stripe buffer ("push") or by the shading kernel itself
-("fused"); a "ready" word per (frame slot, rank) replaces the collective, an "ack" word orders the reuse of a slot's framebuffer.
+CLRT_EXCHANGE selects the exchange (BVH): "nccl" (the above; the default on one GPU), "fused" (the default at world > 1) or "push" —
+both over peer memory (csrc/peer.cu): every rank exports its raster framebuffers + a block of 256 flag words (cudaIpc), and a frame's
+pixels are stored straight into EVERY GPU's framebuffer over NVLink, by one pass over the stripe buffer ("push") or by the shading
+kernel itself ("fused"); a "ready" word per (frame slot, rank) replaces the collective, an "ack" word orders the reuse of a slot's
+framebuffer.  The waiting half of the exchange (everybody ready -> read-back -> ack) runs on its own stream (split exchange), so a
+slot's trace stream never waits for the other GPUs' stripes.  On more than one GPU a stripe is ONE launch (frame_kernel: primary +
+occlusion + shading; CLRT_FRAME_KERNELS), 16 frame slots; measured 8 B200s, Soup-1M 1080p: 0.325 ms per frame, 10.75 Grays/s, 7.05x
+one GPU.
+
+BounceRenderer (bottom of this file) is the configs[3] frame — primary + one diffuse bounce through the generic-ray entry point — with
+three frames in flight on frame slots and an NCCL all-gather per frame.
 
 PyTorch is plumbing here: device memory, the stream shared with NCCL, and the collective.
 """
