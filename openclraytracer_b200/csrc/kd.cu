@@ -166,7 +166,7 @@ constexpr int KD_THREADS = 128;
 #define CLRT_KD_REFILL_MIN 12
 #endif
 #ifndef CLRT_KD_MIN_CTAS
-#define CLRT_KD_MIN_CTAS 6
+#define CLRT_KD_MIN_CTAS 8
 #endif
 #if !CLRT_KD_REFILL
 __device__ __forceinline__ KdHit kd_traverse(Vec3 o, Vec3 d, const KdGrid& g, const KdNode* __restrict__ nodes, uint32_t m,
