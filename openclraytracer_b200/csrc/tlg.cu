@@ -548,12 +548,34 @@ tlg_trace_rays_kernel(const clrt_ray* __restrict__ rays, uint32_t count, const c
 #define CLRT_TLG_REFILL_MIN 8
 #endif
 #ifndef CLRT_TLG_MIN_CTAS
-#define CLRT_TLG_MIN_CTAS 6
+#define CLRT_TLG_MIN_CTAS 7
 #endif
+// The walk state without the step / end members (both follow from the sign of d and the resolution): six registers fewer per walk in the
+// lane-refill kernels, where the top-level walk lives across steps.
+struct WalkC { float tx, ty, tz, dx, dy, dz; int ix, iy, iz; };
+__device__ __forceinline__ void walkc_axis(float o, float d, float inv, float b0, float cs, int r, float p, float& tnext, float& dt, int& i) {
+  i = (int)floorf((p - b0) / cs);
+  i = i < 0 ? 0 : (i > r - 1 ? r - 1 : i);
+  if (d > 0.0f) { tnext = (b0 + (float)(i + 1) * cs - o) * inv; dt = cs * inv; }
+  else if (d < 0.0f) { tnext = (b0 + (float)i * cs - o) * inv; dt = -cs * inv; }
+  else { tnext = RT_FLT_MAX; dt = 0.0f; }
+}
+__device__ __forceinline__ void walkc_setup(WalkC& w, Vec3 o, Vec3 d, Vec3 inv, float b0x, float b0y, float b0z, float csx, float csy, float csz,
+                                            int rx, int ry, int rz, float t_in) {
+  walkc_axis(o.x, d.x, inv.x, b0x, csx, rx, o.x + d.x * t_in, w.tx, w.dx, w.ix);
+  walkc_axis(o.y, d.y, inv.y, b0y, csy, ry, o.y + d.y * t_in, w.ty, w.dy, w.iy);
+  walkc_axis(o.z, d.z, inv.z, b0z, csz, rz, o.z + d.z * t_in, w.tz, w.dz, w.iz);
+}
+// leaves the cell through its nearest face; false when that leaves the grid (an axis with d == 0 is never chosen: its tnext is FLT_MAX)
+__device__ __forceinline__ bool walkc_step(WalkC& w, Vec3 d, int rx, int ry, int rz) {
+  if (w.tx <= w.ty && w.tx <= w.tz) { w.tx += w.dx; if (d.x < 0.0f) { w.ix--; return w.ix != -1; } w.ix++; return w.ix != rx; }
+  if (w.ty <= w.tz) { w.ty += w.dy; if (d.y < 0.0f) { w.iy--; return w.iy != -1; } w.iy++; return w.iy != ry; }
+  w.tz += w.dz; if (d.z < 0.0f) { w.iz--; return w.iz != -1; } w.iz++; return w.iz != rz;
+}
 struct GLane {
   Vec3 o, d, inv;
   GridHit best;
-  Walk T;
+  WalkC T;
   float t_cur;
   uint32_t it;
   bool done;
@@ -577,7 +599,7 @@ __device__ __forceinline__ bool glane_begin(GLane& L, const GridView& V, Vec3 o,
   const float tn = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fminf(az, bz)), tf = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fmaxf(az, bz));
   if (!(tn <= tf) || tf < 0.0f) { L.done = true; return false; }
   const float t_in = fmaxf(tn, 0.0f);
-  walk_setup(L.T, o, d, L.inv, b0x, b0y, b0z, g.stepX, g.stepY, g.stepZ, (int)g.resX, (int)g.resY, (int)g.resZ, t_in);
+  walkc_setup(L.T, o, d, L.inv, b0x, b0y, b0z, g.stepX, g.stepY, g.stepZ, (int)g.resX, (int)g.resY, (int)g.resZ, t_in);
   L.t_cur = t_in; L.it = 0; L.done = false;
   return true;
 }
@@ -589,8 +611,8 @@ __device__ __forceinline__ void glane_top_cell(GLane& L, const GridView& V) {
   const float t_exit = fminf(L.T.tx, fminf(L.T.ty, L.T.tz));
   if (!(cell.x == 0 || cell.y == 0 || cell.z == 0)) {
     const float c0x = g.box.bounds[0].x + (float)L.T.ix * g.stepX, c0y = g.box.bounds[0].y + (float)L.T.iy * g.stepY, c0z = g.box.bounds[0].z + (float)L.T.iz * g.stepZ;
-    Walk Lf;
-    walk_setup(Lf, L.o, L.d, L.inv, c0x, c0y, c0z, g.stepX / (float)cell.x, g.stepY / (float)cell.y, g.stepZ / (float)cell.z,
+    WalkC Lf;
+    walkc_setup(Lf, L.o, L.d, L.inv, c0x, c0y, c0z, g.stepX / (float)cell.x, g.stepY / (float)cell.y, g.stepZ / (float)cell.z,
                (int)cell.x, (int)cell.y, (int)cell.z, L.t_cur);
     const uint32_t leaf_cap = cell.x + cell.y + cell.z + 3u;
     for (uint32_t lit = 0; lit < leaf_cap; lit++) {
@@ -604,13 +626,13 @@ __device__ __forceinline__ void glane_top_cell(GLane& L, const GridView& V) {
       }
       const float l_exit = fminf(Lf.tx, fminf(Lf.ty, Lf.tz));
       if (L.best.t <= l_exit * slack) { L.done = true; return; }
-      if (l_exit >= t_exit || !walk_step(Lf)) break;
+      if (l_exit >= t_exit || !walkc_step(Lf, L.d, (int)cell.x, (int)cell.y, (int)cell.z)) break;
     }
   }
   if (L.best.t <= t_exit * slack) { L.done = true; return; }
   L.t_cur = t_exit;
   L.it++;
-  if (!walk_step(L.T) || L.it >= g.resX + g.resY + g.resZ + 3u) L.done = true;
+  if (!walkc_step(L.T, L.d, (int)g.resX, (int)g.resY, (int)g.resZ) || L.it >= g.resX + g.resY + g.resZ + 3u) L.done = true;
 }
 
 // Job: start(unit, L) -> the lane is busy; the contact of a ray that never enters the grid (or of a slot outside the image) is written at once
